@@ -1,0 +1,177 @@
+/*
+ * rcull.h -- C ABI of librcull.so: B200 (sm_100a) transform -> AABB -> frustum
+ * cull -> prefix-sum compaction for farnoy/renderer's per-frame hot path.
+ *
+ * The reference has no FFI for this stage; its "operator API" is the set of
+ * bevy systems below.  A replacement system makes ONE rcull_frame call per
+ * frame; each entry point cites what it stands in for (paths relative to the
+ * reference tree):
+ *   model_matrix_calculation   src/ecs.rs:52-64
+ *   aabb_calculation           src/ecs.rs:138-181
+ *   coarse_culling             src/renderer/systems/cull_pipeline.rs:99-120
+ *   model_matrices_upload      src/renderer.rs:2266-2288
+ *   cull_pass (emit loop)      src/renderer/systems/cull_pipeline.rs:534-577
+ *   compact_draw_stream.comp   src/shaders/compact_draw_stream.comp:34-63
+ *   pick_lod                   src/renderer/helpers.rs:3-11
+ *
+ * Conventions: every call returns 0 on success or a negative rcull_status and
+ * records a message for rcull_last_error() (thread-local).  The reference
+ * panics (panic = "abort", Cargo.toml:133); a Rust shim would .expect() on the
+ * code.  A context owns all device memory it hands out; one context = one GPU
+ * = externally serialised calls (a system holding ResMut<Ctx>).  There is no
+ * CPU fallback: without a CUDA device rcull_create fails.
+ */
+#ifndef RCULL_H
+#define RCULL_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RCULL_MAX_VIEWS 8
+#define RCULL_MAX_LODS 6 /* scene_loader.rs:739-753: lod 0 + up to 5 simplified */
+
+typedef enum {
+    RCULL_OK = 0,
+    RCULL_ERR_INVALID = -1,  /* bad argument / capacity exceeded */
+    RCULL_ERR_CUDA = -2,     /* a CUDA runtime call failed */
+    RCULL_ERR_NO_DEVICE = -3 /* no sm_100 device visible */
+} rcull_status;
+
+typedef enum {
+    RCULL_PER_ENTITY = 0,        /* one command per visible entity (cull_pass) */
+    RCULL_PER_MESH_INSTANCED = 1 /* one command per non-empty (mesh, lod) slot */
+} rcull_output_mode;
+
+typedef struct rcull_ctx rcull_ctx;
+
+/* Replaces the fixed capacities of generate_work.comp:26,37 (4096 / 2400). */
+typedef struct {
+    int32_t device;             /* CUDA ordinal */
+    uint32_t max_views;         /* 1..RCULL_MAX_VIEWS: camera + shadow views */
+    uint64_t capacity_entities; /* per frame call */
+    uint64_t capacity_visible;  /* per view draw-list capacity; 0 = capacity_entities */
+    uint32_t max_meshes;
+    uint32_t output_mode;       /* rcull_output_mode */
+    uint32_t n_buffers;         /* 1..3 output sets; DoubleBuffered (double_buffered.rs:6-39) */
+    uint32_t materialize_aabb;  /* write the AABB component (debug_aabb consumer) */
+    uint32_t materialize_flags; /* write CoarseCulled per view */
+    float lod_distance;         /* helpers.rs:6 uses 10.0 */
+} rcull_config;
+
+/* GltfMesh (src/renderer.rs:117-126) + consolidate_mesh_buffers offsets
+ * (consolidate_mesh_buffers.rs:100-159).  80 bytes. */
+typedef struct {
+    float aabb_min[3];
+    float aabb_max[3];
+    uint32_t n_lods; /* >= 1 */
+    struct { uint32_t first_index, index_len; } lod[RCULL_MAX_LODS];
+    int32_t vertex_offset;
+} rcull_mesh;
+
+/* Camera.frustum_planes (camera_controller.rs:15-16): left,right,bottom,top,near,far. */
+typedef struct {
+    float planes[6][4];
+} rcull_view;
+
+/* VkDrawIndexedIndirectCommand, stride 20 (generate_work.comp:9-15). */
+typedef struct {
+    uint32_t indexCount;
+    uint32_t instanceCount;
+    uint32_t firstIndex;
+    int32_t vertexOffset;
+    uint32_t firstInstance;
+} rcull_draw_cmd;
+
+/* Device pointers of one output set.  model is shared by all views. */
+typedef struct {
+    float *model;                              /* mat4 column-major [n]   (ModelData.model_buffer) */
+    float *aabb;                               /* mins,maxs [n][6] or NULL */
+    uint8_t *flags[RCULL_MAX_VIEWS];           /* CoarseCulled [n] per view or NULL */
+    rcull_draw_cmd *cmds[RCULL_MAX_VIEWS];     /* IndirectCommandsBuffer, dense from 0 */
+    uint32_t *visible[RCULL_MAX_VIEWS];        /* draw_index of each survivor */
+    uint32_t *counts;                          /* [max_views]  IndirectCommandsCount */
+    uint64_t *index_totals;                    /* [max_views]  sum of indexCount */
+} rcull_outputs;
+
+const char *rcull_last_error(void);
+/* Library/ABI version: major<<16 | minor. */
+uint32_t rcull_version(void);
+
+/* Allocates every device buffer once (replaces StaticBuffer::new / VMA,
+ * cull_pipeline.rs:186-243, renderer.rs:1225-1244). */
+int rcull_create(const rcull_config *cfg, rcull_ctx **out);
+/* Mirrors the explicit .destroy(device) convention (cull_pipeline.rs:276-286). */
+void rcull_destroy(rcull_ctx *ctx);
+
+/* Mesh table = what GltfMesh + ConsolidatedMeshBuffers give cull_pass
+ * (cull_pipeline.rs:540-548).  Host pointer; copied synchronously. */
+int rcull_set_mesh_table(rcull_ctx *ctx, const rcull_mesh *meshes, uint32_t n);
+
+/* SoA component columns: pos_scale = (Position.xyz, Scale), rot = Rotation
+ * (i,j,k,w), mesh = index into the mesh table; entity slot i IS draw_index i
+ * (assign_draw_index, src/ecs.rs:117-136).  Host pointers; async on stream
+ * (0 = default stream) when the host memory is pinned. */
+int rcull_upload_entities(rcull_ctx *ctx, uint64_t first, uint64_t n, const float *pos_scale,
+                          const float *rot, const uint32_t *mesh, void *stream);
+/* Device pointers of the input columns, for callers that fill them in place. */
+int rcull_entity_ptrs(rcull_ctx *ctx, float **pos_scale, float **rot, uint32_t **mesh);
+/* AoS bevy components -> the SoA columns above (host side, no device work):
+ * Position [n][3], Rotation [n][4], Scale [n]. */
+int rcull_pack_components(uint64_t n, const float *position, const float *rotation, const float *scale,
+                          float *pos_scale, float *rot);
+
+/* One frame: model_matrix_calculation + aabb_calculation + coarse_culling per
+ * view + model_matrices_upload + cull_pass emit/prefix-sum + compact_draw_stream,
+ * fused.  views[0] is the camera; cam_pos feeds pick_lod.  draw_index_base is
+ * added to firstInstance / visible indices (range sharding); buffer_ix plays
+ * ImageIndex.  Asynchronous on stream. */
+int rcull_frame(rcull_ctx *ctx, uint64_t n, const rcull_view *views, uint32_t n_views,
+                const float cam_pos[3], uint32_t draw_index_base, uint32_t buffer_ix, void *stream);
+
+/* Host-buffer convenience used by the end-to-end path: upload the columns,
+ * run the frame, read back counts and index totals; blocks until done. */
+int rcull_frame_host(rcull_ctx *ctx, uint64_t n, const float *pos_scale, const float *rot,
+                     const uint32_t *mesh, const rcull_view *views, uint32_t n_views,
+                     const float cam_pos[3], uint32_t draw_index_base, uint32_t buffer_ix,
+                     uint32_t *counts_out, uint64_t *index_totals_out);
+
+int rcull_get_outputs(rcull_ctx *ctx, uint32_t buffer_ix, rcull_outputs *out);
+
+/* Blocking device->host copies for tests and the harness. */
+int rcull_download_counts(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t *counts, uint64_t *index_totals);
+int rcull_download_model(rcull_ctx *ctx, uint32_t buffer_ix, uint64_t first, uint64_t n, float *model);
+int rcull_download_aabb(rcull_ctx *ctx, uint32_t buffer_ix, uint64_t first, uint64_t n, float *aabb);
+int rcull_download_flags(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t view, uint64_t first, uint64_t n, uint8_t *flags);
+int rcull_download_cmds(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t view, uint64_t first, uint64_t n, rcull_draw_cmd *cmds);
+int rcull_download_visible(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t view, uint64_t first, uint64_t n, uint32_t *visible);
+
+/* Range-shard merge step: writes this rank's draw list of one view
+ * into dst_cmds/dst_visible (device pointers into the MERGED lists, already
+ * offset to this rank's slot), adding index_prefix to every firstIndex.  The
+ * collective that moves the slices is the caller's (NCCL allgatherv). */
+int rcull_rebase_into(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t view, uint64_t index_prefix,
+                      rcull_draw_cmd *dst_cmds, uint32_t *dst_visible, void *stream);
+
+/* Harness utility: fills the input columns on the device with the counter-based
+ * synthetic scene (entity i of the global scene = first_global + slot), bit-
+ * identical to renderer_b200/scene.py; avoids shipping 128 M entities from host. */
+int rcull_synth_entities(rcull_ctx *ctx, uint64_t seed, uint64_t first_global, uint64_t n,
+                         float half_box, uint32_t n_meshes, void *stream);
+
+/* Number of kernel launches issued by this context so far (bench accounting). */
+uint64_t rcull_launch_count(rcull_ctx *ctx);
+
+/* Host-side A5 helpers (src/ecs.rs:66-91, shadow_mapping.rs:321-329):
+ * column-major matrices; planes in rcull_view order. */
+void rcull_frustum_planes(const float pv[16], rcull_view *out);
+void rcull_project_camera(float aspect, const float pos[3], const float rot_ijkw[4],
+                          float proj[16], float view[16], float pv[16], rcull_view *out);
+void rcull_light_view(const float pos[3], const float rot_ijkw[4],
+                      float proj[16], float view[16], float pv[16], rcull_view *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

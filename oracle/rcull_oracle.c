@@ -1,0 +1,436 @@
+/*
+ * rcull_oracle.c -- CPU ORACLE (TEST INFRASTRUCTURE, NOT PRODUCT CODE).
+ * See rcull_oracle.h for the scope statement and the "parity unpinned" note.
+ *
+ * Every function restates one reference call site; the arithmetic of the
+ * un-vendored crates (nalgebra 0.29.0 / nalgebra-glm 0.15.0 / ncollide3d
+ * 0.32.0) is written out generically (full 4x4 products, 8 corners, 6 planes)
+ * so that the CUDA path's algebraic shortcuts are checked against the long form.
+ * Compile with -ffp-contract=off: Rust/LLVM never contracts a*b+c into an FMA.
+ */
+#include "rcull_oracle.h"
+
+#include <float.h>
+#include <math.h>
+#include <pthread.h>
+#include <stdlib.h>
+#include <string.h>
+
+/* ---- nalgebra building blocks ------------------------------------------------ */
+
+/* Matrix4 * Vector4 as nalgebra's gemv (blas.rs): y = (1*A[:,0])*x0, then
+ * y = (1*A[:,k])*xk + 1*y for k = 1..3.  a is column-major. */
+static void gemv4(const float a[16], const float x[4], float y[4]) {
+    for (int i = 0; i < 4; i++) y[i] = (1.0f * a[0 * 4 + i]) * x[0];
+    for (int k = 1; k < 4; k++)
+        for (int i = 0; i < 4; i++) y[i] = (1.0f * a[k * 4 + i]) * x[k] + 1.0f * y[i];
+}
+
+/* Matrix4 * Matrix4: one gemv per column of the right operand. */
+void oracle_mat4_mul(const float a[16], const float b[16], float out[16]) {
+    float tmp[16];
+    for (int j = 0; j < 4; j++) gemv4(a, b + 4 * j, tmp + 4 * j);
+    memcpy(out, tmp, sizeof tmp);
+}
+
+static void mat4_identity(float m[16]) {
+    memset(m, 0, 16 * sizeof(float));
+    m[0] = m[5] = m[10] = m[15] = 1.0f;
+}
+
+/* UnitQuaternion::to_rotation_matrix -> to_homogeneous (nalgebra
+ * geometry/quaternion.rs), storage order [i, j, k, w]. */
+static void quat_to_homogeneous(const float q[4], float m[16]) {
+    float i = q[0], j = q[1], k = q[2], w = q[3];
+    float ww = w * w, ii = i * i, jj = j * j, kk = k * k;
+    float ij = i * j * 2.0f, wk = w * k * 2.0f, wj = w * j * 2.0f;
+    float ik = i * k * 2.0f, jk = j * k * 2.0f, wi = w * i * 2.0f;
+    mat4_identity(m);
+    /* row r, column c lives at m[c*4 + r] */
+    m[0 * 4 + 0] = ww + ii - jj - kk; m[1 * 4 + 0] = ij - wk;           m[2 * 4 + 0] = wj + ik;
+    m[0 * 4 + 1] = wk + ij;           m[1 * 4 + 1] = ww - ii + jj - kk; m[2 * 4 + 1] = jk - wi;
+    m[0 * 4 + 2] = ik - wj;           m[1 * 4 + 2] = wi + jk;           m[2 * 4 + 2] = ww - ii - jj + kk;
+}
+
+/* dot for statically sized vectors (nalgebra base/blas.rs dotx unrolls):
+ * dim 3: (a + b) + c;  dim 4: (a + c) + (b + d). */
+static float dot3(const float x[3], const float y[3]) {
+    float a = x[0] * y[0], b = x[1] * y[1], c = x[2] * y[2];
+    return a + b + c;
+}
+static float dot4(const float x[4], const float y[4]) {
+    float a = x[0] * y[0], b = x[1] * y[1], c = x[2] * y[2], d = x[3] * y[3];
+    a += c;
+    b += d;
+    return a + b;
+}
+
+/* ---- A1: model_matrix_calculation (src/ecs.rs:61-62) -------------------------- */
+void oracle_model_matrix(const float pos[3], const float quat[4], float scale, float m[16]) {
+    float t[16], r[16], s[16], tr[16];
+    mat4_identity(t); /* glm::translation(&pos.coords) */
+    t[12] = pos[0]; t[13] = pos[1]; t[14] = pos[2];
+    quat_to_homogeneous(quat, r); /* rot.to_homogeneous() */
+    mat4_identity(s); /* glm::scaling(&Vec3::repeat(scale)) */
+    s[0] = s[5] = s[10] = scale;
+    oracle_mat4_mul(t, r, tr);
+    oracle_mat4_mul(tr, s, m);
+}
+
+/* ---- A2: aabb_calculation (src/ecs.rs:147-179) -------------------------------- */
+void oracle_aabb(const float m[16], const float mn[3], const float mx[3], float mins[3], float maxs[3]) {
+    /* corner order exactly as listed at ecs.rs:151-159 */
+    const float corners[8][3] = {
+        {mn[0], mn[1], mn[2]}, {mx[0], mn[1], mn[2]}, {mn[0], mn[1], mx[2]}, {mx[0], mn[1], mx[2]},
+        {mn[0], mx[1], mn[2]}, {mx[0], mx[1], mn[2]}, {mn[0], mx[1], mx[2]}, {mx[0], mx[1], mx[2]},
+    };
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX};
+    float hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX}; /* f32::MIN */
+    for (int c = 0; c < 8; c++) {
+        float v[4] = {corners[c][0], corners[c][1], corners[c][2], 1.0f}; /* to_homogeneous */
+        float p[4];
+        gemv4(m, v, p);
+        for (int a = 0; a < 3; a++) {
+            float e = p[a] / p[3]; /* vertex.xyz() / vertex.w */
+            lo[a] = fminf(lo[a], e); /* f32::min */
+            hi[a] = fmaxf(hi[a], e);
+        }
+    }
+    for (int a = 0; a < 3; a++) {
+        float c = (hi[a] + lo[a]) / 2.0f;
+        float h = (hi[a] - lo[a]) / 2.0f;
+        /* ncollide3d AABB::from_half_extents: new(center - half, center + half) */
+        mins[a] = c - h;
+        maxs[a] = c + h;
+    }
+}
+
+/* ---- A3: coarse_culling (cull_pipeline.rs:108-118) ---------------------------- */
+int oracle_coarse_culled(const float mins[3], const float maxs[3], const float planes[6][4]) {
+    float half[3], center[4];
+    for (int a = 0; a < 3; a++) {
+        half[a] = (maxs[a] - mins[a]) * 0.5f;   /* AABB::half_extents() */
+        center[a] = (mins[a] + maxs[a]) * 0.5f; /* AABB::center() = na::center(mins, maxs) */
+    }
+    center[3] = 1.0f; /* to_homogeneous */
+    int outside = 0;
+    for (int p = 0; p < 6; p++) {
+        float ab[3] = {fabsf(planes[p][0]), fabsf(planes[p][1]), fabsf(planes[p][2])};
+        float e = dot3(half, ab);
+        float s = dot4(planes[p], center);
+        if (s - e > 0.0f) {
+            outside = 1;
+            break;
+        }
+    }
+    return outside;
+}
+
+/* ---- A4: pick_lod (helpers.rs:3-11) ------------------------------------------- */
+uint32_t oracle_pick_lod(const float cam[3], const float pos[3], uint32_t n_lods, float lod_distance) {
+    float d[3] = {cam[0] - pos[0], cam[1] - pos[1], cam[2] - pos[2]};
+    float n2 = 0.0f;
+    n2 += dot3(d, d); /* norm_squared(): res = 0; res += col.dotc(col) */
+    float dist = sqrtf(n2);
+    return (dist > lod_distance && n_lods > 1) ? 1u : 0u;
+}
+
+/* ---- A5: per-view matrices and planes ----------------------------------------- */
+
+/* planes = -(row3 +/- row_i) for i = 0,1,2 (src/ecs.rs:82-90); order
+ * left, right, bottom, top, near, far (camera_controller.rs:15). */
+void oracle_frustum_planes(const float pv[16], float planes[6][4]) {
+    for (int i = 0; i < 3; i++)
+        for (int c = 0; c < 4; c++) {
+            float r3 = pv[c * 4 + 3], ri = pv[c * 4 + i];
+            planes[2 * i + 0][c] = -(r3 + ri);
+            planes[2 * i + 1][c] = -(r3 - ri);
+        }
+}
+
+/* glm::perspective_lh_zo (nalgebra-glm ext/matrix_clip_space.rs). */
+static void perspective_lh_zo(float aspect, float fovy, float near, float far, float m[16]) {
+    memset(m, 0, 16 * sizeof(float));
+    float tan_half = tanf(fovy / 2.0f);
+    m[0 * 4 + 0] = 1.0f / (aspect * tan_half);
+    m[1 * 4 + 1] = 1.0f / tan_half;
+    m[2 * 4 + 2] = far / (far - near);
+    m[3 * 4 + 2] = -(far * near) / (far - near);
+    m[2 * 4 + 3] = 1.0f;
+}
+
+static void normalize3(float v[3]) {
+    float n = sqrtf(dot3(v, v));
+    v[0] /= n; v[1] /= n; v[2] /= n;
+}
+static void cross3(const float a[3], const float b[3], float o[3]) {
+    o[0] = a[1] * b[2] - a[2] * b[1];
+    o[1] = a[2] * b[0] - a[0] * b[2];
+    o[2] = a[0] * b[1] - a[1] * b[0];
+}
+/* rotate v by unit quaternion q (i,j,k,w) through its rotation matrix. */
+static void quat_rotate(const float q[4], const float v[3], float o[3]) {
+    float r[16];
+    quat_to_homogeneous(q, r);
+    for (int a = 0; a < 3; a++) o[a] = (r[0 * 4 + a] * v[0] + r[1 * 4 + a] * v[1]) + r[2 * 4 + a] * v[2];
+}
+
+/* project_camera (src/ecs.rs:66-91): near 0.1, far 100, fov 70 deg, view =
+ * look_at_lh(position, position + rot*z, rot*y).  tanf and the look-at chain are
+ * not bit-pinned; planes are INPUTS to both the oracle frame and the GPU. */
+void oracle_project_camera(float aspect, const float pos[3], const float rot[4],
+                           float proj[16], float view[16], float pv[16], float planes[6][4]) {
+    const float fwd[3] = {0, 0, 1}, upv[3] = {0, 1, 0};
+    float fovy = 70.0f * 0.017453292519943295f;
+    perspective_lh_zo(aspect, fovy, 0.1f, 100.0f, proj);
+    float f[3], up[3], s[3], u[3];
+    quat_rotate(rot, fwd, f);
+    quat_rotate(rot, upv, up);
+    normalize3(f);
+    cross3(up, f, s);
+    normalize3(s);
+    cross3(f, s, u);
+    mat4_identity(view);
+    for (int c = 0; c < 3; c++) {
+        view[c * 4 + 0] = s[c];
+        view[c * 4 + 1] = u[c];
+        view[c * 4 + 2] = f[c];
+    }
+    view[12] = -dot3(s, pos);
+    view[13] = -dot3(u, pos);
+    view[14] = -dot3(f, pos);
+    oracle_mat4_mul(proj, view, pv);
+    oracle_frustum_planes(pv, planes);
+}
+
+/* UnitQuaternion::look_at_lh(dir, up): the rotation taking world space into a
+ * frame whose +z is dir (left-handed view).  Built from the basis rows. */
+void oracle_quat_look_at_lh(const float dir[3], const float up[3], float q[4]) {
+    float z[3] = {dir[0], dir[1], dir[2]}, x[3], y[3];
+    normalize3(z);
+    cross3(up, z, x);
+    normalize3(x);
+    cross3(z, x, y);
+    /* rotation matrix rows = x, y, z  (world -> view) */
+    float m00 = x[0], m01 = x[1], m02 = x[2];
+    float m10 = y[0], m11 = y[1], m12 = y[2];
+    float m20 = z[0], m21 = z[1], m22 = z[2];
+    float tr = m00 + m11 + m22, s;
+    if (tr > 0.0f) {
+        s = sqrtf(tr + 1.0f) * 2.0f;
+        q[3] = 0.25f * s; q[0] = (m21 - m12) / s; q[1] = (m02 - m20) / s; q[2] = (m10 - m01) / s;
+    } else if (m00 > m11 && m00 > m22) {
+        s = sqrtf(1.0f + m00 - m11 - m22) * 2.0f;
+        q[3] = (m21 - m12) / s; q[0] = 0.25f * s; q[1] = (m01 + m10) / s; q[2] = (m02 + m20) / s;
+    } else if (m11 > m22) {
+        s = sqrtf(1.0f + m11 - m00 - m22) * 2.0f;
+        q[3] = (m02 - m20) / s; q[0] = (m01 + m10) / s; q[1] = 0.25f * s; q[2] = (m12 + m21) / s;
+    } else {
+        s = sqrtf(1.0f + m22 - m00 - m11) * 2.0f;
+        q[3] = (m10 - m01) / s; q[0] = (m02 + m20) / s; q[1] = (m12 + m21) / s; q[2] = 0.25f * s;
+    }
+    float n = sqrtf(dot4(q, q));
+    for (int a = 0; a < 4; a++) q[a] /= n;
+}
+
+/* shadow_mapping_mvp_calculation (shadow_mapping.rs:321-329):
+ * projection = perspective_lh_zo(1, 70 deg, 10, 400);
+ * view = translation(rot * (-pos)) * rot.to_homogeneous().  The reference derives
+ * no planes for lights; BASELINE config 3 applies ecs.rs:82-90 to this pv. */
+void oracle_light_view(const float pos[3], const float rot[4],
+                       float proj[16], float view[16], float pv[16], float planes[6][4]) {
+    float fovy = 70.0f * 0.017453292519943295f;
+    perspective_lh_zo(1.0f, fovy, 10.0f, 400.0f, proj);
+    float neg[3] = {-pos[0], -pos[1], -pos[2]}, t[3], tm[16], rm[16];
+    quat_rotate(rot, neg, t);
+    mat4_identity(tm);
+    tm[12] = t[0]; tm[13] = t[1]; tm[14] = t[2];
+    quat_to_homogeneous(rot, rm);
+    oracle_mat4_mul(tm, rm, view);
+    oracle_mat4_mul(proj, view, pv);
+    oracle_frustum_planes(pv, planes);
+}
+
+/* ---- whole frame, reference-shaped -------------------------------------------- */
+
+typedef struct {
+    const float *pos, *quat, *scale;
+    const uint32_t *mesh_id;
+    const oracle_mesh *meshes;
+    const float *planes;
+    uint32_t n_views;
+    uint64_t n, lo, hi;
+    float *model, *aabb;
+    uint8_t *flags;
+    int pass;
+} frame_job;
+
+static void frame_pass(frame_job *j) {
+    if (j->pass == 0) { /* model_matrix_calculation: Query<(&Position,&Rotation,&Scale,&mut ModelMatrix)> */
+        for (uint64_t i = j->lo; i < j->hi; i++)
+            oracle_model_matrix(j->pos + 3 * i, j->quat + 4 * i, j->scale[i], j->model + 16 * i);
+    } else if (j->pass == 1) { /* aabb_calculation: Query<(&ModelMatrix,&GltfMesh,&mut AABB)> */
+        for (uint64_t i = j->lo; i < j->hi; i++) {
+            const oracle_mesh *m = j->meshes + j->mesh_id[i];
+            oracle_aabb(j->model + 16 * i, m->aabb_min, m->aabb_max, j->aabb + 6 * i, j->aabb + 6 * i + 3);
+        }
+    } else { /* coarse_culling, once per view: Query<(&AABB,&mut CoarseCulled)> */
+        for (uint32_t v = 0; v < j->n_views; v++) {
+            const float(*pl)[4] = (const float(*)[4])(j->planes + 24 * v);
+            for (uint64_t i = j->lo; i < j->hi; i++)
+                j->flags[(uint64_t)v * j->n + i] = (uint8_t)oracle_coarse_culled(j->aabb + 6 * i, j->aabb + 6 * i + 3, pl);
+        }
+    }
+}
+static void *frame_thread(void *p) {
+    frame_pass((frame_job *)p);
+    return NULL;
+}
+
+static void run_pass(frame_job *base, int pass, int n_threads) {
+    if (n_threads <= 1 || base->n < 1024) {
+        frame_job j = *base;
+        j.pass = pass; j.lo = 0; j.hi = base->n;
+        frame_pass(&j);
+        return;
+    }
+    pthread_t *th = (pthread_t *)malloc(sizeof(pthread_t) * n_threads);
+    frame_job *jobs = (frame_job *)malloc(sizeof(frame_job) * n_threads);
+    for (int t = 0; t < n_threads; t++) {
+        jobs[t] = *base;
+        jobs[t].pass = pass;
+        jobs[t].lo = base->n * (uint64_t)t / n_threads;
+        jobs[t].hi = base->n * (uint64_t)(t + 1) / n_threads;
+        pthread_create(&th[t], NULL, frame_thread, &jobs[t]);
+    }
+    for (int t = 0; t < n_threads; t++) pthread_join(th[t], NULL);
+    free(th);
+    free(jobs);
+}
+
+int oracle_frame(const float *pos, const float *quat, const float *scale, const uint32_t *mesh_id,
+                 uint64_t n, const oracle_mesh *meshes, uint32_t n_meshes,
+                 const float *planes, uint32_t n_views, const float cam_pos[3], float lod_distance,
+                 uint32_t draw_index_base, float *model, float *aabb, uint8_t *flags,
+                 oracle_cmd *cmds, uint32_t *visible, uint32_t *counts, uint64_t *index_totals,
+                 int n_threads) {
+    for (uint64_t i = 0; i < n; i++)
+        if (mesh_id[i] >= n_meshes) return -1;
+    float *own_model = NULL, *own_aabb = NULL;
+    uint8_t *own_flags = NULL;
+    if (!model) model = own_model = (float *)malloc(sizeof(float) * 16 * (n ? n : 1));
+    if (!aabb) aabb = own_aabb = (float *)malloc(sizeof(float) * 6 * (n ? n : 1));
+    if (!flags) flags = own_flags = (uint8_t *)malloc((size_t)(n ? n : 1) * (n_views ? n_views : 1));
+    frame_job base = {pos, quat, scale, mesh_id, meshes, planes, n_views, n, 0, n, model, aabb, flags, 0};
+    run_pass(&base, 0, n_threads);
+    run_pass(&base, 1, n_threads);
+    run_pass(&base, 2, n_threads);
+
+    /* cull_pass emit loop (cull_pipeline.rs:534-577) + generate_work.comp:61-67
+     * header write + compact_draw_stream.comp:41 keep-rule, in draw_index order. */
+    for (uint32_t v = 0; v < n_views; v++) {
+        uint32_t index_offset_in_output = 0, count = 0;
+        uint64_t total = 0;
+        const uint8_t *f = flags + (uint64_t)v * n;
+        for (uint64_t i = 0; i < n; i++) {
+            if (f[i]) continue;
+            const oracle_mesh *m = meshes + mesh_id[i];
+            uint32_t lod = oracle_pick_lod(cam_pos, pos + 3 * i, m->n_lods, lod_distance);
+            uint32_t index_len = m->lod[lod].index_len;
+            if (cmds) {
+                oracle_cmd *c = cmds + (uint64_t)v * n + count;
+                c->indexCount = index_len; /* entity-level upper bound */
+                c->instanceCount = 1;
+                c->firstIndex = index_offset_in_output;
+                c->vertexOffset = m->vertex_offset;
+                c->firstInstance = draw_index_base + (uint32_t)i;
+            }
+            if (visible) visible[(uint64_t)v * n + count] = draw_index_base + (uint32_t)i;
+            index_offset_in_output += index_len; /* u32, wraps like release Rust */
+            total += index_len;
+            count++;
+        }
+        if (counts) counts[v] = count;
+        if (index_totals) index_totals[v] = total;
+    }
+    free(own_model);
+    free(own_aabb);
+    free(own_flags);
+    return 0;
+}
+
+/* ---- per-mesh instanced emission (BASELINE config 4) -------------------------- */
+int oracle_emit_per_mesh(const float *pos, const uint32_t *mesh_id, const uint8_t *flags, uint64_t n,
+                         const oracle_mesh *meshes, uint32_t n_meshes, const float cam_pos[3],
+                         float lod_distance, uint32_t draw_index_base,
+                         oracle_cmd *cmds, uint32_t *visible, uint32_t *count, uint64_t *n_instances) {
+    uint32_t n_slots = n_meshes * ORACLE_MAX_LODS;
+    uint32_t *bucket = (uint32_t *)calloc(n_slots + 1, sizeof(uint32_t));
+    uint32_t *cursor = (uint32_t *)calloc(n_slots + 1, sizeof(uint32_t));
+    for (uint64_t i = 0; i < n; i++) {
+        if (flags[i]) continue;
+        if (mesh_id[i] >= n_meshes) { free(bucket); free(cursor); return -1; }
+        const oracle_mesh *m = meshes + mesh_id[i];
+        uint32_t lod = oracle_pick_lod(cam_pos, pos + 3 * i, m->n_lods, lod_distance);
+        bucket[mesh_id[i] * ORACLE_MAX_LODS + lod]++;
+    }
+    uint32_t run = 0, kept = 0;
+    for (uint32_t s = 0; s < n_slots; s++) {
+        cursor[s] = run;
+        if (bucket[s] > 0) { /* instanceCount > 0 keep-rule */
+            const oracle_mesh *m = meshes + s / ORACLE_MAX_LODS;
+            oracle_cmd *c = cmds + kept++;
+            c->indexCount = m->lod[s % ORACLE_MAX_LODS].index_len;
+            c->instanceCount = bucket[s];
+            c->firstIndex = m->lod[s % ORACLE_MAX_LODS].first_index;
+            c->vertexOffset = m->vertex_offset;
+            c->firstInstance = run;
+        }
+        run += bucket[s];
+    }
+    for (uint64_t i = 0; i < n; i++) {
+        if (flags[i]) continue;
+        const oracle_mesh *m = meshes + mesh_id[i];
+        uint32_t lod = oracle_pick_lod(cam_pos, pos + 3 * i, m->n_lods, lod_distance);
+        visible[cursor[mesh_id[i] * ORACLE_MAX_LODS + lod]++] = draw_index_base + (uint32_t)i;
+    }
+    *count = kept;
+    *n_instances = run;
+    free(bucket);
+    free(cursor);
+    return 0;
+}
+
+/* ---- synthetic scene generator twin ------------------------------------------- */
+static uint64_t mix64(uint64_t z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+static uint64_t chan(uint64_t seed, uint64_t i, uint64_t c) {
+    return mix64(seed + (i * 16 + c + 1) * 0x9E3779B97F4A7C15ull);
+}
+static float unit24(uint64_t h) { return (float)(h >> 40) * 5.9604644775390625e-08f; /* 2^-24 */ }
+
+void oracle_synth_entities(uint64_t seed, uint64_t first, uint64_t n, float half_box, uint32_t n_meshes,
+                           float *pos, float *quat, float *scale, uint32_t *mesh_id) {
+    for (uint64_t k = 0; k < n; k++) {
+        uint64_t i = first + k;
+        for (int a = 0; a < 3; a++) pos[3 * k + a] = (unit24(chan(seed, i, a)) * 2.0f - 1.0f) * half_box;
+        scale[k] = unit24(chan(seed, i, 3)) * 3.75f + 0.25f;
+        float c[4];
+        for (int a = 0; a < 4; a++) c[a] = unit24(chan(seed, i, 4 + a)) * 2.0f - 1.0f;
+        float n2 = ((c[0] * c[0] + c[1] * c[1]) + c[2] * c[2]) + c[3] * c[3];
+        if (n2 < 1e-4f) {
+            c[0] = c[1] = c[2] = 0.0f;
+            c[3] = 1.0f;
+        } else {
+            float nn = sqrtf(n2);
+            for (int a = 0; a < 4; a++) c[a] = c[a] / nn;
+        }
+        /* UnitQuaternion::new_normalize (scene_loader.rs:590): q / sqrt(dot4(q,q)) */
+        float nn = sqrtf(dot4(c, c));
+        for (int a = 0; a < 4; a++) quat[4 * k + a] = c[a] / nn;
+        mesh_id[k] = (uint32_t)(((chan(seed, i, 8) >> 32) * (uint64_t)n_meshes) >> 32);
+    }
+}

@@ -1,0 +1,494 @@
+// rcull.cu -- C ABI of librcull.so (see include/rcull.h).  Host side: context,
+// device buffers, launch configuration.  There is no CPU fallback anywhere in
+// this library: every compute entry point launches sm_100a kernels or fails.
+#include "rcull.h"
+
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "rcull_aux.cuh"
+#include "rcull_frame.cuh"
+
+using namespace rcull;
+
+static_assert(sizeof(rcull_mesh) == 80, "rcull_mesh layout");
+static_assert(sizeof(rcull_draw_cmd) == 20, "VkDrawIndexedIndirectCommand stride");
+static_assert(RCULL_MAX_VIEWS == kMaxViews && RCULL_MAX_LODS == kMaxLods, "header/kernel constants");
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(RCULL_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, \
+                        __LINE__);                                                                 \
+    } while (0)
+
+struct OutputSet {
+    float4* model = nullptr;
+    float* aabb = nullptr;
+    uint8_t* flags[kMaxViews] = {};
+    uint32_t* cmds[kMaxViews] = {};
+    uint32_t* visible[kMaxViews] = {};
+    uint32_t* counts = nullptr;
+    unsigned long long* totals = nullptr;
+};
+
+}  // namespace
+
+struct rcull_ctx {
+    rcull_config cfg{};
+    int sm_count = 0;
+    uint64_t cap = 0;      // entity capacity padded to whole tiles
+    uint64_t cap_vis = 0;  // per-view draw-list capacity
+    float4* pos_scale = nullptr;
+    float4* rot = nullptr;
+    uint32_t* mesh = nullptr;
+    float4* mesh_aabb = nullptr;
+    uint4* lod_tab = nullptr;
+    uint32_t n_meshes = 0;
+    OutputSet out[3];
+    uint64_t* status = nullptr;
+    size_t status_bytes = 0;
+    uint32_t* ticket = nullptr;  // [0] = tile ticket, [1] = error flag
+    uint32_t ticket_base = 0;
+    uint32_t epoch = 0;
+    uint64_t launches = 0;
+    float lod_d2_max = 0.f;
+    int blocks_per_sm[kMaxViews + 1] = {};
+    cudaStream_t own_stream = nullptr;
+    uint32_t* h_counts = nullptr;  // pinned
+    unsigned long long* h_totals = nullptr;
+    std::vector<void*> allocs;
+};
+
+namespace {
+
+template <typename T>
+int dev_alloc(rcull_ctx* c, T** p, size_t count) {
+    void* q = nullptr;
+    CU(cudaMalloc(&q, count * sizeof(T) + 256));
+    c->allocs.push_back(q);
+    *p = static_cast<T*>(q);
+    return 0;
+}
+
+// Largest x with sqrtf(x) <= d, so that (sqrtf(d2) > d) == (d2 > x) exactly
+// (helpers.rs:4-6; sqrtf is correctly rounded and monotone on host and device).
+float lod_threshold(float d) {
+    if (std::isnan(d)) return INFINITY;
+    if (d < 0.f) return -1.f;
+    uint32_t lo = 0, hi = 0x7f800000u;  // bit patterns of +0 .. +inf, monotone in value
+    while (lo < hi) {
+        uint32_t mid = lo + (hi - lo + 1) / 2;
+        float x;
+        memcpy(&x, &mid, 4);
+        if (sqrtf(x) <= d) lo = mid; else hi = mid - 1;
+    }
+    float x;
+    memcpy(&x, &lo, 4);
+    return x;
+}
+
+template <int V>
+int configure(rcull_ctx* c) {
+    auto k = transform_cull_compact<V>;
+    CU(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)frame_smem_bytes<V>()));
+    int b = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k, kThreads, frame_smem_bytes<V>()));
+    if (b < 1) return fail(RCULL_ERR_CUDA, "transform_cull_compact<%d> does not fit on an SM", V);
+    c->blocks_per_sm[V] = b;
+    return 0;
+}
+
+template <int V>
+cudaError_t launch(const FrameArgs& a, int grid, cudaStream_t s) {
+    transform_cull_compact<V><<<grid, kThreads, frame_smem_bytes<V>(), s>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* rcull_last_error(void) { return g_err; }
+uint32_t rcull_version(void) { return (0u << 16) | 1u; }
+
+void rcull_destroy(rcull_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->cfg.device);
+    cudaDeviceSynchronize();
+    for (void* p : c->allocs) cudaFree(p);
+    if (c->h_counts) cudaFreeHost(c->h_counts);
+    if (c->h_totals) cudaFreeHost(c->h_totals);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+
+int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
+    if (!cfg || !out) return fail(RCULL_ERR_INVALID, "rcull_create: null argument");
+    *out = nullptr;
+    if (cfg->max_views < 1 || cfg->max_views > RCULL_MAX_VIEWS)
+        return fail(RCULL_ERR_INVALID, "max_views must be 1..%d", RCULL_MAX_VIEWS);
+    if (cfg->n_buffers < 1 || cfg->n_buffers > 3) return fail(RCULL_ERR_INVALID, "n_buffers must be 1..3");
+    if (cfg->capacity_entities == 0 || cfg->capacity_entities > 0xfffff000ull)
+        return fail(RCULL_ERR_INVALID, "capacity_entities must be 1..2^32-4096");
+    if (cfg->max_meshes == 0 || (uint64_t)cfg->max_meshes * kMaxLods > 0xffffffffull)
+        return fail(RCULL_ERR_INVALID, "max_meshes out of range");
+    if (cfg->output_mode > RCULL_PER_MESH_INSTANCED) return fail(RCULL_ERR_INVALID, "bad output_mode");
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0)
+        return fail(RCULL_ERR_NO_DEVICE, "no CUDA device: librcull has no CPU path");
+    if (cfg->device < 0 || cfg->device >= n_dev) return fail(RCULL_ERR_INVALID, "device %d of %d", cfg->device, n_dev);
+    CU(cudaSetDevice(cfg->device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major != 10)
+        return fail(RCULL_ERR_NO_DEVICE, "device %d is sm_%d%d; librcull is built for sm_100a only", cfg->device,
+                    prop.major, prop.minor);
+
+    rcull_ctx* c = new rcull_ctx();
+    c->cfg = *cfg;
+    c->sm_count = prop.multiProcessorCount;
+    c->cap = (cfg->capacity_entities + kTile - 1) / kTile * kTile;
+    c->cap_vis = cfg->capacity_visible ? cfg->capacity_visible : cfg->capacity_entities;
+    c->lod_d2_max = lod_threshold(cfg->lod_distance);
+    int rc = 0;
+#define TRY(x)                \
+    if ((rc = (x)) != 0) {    \
+        rcull_destroy(c);     \
+        return rc;            \
+    }
+    TRY(dev_alloc(c, &c->pos_scale, c->cap));
+    TRY(dev_alloc(c, &c->rot, c->cap));
+    TRY(dev_alloc(c, &c->mesh, c->cap));
+    TRY(dev_alloc(c, &c->mesh_aabb, (size_t)cfg->max_meshes * 2));
+    TRY(dev_alloc(c, &c->lod_tab, (size_t)cfg->max_meshes * kMaxLods));
+    // padding slots of the last tile are staged by TMA like real ones: keep them defined
+    if (cudaMemset(c->pos_scale, 0, c->cap * 16) != cudaSuccess || cudaMemset(c->rot, 0, c->cap * 16) != cudaSuccess ||
+        cudaMemset(c->mesh, 0, c->cap * 4) != cudaSuccess) {
+        rcull_destroy(c);
+        return fail(RCULL_ERR_CUDA, "cudaMemset of input columns failed");
+    }
+    for (uint32_t b = 0; b < cfg->n_buffers; ++b) {
+        OutputSet& o = c->out[b];
+        TRY(dev_alloc(c, &o.model, c->cap * 4));
+        if (cfg->materialize_aabb) TRY(dev_alloc(c, &o.aabb, c->cap * 6));
+        for (uint32_t v = 0; v < cfg->max_views; ++v) {
+            if (cfg->materialize_flags) TRY(dev_alloc(c, &o.flags[v], c->cap));
+            TRY(dev_alloc(c, &o.cmds[v], c->cap_vis * 5));
+            TRY(dev_alloc(c, &o.visible[v], c->cap_vis));
+        }
+        TRY(dev_alloc(c, &o.counts, kMaxViews));
+        TRY(dev_alloc(c, &o.totals, kMaxViews));
+        cudaMemset(o.counts, 0, kMaxViews * 4);
+        cudaMemset(o.totals, 0, kMaxViews * 8);
+    }
+    const size_t max_tiles = c->cap / kTile;
+    c->status_bytes = max_tiles * cfg->max_views * kStatusWords * sizeof(uint64_t);
+    TRY(dev_alloc(c, &c->status, c->status_bytes / sizeof(uint64_t)));
+    TRY(dev_alloc(c, &c->ticket, 2));
+    if (cudaMemset(c->status, 0, c->status_bytes) != cudaSuccess || cudaMemset(c->ticket, 0, 8) != cudaSuccess) {
+        rcull_destroy(c);
+        return fail(RCULL_ERR_CUDA, "cudaMemset of scan state failed");
+    }
+    if (cudaMallocHost((void**)&c->h_counts, kMaxViews * 4) != cudaSuccess ||
+        cudaMallocHost((void**)&c->h_totals, kMaxViews * 8) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        rcull_destroy(c);
+        return fail(RCULL_ERR_CUDA, "host staging / stream creation failed");
+    }
+    TRY(configure<1>(c));
+    TRY(configure<2>(c));
+    TRY(configure<3>(c));
+    TRY(configure<4>(c));
+    TRY(configure<5>(c));
+    TRY(configure<6>(c));
+    TRY(configure<7>(c));
+    TRY(configure<8>(c));
+#undef TRY
+    CU(cudaDeviceSynchronize());
+    *out = c;
+    return RCULL_OK;
+}
+
+int rcull_set_mesh_table(rcull_ctx* c, const rcull_mesh* meshes, uint32_t n) {
+    if (!c || !meshes) return fail(RCULL_ERR_INVALID, "rcull_set_mesh_table: null argument");
+    if (n == 0 || n > c->cfg.max_meshes) return fail(RCULL_ERR_INVALID, "mesh count %u exceeds max_meshes %u", n, c->cfg.max_meshes);
+    std::vector<float4> aabb(2 * (size_t)n);
+    std::vector<uint4> lods((size_t)n * kMaxLods, make_uint4(0, 0, 0, 0));
+    for (uint32_t i = 0; i < n; ++i) {
+        const rcull_mesh& m = meshes[i];
+        // pick_lod .expect("empty index buffer LODs") (helpers.rs:7-9)
+        if (m.n_lods < 1 || m.n_lods > kMaxLods) return fail(RCULL_ERR_INVALID, "mesh %u: n_lods %u not in 1..%d", i, m.n_lods, kMaxLods);
+        float nl;
+        memcpy(&nl, &m.n_lods, 4);
+        aabb[2 * i] = make_float4(m.aabb_min[0], m.aabb_min[1], m.aabb_min[2], nl);
+        aabb[2 * i + 1] = make_float4(m.aabb_max[0], m.aabb_max[1], m.aabb_max[2], 0.f);
+        for (uint32_t l = 0; l < m.n_lods; ++l)
+            lods[(size_t)i * kMaxLods + l] = make_uint4(m.lod[l].index_len, m.lod[l].first_index, (uint32_t)m.vertex_offset, 0);
+    }
+    CU(cudaSetDevice(c->cfg.device));
+    CU(cudaMemcpy(c->mesh_aabb, aabb.data(), aabb.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(c->lod_tab, lods.data(), lods.size() * sizeof(uint4), cudaMemcpyHostToDevice));
+    c->n_meshes = n;
+    return RCULL_OK;
+}
+
+int rcull_upload_entities(rcull_ctx* c, uint64_t first, uint64_t n, const float* pos_scale, const float* rot,
+                          const uint32_t* mesh, void* stream) {
+    if (!c || (n && (!pos_scale || !rot || !mesh))) return fail(RCULL_ERR_INVALID, "rcull_upload_entities: null argument");
+    if (first + n > c->cfg.capacity_entities) return fail(RCULL_ERR_INVALID, "entities [%llu, %llu) exceed capacity %llu", (unsigned long long)first, (unsigned long long)(first + n), (unsigned long long)c->cfg.capacity_entities);
+    if (n == 0) return RCULL_OK;
+    CU(cudaSetDevice(c->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    CU(cudaMemcpyAsync(c->pos_scale + first, pos_scale, n * 16, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(c->rot + first, rot, n * 16, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(c->mesh + first, mesh, n * 4, cudaMemcpyHostToDevice, s));
+    return RCULL_OK;
+}
+
+int rcull_entity_ptrs(rcull_ctx* c, float** pos_scale, float** rot, uint32_t** mesh) {
+    if (!c) return fail(RCULL_ERR_INVALID, "rcull_entity_ptrs: null context");
+    if (pos_scale) *pos_scale = reinterpret_cast<float*>(c->pos_scale);
+    if (rot) *rot = reinterpret_cast<float*>(c->rot);
+    if (mesh) *mesh = c->mesh;
+    return RCULL_OK;
+}
+
+int rcull_pack_components(uint64_t n, const float* position, const float* rotation, const float* scale,
+                          float* pos_scale, float* rot) {
+    if (n && (!position || !rotation || !scale || !pos_scale || !rot))
+        return fail(RCULL_ERR_INVALID, "rcull_pack_components: null argument");
+    for (uint64_t i = 0; i < n; ++i) {
+        pos_scale[4 * i + 0] = position[3 * i + 0];
+        pos_scale[4 * i + 1] = position[3 * i + 1];
+        pos_scale[4 * i + 2] = position[3 * i + 2];
+        pos_scale[4 * i + 3] = scale[i];
+    }
+    memcpy(rot, rotation, n * 16);
+    return RCULL_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------
+// frame
+// ---------------------------------------------------------------------------------
+extern "C" {
+
+int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_views, const float cam_pos[3],
+                uint32_t draw_index_base, uint32_t buffer_ix, void* stream) {
+    if (!c || !views || !cam_pos) return fail(RCULL_ERR_INVALID, "rcull_frame: null argument");
+    if (n > c->cfg.capacity_entities) return fail(RCULL_ERR_INVALID, "n %llu exceeds capacity_entities %llu", (unsigned long long)n, (unsigned long long)c->cfg.capacity_entities);
+    if (n_views < 1 || n_views > c->cfg.max_views) return fail(RCULL_ERR_INVALID, "n_views %u not in 1..%u", n_views, c->cfg.max_views);
+    if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
+    if (c->n_meshes == 0) return fail(RCULL_ERR_INVALID, "rcull_set_mesh_table has not been called");
+    if (c->cfg.output_mode != RCULL_PER_ENTITY) return fail(RCULL_ERR_INVALID, "output mode %u not available in this build", c->cfg.output_mode);
+    CU(cudaSetDevice(c->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    OutputSet& o = c->out[buffer_ix];
+    if (n == 0) {  // empty query: cull_pass still clears the buffers (cull_pipeline.rs:498-511)
+        CU(cudaMemsetAsync(o.counts, 0, kMaxViews * 4, s));
+        CU(cudaMemsetAsync(o.totals, 0, kMaxViews * 8, s));
+        return RCULL_OK;
+    }
+    const uint32_t n_tiles = (uint32_t)((n + kTile - 1) / kTile);
+    if (++c->epoch >= (1u << 30)) {  // epoch tag would wrap: start over from clean status words
+        CU(cudaMemsetAsync(c->status, 0, c->status_bytes, s));
+        c->epoch = 1;
+    }
+    FrameArgs a;
+    memset(&a, 0, sizeof a);
+    a.pos_scale = c->pos_scale;
+    a.rot = c->rot;
+    a.mesh = c->mesh;
+    a.mesh_aabb = c->mesh_aabb;
+    a.lod_tab = c->lod_tab;
+    a.model = o.model;
+    a.aabb = o.aabb;
+    for (uint32_t v = 0; v < n_views; ++v) {
+        a.flags[v] = o.flags[v];
+        a.cmds[v] = o.cmds[v];
+        a.visible[v] = o.visible[v];
+        for (int p = 0; p < 6; ++p) {
+            for (int x = 0; x < 4; ++x) a.planes[v][p][x] = views[v].planes[p][x];
+            for (int x = 0; x < 3; ++x) a.absn[v][p][x] = fabsf(views[v].planes[p][x]);
+        }
+    }
+    a.counts = o.counts;
+    a.totals = o.totals;
+    a.status = c->status;
+    a.ticket = c->ticket;
+    a.error_flag = c->ticket + 1;
+    a.ticket_base = c->ticket_base;
+    a.epoch = c->epoch;
+    a.n = (uint32_t)n;
+    a.n_tiles = n_tiles;
+    a.n_meshes = c->n_meshes;
+    a.draw_index_base = draw_index_base;
+    a.cap_visible = (uint32_t)(c->cap_vis > 0xffffffffull ? 0xffffffffull : c->cap_vis);
+    a.cam[0] = cam_pos[0];
+    a.cam[1] = cam_pos[1];
+    a.cam[2] = cam_pos[2];
+    a.lod_d2_max = c->lod_d2_max;
+    int grid = c->sm_count * c->blocks_per_sm[n_views];
+    if ((uint32_t)grid > n_tiles) grid = (int)n_tiles;
+    cudaError_t e = cudaSuccess;
+    switch (n_views) {
+        case 1: e = launch<1>(a, grid, s); break;
+        case 2: e = launch<2>(a, grid, s); break;
+        case 3: e = launch<3>(a, grid, s); break;
+        case 4: e = launch<4>(a, grid, s); break;
+        case 5: e = launch<5>(a, grid, s); break;
+        case 6: e = launch<6>(a, grid, s); break;
+        case 7: e = launch<7>(a, grid, s); break;
+        case 8: e = launch<8>(a, grid, s); break;
+    }
+    if (e != cudaSuccess) return fail(RCULL_ERR_CUDA, "transform_cull_compact launch failed: %s", cudaGetErrorString(e));
+    c->ticket_base += n_tiles + (uint32_t)grid;  // every CTA draws exactly one ticket past the end
+    c->launches += 1;
+    return RCULL_OK;
+}
+
+static int check_device_error(rcull_ctx* c) {
+    uint32_t flag = 0;
+    CU(cudaMemcpy(&flag, c->ticket + 1, 4, cudaMemcpyDeviceToHost));
+    if (flag) {
+        cudaMemset(c->ticket + 1, 0, 4);
+        return fail(RCULL_ERR_INVALID, "mesh id out of range of the mesh table (Vertex/Index buffer not consolidated, cull_pipeline.rs:543)");
+    }
+    return RCULL_OK;
+}
+
+int rcull_frame_host(rcull_ctx* c, uint64_t n, const float* pos_scale, const float* rot, const uint32_t* mesh,
+                     const rcull_view* views, uint32_t n_views, const float cam_pos[3], uint32_t draw_index_base,
+                     uint32_t buffer_ix, uint32_t* counts_out, uint64_t* index_totals_out) {
+    if (!c) return fail(RCULL_ERR_INVALID, "rcull_frame_host: null context");
+    int rc = rcull_upload_entities(c, 0, n, pos_scale, rot, mesh, c->own_stream);
+    if (rc) return rc;
+    rc = rcull_frame(c, n, views, n_views, cam_pos, draw_index_base, buffer_ix, c->own_stream);
+    if (rc) return rc;
+    OutputSet& o = c->out[buffer_ix];
+    CU(cudaMemcpyAsync(c->h_counts, o.counts, kMaxViews * 4, cudaMemcpyDeviceToHost, c->own_stream));
+    CU(cudaMemcpyAsync(c->h_totals, o.totals, kMaxViews * 8, cudaMemcpyDeviceToHost, c->own_stream));
+    CU(cudaStreamSynchronize(c->own_stream));
+    for (uint32_t v = 0; v < n_views; ++v) {
+        if (counts_out) counts_out[v] = c->h_counts[v];
+        if (index_totals_out) index_totals_out[v] = c->h_totals[v];
+    }
+    return RCULL_OK;
+}
+
+int rcull_get_outputs(rcull_ctx* c, uint32_t buffer_ix, rcull_outputs* out) {
+    if (!c || !out) return fail(RCULL_ERR_INVALID, "rcull_get_outputs: null argument");
+    if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
+    const OutputSet& o = c->out[buffer_ix];
+    memset(out, 0, sizeof *out);
+    out->model = reinterpret_cast<float*>(o.model);
+    out->aabb = o.aabb;
+    for (int v = 0; v < kMaxViews; ++v) {
+        out->flags[v] = o.flags[v];
+        out->cmds[v] = reinterpret_cast<rcull_draw_cmd*>(o.cmds[v]);
+        out->visible[v] = o.visible[v];
+    }
+    out->counts = o.counts;
+    out->index_totals = reinterpret_cast<uint64_t*>(o.totals);
+    return RCULL_OK;
+}
+
+#define DL_PROLOGUE(what)                                                                         \
+    if (!c || !dst) return fail(RCULL_ERR_INVALID, what ": null argument");                       \
+    if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, what ": buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers); \
+    CU(cudaSetDevice(c->cfg.device));                                                             \
+    CU(cudaDeviceSynchronize());
+
+int rcull_download_counts(rcull_ctx* c, uint32_t buffer_ix, uint32_t* dst, uint64_t* index_totals) {
+    DL_PROLOGUE("rcull_download_counts");
+    int rc = check_device_error(c);
+    if (rc) return rc;
+    CU(cudaMemcpy(dst, c->out[buffer_ix].counts, c->cfg.max_views * 4, cudaMemcpyDeviceToHost));
+    if (index_totals) CU(cudaMemcpy(index_totals, c->out[buffer_ix].totals, c->cfg.max_views * 8, cudaMemcpyDeviceToHost));
+    return RCULL_OK;
+}
+int rcull_download_model(rcull_ctx* c, uint32_t buffer_ix, uint64_t first, uint64_t n, float* dst) {
+    DL_PROLOGUE("rcull_download_model");
+    if (first + n > c->cap) return fail(RCULL_ERR_INVALID, "model range out of bounds");
+    CU(cudaMemcpy(dst, c->out[buffer_ix].model + first * 4, n * 64, cudaMemcpyDeviceToHost));
+    return RCULL_OK;
+}
+int rcull_download_aabb(rcull_ctx* c, uint32_t buffer_ix, uint64_t first, uint64_t n, float* dst) {
+    DL_PROLOGUE("rcull_download_aabb");
+    if (!c->out[buffer_ix].aabb) return fail(RCULL_ERR_INVALID, "context created without materialize_aabb");
+    if (first + n > c->cap) return fail(RCULL_ERR_INVALID, "aabb range out of bounds");
+    CU(cudaMemcpy(dst, c->out[buffer_ix].aabb + first * 6, n * 24, cudaMemcpyDeviceToHost));
+    return RCULL_OK;
+}
+int rcull_download_flags(rcull_ctx* c, uint32_t buffer_ix, uint32_t view, uint64_t first, uint64_t n, uint8_t* dst) {
+    DL_PROLOGUE("rcull_download_flags");
+    if (view >= c->cfg.max_views || !c->out[buffer_ix].flags[view]) return fail(RCULL_ERR_INVALID, "flags not materialised for view %u", view);
+    if (first + n > c->cap) return fail(RCULL_ERR_INVALID, "flags range out of bounds");
+    CU(cudaMemcpy(dst, c->out[buffer_ix].flags[view] + first, n, cudaMemcpyDeviceToHost));
+    return RCULL_OK;
+}
+int rcull_download_cmds(rcull_ctx* c, uint32_t buffer_ix, uint32_t view, uint64_t first, uint64_t n, rcull_draw_cmd* dst) {
+    DL_PROLOGUE("rcull_download_cmds");
+    if (view >= c->cfg.max_views) return fail(RCULL_ERR_INVALID, "view %u of %u", view, c->cfg.max_views);
+    if (first + n > c->cap_vis) return fail(RCULL_ERR_INVALID, "command range out of bounds");
+    CU(cudaMemcpy(dst, c->out[buffer_ix].cmds[view] + first * 5, n * 20, cudaMemcpyDeviceToHost));
+    return RCULL_OK;
+}
+int rcull_download_visible(rcull_ctx* c, uint32_t buffer_ix, uint32_t view, uint64_t first, uint64_t n, uint32_t* dst) {
+    DL_PROLOGUE("rcull_download_visible");
+    if (view >= c->cfg.max_views) return fail(RCULL_ERR_INVALID, "view %u of %u", view, c->cfg.max_views);
+    if (first + n > c->cap_vis) return fail(RCULL_ERR_INVALID, "visible range out of bounds");
+    CU(cudaMemcpy(dst, c->out[buffer_ix].visible[view] + first, n * 4, cudaMemcpyDeviceToHost));
+    return RCULL_OK;
+}
+
+int rcull_rebase_into(rcull_ctx* c, uint32_t buffer_ix, uint32_t view, uint64_t index_prefix, rcull_draw_cmd* dst_cmds,
+                      uint32_t* dst_visible, void* stream) {
+    if (!c || !dst_cmds || !dst_visible) return fail(RCULL_ERR_INVALID, "rcull_rebase_into: null argument");
+    if (buffer_ix >= c->cfg.n_buffers || view >= c->cfg.max_views) return fail(RCULL_ERR_INVALID, "rcull_rebase_into: bad buffer/view");
+    CU(cudaSetDevice(c->cfg.device));
+    const OutputSet& o = c->out[buffer_ix];
+    rebase_into<<<c->sm_count * 4, 256, 0, (cudaStream_t)stream>>>(
+        o.cmds[view], o.visible[view], o.counts + view, (uint32_t)(c->cap_vis > 0xffffffffull ? 0xffffffffull : c->cap_vis),
+        (uint32_t)index_prefix, reinterpret_cast<uint32_t*>(dst_cmds), dst_visible);
+    CU(cudaGetLastError());
+    c->launches += 1;
+    return RCULL_OK;
+}
+
+int rcull_synth_entities(rcull_ctx* c, uint64_t seed, uint64_t first_global, uint64_t n, float half_box,
+                         uint32_t n_meshes, void* stream) {
+    if (!c) return fail(RCULL_ERR_INVALID, "rcull_synth_entities: null context");
+    if (n > c->cfg.capacity_entities) return fail(RCULL_ERR_INVALID, "n exceeds capacity_entities");
+    if (n == 0) return RCULL_OK;
+    CU(cudaSetDevice(c->cfg.device));
+    synth_entities<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(seed, first_global, (uint32_t)n, half_box,
+                                                                             n_meshes, c->pos_scale, c->rot, c->mesh);
+    CU(cudaGetLastError());
+    c->launches += 1;
+    return RCULL_OK;
+}
+
+uint64_t rcull_launch_count(rcull_ctx* c) { return c ? c->launches : 0; }
+
+}  // extern "C"

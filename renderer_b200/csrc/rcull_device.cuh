@@ -1,0 +1,147 @@
+// rcull_device.cuh -- device-side primitives for librcull (sm_100a only).
+//
+// PTX wrappers for the TMA bulk-copy / mbarrier input pipeline and the
+// release/acquire tile-status words of the decoupled-lookback scan, plus the
+// per-entity arithmetic pinned to the reference's operation order.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rcull {
+
+constexpr uint32_t kFullMask = 0xffffffffu;
+
+// ---- mbarrier + 1-D bulk async copy (TMA engine, SASS UBLKCP) ------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+// Orders earlier generic-proxy smem accesses before later async-proxy (TMA) writes.
+__device__ __forceinline__ void fence_proxy_async() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// global -> shared bulk copy; bytes % 16 == 0, both addresses 16-B aligned.
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+// ---- tile-status words (decoupled lookback) --------------------------------------
+__device__ __forceinline__ uint64_t ld_acquire(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint64_t ld_relaxed(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed(uint64_t* p, uint64_t v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_release(uint64_t* p, uint64_t v) {
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// ---- warp helpers ----------------------------------------------------------------
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
+__device__ __forceinline__ uint32_t lanemask_lt() {
+    uint32_t m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+__device__ __forceinline__ uint64_t warp_sum_u64(uint64_t v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);
+    return v;
+}
+__device__ __forceinline__ uint32_t warp_incl_scan_u32(uint32_t v, uint32_t lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(kFullMask, v, o);
+        if (lane >= (uint32_t)o) v += t;
+    }
+    return v;
+}
+
+// ---- per-entity arithmetic (operation order = SURVEY 8a; compiled -fmad=false) ----
+struct Mat34 {  // upper 3 rows of the column-major model matrix; row 3 is (0,0,0,1)
+    float m00, m10, m20;  // column 0
+    float m01, m11, m21;  // column 1
+    float m02, m12, m22;  // column 2
+    float tx, ty, tz;     // column 3
+};
+
+// A1: glm::translation(pos) * rot.to_homogeneous() * glm::scaling(repeat(scale))
+// (src/ecs.rs:61-62).  The generic 4x4 products only add exact zeros around
+// fl(R_rc * s) and t, so the result is computed directly.
+__device__ __forceinline__ Mat34 model_matrix(float4 ps, float4 q) {
+    const float i = q.x, j = q.y, k = q.z, w = q.w, s = ps.w;
+    const float ww = __fmul_rn(w, w), ii = __fmul_rn(i, i), jj = __fmul_rn(j, j), kk = __fmul_rn(k, k);
+    const float ij = __fmul_rn(__fmul_rn(i, j), 2.0f), wk = __fmul_rn(__fmul_rn(w, k), 2.0f);
+    const float wj = __fmul_rn(__fmul_rn(w, j), 2.0f), ik = __fmul_rn(__fmul_rn(i, k), 2.0f);
+    const float jk = __fmul_rn(__fmul_rn(j, k), 2.0f), wi = __fmul_rn(__fmul_rn(w, i), 2.0f);
+    Mat34 m;
+    m.m00 = __fmul_rn(__fsub_rn(__fsub_rn(__fadd_rn(ww, ii), jj), kk), s);
+    m.m01 = __fmul_rn(__fsub_rn(ij, wk), s);
+    m.m02 = __fmul_rn(__fadd_rn(wj, ik), s);
+    m.m10 = __fmul_rn(__fadd_rn(wk, ij), s);
+    m.m11 = __fmul_rn(__fsub_rn(__fadd_rn(__fsub_rn(ww, ii), jj), kk), s);
+    m.m12 = __fmul_rn(__fsub_rn(jk, wi), s);
+    m.m20 = __fmul_rn(__fsub_rn(ik, wj), s);
+    m.m21 = __fmul_rn(__fadd_rn(wi, jk), s);
+    m.m22 = __fmul_rn(__fadd_rn(__fsub_rn(__fsub_rn(ww, ii), jj), kk), s);
+    m.tx = ps.x;
+    m.ty = ps.y;
+    m.tz = ps.z;
+    return m;
+}
+
+// A2 for one row of M: min/max over the 8 transformed corners.  Each corner is
+// fl(fl(fl(a*X + b*Y) + c*Z) + t) (nalgebra gemv order) and rounded addition is
+// monotone in each argument, so the extremum over {min,max}^3 is reached at the
+// per-term extrema: 6 products and 6 sums instead of 8 full transforms.
+__device__ __forceinline__ void row_extent(float a, float b, float c, float t, float4 mn, float4 mx, float& lo,
+                                           float& hi) {
+    const float ax0 = __fmul_rn(a, mn.x), ax1 = __fmul_rn(a, mx.x);
+    const float by0 = __fmul_rn(b, mn.y), by1 = __fmul_rn(b, mx.y);
+    const float cz0 = __fmul_rn(c, mn.z), cz1 = __fmul_rn(c, mx.z);
+    lo = __fadd_rn(t, __fadd_rn(fminf(cz0, cz1), __fadd_rn(fminf(by0, by1), fminf(ax0, ax1))));
+    hi = __fadd_rn(t, __fadd_rn(fmaxf(cz0, cz1), __fadd_rn(fmaxf(by0, by1), fmaxf(ax0, ax1))));
+}
+
+// A2 tail (src/ecs.rs:173-178) + ncollide3d AABB::from_half_extents.
+__device__ __forceinline__ void aabb_store_form(float lo, float hi, float& mins, float& maxs) {
+    const float c = __fmul_rn(__fadd_rn(hi, lo), 0.5f);  // (max+min)/2.0, exact same rounding as *0.5
+    const float h = __fmul_rn(__fsub_rn(hi, lo), 0.5f);
+    mins = __fsub_rn(c, h);
+    maxs = __fadd_rn(c, h);
+}
+
+}  // namespace rcull

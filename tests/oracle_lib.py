@@ -1,0 +1,149 @@
+"""ctypes wrapper of oracle/librcull_oracle.so -- TEST INFRASTRUCTURE.
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs import this."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PATH = os.path.join(ROOT, "oracle", "librcull_oracle.so")
+
+MESH_DTYPE = np.dtype(
+    [("aabb_min", "<f4", (3,)), ("aabb_max", "<f4", (3,)), ("n_lods", "<u4"), ("lod", "<u4", (6, 2)), ("vertex_offset", "<i4")]
+)
+CMD_DTYPE = np.dtype(
+    [("indexCount", "<u4"), ("instanceCount", "<u4"), ("firstIndex", "<u4"), ("vertexOffset", "<i4"), ("firstInstance", "<u4")]
+)
+_P, _u32, _u64, _f = C.c_void_p, C.c_uint32, C.c_uint64, C.c_float
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(PATH)
+        L.oracle_model_matrix.argtypes = [_P, _P, _f, _P]
+        L.oracle_aabb.argtypes = [_P] * 5
+        L.oracle_coarse_culled.argtypes = [_P, _P, _P]
+        L.oracle_coarse_culled.restype = C.c_int
+        L.oracle_pick_lod.argtypes = [_P, _P, _u32, _f]
+        L.oracle_pick_lod.restype = _u32
+        L.oracle_frustum_planes.argtypes = [_P, _P]
+        L.oracle_project_camera.argtypes = [_f, _P, _P, _P, _P, _P, _P]
+        L.oracle_light_view.argtypes = [_P] * 6
+        L.oracle_quat_look_at_lh.argtypes = [_P, _P, _P]
+        L.oracle_mat4_mul.argtypes = [_P, _P, _P]
+        L.oracle_frame.argtypes = [_P, _P, _P, _P, _u64, _P, _u32, _P, _u32, _P, _f, _u32, _P, _P, _P, _P, _P, _P, _P, C.c_int]
+        L.oracle_frame.restype = C.c_int
+        L.oracle_emit_per_mesh.argtypes = [_P, _P, _P, _u64, _P, _u32, _P, _f, _u32, _P, _P, _P, _P]
+        L.oracle_emit_per_mesh.restype = C.c_int
+        L.oracle_synth_entities.argtypes = [_u64, _u64, _u64, _f, _u32, _P, _P, _P, _P]
+        _lib = L
+    return _lib
+
+
+def p(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+def f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def model_matrix(pos, quat, scale):
+    m = np.empty(16, np.float32)
+    lib().oracle_model_matrix(p(f32(pos)), p(f32(quat)), float(scale), p(m))
+    return m
+
+
+def aabb(m, mesh_min, mesh_max):
+    lo, hi = np.empty(3, np.float32), np.empty(3, np.float32)
+    lib().oracle_aabb(p(f32(m)), p(f32(mesh_min)), p(f32(mesh_max)), p(lo), p(hi))
+    return lo, hi
+
+
+def coarse_culled(mins, maxs, planes):
+    return bool(lib().oracle_coarse_culled(p(f32(mins)), p(f32(maxs)), p(f32(planes))))
+
+
+def pick_lod(cam, pos, n_lods, lod_distance=10.0):
+    return int(lib().oracle_pick_lod(p(f32(cam)), p(f32(pos)), n_lods, lod_distance))
+
+
+def frustum_planes(pv):
+    out = np.empty((6, 4), np.float32)
+    lib().oracle_frustum_planes(p(f32(pv)), p(out))
+    return out
+
+
+def project_camera(aspect, pos, rot):
+    proj, view, pv = (np.empty(16, np.float32) for _ in range(3))
+    planes = np.empty((6, 4), np.float32)
+    lib().oracle_project_camera(aspect, p(f32(pos)), p(f32(rot)), p(proj), p(view), p(pv), p(planes))
+    return proj, view, pv, planes
+
+
+def light_view(pos, rot):
+    proj, view, pv = (np.empty(16, np.float32) for _ in range(3))
+    planes = np.empty((6, 4), np.float32)
+    lib().oracle_light_view(p(f32(pos)), p(f32(rot)), p(proj), p(view), p(pv), p(planes))
+    return proj, view, pv, planes
+
+
+def quat_look_at_lh(direction, up=(0, 1, 0)):
+    q = np.empty(4, np.float32)
+    lib().oracle_quat_look_at_lh(p(f32(direction)), p(f32(up)), p(q))
+    return q
+
+
+def synth_entities(seed, first, n, half_box, n_meshes):
+    pos, quat = np.empty((n, 3), np.float32), np.empty((n, 4), np.float32)
+    scale, mesh = np.empty(n, np.float32), np.empty(n, np.uint32)
+    lib().oracle_synth_entities(seed, first, n, half_box, n_meshes, p(pos), p(quat), p(scale), p(mesh))
+    return pos, quat, scale, mesh
+
+
+def frame(pos, quat, scale, mesh_id, meshes, planes, cam_pos, lod_distance=10.0, draw_index_base=0,
+          n_threads=1, want=("model", "aabb", "flags", "cmds", "visible")):
+    """Runs oracle_frame; returns a dict of the requested outputs (lists trimmed to counts)."""
+    pos, quat, scale = f32(pos).reshape(-1, 3), f32(quat).reshape(-1, 4), f32(scale).reshape(-1)
+    mesh_id = np.ascontiguousarray(mesh_id, np.uint32)
+    meshes = np.ascontiguousarray(meshes, MESH_DTYPE)
+    planes = f32(planes).reshape(-1, 6, 4)
+    n, v = len(scale), len(planes)
+    out = {
+        "model": np.empty((n, 16), np.float32) if "model" in want else None,
+        "aabb": np.empty((n, 6), np.float32) if "aabb" in want else None,
+        "flags": np.empty((v, n), np.uint8) if "flags" in want else None,
+        "cmds": np.empty((v, max(n, 1)), CMD_DTYPE) if "cmds" in want else None,
+        "visible": np.empty((v, max(n, 1)), np.uint32) if "visible" in want else None,
+    }
+    counts, totals = np.zeros(v, np.uint32), np.zeros(v, np.uint64)
+    rc = lib().oracle_frame(p(pos), p(quat), p(scale), p(mesh_id), n, p(meshes), len(meshes), p(planes), v,
+                            p(f32(cam_pos)), lod_distance, draw_index_base, p(out["model"]), p(out["aabb"]),
+                            p(out["flags"]), p(out["cmds"]), p(out["visible"]), p(counts), p(totals), n_threads)
+    if rc != 0:
+        raise ValueError("oracle_frame: mesh id out of range")
+    out["counts"], out["totals"] = counts, totals
+    if out["cmds"] is not None:
+        out["cmds"] = [out["cmds"][k, : counts[k]] for k in range(v)]
+    if out["visible"] is not None:
+        out["visible"] = [out["visible"][k, : counts[k]] for k in range(v)]
+    return out
+
+
+def emit_per_mesh(pos, mesh_id, flags, meshes, cam_pos, lod_distance=10.0, draw_index_base=0):
+    pos = f32(pos).reshape(-1, 3)
+    n = len(pos)
+    meshes = np.ascontiguousarray(meshes, MESH_DTYPE)
+    cmds = np.empty(len(meshes) * 6, CMD_DTYPE)
+    visible = np.empty(max(n, 1), np.uint32)
+    count, inst = _u32(0), _u64(0)
+    rc = lib().oracle_emit_per_mesh(p(pos), p(np.ascontiguousarray(mesh_id, np.uint32)), p(np.ascontiguousarray(flags, np.uint8)),
+                                    n, p(meshes), len(meshes), p(f32(cam_pos)), lod_distance, draw_index_base,
+                                    p(cmds), p(visible), C.byref(count), C.byref(inst))
+    if rc != 0:
+        raise ValueError("oracle_emit_per_mesh failed")
+    return cmds[: count.value], visible[: inst.value]
