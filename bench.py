@@ -1,0 +1,298 @@
+#!/usr/bin/env python
+"""bench.py -- entities/s through transform + cull + compact (BASELINE.json metric).
+
+One "step" = one pass of the hot path (rcull_frame; plus the draw-list merge when
+N > 1) over one batch of synthetic entities.  Workload (config.workload):
+  16m_5view  BASELINE configs[2]: 16 Mi entities PER GPU, camera + 4 shadow views
+             (the configuration north_star's 70 %-of-roofline target is quoted on;
+             at N > 1 it becomes configs[4]: range shards + NCCL merge, weak scaling)
+  1m_1view   BASELINE configs[1]: 1 M entities, camera only (fits in L2: flushed)
+Prints ONE JSON line (rank 0).  `--impl reference` times the CPU oracle -- the
+reference's Rust/bevy code cannot be built on this box -- on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    "16m_5view": dict(n=16 * 1024 * 1024, n_views=5, half_box=600.0),
+    "16m_1view": dict(n=16 * 1024 * 1024, n_views=1, half_box=600.0),
+    "1m_1view": dict(n=1_000_000, n_views=1, half_box=250.0),
+}
+METRIC = "entities/sec transformed+culled+compacted"
+UNIT = "entities/s"
+CPU_SAMPLE = 2 * 1024 * 1024  # entities per CPU-baseline step (bounded sample of the workload)
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons DURING the timed region."""
+
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index: int):
+        self.index, self.samples, self._stop = index, [], threading.Event()
+        self._t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def __enter__(self):
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        sm = [float(s[0]) for s in self.samples if s and s[0].replace(".", "").isdigit()]
+        mx = [float(s[1]) for s in self.samples if len(s) > 1 and s[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for s in self.samples for i in range(4) if len(s) > 2 + i and s[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def cpu_baseline(wl, steps: int, warmup: int, threads: int):
+    """The oracle (kind "port") on a bounded sample of the workload, all host threads."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O  # CPU-baseline leg: the one place bench.py may execute oracle/
+    from renderer_b200 import scene
+
+    n = min(CPU_SAMPLE, wl["n"])
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, wl["half_box"])
+    pos, quat, scale = scene.to_components(ps, rot)
+    meshes = scene.synth_mesh_table()
+    views = scene.scene_views(wl["n_views"])
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        r = O.frame(pos, quat, scale, mesh, meshes, views, scene.CAMERA_POS, n_threads=threads, want=("cmds", "visible"))
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    t = float(np.mean(times))
+    return {"value": n / t, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"first {n} entities of the workload, {wl['n_views']} views, {steps} steps, reference-shaped passes + serial emit",
+            "ms_per_step": t * 1e3, "visible": [int(c) for c in r["counts"]]}
+
+
+def gpu_arm(args, wl):
+    import torch
+    import torch.distributed as dist
+
+    from renderer_b200 import CullContext, scene
+    from renderer_b200.shard import ShardMerger, _wrap_device
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: librcull has no CPU path (use --impl reference for the CPU oracle)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    n, n_views = wl["n"], wl["n_views"]
+    lo = rank * n  # weak scaling: every rank owns n entities of an (n * world)-entity scene
+    meshes = scene.synth_mesh_table()
+    views = scene.scene_views(n_views)
+    ctx = CullContext(n, max_views=n_views, max_meshes=len(meshes), device=local_rank)
+    ctx.set_mesh_table(meshes)
+    stream = torch.cuda.Stream(device=dev)
+    sh = stream.cuda_stream
+    ctx.synth_entities(scene.SEED, lo, n, wl["half_box"], len(meshes), stream=sh)
+    stream.synchronize()
+
+    merger = None
+    if world > 1:
+        ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, stream=sh)
+        stream.synchronize()
+        c0, _ = ctx.counts()
+        tot = torch.tensor([int(c0[:n_views].max())], dtype=torch.int64, device=dev)
+        dist.all_reduce(tot)
+        merger = ShardMerger(n_views, int(tot.item() * 1.05) + 1024, dev)
+
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev) if n * 36 < 256e6 else None
+
+    def step():
+        ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, stream=sh)
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(stream):
+        for _ in range(args.warmup):
+            step()
+            if merger:
+                merger.merge_from_context(ctx, stream=sh)
+            if flush is not None:
+                flush.zero_()
+        sync_all()
+        ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+        launches0 = ctx.launch_count
+        with ClockSampler(local_rank) as clocks:
+            for i in range(args.steps):
+                ev[i][0].record(stream)
+                step()
+                ev[i][1].record(stream)
+                if merger:
+                    merger.merge_from_context(ctx, stream=sh)
+                ev[i][2].record(stream)
+                if flush is not None:
+                    flush.zero_()
+            sync_all()
+        launches = ctx.launch_count - launches0
+    t_frame = sum(e[0].elapsed_time(e[1]) for e in ev) / 1e3  # seconds, all steps
+    t_step = sum(e[0].elapsed_time(e[2]) for e in ev) / 1e3
+    counts, totals = ctx.counts()
+    counts = counts[:n_views].astype(np.int64)
+
+    # ---- end to end: host (pinned) buffers in, counts out, through rcull_frame_host ----
+    hp = torch.empty((n, 4), dtype=torch.float32).pin_memory()
+    hr = torch.empty((n, 4), dtype=torch.float32).pin_memory()
+    hm = torch.empty((n,), dtype=torch.int32).pin_memory()
+    p_ps, p_rot, p_mesh = ctx.entity_ptrs()
+    hp.copy_(_wrap_device(torch, p_ps, n * 4, torch.float32, dev).view(n, 4))
+    hr.copy_(_wrap_device(torch, p_rot, n * 4, torch.float32, dev).view(n, 4))
+    hm.copy_(_wrap_device(torch, p_mesh, n, torch.int32, dev))
+    torch.cuda.synchronize()
+    a_ps, a_rot, a_mesh = hp.numpy(), hr.numpy(), hm.numpy().view(np.uint32)
+    e2e_steps = max(1, min(args.steps, 10))
+
+    def e2e_step():
+        c, _ = ctx.frame_host(a_ps, a_rot, a_mesh, views, scene.CAMERA_POS, draw_index_base=lo)
+        if merger:
+            merger.merge_from_context(ctx)
+            torch.cuda.synchronize()
+        return c
+
+    for _ in range(2):
+        c_e2e = e2e_step()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        c_e2e = e2e_step()
+    sync_all()
+    t_e2e = time.perf_counter() - t0
+    assert np.array_equal(np.asarray(c_e2e, np.int64), counts), "end-to-end path disagrees with the resident path"
+
+    # ---- reduce over ranks: time = max, work = sum ----
+    times = torch.tensor([t_step, t_frame, t_e2e], dtype=torch.float64, device=dev)
+    vis = torch.tensor(counts, dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+        dist.all_reduce(vis)
+    t_step, t_frame, t_e2e = (float(x) for x in times.tolist())
+    vis = vis.cpu().numpy()
+    n_total = n * world
+
+    if rank == 0:
+        peak, peak_kind = load_peaks()
+        v_frac = counts / float(n)  # this rank's visible fractions (rank 0's launch is the one timed)
+        bytes_per_entity = 36.0 + 64.0 + 24.0 * float(v_frac.sum())
+        t_launch = t_frame / args.steps
+        achieved = n * bytes_per_entity / t_launch / 1e9
+        line = {
+            "metric": METRIC, "value": n_total * args.steps / t_step, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_step / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {
+                "workload": args.workload, "entities_per_gpu": n, "entities_total": n_total, "n_views": n_views,
+                "half_box": wl["half_box"], "visible_fraction_per_view": [round(float(x), 6) for x in vis / float(n_total)],
+                "sharding": "contiguous range per rank" if world > 1 else "none",
+                "merge": "NCCL all_gather(counts) + in-place broadcast allgatherv" if world > 1 else "none",
+                "l2": "flushed between iterations (256 MB write)" if flush is not None else "inputs (36 B x n) exceed L2",
+            },
+            "e2e": {"value": n_total * e2e_steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": n * 36,
+                    "d2h_bytes_per_step": 96, "steps": e2e_steps, "ms_per_step": t_e2e / e2e_steps * 1e3,
+                    "api": "rcull_frame_host (pinned host columns in, counts + index totals out)"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_kind": peak_kind, "kernel": f"transform_cull_compact<{n_views}>",
+                         "bytes_per_entity": bytes_per_entity, "ms_per_launch": t_launch * 1e3},
+            "clocks": clocks.summary(),
+        }
+        if world == 1:
+            line["cpu_baseline"] = cpu_baseline(wl, steps=3, warmup=1, threads=os.cpu_count() or 1)
+        prof = os.path.join(ROOT, "profiles", "r01_traffic.json")
+        if os.path.exists(prof):
+            try:
+                line["roofline"]["traffic"] = json.load(open(prof)).get(args.workload)
+            except Exception:
+                pass
+        print(json.dumps(line), flush=True)
+    ctx.destroy()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def reference_arm(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    b = cpu_baseline(wl, steps=args.steps, warmup=min(args.warmup, 2), threads=threads)
+    n_sample = min(CPU_SAMPLE, wl["n"])
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": b["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": min(args.warmup, 2), "ms_per_step": b["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "entities_per_step": n_sample, "n_views": wl["n_views"], "half_box": wl["half_box"],
+                   "note": "CPU oracle (C restatement of the reference's bevy systems; Rust toolchain absent), all host threads"},
+        "cpu_baseline": {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": b["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="16m_5view", choices=sorted(WORKLOADS))
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        reference_arm(args, wl)
+    else:
+        gpu_arm(args, wl)
+
+
+if __name__ == "__main__":
+    main()

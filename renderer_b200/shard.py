@@ -1,0 +1,146 @@
+"""Range sharding across GPUs and the one exchange step.
+
+Entities are split into contiguous ranges, one per rank; every rank runs the
+single-GPU frame on its range with global draw indices (draw_index_base = lo)
+and LOCAL firstIndex.  The merge is:
+
+  1. all_gather of per-rank, per-view (count, index_total);
+  2. exclusive prefixes over ranks -> every rank's slot in the merged lists and
+     the amount to add to its firstIndex;
+  3. each rank rebases its list straight into its slot of the merged buffers
+     (rcull_rebase_into, a device kernel) and the slices are exchanged in place
+     with one broadcast per (rank, view, buffer) -- NCCL has no allgatherv.
+
+Because slots are ordered by rank and ranges are ascending, the merged list is
+byte-identical to the single-GPU list.  The planning arithmetic is plain numpy
+and backend-agnostic; torch.distributed (nccl on GPUs, gloo in CPU tests) only
+moves bytes.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+
+
+def shard_range(n_total: int, world: int, rank: int) -> tuple[int, int]:
+    """Contiguous range [lo, hi) of rank; ragged when world does not divide n_total."""
+    return n_total * rank // world, n_total * (rank + 1) // world
+
+
+@dataclass
+class MergePlan:
+    count_prefix: np.ndarray  # [world, views] u64: slot start (in commands) of each rank
+    index_prefix: np.ndarray  # [world, views] u64: sum of earlier ranks' index totals
+    counts: np.ndarray  # [views] merged survivor counts
+    totals: np.ndarray  # [views] merged index totals
+
+
+def plan_merge(counts_all: np.ndarray, totals_all: np.ndarray) -> MergePlan:
+    """counts_all/totals_all: [world, views] as gathered from every rank."""
+    c = np.asarray(counts_all, np.uint64)
+    t = np.asarray(totals_all, np.uint64)
+    cp = np.zeros_like(c)
+    tp = np.zeros_like(t)
+    cp[1:] = np.cumsum(c, axis=0)[:-1]
+    tp[1:] = np.cumsum(t, axis=0)[:-1]
+    return MergePlan(cp, tp, c.sum(axis=0), t.sum(axis=0))
+
+
+class ShardMerger:
+    """Owns the merged draw lists of one rank and runs the exchange.
+
+    merged_cmds[k] is an int32 tensor of 5 * capacity words (20-B commands),
+    merged_visible[k] an int32 tensor of capacity words, on `device`.
+    """
+
+    def __init__(self, n_views: int, capacity: int, device, group=None):
+        import torch
+        import torch.distributed as dist
+
+        self.torch, self.dist = torch, dist
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.n_views = n_views
+        self.capacity = capacity
+        self.device = device
+        self.merged_cmds = [torch.empty(capacity * 5, dtype=torch.int32, device=device) for _ in range(n_views)]
+        self.merged_visible = [torch.empty(capacity, dtype=torch.int32, device=device) for _ in range(n_views)]
+        self._meta = torch.zeros(2 * n_views, dtype=torch.int64, device=device)
+        self._meta_all = torch.zeros(self.world, 2 * n_views, dtype=torch.int64, device=device)
+        self.plan: MergePlan | None = None
+        self.bytes_received = 0
+
+    def gather_meta(self, counts_dev, totals_dev) -> MergePlan:
+        """counts_dev/totals_dev: device tensors (or numpy) with this rank's per-view
+        counts and index totals.  One small all_gather + one host read."""
+        torch = self.torch
+        v = self.n_views
+        self._meta[:v] = torch.as_tensor(counts_dev, device=self.device)[:v].to(torch.int64)
+        self._meta[v:] = torch.as_tensor(totals_dev, device=self.device)[:v].to(torch.int64)
+        self.dist.all_gather_into_tensor(self._meta_all, self._meta, group=self.group)
+        m = self._meta_all.cpu().numpy().astype(np.uint64)
+        self.plan = plan_merge(m[:, :v], m[:, v:])
+        if int(self.plan.counts.max(initial=0)) > self.capacity:
+            raise ValueError(f"merged draw list of {int(self.plan.counts.max())} commands exceeds capacity {self.capacity}")
+        return self.plan
+
+    def exchange(self, counts_all: np.ndarray) -> None:
+        """In-place allgatherv: rank r's slot of every merged list is broadcast from r.
+        Call after this rank wrote its own slot (rebase step)."""
+        dist, plan = self.dist, self.plan
+        works = []
+        recv = 0
+        for k in range(self.n_views):
+            for r in range(self.world):
+                n = int(counts_all[r, k])
+                if n == 0:
+                    continue
+                off = int(plan.count_prefix[r, k])
+                src = dist.get_global_rank(self.group, r) if self.group is not None else r
+                works.append(dist.broadcast(self.merged_cmds[k][off * 5 : (off + n) * 5], src=src, group=self.group, async_op=True))
+                works.append(dist.broadcast(self.merged_visible[k][off : off + n], src=src, group=self.group, async_op=True))
+                if r != self.rank:
+                    recv += n * 24
+        for w in works:
+            w.wait()
+        self.bytes_received = recv
+
+    def merge_from_context(self, ctx, buffer_ix: int = 0, stream: int = 0) -> MergePlan:
+        """GPU path: meta exchange, device-side rebase into the merged slot, exchange."""
+        torch = self.torch
+        o = ctx.outputs(buffer_ix)
+        v = self.n_views
+        counts = _wrap_device(torch, o.counts, v, torch.int32, self.device)
+        totals = _wrap_device(torch, o.index_totals, v, torch.int64, self.device)
+        plan = self.gather_meta(counts, totals)
+        m = self._meta_all.cpu().numpy().astype(np.uint64)
+        for k in range(v):
+            off = int(plan.count_prefix[self.rank, k])
+            ctx.rebase_into(
+                k,
+                int(plan.index_prefix[self.rank, k]) & 0xFFFFFFFF,
+                self.merged_cmds[k].data_ptr() + off * 20,
+                self.merged_visible[k].data_ptr() + off * 4,
+                buffer_ix=buffer_ix,
+                stream=stream,
+            )
+        self.exchange(m[:, :v])
+        return plan
+
+
+def _wrap_device(torch, ptr: int, n: int, dtype, device):
+    """Zero-copy torch view of a librcull device buffer (for NCCL plumbing only)."""
+    itemsize = torch.empty((), dtype=dtype).element_size()
+
+    class _Holder:
+        __cuda_array_interface__ = {
+            "shape": (n,),
+            "typestr": "<i%d" % itemsize,
+            "data": (int(ptr), False),
+            "version": 3,
+            "strides": None,
+        }
+
+    return torch.as_tensor(_Holder(), device=device)

@@ -1,0 +1,188 @@
+"""GPU parity: librcull (through the C ABI) against the CPU oracle on the same
+seeded inputs.  Integer/index outputs must be bit-exact; model matrices are
+compared with == on floats (bit-exact up to the sign of zero, well inside the
+1e-6 relative tolerance north_star allows)."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from renderer_b200 import CullContext, RcullError, scene
+
+pytestmark = pytest.mark.gpu
+
+MESHES = scene.synth_mesh_table()
+
+
+def run_and_compare(n, n_views, half_box, *, seed=scene.SEED, first=0, base=0, lod_distance=10.0, ctx=None,
+                    meshes=MESHES, threads=8):
+    ps, rot, mesh = scene.synth_entities(seed, first, n, half_box, len(meshes))
+    views = scene.scene_views(n_views)
+    own = ctx is None
+    if own:
+        ctx = CullContext(max(n, 1), max_views=n_views, max_meshes=len(meshes), materialize_aabb=True,
+                          materialize_flags=True, lod_distance=lod_distance)
+        ctx.set_mesh_table(meshes)
+    try:
+        ctx.n = 0
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(views, scene.CAMERA_POS, n=n, draw_index_base=base)
+        counts, totals = ctx.counts()
+        pos, quat, scale = scene.to_components(ps, rot)
+        ref = O.frame(pos, quat, scale, mesh, meshes, views, scene.CAMERA_POS, lod_distance=lod_distance,
+                      draw_index_base=base, n_threads=threads)
+        assert np.array_equal(counts[:n_views], ref["counts"])
+        assert np.array_equal(totals[:n_views], ref["totals"])
+        if n:
+            assert np.array_equal(ctx.model(n), ref["model"])
+            assert np.array_equal(ctx.aabb(n), ref["aabb"])
+        for k in range(n_views):
+            c = int(counts[k])
+            if n:
+                assert np.array_equal(ctx.flags(k, n), ref["flags"][k]), f"view {k} flags"
+            assert np.array_equal(ctx.visible(k, c), ref["visible"][k]), f"view {k} visible"
+            assert np.array_equal(ctx.cmds(k, c), ref["cmds"][k]), f"view {k} cmds"
+        return counts[:n_views], n
+    finally:
+        if own:
+            ctx.destroy()
+
+
+def test_config1_10k_single_camera():
+    counts, n = run_and_compare(10_000, 1, 60.0)
+    assert 0 < counts[0] < n
+
+
+def test_config1_10k_five_views():
+    run_and_compare(10_000, 5, 60.0)
+
+
+@pytest.mark.parametrize("n", [0, 1, 31, 32, 33, 127, 128, 129, 1023, 1024, 1025, 2047, 4097, 5000])
+def test_ragged_sizes(n):
+    run_and_compare(n, 2, 30.0)
+
+
+@pytest.mark.parametrize("n_views", [1, 2, 3, 4, 5, 6, 7, 8])
+def test_every_view_count(n_views):
+    run_and_compare(3000, n_views, 50.0)
+
+
+def test_all_visible_dense_lists():
+    # everything inside the light frustum at the origin: exercises full-tile emission
+    counts, n = run_and_compare(20_000, 2, 4.0)
+    assert counts[1] > 0.5 * n
+
+
+def test_none_visible():
+    meshes = MESHES
+    n = 3000
+    ps, rot, mesh = scene.synth_entities(7, 0, n, 10.0)
+    ps[:, 2] = -500.0  # far behind the camera
+    with CullContext(n, max_views=1, max_meshes=len(meshes)) as ctx:
+        ctx.set_mesh_table(meshes)
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(scene.scene_views(1), scene.CAMERA_POS)
+        counts, totals = ctx.counts()
+        assert counts[0] == 0 and totals[0] == 0
+
+
+def test_config2_1m_camera():
+    counts, n = run_and_compare(1_000_000, 1, 250.0)
+    assert counts[0] > 0
+
+
+def test_draw_index_base_and_lod_distance():
+    run_and_compare(7000, 2, 40.0, base=123_456, lod_distance=25.5)
+    run_and_compare(7000, 1, 40.0, lod_distance=0.0)
+    run_and_compare(7000, 1, 40.0, lod_distance=1e9)
+
+
+def test_context_reuse_many_frames():
+    """Ticket / epoch bookkeeping across frames of different sizes on one context."""
+    n_max = 40_000
+    ctx = CullContext(n_max, max_views=3, max_meshes=len(MESHES), materialize_aabb=True, materialize_flags=True)
+    ctx.set_mesh_table(MESHES)
+    try:
+        for i, (n, v, hb) in enumerate([(40_000, 3, 60.0), (1000, 1, 20.0), (33_333, 2, 80.0), (40_000, 3, 60.0), (5, 1, 5.0)]):
+            run_and_compare(n, v, hb, seed=100 + i, ctx=ctx)
+    finally:
+        ctx.destroy()
+
+
+def test_double_buffered_outputs():
+    n = 6000
+    ps, rot, mesh = scene.synth_entities(3, 0, n, 40.0)
+    views = scene.scene_views(1)
+    with CullContext(n, max_views=1, max_meshes=len(MESHES), n_buffers=2) as ctx:
+        ctx.set_mesh_table(MESHES)
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(views, scene.CAMERA_POS, buffer_ix=0)
+        c0, _ = ctx.counts(0)
+        ps2 = ps.copy()
+        ps2[:, :3] *= 0.5
+        ctx.upload_entities(ps2, rot, mesh)
+        ctx.frame(views, scene.CAMERA_POS, buffer_ix=1)
+        c1, _ = ctx.counts(1)
+        c0b, _ = ctx.counts(0)
+        assert c0[0] == c0b[0] and c1[0] != c0[0]
+        assert np.array_equal(ctx.model(n, buffer_ix=0)[:, 12:15], ps[:, :3])
+        assert np.array_equal(ctx.model(n, buffer_ix=1)[:, 12:15], ps2[:, :3])
+
+
+def test_capacity_visible_clamps_writes_not_count():
+    n = 5000
+    ps, rot, mesh = scene.synth_entities(5, 0, n, 4.0)
+    views = scene.scene_views(2)[1:]
+    with CullContext(n, max_views=1, max_meshes=len(MESHES), capacity_visible=100) as ctx:
+        ctx.set_mesh_table(MESHES)
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(views, scene.CAMERA_POS)
+        counts, _ = ctx.counts()
+        assert counts[0] > 100  # the true survivor count is still reported
+        pos, quat, scale = scene.to_components(ps, rot)
+        ref = O.frame(pos, quat, scale, mesh, MESHES, views, scene.CAMERA_POS)
+        assert counts[0] == ref["counts"][0]
+        assert np.array_equal(ctx.cmds(0, 100), ref["cmds"][0][:100])
+
+
+def test_errors_are_loud():
+    with pytest.raises(RcullError):
+        CullContext(0)
+    with pytest.raises(RcullError):
+        CullContext(10, max_views=9)
+    with CullContext(100, max_views=1, max_meshes=4) as ctx:
+        with pytest.raises(RcullError):  # frame before mesh table
+            ctx.frame(scene.scene_views(1), scene.CAMERA_POS, n=10)
+        with pytest.raises(RcullError):
+            ctx.set_mesh_table(MESHES)  # 16 > max_meshes
+        ctx.set_mesh_table(MESHES[:4])
+        with pytest.raises(RcullError):
+            ctx.frame(scene.scene_views(2), scene.CAMERA_POS, n=10)  # n_views > max_views
+        with pytest.raises(RcullError):
+            ctx.frame(scene.scene_views(1), scene.CAMERA_POS, n=101)  # n > capacity
+        ps, rot, mesh = scene.synth_entities(1, 0, 100, 10.0, 16)  # mesh ids up to 15 > table of 4
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(scene.scene_views(1), scene.CAMERA_POS)
+        with pytest.raises(RcullError):
+            ctx.counts()
+        bad = MESHES[:1].copy()
+        bad["n_lods"] = 0
+        with pytest.raises(RcullError):
+            ctx.set_mesh_table(bad)
+
+
+def test_device_generator_matches_host_twin():
+    n, first = 50_000, 1_234_567
+    ps, rot, mesh = scene.synth_entities(scene.SEED, first, n, 250.0)
+    views = scene.scene_views(1)
+    with CullContext(n, max_views=1, max_meshes=len(MESHES)) as a, CullContext(n, max_views=1, max_meshes=len(MESHES)) as b:
+        for c in (a, b):
+            c.set_mesh_table(MESHES)
+        a.upload_entities(ps, rot, mesh)
+        b.synth_entities(scene.SEED, first, n, 250.0, len(MESHES))
+        a.frame(views, scene.CAMERA_POS)
+        b.frame(views, scene.CAMERA_POS)
+        assert np.array_equal(a.model(n), b.model(n))
+        ca, ta = a.counts()
+        cb, tb = b.counts()
+        assert ca[0] == cb[0] and ta[0] == tb[0]
+        assert np.array_equal(a.cmds(0, int(ca[0])), b.cmds(0, int(cb[0])))
