@@ -133,11 +133,12 @@ class ShardMerger:
 def _wrap_device(torch, ptr: int, n: int, dtype, device):
     """Zero-copy torch view of a librcull device buffer (for NCCL plumbing only)."""
     itemsize = torch.empty((), dtype=dtype).element_size()
+    kind = "f" if dtype.is_floating_point else "i"
 
     class _Holder:
         __cuda_array_interface__ = {
             "shape": (n,),
-            "typestr": "<i%d" % itemsize,
+            "typestr": "<%s%d" % (kind, itemsize),
             "data": (int(ptr), False),
             "version": 3,
             "strides": None,
