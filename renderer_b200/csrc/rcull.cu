@@ -48,6 +48,7 @@ struct OutputSet {
     uint32_t* visible[kMaxViews] = {};
     uint32_t* counts = nullptr;
     unsigned long long* totals = nullptr;
+    CUtensorMap model_map;  // model buffer as [cap/2 rows][32 floats], 16-row boxes, 128-B swizzle
 };
 
 }  // namespace
@@ -64,14 +65,14 @@ struct rcull_ctx {
     uint4* lod_tab = nullptr;
     uint32_t n_meshes = 0;
     OutputSet out[3];
-    uint64_t* status = nullptr;
+    ulonglong2* status = nullptr;
     size_t status_bytes = 0;
     uint32_t* ticket = nullptr;  // [0] = tile ticket, [1] = error flag
     uint32_t ticket_base = 0;
     uint32_t epoch = 0;
     uint64_t launches = 0;
     float lod_d2_max = 0.f;
-    int blocks_per_sm[kMaxViews + 1] = {};
+    int blocks_per_sm[kMaxViews + 1][2] = {};
     cudaStream_t own_stream = nullptr;
     uint32_t* h_counts = nullptr;  // pinned
     unsigned long long* h_totals = nullptr;
@@ -106,21 +107,51 @@ float lod_threshold(float d) {
     return x;
 }
 
-template <int V>
+template <int V, bool M>
 int configure(rcull_ctx* c) {
-    auto k = transform_cull_compact<V>;
+    auto k = transform_cull_compact<V, M>;
     CU(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)frame_smem_bytes<V>()));
     int b = 0;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k, kThreads, frame_smem_bytes<V>()));
-    if (b < 1) return fail(RCULL_ERR_CUDA, "transform_cull_compact<%d> does not fit on an SM", V);
-    c->blocks_per_sm[V] = b;
+    if (b < 1) return fail(RCULL_ERR_CUDA, "transform_cull_compact<%d,%d> does not fit on an SM", V, (int)M);
+    c->blocks_per_sm[V][M] = b;
     return 0;
 }
 
 template <int V>
-cudaError_t launch(const FrameArgs& a, int grid, cudaStream_t s) {
-    transform_cull_compact<V><<<grid, kThreads, frame_smem_bytes<V>(), s>>>(a);
+cudaError_t launch(bool mat, const FrameArgs& a, const CUtensorMap& map, int grid, cudaStream_t s) {
+    if (mat)
+        transform_cull_compact<V, true><<<grid, kThreads, frame_smem_bytes<V>(), s>>>(a, map);
+    else
+        transform_cull_compact<V, false><<<grid, kThreads, frame_smem_bytes<V>(), s>>>(a, map);
     return cudaGetLastError();
+}
+
+// cuTensorMapEncodeTiled is a driver entry point; librcull links cudart statically
+// and resolves it at run time instead of linking libcuda.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int make_model_map(CUtensorMap* map, float4* model, uint64_t cap) {
+    static EncodeTiledFn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        CU(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+        if (qres != cudaDriverEntryPointSuccess || !fn)
+            return fail(RCULL_ERR_CUDA, "cuTensorMapEncodeTiled is not available in this driver");
+        encode = reinterpret_cast<EncodeTiledFn>(fn);
+    }
+    const cuuint64_t dims[2] = {32, cap / 2};      // 32 floats = 2 matrices per 128-B row
+    const cuuint64_t strides[1] = {128};           // bytes between rows
+    const cuuint32_t box[2] = {32, 16};            // 16 rows = 32 matrices = 2 KB
+    const cuuint32_t elem[2] = {1, 1};
+    CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, model, dims, strides, box, elem,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(RCULL_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return 0;
 }
 
 }  // namespace
@@ -189,6 +220,7 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
     for (uint32_t b = 0; b < cfg->n_buffers; ++b) {
         OutputSet& o = c->out[b];
         TRY(dev_alloc(c, &o.model, c->cap * 4));
+        TRY(make_model_map(&o.model_map, o.model, c->cap));
         if (cfg->materialize_aabb) TRY(dev_alloc(c, &o.aabb, c->cap * 6));
         for (uint32_t v = 0; v < cfg->max_views; ++v) {
             if (cfg->materialize_flags) TRY(dev_alloc(c, &o.flags[v], c->cap));
@@ -201,8 +233,8 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
         cudaMemset(o.totals, 0, kMaxViews * 8);
     }
     const size_t max_tiles = c->cap / kTile;
-    c->status_bytes = max_tiles * cfg->max_views * kStatusWords * sizeof(uint64_t);
-    TRY(dev_alloc(c, &c->status, c->status_bytes / sizeof(uint64_t)));
+    c->status_bytes = max_tiles * cfg->max_views * sizeof(ulonglong2);
+    TRY(dev_alloc(c, &c->status, max_tiles * cfg->max_views));
     TRY(dev_alloc(c, &c->ticket, 2));
     if (cudaMemset(c->status, 0, c->status_bytes) != cudaSuccess || cudaMemset(c->ticket, 0, 8) != cudaSuccess) {
         rcull_destroy(c);
@@ -214,14 +246,22 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
         rcull_destroy(c);
         return fail(RCULL_ERR_CUDA, "host staging / stream creation failed");
     }
-    TRY(configure<1>(c));
-    TRY(configure<2>(c));
-    TRY(configure<3>(c));
-    TRY(configure<4>(c));
-    TRY(configure<5>(c));
-    TRY(configure<6>(c));
-    TRY(configure<7>(c));
-    TRY(configure<8>(c));
+    TRY((configure<1, false>(c)));
+    TRY((configure<1, true>(c)));
+    TRY((configure<2, false>(c)));
+    TRY((configure<2, true>(c)));
+    TRY((configure<3, false>(c)));
+    TRY((configure<3, true>(c)));
+    TRY((configure<4, false>(c)));
+    TRY((configure<4, true>(c)));
+    TRY((configure<5, false>(c)));
+    TRY((configure<5, true>(c)));
+    TRY((configure<6, false>(c)));
+    TRY((configure<6, true>(c)));
+    TRY((configure<7, false>(c)));
+    TRY((configure<7, true>(c)));
+    TRY((configure<8, false>(c)));
+    TRY((configure<8, true>(c)));
 #undef TRY
     CU(cudaDeviceSynchronize());
     *out = c;
@@ -321,16 +361,13 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     a.mesh = c->mesh;
     a.mesh_aabb = c->mesh_aabb;
     a.lod_tab = c->lod_tab;
-    a.model = o.model;
     a.aabb = o.aabb;
     for (uint32_t v = 0; v < n_views; ++v) {
         a.flags[v] = o.flags[v];
         a.cmds[v] = o.cmds[v];
         a.visible[v] = o.visible[v];
-        for (int p = 0; p < 6; ++p) {
-            for (int x = 0; x < 4; ++x) a.planes[v][p][x] = views[v].planes[p][x];
-            for (int x = 0; x < 3; ++x) a.absn[v][p][x] = fabsf(views[v].planes[p][x]);
-        }
+        for (int p = 0; p < 6; ++p)
+            a.planes[v][p] = make_float4(views[v].planes[p][0], views[v].planes[p][1], views[v].planes[p][2], views[v].planes[p][3]);
     }
     a.counts = o.counts;
     a.totals = o.totals;
@@ -348,18 +385,19 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     a.cam[1] = cam_pos[1];
     a.cam[2] = cam_pos[2];
     a.lod_d2_max = c->lod_d2_max;
-    int grid = c->sm_count * c->blocks_per_sm[n_views];
+    const bool mat = c->cfg.materialize_aabb || c->cfg.materialize_flags;
+    int grid = c->sm_count * c->blocks_per_sm[n_views][mat];
     if ((uint32_t)grid > n_tiles) grid = (int)n_tiles;
     cudaError_t e = cudaSuccess;
     switch (n_views) {
-        case 1: e = launch<1>(a, grid, s); break;
-        case 2: e = launch<2>(a, grid, s); break;
-        case 3: e = launch<3>(a, grid, s); break;
-        case 4: e = launch<4>(a, grid, s); break;
-        case 5: e = launch<5>(a, grid, s); break;
-        case 6: e = launch<6>(a, grid, s); break;
-        case 7: e = launch<7>(a, grid, s); break;
-        case 8: e = launch<8>(a, grid, s); break;
+        case 1: e = launch<1>(mat, a, o.model_map, grid, s); break;
+        case 2: e = launch<2>(mat, a, o.model_map, grid, s); break;
+        case 3: e = launch<3>(mat, a, o.model_map, grid, s); break;
+        case 4: e = launch<4>(mat, a, o.model_map, grid, s); break;
+        case 5: e = launch<5>(mat, a, o.model_map, grid, s); break;
+        case 6: e = launch<6>(mat, a, o.model_map, grid, s); break;
+        case 7: e = launch<7>(mat, a, o.model_map, grid, s); break;
+        case 8: e = launch<8>(mat, a, o.model_map, grid, s); break;
     }
     if (e != cudaSuccess) return fail(RCULL_ERR_CUDA, "transform_cull_compact launch failed: %s", cudaGetErrorString(e));
     c->ticket_base += n_tiles + (uint32_t)grid;  // every CTA draws exactly one ticket past the end

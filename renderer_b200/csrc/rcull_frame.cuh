@@ -1,32 +1,38 @@
 // rcull_frame.cuh -- the fused transform + AABB + multi-view cull + compaction
 // kernel (SURVEY 8a rows A1-A7 in one launch).
 //
-// Shape: persistent CTAs (grid = SMs x resident CTAs), tiles of kTile entities
-// handed out by an atomic ticket, SoA input tiles staged into shared memory by
-// the TMA engine (cp.async.bulk + mbarrier, two stages: tile i+1 streams in
-// while tile i is processed), one thread per entity for the arithmetic, warp
-// ballot/popc compaction into per-warp visible lists in shared memory, and a
-// single-pass decoupled-lookback scan over tiles that carries, per view, the
-// survivor count and the running sum of index_len (firstIndex).
+// Shape: persistent, warp-specialised CTAs (grid = SMs x resident CTAs).
+//   * 8 COMPUTE warps: one thread per entity, 4 entities per thread per tile.
+//     Inputs come out of shared memory (staged there by TMA), model matrices go
+//     back through a swizzled shared-memory box and a 2-D TMA tensor store, the
+//     plane tests run planes-outer / entities-inner so each plane is fetched once
+//     per 4 entities, survivors are ballot-compacted into per-warp lists.
+//   * 1 SCAN warp: draws tile tickets, issues the TMA loads (two stages), and for
+//     every finished tile runs the decoupled look-back (count and index sum per
+//     view in one 16-byte descriptor) and emits the draw commands while the
+//     compute warps are already working on the next tile.
+// Warps synchronise through mbarriers only; there is no CTA-wide barrier in the
+// tile loop.
 #pragma once
+#include <cuda.h>  // CUtensorMap (type only; the encoder is resolved at run time)
+
 #include "rcull_device.cuh"
 
 namespace rcull {
 
-constexpr int kThreads = 256;
-constexpr int kWarps = kThreads / 32;
-constexpr int kItems = 4;                  // entities per thread per tile
-constexpr int kTile = kThreads * kItems;   // 1024 entities
-constexpr int kWarpSpan = 32 * kItems;     // entities owned by one warp
+constexpr int kComputeWarps = 8;
+constexpr int kThreads = (kComputeWarps + 1) * 32;  // + scan warp
+constexpr int kItems = 4;                           // entities per thread per tile
+constexpr int kTile = kComputeWarps * 32 * kItems;  // 1024 entities
+constexpr int kWarpSpan = 32 * kItems;              // entities owned by one compute warp
 constexpr int kStages = 2;
 constexpr int kMaxViews = 8;
 constexpr int kMaxLods = 6;
 constexpr uint32_t kStageBytes = kTile * (16 + 16 + 4);  // pos_scale + rot + mesh
+constexpr int kMatBoxBytes = 32 * 64;                    // 32 model matrices = one TMA store box
 
-// Tile status: 4 u64 per (view, tile): [0] = epoch:30 | flag:2 | count:32,
-// [1] = index sum of the tile alone, [2] = inclusive index sum, [3] pad.
+// Tile descriptor: x = epoch:30 | flag:2 | count:32, y = index sum.
 constexpr uint64_t kFlagAgg = 1, kFlagIncl = 2;
-constexpr int kStatusWords = 4;
 
 struct FrameArgs {
     const float4* pos_scale;
@@ -34,14 +40,13 @@ struct FrameArgs {
     const uint32_t* mesh;
     const float4* mesh_aabb;  // [M][2]: (min.xyz, n_lods), (max.xyz, -)
     const uint4* lod_tab;     // [M*kMaxLods]: index_len, first_index, vertex_offset, 0
-    float4* model;
     float* aabb;              // optional [n][6]
     uint8_t* flags[kMaxViews];  // optional [n]
     uint32_t* cmds[kMaxViews];  // 5 words per command
     uint32_t* visible[kMaxViews];
     uint32_t* counts;
     unsigned long long* totals;
-    uint64_t* status;
+    ulonglong2* status;  // [views][n_tiles]
     uint32_t* ticket;
     uint32_t* error_flag;
     uint32_t ticket_base;
@@ -53,174 +58,326 @@ struct FrameArgs {
     uint32_t cap_visible;
     float cam[3];
     float lod_d2_max;  // lod 1 iff |cam-pos|^2 > lod_d2_max  (== sqrt(d2) > lod_distance)
-    float planes[kMaxViews][6][4];
-    float absn[kMaxViews][6][3];
+    float4 planes[kMaxViews][6];
 };
 
 struct FrameSmem {
-    // stage buffers first: 16-B aligned bulk-copy destinations
+    // TMA destinations / sources first (1024-B aligned for the 128-B swizzle)
+    float4 mat[kComputeWarps][kMatBoxBytes / 16];  // per-warp model-matrix store box
     float4 pos_scale[kStages][kTile];
     float4 rot[kStages][kTile];
-    uint32_t mesh[kStages][kTile];          // overwritten in place by the (mesh, lod) slot
-    float4 mat[kWarps][128];                // per-warp 2 KB matrix transpose buffer
-    uint64_t wlen[kMaxViews][kWarps];
-    uint64_t excl_len[kMaxViews];
-    uint64_t bar[kStages];
-    uint32_t wcnt[kMaxViews][kWarps];
-    uint32_t excl_cnt[kMaxViews];
+    uint32_t mesh[kStages][kTile];
+    uint32_t slot[kTile];  // (mesh, lod) slot of every entity of the tile whose lists are pending
+    uint64_t full[kStages];
+    uint64_t empty[kStages];
+    uint64_t done;   // compute warps -> scan warp: lists and aggregates of a tile are written
+    uint64_t bases;  // scan warp -> compute warps: output offsets of that tile are known
+    uint64_t wlen[kMaxViews][kComputeWarps];   // per-warp index sums of the pending tile
+    uint32_t wcnt[kMaxViews][kComputeWarps];   // per-warp survivor counts
+    uint32_t adj_cnt[kMaxViews][kComputeWarps];  // output slot of combined-list entry i of view k: adj_cnt + i
+    uint32_t adj_len[kMaxViews][kComputeWarps];  // firstIndex of it: adj_len + exclusive len scan up to i
     uint32_t tile_of_stage[kStages];
-    // followed by: uint16_t list[V][kTile]
+    // followed by: uint16_t wlist[kComputeWarps][V * kWarpSpan] -- per-warp combined
+    // survivor list, view-major, entry = view << 7 | slot-in-warp-span
 };
 
 template <int V>
 constexpr size_t frame_smem_bytes() {
-    return sizeof(FrameSmem) + sizeof(uint16_t) * V * kTile;
+    return sizeof(FrameSmem) + sizeof(uint16_t) * V * kTile + 1024;  // + slack to align the base
 }
 
-// Lookback for one view, run by one whole warp.  Returns the exclusive prefix
-// (count, index sum) of `tile` and publishes this tile's words.
-__device__ __forceinline__ void lookback(uint64_t* status_view, uint32_t tile, uint32_t epoch, uint32_t agg_cnt,
-                                         uint64_t agg_len, uint32_t& excl_cnt, uint64_t& excl_len) {
-    const uint32_t lane = lane_id();
+__device__ __forceinline__ FrameSmem& frame_smem(unsigned char* raw) {
+    const uint32_t a = smem_u32(raw);
+    return *reinterpret_cast<FrameSmem*>(raw + ((1024u - (a & 1023u)) & 1023u));
+}
+
+// ---------------------------------------------------------------------------------
+// scan warp: decoupled look-back over tiles, all views of one tile together
+// ---------------------------------------------------------------------------------
+__device__ __forceinline__ bool desc_ready(const ulonglong2& d, uint32_t epoch) {
+    return (uint32_t)(d.x >> 34) == epoch && ((d.x >> 32) & 3ull) != 0ull;
+}
+
+// Publishes the aggregates of `tile`, resolves its exclusive prefixes (count and
+// index sum per view) and publishes the inclusive values.  Whole warp; inputs and
+// outputs are warp-uniform.
+template <int V>
+__device__ __forceinline__ void lookback_tile(ulonglong2* status, uint32_t n_tiles, uint32_t tile, uint32_t epoch,
+                                              uint32_t lane, const uint32_t (&agg_cnt)[V],
+                                              const uint64_t (&agg_len)[V], uint32_t (&excl_cnt)[V],
+                                              uint64_t (&excl_len)[V]) {
     const uint64_t tag = (uint64_t)epoch << 34;
-    uint64_t* mine = status_view + (size_t)tile * kStatusWords;
-    uint32_t ecnt = 0;
-    uint64_t elen = 0;
-    if (tile != 0) {
-        if (lane == 0) {
-            st_relaxed(mine + 1, agg_len);
-            st_release(mine, tag | (kFlagAgg << 32) | agg_cnt);
+    if (tile == 0) {
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+            excl_cnt[k] = 0;
+            excl_len[k] = 0;
+            if (lane == 0) st_relaxed_v2(status + (size_t)k * n_tiles, tag | (kFlagIncl << 32) | agg_cnt[k], agg_len[k]);
         }
-        int pred = (int)tile - 1 - (int)lane;
-        while (true) {
-            uint64_t a = tag | (kFlagIncl << 32);  // virtual tile -1: inclusive prefix 0
-            const uint64_t* w = status_view + (size_t)(pred < 0 ? 0 : pred) * kStatusWords;
-            bool ok = true;
-            do {  // spin until every real predecessor in the window has published for this frame
-                if (pred >= 0) {
-                    a = ld_acquire(w);
-                    ok = (a >> 34) == (uint64_t)epoch && ((a >> 32) & 3) != 0;
-                }
-            } while (!__all_sync(kFullMask, ok));
-            const uint32_t flag = (uint32_t)(a >> 32) & 3u;
-            const uint32_t incl_mask = __ballot_sync(kFullMask, flag == kFlagIncl);
-            const uint32_t first = incl_mask ? (uint32_t)__ffs(incl_mask) - 1u : 32u;
-            const bool use = lane <= first;
-            uint32_t c = use ? (uint32_t)a : 0u;
-            uint64_t l = 0;
-            if (use && pred >= 0) l = ld_relaxed(w + (flag == kFlagIncl ? 2 : 1));
-            ecnt += __reduce_add_sync(kFullMask, c);
-            elen += warp_sum_u64(l);
-            if (incl_mask) break;
-            pred -= 32;
-        }
+        return;
     }
     if (lane == 0) {
-        st_relaxed(mine + 2, elen + agg_len);
-        st_release(mine, tag | (kFlagIncl << 32) | (uint32_t)(ecnt + agg_cnt));
+#pragma unroll
+        for (int k = 0; k < V; ++k)
+            st_relaxed_v2(status + (size_t)k * n_tiles + tile, tag | (kFlagAgg << 32) | agg_cnt[k], agg_len[k]);
     }
-    excl_cnt = ecnt;
-    excl_len = elen;
+    const ulonglong2 virt = make_ulonglong2(tag | (kFlagIncl << 32), 0ull);  // tile -1: inclusive prefix 0
+    const int pred0 = (int)tile - 1 - (int)lane;
+    ulonglong2 first[V];
+#pragma unroll
+    for (int k = 0; k < V; ++k)  // V independent loads in flight
+        first[k] = pred0 >= 0 ? ld_relaxed_v2(status + (size_t)k * n_tiles + pred0) : virt;
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+        const ulonglong2* sv = status + (size_t)k * n_tiles;
+        ulonglong2 d = first[k];
+        int pred = pred0;
+        uint32_t ecnt = 0;
+        uint64_t elen = 0;
+        while (true) {
+            bool ok = pred < 0 || desc_ready(d, epoch);
+            while (!__all_sync(kFullMask, ok)) {  // a predecessor in the window has not published yet
+                if (!ok) {
+                    d = ld_relaxed_v2(sv + pred);
+                    ok = desc_ready(d, epoch);
+                }
+            }
+            const uint32_t flag = (uint32_t)(d.x >> 32) & 3u;
+            const uint32_t incl_mask = __ballot_sync(kFullMask, flag == kFlagIncl);
+            const uint32_t stop = incl_mask ? (uint32_t)__ffs(incl_mask) - 1u : 31u;
+            const bool use = lane <= stop;
+            ecnt += __reduce_add_sync(kFullMask, use ? (uint32_t)d.x : 0u);
+            elen += warp_sum_u64(use ? d.y : 0ull);
+            if (incl_mask) break;
+            pred -= 32;
+            d = pred >= 0 ? ld_relaxed_v2(sv + pred) : virt;
+        }
+        excl_cnt[k] = ecnt;
+        excl_len[k] = elen;
+        if (lane == 0)
+            st_relaxed_v2(status + (size_t)k * n_tiles + tile, tag | (kFlagIncl << 32) | (uint32_t)(ecnt + agg_cnt[k]),
+                          elen + agg_len[k]);
+    }
 }
 
+
+// Scan-warp work for one finished tile: per-warp prefixes, look-back, output offsets.
+// Lanes 0..7 stand for the eight compute warps.
 template <int V>
-__global__ void __launch_bounds__(kThreads, 2) transform_cull_compact(const __grid_constant__ FrameArgs args) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    FrameSmem& sm = *reinterpret_cast<FrameSmem*>(smem_raw);
-    uint16_t* list = reinterpret_cast<uint16_t*>(smem_raw + sizeof(FrameSmem));  // [V][kTile]
+__device__ __forceinline__ void scan_tile(const FrameArgs& args, FrameSmem& sm, uint32_t tile, uint32_t lane) {
+    uint32_t agg_cnt[V], excl_cnt[V];
+    uint64_t agg_len[V], excl_len[V];
+    uint32_t rel_cnt[V], rel_len[V];  // (prefix over lower warps) - (start of view k in the warp's combined list)
+    uint32_t vstart_c = 0, vstart_l = 0;
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+        const uint32_t c = lane < kComputeWarps ? sm.wcnt[k][lane] : 0u;
+        const uint64_t l = lane < kComputeWarps ? sm.wlen[k][lane] : 0ull;
+        uint32_t ic = c;
+        uint64_t il = l;
+#pragma unroll
+        for (int o = 1; o < kComputeWarps; o <<= 1) {
+            const uint32_t tc = __shfl_up_sync(kFullMask, ic, o);
+            const uint64_t tl = __shfl_up_sync(kFullMask, il, o);
+            if (lane >= (uint32_t)o) {
+                ic += tc;
+                il += tl;
+            }
+        }
+        agg_cnt[k] = __shfl_sync(kFullMask, ic, kComputeWarps - 1);
+        agg_len[k] = __shfl_sync(kFullMask, il, kComputeWarps - 1);
+        rel_cnt[k] = (ic - c) - vstart_c;
+        rel_len[k] = (uint32_t)(il - l) - vstart_l;
+        vstart_c += c;
+        vstart_l += (uint32_t)l;
+    }
+    lookback_tile<V>(args.status, args.n_tiles, tile, args.epoch, lane, agg_cnt, agg_len, excl_cnt, excl_len);
+    if (lane < kComputeWarps) {
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+            sm.adj_cnt[k][lane] = excl_cnt[k] + rel_cnt[k];
+            sm.adj_len[k][lane] = (uint32_t)excl_len[k] + rel_len[k];  // firstIndex is u32 and wraps like the reference's
+        }
+    }
+    if (tile == args.n_tiles - 1 && lane == 0) {
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+            args.counts[k] = excl_cnt[k] + agg_cnt[k];
+            args.totals[k] = excl_len[k] + agg_len[k];
+        }
+    }
+}
+
+// Compute-warp emission of its own survivors of the pending tile: one pass over the
+// warp's combined (all views) list, stable within every view.
+template <int V>
+__device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameSmem& sm, const uint16_t* wlist,
+                                             uint32_t tile_base, uint32_t warp, uint32_t lane) {
+    uint32_t total = 0;
+#pragma unroll
+    for (int k = 0; k < V; ++k) total += sm.wcnt[k][warp];
+    uint32_t carry = 0;
+    for (uint32_t i0 = 0; i0 < total; i0 += 32) {
+        const uint32_t i = i0 + lane;
+        const bool act = i < total;
+        uint32_t k = 0, e = 0;
+        uint4 L = make_uint4(0, 0, 0, 0);
+        if (act) {
+            const uint32_t entry = wlist[i];
+            k = entry >> 7;
+            e = warp * kWarpSpan + (entry & 127u);
+            L = __ldg(args.lod_tab + sm.slot[e]);
+        }
+        const uint32_t incl = warp_incl_scan_u32(L.x, lane);
+        const uint32_t excl = carry + incl - L.x;
+        carry += __shfl_sync(kFullMask, incl, 31);
+        if (act) {
+            const uint32_t pos = sm.adj_cnt[k][warp] + i;
+            if (pos < args.cap_visible) {
+                const uint32_t draw_index = args.draw_index_base + tile_base + e;
+                uint32_t* c = args.cmds[k] + (size_t)pos * 5;
+                c[0] = L.x;                            // indexCount (entity-level upper bound)
+                c[1] = 1u;                             // instanceCount
+                c[2] = sm.adj_len[k][warp] + excl;     // firstIndex: running sum of earlier survivors' index_len
+                c[3] = L.z;                            // vertexOffset
+                c[4] = draw_index;                     // firstInstance
+                args.visible[k][pos] = draw_index;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------
+// the kernel
+// ---------------------------------------------------------------------------------
+// kMat: the optional AABB / CoarseCulled outputs exist (checked per pointer); the
+// hot variant (kMat = false) carries none of that code.
+template <int V, bool kMat>
+__global__ void __maxnreg__(112)
+    transform_cull_compact(const __grid_constant__ FrameArgs args, const __grid_constant__ CUtensorMap model_map) {
+    extern __shared__ unsigned char smem_raw[];
+    FrameSmem& sm = frame_smem(smem_raw);
 
     const uint32_t tid = threadIdx.x;
     const uint32_t lane = tid & 31u;
     const uint32_t warp = tid >> 5;
-    const uint32_t lt = lanemask_lt();
-
-    auto issue_tile = [&](uint32_t stage, uint32_t tile) {
-        uint64_t* bar = &sm.bar[stage];
-        mbar_expect_tx(bar, kStageBytes);
-        bulk_g2s(sm.pos_scale[stage], args.pos_scale + (size_t)tile * kTile, kTile * 16, bar);
-        bulk_g2s(sm.rot[stage], args.rot + (size_t)tile * kTile, kTile * 16, bar);
-        bulk_g2s(sm.mesh[stage], args.mesh + (size_t)tile * kTile, kTile * 4, bar);
-    };
 
     if (tid == 0) {
-        mbar_init(&sm.bar[0], 1);
-        mbar_init(&sm.bar[1], 1);
+#pragma unroll
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&sm.full[s], 1);
+            mbar_init(&sm.empty[s], kComputeWarps);
+        }
+        mbar_init(&sm.done, kComputeWarps);
+        mbar_init(&sm.bases, 1);
         fence_mbar_init();
-        const uint32_t t0 = atomicAdd(args.ticket, 1u) - args.ticket_base;
-        sm.tile_of_stage[0] = t0;
-        if (t0 < args.n_tiles) issue_tile(0, t0);
     }
     __syncthreads();
 
-    for (uint32_t it = 0;; ++it) {
+    if (warp == kComputeWarps) {
+        // =============================== scan / IO warp ===============================
+        auto claim_tile = [&](uint32_t stage) -> uint32_t {  // lane 0 only
+            const uint32_t t = atomicAdd(args.ticket, 1u) - args.ticket_base;
+            sm.tile_of_stage[stage] = t;
+            uint64_t* bar = &sm.full[stage];
+            if (t < args.n_tiles) {
+                fence_proxy_async();
+                mbar_expect_tx(bar, kStageBytes);
+                bulk_g2s(sm.pos_scale[stage], args.pos_scale + (size_t)t * kTile, kTile * 16, bar);
+                bulk_g2s(sm.rot[stage], args.rot + (size_t)t * kTile, kTile * 16, bar);
+                bulk_g2s(sm.mesh[stage], args.mesh + (size_t)t * kTile, kTile * 4, bar);
+            } else {
+                mbar_arrive(bar);  // end marker: the compute warps read tile_of_stage and leave
+            }
+            return t;
+        };
+        uint32_t cur = 0;
+        if (lane == 0) cur = claim_tile(0);
+        cur = __shfl_sync(kFullMask, cur, 0);
+        for (uint32_t it = 0; cur < args.n_tiles; ++it) {
+            const uint32_t stage = it & 1u;
+            uint32_t nxt = 0;
+            if (lane == 0) {  // prefetch the next tile into the other stage
+                if (it >= 1) mbar_wait(&sm.empty[stage ^ 1u], ((it - 1) >> 1) & 1u);
+                nxt = claim_tile(stage ^ 1u);
+            }
+            nxt = __shfl_sync(kFullMask, nxt, 0);
+            mbar_wait(&sm.done, it & 1u);
+            scan_tile<V>(args, sm, cur, lane);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.bases);
+            cur = nxt;
+        }
+        return;
+    }
+
+    // ================================= compute warps =================================
+    uint16_t* const wlist =
+        reinterpret_cast<uint16_t*>(reinterpret_cast<unsigned char*>(&sm) + sizeof(FrameSmem)) + warp * (V * kWarpSpan);
+    const uint32_t lt = (1u << lane) - 1u;
+    // swizzled (128-B pattern) byte offsets of this lane's four matrix columns in the warp's store box
+    unsigned char* const box = reinterpret_cast<unsigned char*>(sm.mat[warp]);
+    const uint32_t mrow = lane >> 1, mhalf = (lane & 1u) * 4u;
+    const uint32_t moff0 = mrow * 128u + (((mhalf + 0u) ^ (mrow & 7u)) << 4);
+    const uint32_t moff1 = mrow * 128u + (((mhalf + 1u) ^ (mrow & 7u)) << 4);
+    const uint32_t moff2 = mrow * 128u + (((mhalf + 2u) ^ (mrow & 7u)) << 4);
+    const uint32_t moff3 = mrow * 128u + (((mhalf + 3u) ^ (mrow & 7u)) << 4);
+    const uint32_t e0 = warp * kWarpSpan + lane;  // slot in tile of item 0; item j adds 32*j
+
+    uint32_t it = 0, prev_base = 0;
+    for (;; ++it) {
         const uint32_t stage = it & 1u;
+        mbar_wait(&sm.full[stage], (it >> 1) & 1u);
         const uint32_t tile = sm.tile_of_stage[stage];
         if (tile >= args.n_tiles) break;
-        if (tid == 0) {  // prefetch the next tile into the other stage
-            const uint32_t t1 = atomicAdd(args.ticket, 1u) - args.ticket_base;
-            sm.tile_of_stage[stage ^ 1u] = t1;
-            if (t1 < args.n_tiles) {
-                fence_proxy_async();
-                issue_tile(stage ^ 1u, t1);
-            }
-        }
-        mbar_wait(&sm.bar[stage], (it >> 1) & 1u);
-
         const uint32_t tile_base = tile * kTile;
-        uint32_t wcnt[V];
-        uint64_t wlen[V];
+
+        float4 ps[kItems], q[kItems];
+        uint32_t mid[kItems];
 #pragma unroll
-        for (int k = 0; k < V; ++k) {
-            wcnt[k] = 0;
-            wlen[k] = 0;
+        for (int j = 0; j < kItems; ++j) {
+            ps[j] = sm.pos_scale[stage][e0 + 32 * j];
+            q[j] = sm.rot[stage][e0 + 32 * j];
+            mid[j] = sm.mesh[stage][e0 + 32 * j];
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[stage]);  // inputs are in registers: the stage can be refilled
 
-        // ---------------- phase A: one entity per thread per item ----------------
-#pragma unroll 1
-        for (int item = 0; item < kItems; ++item) {
-            const uint32_t e = warp * kWarpSpan + item * 32 + lane;  // slot in tile
-            const uint32_t g = tile_base + e;                         // slot in frame
-            const bool valid = g < args.n;
-            float4 ps = sm.pos_scale[stage][e];
-            float4 q = sm.rot[stage][e];
-            uint32_t mid = sm.mesh[stage][e];
-            if (!valid) {
-                ps = make_float4(0.f, 0.f, 0.f, 1.f);
-                q = make_float4(0.f, 0.f, 0.f, 1.f);
-                mid = 0;
-            }
-            if (mid >= args.n_meshes) {
-                atomicOr(args.error_flag, 1u);
-                mid = 0;
-            }
-            const Mat34 m = model_matrix(ps, q);
-
-            // model matrix out: transpose through the warp's smem buffer so that
-            // every global store instruction covers 512 contiguous bytes.
-            {
-                float4* buf = sm.mat[warp];
-                const uint32_t sw = (lane >> 1) & 3u;
-                buf[lane * 4 + (0u ^ sw)] = make_float4(m.m00, m.m10, m.m20, 0.f);
-                buf[lane * 4 + (1u ^ sw)] = make_float4(m.m01, m.m11, m.m21, 0.f);
-                buf[lane * 4 + (2u ^ sw)] = make_float4(m.m02, m.m12, m.m22, 0.f);
-                buf[lane * 4 + (3u ^ sw)] = make_float4(m.tx, m.ty, m.tz, 1.f);
-                __syncwarp();
-                const uint32_t g0 = tile_base + warp * kWarpSpan + item * 32;  // first entity of this pass
-                float4* out = args.model + (size_t)g0 * 4;
+        float cx[kItems], cy[kItems], cz[kItems], hx[kItems], hy[kItems], hz[kItems];
+        uint32_t slot[kItems];
+        bool valid[kItems];
 #pragma unroll
-                for (int r = 0; r < 4; ++r) {
-                    const uint32_t p = r * 32 + lane;
-                    const uint32_t el = p >> 2;
-                    const uint32_t col = (p & 3u) ^ ((el >> 1) & 3u);
-                    const float4 v = buf[p];
-                    if (g0 + el < args.n) __stcs(out + el * 4 + col, v);
-                }
-                __syncwarp();
+        for (int j = 0; j < kItems; ++j) {
+            const uint32_t g = tile_base + e0 + 32 * j;  // slot in frame
+            valid[j] = g < args.n;
+            if (!valid[j]) {
+                ps[j] = make_float4(0.f, 0.f, 0.f, 1.f);
+                q[j] = make_float4(0.f, 0.f, 0.f, 1.f);
+                mid[j] = 0;
+            }
+            if (mid[j] >= args.n_meshes) {
+                atomicOr(args.error_flag, 1u);
+                mid[j] = 0;
+            }
+            const Mat34 m = model_matrix(ps[j], q[j]);
+
+            // model matrix out: swizzled box in smem -> one 2 KB TMA tensor store per warp and item
+            if (lane == 0) bulk_wait_read0();  // the previous store has finished reading the box
+            __syncwarp();
+            *reinterpret_cast<float4*>(box + moff0) = make_float4(m.m00, m.m10, m.m20, 0.f);
+            *reinterpret_cast<float4*>(box + moff1) = make_float4(m.m01, m.m11, m.m21, 0.f);
+            *reinterpret_cast<float4*>(box + moff2) = make_float4(m.m02, m.m12, m.m22, 0.f);
+            *reinterpret_cast<float4*>(box + moff3) = make_float4(m.tx, m.ty, m.tz, 1.f);
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_2d(&model_map, box, 0, (int)((tile_base + warp * kWarpSpan + 32 * j) >> 1));
+                bulk_commit();
             }
 
             // A2: world AABB
-            const float4 mn = __ldg(args.mesh_aabb + 2 * mid);
-            const float4 mx = __ldg(args.mesh_aabb + 2 * mid + 1);
+            const float4 mn = __ldg(args.mesh_aabb + 2 * mid[j]);
+            const float4 mx = __ldg(args.mesh_aabb + 2 * mid[j] + 1);
             float lox, hix, loy, hiy, loz, hiz;
             row_extent(m.m00, m.m01, m.m02, m.tx, mn, mx, lox, hix);
             row_extent(m.m10, m.m11, m.m12, m.ty, mn, mx, loy, hiy);
@@ -229,129 +386,91 @@ __global__ void __launch_bounds__(kThreads, 2) transform_cull_compact(const __gr
             aabb_store_form(lox, hix, minx, maxx);
             aabb_store_form(loy, hiy, miny, maxy);
             aabb_store_form(loz, hiz, minz, maxz);
-            if (args.aabb != nullptr && valid) {
+            if (kMat && args.aabb != nullptr && valid[j]) {
                 float* a = args.aabb + (size_t)g * 6;
                 a[0] = minx; a[1] = miny; a[2] = minz;
                 a[3] = maxx; a[4] = maxy; a[5] = maxz;
             }
             // A3 inputs: ncollide half_extents() / center() of the STORED box
-            const float hx = __fmul_rn(__fsub_rn(maxx, minx), 0.5f), cx = __fmul_rn(__fadd_rn(minx, maxx), 0.5f);
-            const float hy = __fmul_rn(__fsub_rn(maxy, miny), 0.5f), cy = __fmul_rn(__fadd_rn(miny, maxy), 0.5f);
-            const float hz = __fmul_rn(__fsub_rn(maxz, minz), 0.5f), cz = __fmul_rn(__fadd_rn(minz, maxz), 0.5f);
+            hx[j] = __fmul_rn(__fsub_rn(maxx, minx), 0.5f); cx[j] = __fmul_rn(__fadd_rn(minx, maxx), 0.5f);
+            hy[j] = __fmul_rn(__fsub_rn(maxy, miny), 0.5f); cy[j] = __fmul_rn(__fadd_rn(miny, maxy), 0.5f);
+            hz[j] = __fmul_rn(__fsub_rn(maxz, minz), 0.5f); cz[j] = __fmul_rn(__fadd_rn(minz, maxz), 0.5f);
 
-            // A4: pick_lod, then the (mesh, lod) slot replaces the mesh id in smem
-            const float dx = __fsub_rn(args.cam[0], ps.x), dy = __fsub_rn(args.cam[1], ps.y),
-                        dz = __fsub_rn(args.cam[2], ps.z);
+            // A4: pick_lod -> (mesh, lod) slot
+            const float dx = __fsub_rn(args.cam[0], ps[j].x), dy = __fsub_rn(args.cam[1], ps[j].y),
+                        dz = __fsub_rn(args.cam[2], ps[j].z);
             const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
             const uint32_t n_lods = __float_as_uint(mn.w);
-            const uint32_t lod = (d2 > args.lod_d2_max && n_lods > 1u) ? 1u : 0u;
-            const uint32_t slot = mid * kMaxLods + lod;
-            sm.mesh[stage][e] = slot;
-
-            // A3 per view + ballot compaction into the warp's list segment
-            bool any_vis = false;
-            bool vis[V];
-#pragma unroll
-            for (int k = 0; k < V; ++k) {
-                bool outside = false;
-#pragma unroll
-                for (int p = 0; p < 6; ++p) {
-                    const float ee = __fadd_rn(
-                        __fadd_rn(__fmul_rn(hx, args.absn[k][p][0]), __fmul_rn(hy, args.absn[k][p][1])),
-                        __fmul_rn(hz, args.absn[k][p][2]));
-                    const float s = __fadd_rn(
-                        __fadd_rn(__fmul_rn(args.planes[k][p][0], cx), __fmul_rn(args.planes[k][p][2], cz)),
-                        __fadd_rn(__fmul_rn(args.planes[k][p][1], cy), args.planes[k][p][3]));
-                    outside = outside || (__fsub_rn(s, ee) > 0.0f);
-                }
-                vis[k] = valid && !outside;
-                any_vis = any_vis || vis[k];
-                if (args.flags[k] != nullptr && valid) args.flags[k][g] = outside ? 1 : 0;
-            }
-            uint32_t len = 0;
-            if (any_vis) len = __ldg(args.lod_tab + slot).x;
-#pragma unroll
-            for (int k = 0; k < V; ++k) {
-                const uint32_t b = __ballot_sync(kFullMask, vis[k]);
-                if (vis[k]) {
-                    list[k * kTile + warp * kWarpSpan + wcnt[k] + __popc(b & lt)] = (uint16_t)e;
-                    wlen[k] += len;
-                }
-                wcnt[k] += __popc(b);
-            }
+            slot[j] = mid[j] * kMaxLods + ((d2 > args.lod_d2_max && n_lods > 1u) ? 1u : 0u);
         }
 
-        // warp aggregates -> smem
+        // the previous tile's offsets are known by now (the scan warp worked while we did the
+        // transforms): emit its commands, which frees this warp's list and slot segment
+        if (it >= 1) {
+            mbar_wait(&sm.bases, (it - 1) & 1u);
+            emit_pending<V>(args, sm, wlist, prev_base, warp, lane);
+            __syncwarp();
+        }
+        prev_base = tile_base;
+        uint32_t len_lo[kItems], len_hi[kItems];
+#pragma unroll
+        for (int j = 0; j < kItems; ++j) {
+            sm.slot[e0 + 32 * j] = slot[j];
+            const uint32_t len = __ldg(args.lod_tab + slot[j]).x;
+            len_lo[j] = len & 0xffffu;
+            len_hi[j] = len >> 16;
+        }
+
+        // A3 per view: planes outer, the thread's 4 entities inner
+        uint32_t woff = 0;  // start of view k in the warp's combined list
 #pragma unroll
         for (int k = 0; k < V; ++k) {
-            const uint64_t t = warp_sum_u64(wlen[k]);
-            if (lane == 0) {
-                sm.wcnt[k][warp] = wcnt[k];
-                sm.wlen[k][warp] = t;
-            }
-        }
-        __syncthreads();
-
-        // ---------------- tile prefix: warp k looks back for view k ----------------
-        for (int k = warp; k < V; k += kWarps) {
-            uint32_t c = lane < kWarps ? sm.wcnt[k][lane] : 0u;
-            uint64_t l = lane < kWarps ? sm.wlen[k][lane] : 0ull;
-            c = __reduce_add_sync(kFullMask, c);
-            l = warp_sum_u64(l);
-            uint32_t ec;
-            uint64_t el;
-            lookback(args.status + (size_t)k * args.n_tiles * kStatusWords, tile, args.epoch, c, l, ec, el);
-            if (lane == 0) {
-                sm.excl_cnt[k] = ec;
-                sm.excl_len[k] = el;
-                if (tile == args.n_tiles - 1) {
-                    args.counts[k] = ec + c;
-                    args.totals[k] = el + l;
-                }
-            }
-        }
-        __syncthreads();
-
-        // ---------------- phase B: emit commands from the warp's list ----------------
+            bool outside[kItems];
 #pragma unroll
-        for (int k = 0; k < V; ++k) {
-            const uint32_t cw = wcnt[k];
-            if (cw == 0) continue;
-            uint32_t cnt_base = sm.excl_cnt[k];
-            uint32_t len_base = (uint32_t)sm.excl_len[k];
-            for (uint32_t w = 0; w < warp; ++w) {
-                cnt_base += sm.wcnt[k][w];
-                len_base += (uint32_t)sm.wlen[k][w];
-            }
-            uint32_t* cmds = args.cmds[k];
-            uint32_t* visible = args.visible[k];
-            for (uint32_t j0 = 0; j0 < cw; j0 += 32) {
-                const uint32_t j = j0 + lane;
-                const bool act = j < cw;
-                uint32_t e = 0;
-                uint4 L = make_uint4(0, 0, 0, 0);
-                if (act) {
-                    e = list[k * kTile + warp * kWarpSpan + j];
-                    L = __ldg(args.lod_tab + sm.mesh[stage][e]);
-                }
-                const uint32_t incl = warp_incl_scan_u32(L.x, lane);
-                const uint32_t first_index = len_base + incl - L.x;
-                len_base += __shfl_sync(kFullMask, incl, 31);
-                const uint32_t pos = cnt_base + j;
-                if (act && pos < args.cap_visible) {
-                    const uint32_t draw_index = args.draw_index_base + tile_base + e;
-                    uint32_t* c = cmds + (size_t)pos * 5;
-                    c[0] = L.x;          // indexCount (entity-level upper bound)
-                    c[1] = 1u;           // instanceCount
-                    c[2] = first_index;  // running sum of earlier survivors' index_len
-                    c[3] = L.z;          // vertexOffset
-                    c[4] = draw_index;   // firstInstance
-                    visible[pos] = draw_index;
+            for (int j = 0; j < kItems; ++j) outside[j] = false;
+#pragma unroll
+            for (int p = 0; p < 6; ++p) {
+                const float4 pl = args.planes[k][p];
+                const float ax = fabsf(pl.x), ay = fabsf(pl.y), az = fabsf(pl.z);
+#pragma unroll
+                for (int j = 0; j < kItems; ++j) {
+                    const float ee = __fadd_rn(__fadd_rn(__fmul_rn(hx[j], ax), __fmul_rn(hy[j], ay)), __fmul_rn(hz[j], az));
+                    const float s = __fadd_rn(__fadd_rn(__fmul_rn(pl.x, cx[j]), __fmul_rn(pl.z, cz[j])),
+                                              __fadd_rn(__fmul_rn(pl.y, cy[j]), pl.w));
+                    // (s - e > 0.0) == (s > e): the rounded difference of two floats keeps its sign,
+                    // and both forms are false for NaN and for inf - inf
+                    outside[j] = outside[j] || (s > ee);
                 }
             }
+            uint32_t wc = 0, lo = 0, hi = 0;
+#pragma unroll
+            for (int j = 0; j < kItems; ++j) {
+                const bool vis = valid[j] && !outside[j];
+                if (kMat && args.flags[k] != nullptr && valid[j]) args.flags[k][tile_base + e0 + 32 * j] = outside[j] ? 1 : 0;
+                const uint32_t b = __ballot_sync(kFullMask, vis);
+                if (vis) {
+                    wlist[woff + wc + __popc(b & lt)] = (uint16_t)((k << 7) | (lane + 32 * j));
+                    lo += len_lo[j];
+                    hi += len_hi[j];
+                }
+                wc += __popc(b);
+            }
+            lo = __reduce_add_sync(kFullMask, lo);  // 128 x 16-bit pieces: no overflow
+            hi = __reduce_add_sync(kFullMask, hi);
+            if (lane == 0) {
+                sm.wcnt[k][warp] = wc;
+                sm.wlen[k][warp] = (uint64_t)lo + ((uint64_t)hi << 16);
+            }
+            woff += wc;
         }
-        __syncthreads();  // stage buffers, list and aggregates are free again
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.done);
     }
+    if (it >= 1) {  // the last tile of this CTA is still pending
+        mbar_wait(&sm.bases, (it - 1) & 1u);
+        emit_pending<V>(args, sm, wlist, prev_base, warp, lane);
+    }
+    if (lane == 0) bulk_wait_read0();
 }
 
 }  // namespace rcull
