@@ -67,23 +67,26 @@ struct FrameSmem {
     float4 pos_scale[kStages][kTile];
     float4 rot[kStages][kTile];
     uint32_t mesh[kStages][kTile];
-    uint32_t slot[kTile];  // (mesh, lod) slot of every entity of the tile whose lists are pending
+    // Survivor bookkeeping is double-buffered (buffer = tile iteration & 1): the scan warp
+    // resolves the offsets of tile i while the compute warps are one to two tiles ahead.
+    uint32_t slot[2][kTile];  // (mesh, lod) slot of every entity
     uint64_t full[kStages];
     uint64_t empty[kStages];
-    uint64_t done;   // compute warps -> scan warp: lists and aggregates of a tile are written
-    uint64_t bases;  // scan warp -> compute warps: output offsets of that tile are known
-    uint64_t wlen[kMaxViews][kComputeWarps];   // per-warp index sums of the pending tile
-    uint32_t wcnt[kMaxViews][kComputeWarps];   // per-warp survivor counts
-    uint32_t adj_cnt[kMaxViews][kComputeWarps];  // output slot of combined-list entry i of view k: adj_cnt + i
-    uint32_t adj_len[kMaxViews][kComputeWarps];  // firstIndex of it: adj_len + exclusive len scan up to i
+    uint64_t done[2];   // compute warps -> scan warp: lists and aggregates of a tile are written
+    uint64_t bases[2];  // scan warp -> compute warps: output offsets of that tile are known
+    uint64_t wlen[2][kMaxViews][kComputeWarps];   // per-warp index sums
+    uint32_t wcnt[2][kMaxViews][kComputeWarps];   // per-warp survivor counts
+    uint32_t adj_cnt[2][kMaxViews][kComputeWarps];  // output slot of combined-list entry i of view k: adj_cnt + i
+    uint32_t adj_len[2][kMaxViews][kComputeWarps];  // firstIndex of it: adj_len + exclusive len scan up to i
     uint32_t tile_of_stage[kStages];
-    // followed by: uint16_t wlist[kComputeWarps][V * kWarpSpan] -- per-warp combined
-    // survivor list, view-major, entry = view << 7 | slot-in-warp-span
+    // followed by: uint8_t wlist[2][kComputeWarps][V * kWarpSpan] -- per-warp combined
+    // survivor list, view-major, entry = slot in the warp's span (the view follows
+    // from the entry's position and the per-view counts)
 };
 
 template <int V>
 constexpr size_t frame_smem_bytes() {
-    return sizeof(FrameSmem) + sizeof(uint16_t) * V * kTile + 1024;  // + slack to align the base
+    return sizeof(FrameSmem) + 2 * V * kTile + 1024;  // + slack to align the base
 }
 
 __device__ __forceinline__ FrameSmem& frame_smem(unsigned char* raw) {
@@ -98,14 +101,18 @@ __device__ __forceinline__ bool desc_ready(const ulonglong2& d, uint32_t epoch) 
     return (uint32_t)(d.x >> 34) == epoch && ((d.x >> 32) & 3ull) != 0ull;
 }
 
+
 // Publishes the aggregates of `tile`, resolves its exclusive prefixes (count and
 // index sum per view) and publishes the inclusive values.  Whole warp; inputs and
-// outputs are warp-uniform.
+// outputs are warp-uniform.  All views advance together and every round inspects
+// 32*U predecessors with all loads in flight at once: CTAs run in waves, so the
+// last tile of a wave has to walk back over a whole wave of aggregates.
 template <int V>
 __device__ __forceinline__ void lookback_tile(ulonglong2* status, uint32_t n_tiles, uint32_t tile, uint32_t epoch,
                                               uint32_t lane, const uint32_t (&agg_cnt)[V],
                                               const uint64_t (&agg_len)[V], uint32_t (&excl_cnt)[V],
                                               uint64_t (&excl_len)[V]) {
+    constexpr int U = V <= 4 ? 4 : 2;
     const uint64_t tag = (uint64_t)epoch << 34;
     if (tile == 0) {
 #pragma unroll
@@ -122,57 +129,82 @@ __device__ __forceinline__ void lookback_tile(ulonglong2* status, uint32_t n_til
             st_relaxed_v2(status + (size_t)k * n_tiles + tile, tag | (kFlagAgg << 32) | agg_cnt[k], agg_len[k]);
     }
     const ulonglong2 virt = make_ulonglong2(tag | (kFlagIncl << 32), 0ull);  // tile -1: inclusive prefix 0
-    const int pred0 = (int)tile - 1 - (int)lane;
-    ulonglong2 first[V];
-#pragma unroll
-    for (int k = 0; k < V; ++k)  // V independent loads in flight
-        first[k] = pred0 >= 0 ? ld_relaxed_v2(status + (size_t)k * n_tiles + pred0) : virt;
+    uint32_t acc_c[V];
+    uint64_t acc_l[V];
+    bool open[V];
 #pragma unroll
     for (int k = 0; k < V; ++k) {
-        const ulonglong2* sv = status + (size_t)k * n_tiles;
-        ulonglong2 d = first[k];
-        int pred = pred0;
-        uint32_t ecnt = 0;
-        uint64_t elen = 0;
-        while (true) {
-            bool ok = pred < 0 || desc_ready(d, epoch);
+        acc_c[k] = 0;
+        acc_l[k] = 0;
+        open[k] = true;
+    }
+    int base = (int)tile - 1 - (int)lane;  // this lane's nearest predecessor in the current window
+    bool any_open = true;
+    while (any_open) {
+        ulonglong2 d[V][U];
+#pragma unroll
+        for (int k = 0; k < V; ++k)
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int p = base - 32 * u;
+                d[k][u] = (open[k] && p >= 0) ? ld_relaxed_v2(status + (size_t)k * n_tiles + p) : virt;
+            }
+        any_open = false;
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+            if (!open[k]) continue;
+            bool ok = true;
+#pragma unroll
+            for (int u = 0; u < U; ++u) ok = ok && desc_ready(d[k][u], epoch);
             while (!__all_sync(kFullMask, ok)) {  // a predecessor in the window has not published yet
-                if (!ok) {
-                    d = ld_relaxed_v2(sv + pred);
-                    ok = desc_ready(d, epoch);
+                ok = true;
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    if (!desc_ready(d[k][u], epoch)) d[k][u] = ld_relaxed_v2(status + (size_t)k * n_tiles + (base - 32 * u));
+                    ok = ok && desc_ready(d[k][u], epoch);
                 }
             }
-            const uint32_t flag = (uint32_t)(d.x >> 32) & 3u;
-            const uint32_t incl_mask = __ballot_sync(kFullMask, flag == kFlagIncl);
-            const uint32_t stop = incl_mask ? (uint32_t)__ffs(incl_mask) - 1u : 31u;
-            const bool use = lane <= stop;
-            ecnt += __reduce_add_sync(kFullMask, use ? (uint32_t)d.x : 0u);
-            elen += warp_sum_u64(use ? d.y : 0ull);
-            if (incl_mask) break;
-            pred -= 32;
-            d = pred >= 0 ? ld_relaxed_v2(sv + pred) : virt;
+            bool stopped = false;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const uint32_t incl_mask = __ballot_sync(kFullMask, ((uint32_t)(d[k][u].x >> 32) & 3u) == kFlagIncl);
+                if (!stopped) {
+                    const uint32_t stop = incl_mask ? (uint32_t)__ffs(incl_mask) - 1u : 31u;
+                    if (lane <= stop) {
+                        acc_c[k] += (uint32_t)d[k][u].x;
+                        acc_l[k] += d[k][u].y;
+                    }
+                    stopped = incl_mask != 0u;
+                }
+            }
+            open[k] = !stopped;
+            any_open = any_open || !stopped;
         }
-        excl_cnt[k] = ecnt;
-        excl_len[k] = elen;
+        base -= 32 * U;
+    }
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+        excl_cnt[k] = __reduce_add_sync(kFullMask, acc_c[k]);
+        excl_len[k] = warp_sum_u64(acc_l[k]);
         if (lane == 0)
-            st_relaxed_v2(status + (size_t)k * n_tiles + tile, tag | (kFlagIncl << 32) | (uint32_t)(ecnt + agg_cnt[k]),
-                          elen + agg_len[k]);
+            st_relaxed_v2(status + (size_t)k * n_tiles + tile,
+                          tag | (kFlagIncl << 32) | (uint32_t)(excl_cnt[k] + agg_cnt[k]), excl_len[k] + agg_len[k]);
     }
 }
-
 
 // Scan-warp work for one finished tile: per-warp prefixes, look-back, output offsets.
 // Lanes 0..7 stand for the eight compute warps.
 template <int V>
-__device__ __forceinline__ void scan_tile(const FrameArgs& args, FrameSmem& sm, uint32_t tile, uint32_t lane) {
+__device__ __forceinline__ void scan_tile(const FrameArgs& args, FrameSmem& sm, uint32_t buf, uint32_t tile,
+                                          uint32_t lane) {
     uint32_t agg_cnt[V], excl_cnt[V];
     uint64_t agg_len[V], excl_len[V];
     uint32_t rel_cnt[V], rel_len[V];  // (prefix over lower warps) - (start of view k in the warp's combined list)
     uint32_t vstart_c = 0, vstart_l = 0;
 #pragma unroll
     for (int k = 0; k < V; ++k) {
-        const uint32_t c = lane < kComputeWarps ? sm.wcnt[k][lane] : 0u;
-        const uint64_t l = lane < kComputeWarps ? sm.wlen[k][lane] : 0ull;
+        const uint32_t c = lane < kComputeWarps ? sm.wcnt[buf][k][lane] : 0u;
+        const uint64_t l = lane < kComputeWarps ? sm.wlen[buf][k][lane] : 0ull;
         uint32_t ic = c;
         uint64_t il = l;
 #pragma unroll
@@ -195,8 +227,8 @@ __device__ __forceinline__ void scan_tile(const FrameArgs& args, FrameSmem& sm, 
     if (lane < kComputeWarps) {
 #pragma unroll
         for (int k = 0; k < V; ++k) {
-            sm.adj_cnt[k][lane] = excl_cnt[k] + rel_cnt[k];
-            sm.adj_len[k][lane] = (uint32_t)excl_len[k] + rel_len[k];  // firstIndex is u32 and wraps like the reference's
+            sm.adj_cnt[buf][k][lane] = excl_cnt[k] + rel_cnt[k];
+            sm.adj_len[buf][k][lane] = (uint32_t)excl_len[k] + rel_len[k];  // firstIndex is u32 and wraps like the reference's
         }
     }
     if (tile == args.n_tiles - 1 && lane == 0) {
@@ -208,14 +240,18 @@ __device__ __forceinline__ void scan_tile(const FrameArgs& args, FrameSmem& sm, 
     }
 }
 
-// Compute-warp emission of its own survivors of the pending tile: one pass over the
+// Compute-warp emission of its own survivors of a pending tile: one pass over the
 // warp's combined (all views) list, stable within every view.
 template <int V>
-__device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameSmem& sm, const uint16_t* wlist,
-                                             uint32_t tile_base, uint32_t warp, uint32_t lane) {
+__device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameSmem& sm, const uint8_t* wlist,
+                                             uint32_t buf, uint32_t tile_base, uint32_t warp, uint32_t lane) {
+    uint32_t vend[V];  // end of view k in the combined list
     uint32_t total = 0;
 #pragma unroll
-    for (int k = 0; k < V; ++k) total += sm.wcnt[k][warp];
+    for (int k = 0; k < V; ++k) {
+        total += sm.wcnt[buf][k][warp];
+        vend[k] = total;
+    }
     uint32_t carry = 0;
     for (uint32_t i0 = 0; i0 < total; i0 += 32) {
         const uint32_t i = i0 + lane;
@@ -223,24 +259,24 @@ __device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameS
         uint32_t k = 0, e = 0;
         uint4 L = make_uint4(0, 0, 0, 0);
         if (act) {
-            const uint32_t entry = wlist[i];
-            k = entry >> 7;
-            e = warp * kWarpSpan + (entry & 127u);
-            L = __ldg(args.lod_tab + sm.slot[e]);
+#pragma unroll
+            for (int kk = 0; kk < V - 1; ++kk) k += i >= vend[kk] ? 1u : 0u;
+            e = warp * kWarpSpan + wlist[i];
+            L = __ldg(args.lod_tab + sm.slot[buf][e]);
         }
         const uint32_t incl = warp_incl_scan_u32(L.x, lane);
         const uint32_t excl = carry + incl - L.x;
         carry += __shfl_sync(kFullMask, incl, 31);
         if (act) {
-            const uint32_t pos = sm.adj_cnt[k][warp] + i;
+            const uint32_t pos = sm.adj_cnt[buf][k][warp] + i;
             if (pos < args.cap_visible) {
                 const uint32_t draw_index = args.draw_index_base + tile_base + e;
                 uint32_t* c = args.cmds[k] + (size_t)pos * 5;
-                c[0] = L.x;                            // indexCount (entity-level upper bound)
-                c[1] = 1u;                             // instanceCount
-                c[2] = sm.adj_len[k][warp] + excl;     // firstIndex: running sum of earlier survivors' index_len
-                c[3] = L.z;                            // vertexOffset
-                c[4] = draw_index;                     // firstInstance
+                c[0] = L.x;                               // indexCount (entity-level upper bound)
+                c[1] = 1u;                                // instanceCount
+                c[2] = sm.adj_len[buf][k][warp] + excl;   // firstIndex: running sum of earlier survivors' index_len
+                c[3] = L.z;                               // vertexOffset
+                c[4] = draw_index;                        // firstInstance
                 args.visible[k][pos] = draw_index;
             }
         }
@@ -268,8 +304,11 @@ __global__ void __maxnreg__(112)
             mbar_init(&sm.full[s], 1);
             mbar_init(&sm.empty[s], kComputeWarps);
         }
-        mbar_init(&sm.done, kComputeWarps);
-        mbar_init(&sm.bases, 1);
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&sm.done[b], kComputeWarps);
+            mbar_init(&sm.bases[b], 1);
+        }
         fence_mbar_init();
     }
     __syncthreads();
@@ -302,18 +341,17 @@ __global__ void __maxnreg__(112)
                 nxt = claim_tile(stage ^ 1u);
             }
             nxt = __shfl_sync(kFullMask, nxt, 0);
-            mbar_wait(&sm.done, it & 1u);
-            scan_tile<V>(args, sm, cur, lane);
+            mbar_wait(&sm.done[stage], (it >> 1) & 1u);
+            scan_tile<V>(args, sm, stage, cur, lane);
             __syncwarp();
-            if (lane == 0) mbar_arrive(&sm.bases);
+            if (lane == 0) mbar_arrive(&sm.bases[stage]);
             cur = nxt;
         }
         return;
     }
 
     // ================================= compute warps =================================
-    uint16_t* const wlist =
-        reinterpret_cast<uint16_t*>(reinterpret_cast<unsigned char*>(&sm) + sizeof(FrameSmem)) + warp * (V * kWarpSpan);
+    uint8_t* const wlist_base = reinterpret_cast<uint8_t*>(&sm) + sizeof(FrameSmem) + warp * (V * kWarpSpan);
     const uint32_t lt = (1u << lane) - 1u;
     // swizzled (128-B pattern) byte offsets of this lane's four matrix columns in the warp's store box
     unsigned char* const box = reinterpret_cast<unsigned char*>(sm.mat[warp]);
@@ -324,13 +362,15 @@ __global__ void __maxnreg__(112)
     const uint32_t moff3 = mrow * 128u + (((mhalf + 3u) ^ (mrow & 7u)) << 4);
     const uint32_t e0 = warp * kWarpSpan + lane;  // slot in tile of item 0; item j adds 32*j
 
-    uint32_t it = 0, prev_base = 0;
+    uint32_t it = 0;
+    uint32_t base_of[2] = {0, 0};  // tile_base of the tile pending in each buffer
     for (;; ++it) {
-        const uint32_t stage = it & 1u;
+        const uint32_t stage = it & 1u;  // input stage and bookkeeping buffer of this tile
         mbar_wait(&sm.full[stage], (it >> 1) & 1u);
         const uint32_t tile = sm.tile_of_stage[stage];
         if (tile >= args.n_tiles) break;
         const uint32_t tile_base = tile * kTile;
+        uint8_t* const wlist = wlist_base + stage * (V * kTile);
 
         float4 ps[kItems], q[kItems];
         uint32_t mid[kItems];
@@ -404,18 +444,18 @@ __global__ void __maxnreg__(112)
             slot[j] = mid[j] * kMaxLods + ((d2 > args.lod_d2_max && n_lods > 1u) ? 1u : 0u);
         }
 
-        // the previous tile's offsets are known by now (the scan warp worked while we did the
-        // transforms): emit its commands, which frees this warp's list and slot segment
-        if (it >= 1) {
-            mbar_wait(&sm.bases, (it - 1) & 1u);
-            emit_pending<V>(args, sm, wlist, prev_base, warp, lane);
+        // The tile that used this bookkeeping buffer two iterations ago has had more than a
+        // whole tile time for its look-back: emit its commands, which frees the buffer.
+        if (it >= 2) {
+            mbar_wait(&sm.bases[stage], ((it - 2) >> 1) & 1u);
+            emit_pending<V>(args, sm, wlist, stage, base_of[stage], warp, lane);
             __syncwarp();
         }
-        prev_base = tile_base;
+        base_of[stage] = tile_base;
         uint32_t len_lo[kItems], len_hi[kItems];
 #pragma unroll
         for (int j = 0; j < kItems; ++j) {
-            sm.slot[e0 + 32 * j] = slot[j];
+            sm.slot[stage][e0 + 32 * j] = slot[j];
             const uint32_t len = __ldg(args.lod_tab + slot[j]).x;
             len_lo[j] = len & 0xffffu;
             len_hi[j] = len >> 16;
@@ -449,7 +489,7 @@ __global__ void __maxnreg__(112)
                 if (kMat && args.flags[k] != nullptr && valid[j]) args.flags[k][tile_base + e0 + 32 * j] = outside[j] ? 1 : 0;
                 const uint32_t b = __ballot_sync(kFullMask, vis);
                 if (vis) {
-                    wlist[woff + wc + __popc(b & lt)] = (uint16_t)((k << 7) | (lane + 32 * j));
+                    wlist[woff + wc + __popc(b & lt)] = (uint8_t)(lane + 32 * j);
                     lo += len_lo[j];
                     hi += len_hi[j];
                 }
@@ -458,17 +498,22 @@ __global__ void __maxnreg__(112)
             lo = __reduce_add_sync(kFullMask, lo);  // 128 x 16-bit pieces: no overflow
             hi = __reduce_add_sync(kFullMask, hi);
             if (lane == 0) {
-                sm.wcnt[k][warp] = wc;
-                sm.wlen[k][warp] = (uint64_t)lo + ((uint64_t)hi << 16);
+                sm.wcnt[stage][k][warp] = wc;
+                sm.wlen[stage][k][warp] = (uint64_t)lo + ((uint64_t)hi << 16);
             }
             woff += wc;
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.done);
+        if (lane == 0) mbar_arrive(&sm.done[stage]);
     }
-    if (it >= 1) {  // the last tile of this CTA is still pending
-        mbar_wait(&sm.bases, (it - 1) & 1u);
-        emit_pending<V>(args, sm, wlist, prev_base, warp, lane);
+    // up to two tiles of this CTA are still pending: iterations it-2 and it-1, in that order
+#pragma unroll
+    for (int back = 2; back >= 1; --back) {
+        if (it >= (uint32_t)back) {
+            const uint32_t pit = it - back, b = pit & 1u;
+            mbar_wait(&sm.bases[b], (pit >> 1) & 1u);
+            emit_pending<V>(args, sm, wlist_base + b * (V * kTile), b, base_of[b], warp, lane);
+        }
     }
     if (lane == 0) bulk_wait_read0();
 }
