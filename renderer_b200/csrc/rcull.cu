@@ -111,6 +111,7 @@ template <int V, bool M>
 int configure(rcull_ctx* c) {
     auto k = transform_cull_compact<V, M>;
     CU(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)frame_smem_bytes<V>()));
+    CU(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     int b = 0;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k, kThreads, frame_smem_bytes<V>()));
     if (b < 1) return fail(RCULL_ERR_CUDA, "transform_cull_compact<%d,%d> does not fit on an SM", V, (int)M);

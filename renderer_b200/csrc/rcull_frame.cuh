@@ -20,10 +20,10 @@
 
 namespace rcull {
 
-constexpr int kComputeWarps = 8;
+constexpr int kComputeWarps = 7;  // + 1 scan warp = 8 warps: two CTAs fill an SM's register file at 112 regs
 constexpr int kThreads = (kComputeWarps + 1) * 32;  // + scan warp
 constexpr int kItems = 4;                           // entities per thread per tile
-constexpr int kTile = kComputeWarps * 32 * kItems;  // 1024 entities
+constexpr int kTile = kComputeWarps * 32 * kItems;  // 896 entities
 constexpr int kWarpSpan = 32 * kItems;              // entities owned by one compute warp
 constexpr int kStages = 2;
 constexpr int kMaxViews = 8;
@@ -78,7 +78,7 @@ struct FrameSmem {
     uint32_t wcnt[2][kMaxViews][kComputeWarps];   // per-warp survivor counts
     uint32_t adj_cnt[2][kMaxViews][kComputeWarps];  // output slot of combined-list entry i of view k: adj_cnt + i
     uint32_t adj_len[2][kMaxViews][kComputeWarps];  // firstIndex of it: adj_len + exclusive len scan up to i
-    uint32_t tile_of_stage[kStages];
+    uint32_t tile_ring[4];  // tile id of iteration it at [it & 3]
     // followed by: uint8_t wlist[2][kComputeWarps][V * kWarpSpan] -- per-warp combined
     // survivor list, view-major, entry = slot in the warp's span (the view follows
     // from the entry's position and the per-view counts)
@@ -314,38 +314,15 @@ __global__ void __maxnreg__(112)
     __syncthreads();
 
     if (warp == kComputeWarps) {
-        // =============================== scan / IO warp ===============================
-        auto claim_tile = [&](uint32_t stage) -> uint32_t {  // lane 0 only
-            const uint32_t t = atomicAdd(args.ticket, 1u) - args.ticket_base;
-            sm.tile_of_stage[stage] = t;
-            uint64_t* bar = &sm.full[stage];
-            if (t < args.n_tiles) {
-                fence_proxy_async();
-                mbar_expect_tx(bar, kStageBytes);
-                bulk_g2s(sm.pos_scale[stage], args.pos_scale + (size_t)t * kTile, kTile * 16, bar);
-                bulk_g2s(sm.rot[stage], args.rot + (size_t)t * kTile, kTile * 16, bar);
-                bulk_g2s(sm.mesh[stage], args.mesh + (size_t)t * kTile, kTile * 4, bar);
-            } else {
-                mbar_arrive(bar);  // end marker: the compute warps read tile_of_stage and leave
-            }
-            return t;
-        };
-        uint32_t cur = 0;
-        if (lane == 0) cur = claim_tile(0);
-        cur = __shfl_sync(kFullMask, cur, 0);
-        for (uint32_t it = 0; cur < args.n_tiles; ++it) {
-            const uint32_t stage = it & 1u;
-            uint32_t nxt = 0;
-            if (lane == 0) {  // prefetch the next tile into the other stage
-                if (it >= 1) mbar_wait(&sm.empty[stage ^ 1u], ((it - 1) >> 1) & 1u);
-                nxt = claim_tile(stage ^ 1u);
-            }
-            nxt = __shfl_sync(kFullMask, nxt, 0);
-            mbar_wait(&sm.done[stage], (it >> 1) & 1u);
-            scan_tile<V>(args, sm, stage, cur, lane);
+        // ================================== scan warp ==================================
+        for (uint32_t it = 0;; ++it) {
+            const uint32_t buf = it & 1u;
+            mbar_wait(&sm.done[buf], (it >> 1) & 1u);
+            const uint32_t tile = sm.tile_ring[it & 3u];
+            if (tile >= args.n_tiles) break;  // end marker, passed on by the compute warps
+            scan_tile<V>(args, sm, buf, tile, lane);
             __syncwarp();
-            if (lane == 0) mbar_arrive(&sm.bases[stage]);
-            cur = nxt;
+            if (lane == 0) mbar_arrive(&sm.bases[buf]);
         }
         return;
     }
@@ -362,12 +339,38 @@ __global__ void __maxnreg__(112)
     const uint32_t moff3 = mrow * 128u + (((mhalf + 3u) ^ (mrow & 7u)) << 4);
     const uint32_t e0 = warp * kWarpSpan + lane;  // slot in tile of item 0; item j adds 32*j
 
+    // Compute warp 0, lane 0 is also the producer: it draws tile tickets and issues the TMA
+    // loads one tile ahead, as soon as the other stage has been read by every compute warp.
+    const bool producer = tid == 0;
+    bool more = true;  // producer only: the last ticket drawn was a real tile
+    auto claim_tile = [&](uint32_t for_it) {
+        const uint32_t stage = for_it & 1u;
+        const uint32_t t = atomicAdd(args.ticket, 1u) - args.ticket_base;
+        sm.tile_ring[for_it & 3u] = t;
+        uint64_t* bar = &sm.full[stage];
+        if (t < args.n_tiles) {
+            fence_proxy_async();
+            mbar_expect_tx(bar, kStageBytes);
+            bulk_g2s(sm.pos_scale[stage], args.pos_scale + (size_t)t * kTile, kTile * 16, bar);
+            bulk_g2s(sm.rot[stage], args.rot + (size_t)t * kTile, kTile * 16, bar);
+            bulk_g2s(sm.mesh[stage], args.mesh + (size_t)t * kTile, kTile * 4, bar);
+        } else {
+            mbar_arrive(bar);  // end marker: every warp reads tile_ring and leaves
+            more = false;
+        }
+    };
+    if (producer) claim_tile(0);
+
     uint32_t it = 0;
-    uint32_t base_of[2] = {0, 0};  // tile_base of the tile pending in each buffer
+    uint32_t base_of0 = 0, base_of1 = 0;  // tile_base of the tile pending in each bookkeeping buffer
     for (;; ++it) {
         const uint32_t stage = it & 1u;  // input stage and bookkeeping buffer of this tile
+        if (producer && more) {
+            if (it >= 1) mbar_wait(&sm.empty[stage ^ 1u], ((it - 1) >> 1) & 1u);
+            claim_tile(it + 1);
+        }
         mbar_wait(&sm.full[stage], (it >> 1) & 1u);
-        const uint32_t tile = sm.tile_of_stage[stage];
+        const uint32_t tile = sm.tile_ring[it & 3u];
         if (tile >= args.n_tiles) break;
         const uint32_t tile_base = tile * kTile;
         uint8_t* const wlist = wlist_base + stage * (V * kTile);
@@ -448,10 +451,10 @@ __global__ void __maxnreg__(112)
         // whole tile time for its look-back: emit its commands, which frees the buffer.
         if (it >= 2) {
             mbar_wait(&sm.bases[stage], ((it - 2) >> 1) & 1u);
-            emit_pending<V>(args, sm, wlist, stage, base_of[stage], warp, lane);
+            emit_pending<V>(args, sm, wlist, stage, stage ? base_of1 : base_of0, warp, lane);
             __syncwarp();
         }
-        base_of[stage] = tile_base;
+        if (stage) base_of1 = tile_base; else base_of0 = tile_base;
         uint32_t len_lo[kItems], len_hi[kItems];
 #pragma unroll
         for (int j = 0; j < kItems; ++j) {
@@ -512,9 +515,13 @@ __global__ void __maxnreg__(112)
         if (it >= (uint32_t)back) {
             const uint32_t pit = it - back, b = pit & 1u;
             mbar_wait(&sm.bases[b], (pit >> 1) & 1u);
-            emit_pending<V>(args, sm, wlist_base + b * (V * kTile), b, base_of[b], warp, lane);
+            emit_pending<V>(args, sm, wlist_base + b * (V * kTile), b, b ? base_of1 : base_of0, warp, lane);
         }
     }
+    // pass the end marker on to the scan warp (after the waits above, so that this barrier
+    // never runs two phases ahead of its reader)
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&sm.done[it & 1u]);
     if (lane == 0) bulk_wait_read0();
 }
 
