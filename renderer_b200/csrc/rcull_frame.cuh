@@ -78,6 +78,8 @@ struct FrameSmem {
     uint32_t wcnt[2][kMaxViews][kComputeWarps];   // per-warp survivor counts
     uint32_t adj_cnt[2][kMaxViews][kComputeWarps];  // output slot of combined-list entry i of view k: adj_cnt + i
     uint32_t adj_len[2][kMaxViews][kComputeWarps];  // firstIndex of it: adj_len + exclusive len scan up to i
+    uint64_t agg_len[2][kMaxViews];  // tile aggregates kept between publish and resolve
+    uint32_t agg_cnt[2][kMaxViews];
     uint32_t tile_ring[4];  // tile id of iteration it at [it & 3]
     // followed by: uint8_t wlist[2][kComputeWarps][V * kWarpSpan] -- per-warp combined
     // survivor list, view-major, entry = slot in the warp's span (the view follows
@@ -102,141 +104,152 @@ __device__ __forceinline__ bool desc_ready(const ulonglong2& d, uint32_t epoch) 
 }
 
 
-// Publishes the aggregates of `tile`, resolves its exclusive prefixes (count and
-// index sum per view) and publishes the inclusive values.  Whole warp; inputs and
-// outputs are warp-uniform.  All views advance together and every round inspects
-// 32*U predecessors with all loads in flight at once: CTAs run in waves, so the
-// last tile of a wave has to walk back over a whole wave of aggregates.
+// The scan warp never blocks on another CTA.  It is a small state machine over the
+// CTA's tiles in claim order:
+//   publish  -- as soon as the compute warps are done with a tile, reduce their
+//               per-warp counts / index sums and publish the tile AGGREGATE; this only
+//               depends on the CTA's own work, so aggregates appear without delay;
+//   resolve  -- for the oldest unresolved tile, one look-back round per pass: all views
+//               together, 32*U predecessors per view with every load in flight at
+//               once (CTAs run in waves, so the last tile of a wave walks back over a
+//               whole wave of aggregates).  A window that is not fully published yet
+//               is simply retried on the next pass.
 template <int V>
-__device__ __forceinline__ void lookback_tile(ulonglong2* status, uint32_t n_tiles, uint32_t tile, uint32_t epoch,
-                                              uint32_t lane, const uint32_t (&agg_cnt)[V],
-                                              const uint64_t (&agg_len)[V], uint32_t (&excl_cnt)[V],
-                                              uint64_t (&excl_len)[V]) {
+__device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, uint32_t lane) {
     constexpr int U = V <= 4 ? 4 : 2;
+    const uint32_t epoch = args.epoch, n_tiles = args.n_tiles;
     const uint64_t tag = (uint64_t)epoch << 34;
-    if (tile == 0) {
-#pragma unroll
-        for (int k = 0; k < V; ++k) {
-            excl_cnt[k] = 0;
-            excl_len[k] = 0;
-            if (lane == 0) st_relaxed_v2(status + (size_t)k * n_tiles, tag | (kFlagIncl << 32) | agg_cnt[k], agg_len[k]);
-        }
-        return;
-    }
-    if (lane == 0) {
-#pragma unroll
-        for (int k = 0; k < V; ++k)
-            st_relaxed_v2(status + (size_t)k * n_tiles + tile, tag | (kFlagAgg << 32) | agg_cnt[k], agg_len[k]);
-    }
     const ulonglong2 virt = make_ulonglong2(tag | (kFlagIncl << 32), 0ull);  // tile -1: inclusive prefix 0
-    uint32_t acc_c[V];
+    ulonglong2* const status = args.status;
+    uint32_t pub = 0, res = 0;  // tiles published / resolved so far (iteration numbers)
+    bool ended = false, active = false;
+    uint32_t acc_c[V], tile = 0;
     uint64_t acc_l[V];
     bool open[V];
+    int base = 0;
+    while (true) {
+        bool progress = false;
+        // ---- publish ----
+        if (!ended && pub - res < 2u && mbar_test(&sm.done[pub & 1u], (pub >> 1) & 1u)) {
+            const uint32_t buf = pub & 1u, t = sm.tile_ring[pub & 3u];
+            progress = true;
+            if (t >= n_tiles) {
+                ended = true;  // end marker, passed on by the compute warps
+            } else {
+                uint32_t vstart_c = 0, vstart_l = 0;
 #pragma unroll
-    for (int k = 0; k < V; ++k) {
-        acc_c[k] = 0;
-        acc_l[k] = 0;
-        open[k] = true;
-    }
-    int base = (int)tile - 1 - (int)lane;  // this lane's nearest predecessor in the current window
-    bool any_open = true;
-    while (any_open) {
-        ulonglong2 d[V][U];
+                for (int k = 0; k < V; ++k) {  // lanes 0..6 stand for the compute warps
+                    const uint32_t c = lane < kComputeWarps ? sm.wcnt[buf][k][lane] : 0u;
+                    const uint64_t l = lane < kComputeWarps ? sm.wlen[buf][k][lane] : 0ull;
+                    uint32_t ic = c;
+                    uint64_t il = l;
 #pragma unroll
-        for (int k = 0; k < V; ++k)
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int p = base - 32 * u;
-                d[k][u] = (open[k] && p >= 0) ? ld_relaxed_v2(status + (size_t)k * n_tiles + p) : virt;
+                    for (int o = 1; o < kComputeWarps; o <<= 1) {
+                        const uint32_t tc = __shfl_up_sync(kFullMask, ic, o);
+                        const uint64_t tl = __shfl_up_sync(kFullMask, il, o);
+                        if (lane >= (uint32_t)o) {
+                            ic += tc;
+                            il += tl;
+                        }
+                    }
+                    if (lane < kComputeWarps) {
+                        // (prefix over lower warps) - (start of view k in the warp's combined list);
+                        // the tile's exclusive prefix is added when it is resolved
+                        sm.adj_cnt[buf][k][lane] = (ic - c) - vstart_c;
+                        sm.adj_len[buf][k][lane] = (uint32_t)(il - l) - vstart_l;
+                    }
+                    if (lane == kComputeWarps - 1) {
+                        sm.agg_cnt[buf][k] = ic;
+                        sm.agg_len[buf][k] = il;
+                        st_relaxed_v2(status + (size_t)k * n_tiles + t, tag | ((t == 0 ? kFlagIncl : kFlagAgg) << 32) | ic, il);
+                    }
+                    vstart_c += c;
+                    vstart_l += (uint32_t)l;
+                }
+                __syncwarp();
+                ++pub;
             }
-        any_open = false;
+        }
+        // ---- resolve ----
+        if (res < pub) {
+            if (!active) {
+                tile = sm.tile_ring[res & 3u];
+                base = (int)tile - 1 - (int)lane;  // this lane's nearest predecessor in the current window
 #pragma unroll
-        for (int k = 0; k < V; ++k) {
-            if (!open[k]) continue;
-            bool ok = true;
+                for (int k = 0; k < V; ++k) {
+                    acc_c[k] = 0;
+                    acc_l[k] = 0;
+                    open[k] = tile != 0;
+                }
+                active = true;
+            }
+            ulonglong2 d[V][U];
 #pragma unroll
-            for (int u = 0; u < U; ++u) ok = ok && desc_ready(d[k][u], epoch);
-            while (!__all_sync(kFullMask, ok)) {  // a predecessor in the window has not published yet
-                ok = true;
+            for (int k = 0; k < V; ++k)
 #pragma unroll
                 for (int u = 0; u < U; ++u) {
-                    if (!desc_ready(d[k][u], epoch)) d[k][u] = ld_relaxed_v2(status + (size_t)k * n_tiles + (base - 32 * u));
-                    ok = ok && desc_ready(d[k][u], epoch);
+                    const int p = base - 32 * u;
+                    d[k][u] = (open[k] && p >= 0) ? ld_relaxed_v2(status + (size_t)k * n_tiles + p) : virt;
                 }
-            }
-            bool stopped = false;
+            // all views walk the same windows: a round only counts when every open view can use it
+            bool ok = true;
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const uint32_t incl_mask = __ballot_sync(kFullMask, ((uint32_t)(d[k][u].x >> 32) & 3u) == kFlagIncl);
-                if (!stopped) {
-                    const uint32_t stop = incl_mask ? (uint32_t)__ffs(incl_mask) - 1u : 31u;
-                    if (lane <= stop) {
-                        acc_c[k] += (uint32_t)d[k][u].x;
-                        acc_l[k] += d[k][u].y;
+            for (int k = 0; k < V; ++k)
+#pragma unroll
+                for (int u = 0; u < U; ++u) ok = ok && desc_ready(d[k][u], epoch);
+            if (__all_sync(kFullMask, ok)) {
+                progress = true;
+                bool any_open = false;
+#pragma unroll
+                for (int k = 0; k < V; ++k) {
+                    if (!open[k]) continue;
+                    bool stopped = false;
+#pragma unroll
+                    for (int u = 0; u < U; ++u) {
+                        const uint32_t incl_mask = __ballot_sync(kFullMask, ((uint32_t)(d[k][u].x >> 32) & 3u) == kFlagIncl);
+                        if (!stopped) {
+                            const uint32_t stop = incl_mask ? (uint32_t)__ffs(incl_mask) - 1u : 31u;
+                            if (lane <= stop) {
+                                acc_c[k] += (uint32_t)d[k][u].x;
+                                acc_l[k] += d[k][u].y;
+                            }
+                            stopped = incl_mask != 0u;
+                        }
                     }
-                    stopped = incl_mask != 0u;
+                    open[k] = !stopped;
+                    any_open = any_open || !stopped;
+                }
+                base -= 32 * U;
+                if (!any_open) {  // resolved: publish inclusive values, hand the offsets to the compute warps
+                    const uint32_t buf = res & 1u;
+#pragma unroll
+                    for (int k = 0; k < V; ++k) {
+                        const uint32_t ec = __reduce_add_sync(kFullMask, acc_c[k]);
+                        const uint64_t el = warp_sum_u64(acc_l[k]);
+                        if (lane < kComputeWarps) {
+                            sm.adj_cnt[buf][k][lane] += ec;
+                            sm.adj_len[buf][k][lane] += (uint32_t)el;  // firstIndex is u32 and wraps like the reference's
+                        }
+                        if (lane == 0) {
+                            const uint32_t ic = ec + sm.agg_cnt[buf][k];
+                            const uint64_t il = el + sm.agg_len[buf][k];
+                            if (tile != 0) st_relaxed_v2(status + (size_t)k * n_tiles + tile, tag | (kFlagIncl << 32) | ic, il);
+                            if (tile == n_tiles - 1) {
+                                args.counts[k] = ic;
+                                args.totals[k] = il;
+                            }
+                        }
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&sm.bases[buf]);
+                    ++res;
+                    active = false;
                 }
             }
-            open[k] = !stopped;
-            any_open = any_open || !stopped;
+        } else if (ended) {
+            break;
         }
-        base -= 32 * U;
-    }
-#pragma unroll
-    for (int k = 0; k < V; ++k) {
-        excl_cnt[k] = __reduce_add_sync(kFullMask, acc_c[k]);
-        excl_len[k] = warp_sum_u64(acc_l[k]);
-        if (lane == 0)
-            st_relaxed_v2(status + (size_t)k * n_tiles + tile,
-                          tag | (kFlagIncl << 32) | (uint32_t)(excl_cnt[k] + agg_cnt[k]), excl_len[k] + agg_len[k]);
-    }
-}
-
-// Scan-warp work for one finished tile: per-warp prefixes, look-back, output offsets.
-// Lanes 0..7 stand for the eight compute warps.
-template <int V>
-__device__ __forceinline__ void scan_tile(const FrameArgs& args, FrameSmem& sm, uint32_t buf, uint32_t tile,
-                                          uint32_t lane) {
-    uint32_t agg_cnt[V], excl_cnt[V];
-    uint64_t agg_len[V], excl_len[V];
-    uint32_t rel_cnt[V], rel_len[V];  // (prefix over lower warps) - (start of view k in the warp's combined list)
-    uint32_t vstart_c = 0, vstart_l = 0;
-#pragma unroll
-    for (int k = 0; k < V; ++k) {
-        const uint32_t c = lane < kComputeWarps ? sm.wcnt[buf][k][lane] : 0u;
-        const uint64_t l = lane < kComputeWarps ? sm.wlen[buf][k][lane] : 0ull;
-        uint32_t ic = c;
-        uint64_t il = l;
-#pragma unroll
-        for (int o = 1; o < kComputeWarps; o <<= 1) {
-            const uint32_t tc = __shfl_up_sync(kFullMask, ic, o);
-            const uint64_t tl = __shfl_up_sync(kFullMask, il, o);
-            if (lane >= (uint32_t)o) {
-                ic += tc;
-                il += tl;
-            }
-        }
-        agg_cnt[k] = __shfl_sync(kFullMask, ic, kComputeWarps - 1);
-        agg_len[k] = __shfl_sync(kFullMask, il, kComputeWarps - 1);
-        rel_cnt[k] = (ic - c) - vstart_c;
-        rel_len[k] = (uint32_t)(il - l) - vstart_l;
-        vstart_c += c;
-        vstart_l += (uint32_t)l;
-    }
-    lookback_tile<V>(args.status, args.n_tiles, tile, args.epoch, lane, agg_cnt, agg_len, excl_cnt, excl_len);
-    if (lane < kComputeWarps) {
-#pragma unroll
-        for (int k = 0; k < V; ++k) {
-            sm.adj_cnt[buf][k][lane] = excl_cnt[k] + rel_cnt[k];
-            sm.adj_len[buf][k][lane] = (uint32_t)excl_len[k] + rel_len[k];  // firstIndex is u32 and wraps like the reference's
-        }
-    }
-    if (tile == args.n_tiles - 1 && lane == 0) {
-#pragma unroll
-        for (int k = 0; k < V; ++k) {
-            args.counts[k] = excl_cnt[k] + agg_cnt[k];
-            args.totals[k] = excl_len[k] + agg_len[k];
-        }
+        if (!progress) __nanosleep(100);
     }
 }
 
@@ -314,16 +327,7 @@ __global__ void __maxnreg__(112)
     __syncthreads();
 
     if (warp == kComputeWarps) {
-        // ================================== scan warp ==================================
-        for (uint32_t it = 0;; ++it) {
-            const uint32_t buf = it & 1u;
-            mbar_wait(&sm.done[buf], (it >> 1) & 1u);
-            const uint32_t tile = sm.tile_ring[it & 3u];
-            if (tile >= args.n_tiles) break;  // end marker, passed on by the compute warps
-            scan_tile<V>(args, sm, buf, tile, lane);
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&sm.bases[buf]);
-        }
+        scan_warp<V>(args, sm, lane);
         return;
     }
 
