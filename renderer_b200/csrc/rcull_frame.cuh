@@ -26,6 +26,8 @@ constexpr int kItems = 4;                           // entities per thread per t
 constexpr int kTile = kComputeWarps * 32 * kItems;  // 896 entities
 constexpr int kWarpSpan = 32 * kItems;              // entities owned by one compute warp
 constexpr int kStages = 2;
+constexpr int kMaxBufs = 4;   // survivor bookkeeping ring (tiles whose commands are not emitted yet)
+constexpr int kRing = 8;      // tile-id ring: bookkeeping ring + the tile being loaded + slack
 constexpr int kMaxViews = 8;
 constexpr int kMaxLods = 6;
 constexpr uint32_t kStageBytes = kTile * (16 + 16 + 4);  // pos_scale + rot + mesh
@@ -67,28 +69,32 @@ struct FrameSmem {
     float4 pos_scale[kStages][kTile];
     float4 rot[kStages][kTile];
     uint32_t mesh[kStages][kTile];
-    // Survivor bookkeeping is double-buffered (buffer = tile iteration & 1): the scan warp
-    // resolves the offsets of tile i while the compute warps are one to two tiles ahead.
-    uint32_t slot[2][kTile];  // (mesh, lod) slot of every entity
+    // Survivor bookkeeping is a ring of frame_bufs<V>() tiles (buffer = iteration % bufs): the
+    // scan warp resolves the offsets of tile i while the compute warps run several tiles ahead.
+    uint32_t slot[kMaxBufs][kTile];  // (mesh, lod) slot of every entity
     uint64_t full[kStages];
     uint64_t empty[kStages];
-    uint64_t done[2];   // compute warps -> scan warp: lists and aggregates of a tile are written
-    uint64_t bases[2];  // scan warp -> compute warps: output offsets of that tile are known
-    uint64_t wlen[2][kMaxViews][kComputeWarps];   // per-warp index sums
-    uint32_t wcnt[2][kMaxViews][kComputeWarps];   // per-warp survivor counts
-    uint32_t adj_cnt[2][kMaxViews][kComputeWarps];  // output slot of combined-list entry i of view k: adj_cnt + i
-    uint32_t adj_len[2][kMaxViews][kComputeWarps];  // firstIndex of it: adj_len + exclusive len scan up to i
-    uint64_t agg_len[2][kMaxViews];  // tile aggregates kept between publish and resolve
-    uint32_t agg_cnt[2][kMaxViews];
-    uint32_t tile_ring[4];  // tile id of iteration it at [it & 3]
-    // followed by: uint8_t wlist[2][kComputeWarps][V * kWarpSpan] -- per-warp combined
+    uint64_t done[kMaxBufs];   // compute warps -> scan warp: lists and aggregates of a tile are written
+    uint64_t bases[kMaxBufs];  // scan warp -> compute warps: output offsets of that tile are known
+    uint64_t wlen[kMaxBufs][kMaxViews][kComputeWarps];   // per-warp index sums
+    uint32_t wcnt[kMaxBufs][kMaxViews][kComputeWarps];   // per-warp survivor counts
+    uint32_t adj_cnt[kMaxBufs][kMaxViews][kComputeWarps];  // output slot of combined-list entry i of view k: adj_cnt + i
+    uint32_t adj_len[kMaxBufs][kMaxViews][kComputeWarps];  // firstIndex of it: adj_len + exclusive len scan up to i
+    uint64_t agg_len[kMaxBufs][kMaxViews];  // tile aggregates kept between publish and resolve
+    uint32_t agg_cnt[kMaxBufs][kMaxViews];
+    uint32_t tile_ring[kRing];  // tile id of iteration it at [it % kRing]
+    // followed by: uint8_t wlist[bufs][kComputeWarps][V * kWarpSpan] -- per-warp combined
     // survivor list, view-major, entry = slot in the warp's span (the view follows
     // from the entry's position and the per-view counts)
 };
 
 template <int V>
+__host__ __device__ constexpr int frame_bufs() {
+    return V <= 4 ? 4 : V <= 7 ? 3 : 2;  // what still lets two CTAs share an SM's shared memory
+}
+template <int V>
 constexpr size_t frame_smem_bytes() {
-    return sizeof(FrameSmem) + 2 * V * kTile + 1024;  // + slack to align the base
+    return sizeof(FrameSmem) + frame_bufs<V>() * V * kTile + 1024;  // + slack to align the base
 }
 
 __device__ __forceinline__ FrameSmem& frame_smem(unsigned char* raw) {
@@ -117,6 +123,7 @@ __device__ __forceinline__ bool desc_ready(const ulonglong2& d, uint32_t epoch) 
 template <int V>
 __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, uint32_t lane) {
     constexpr int U = V <= 4 ? 4 : 2;
+    constexpr uint32_t B = frame_bufs<V>();
     const uint32_t epoch = args.epoch, n_tiles = args.n_tiles;
     const uint64_t tag = (uint64_t)epoch << 34;
     const ulonglong2 virt = make_ulonglong2(tag | (kFlagIncl << 32), 0ull);  // tile -1: inclusive prefix 0
@@ -130,8 +137,8 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
     while (true) {
         bool progress = false;
         // ---- publish ----
-        if (!ended && pub - res < 2u && mbar_test(&sm.done[pub & 1u], (pub >> 1) & 1u)) {
-            const uint32_t buf = pub & 1u, t = sm.tile_ring[pub & 3u];
+        if (!ended && pub - res < B && mbar_test(&sm.done[pub % B], (pub / B) & 1u)) {
+            const uint32_t buf = pub % B, t = sm.tile_ring[pub % kRing];
             progress = true;
             if (t >= n_tiles) {
                 ended = true;  // end marker, passed on by the compute warps
@@ -173,7 +180,7 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
         // ---- resolve ----
         if (res < pub) {
             if (!active) {
-                tile = sm.tile_ring[res & 3u];
+                tile = sm.tile_ring[res % kRing];
                 base = (int)tile - 1 - (int)lane;  // this lane's nearest predecessor in the current window
 #pragma unroll
                 for (int k = 0; k < V; ++k) {
@@ -221,7 +228,7 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
                 }
                 base -= 32 * U;
                 if (!any_open) {  // resolved: publish inclusive values, hand the offsets to the compute warps
-                    const uint32_t buf = res & 1u;
+                    const uint32_t buf = res % B;
 #pragma unroll
                     for (int k = 0; k < V; ++k) {
                         const uint32_t ec = __reduce_add_sync(kFullMask, acc_c[k]);
@@ -249,7 +256,7 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
         } else if (ended) {
             break;
         }
-        if (!progress) __nanosleep(100);
+        if (!progress) __nanosleep(200);
     }
 }
 
@@ -318,7 +325,7 @@ __global__ void __maxnreg__(112)
             mbar_init(&sm.empty[s], kComputeWarps);
         }
 #pragma unroll
-        for (int b = 0; b < 2; ++b) {
+        for (int b = 0; b < kMaxBufs; ++b) {
             mbar_init(&sm.done[b], kComputeWarps);
             mbar_init(&sm.bases[b], 1);
         }
@@ -350,7 +357,7 @@ __global__ void __maxnreg__(112)
     auto claim_tile = [&](uint32_t for_it) {
         const uint32_t stage = for_it & 1u;
         const uint32_t t = atomicAdd(args.ticket, 1u) - args.ticket_base;
-        sm.tile_ring[for_it & 3u] = t;
+        sm.tile_ring[for_it % kRing] = t;
         uint64_t* bar = &sm.full[stage];
         if (t < args.n_tiles) {
             fence_proxy_async();
@@ -366,18 +373,25 @@ __global__ void __maxnreg__(112)
     if (producer) claim_tile(0);
 
     uint32_t it = 0;
-    uint32_t base_of0 = 0, base_of1 = 0;  // tile_base of the tile pending in each bookkeeping buffer
+    constexpr uint32_t B = frame_bufs<V>();
+    uint32_t emitted = 0;  // iterations [emitted, it) of this CTA still have their commands pending
+    auto emit_next = [&]() {
+        const uint32_t b = emitted % B;
+        emit_pending<V>(args, sm, wlist_base + b * (V * kTile), b, sm.tile_ring[emitted % kRing] * kTile, warp, lane);
+        ++emitted;
+    };
     for (;; ++it) {
-        const uint32_t stage = it & 1u;  // input stage and bookkeeping buffer of this tile
+        const uint32_t stage = it & 1u;  // input stage of this tile
+        const uint32_t buf = it % B;     // bookkeeping buffer of this tile
         if (producer && more) {
             if (it >= 1) mbar_wait(&sm.empty[stage ^ 1u], ((it - 1) >> 1) & 1u);
             claim_tile(it + 1);
         }
         mbar_wait(&sm.full[stage], (it >> 1) & 1u);
-        const uint32_t tile = sm.tile_ring[it & 3u];
+        const uint32_t tile = sm.tile_ring[it % kRing];
         if (tile >= args.n_tiles) break;
         const uint32_t tile_base = tile * kTile;
-        uint8_t* const wlist = wlist_base + stage * (V * kTile);
+        uint8_t* const wlist = wlist_base + buf * (V * kTile);
 
         float4 ps[kItems], q[kItems];
         uint32_t mid[kItems];
@@ -451,18 +465,24 @@ __global__ void __maxnreg__(112)
             slot[j] = mid[j] * kMaxLods + ((d2 > args.lod_d2_max && n_lods > 1u) ? 1u : 0u);
         }
 
-        // The tile that used this bookkeeping buffer two iterations ago has had more than a
-        // whole tile time for its look-back: emit its commands, which frees the buffer.
-        if (it >= 2) {
-            mbar_wait(&sm.bases[stage], ((it - 2) >> 1) & 1u);
-            emit_pending<V>(args, sm, wlist, stage, stage ? base_of1 : base_of0, warp, lane);
-            __syncwarp();
+        // Emit the commands of earlier tiles whose output offsets the scan warp has resolved
+        // by now; only the tile that owns this iteration's bookkeeping buffer is waited for.
+        while (emitted < it) {
+            const uint32_t b = emitted % B, parity = (emitted / B) & 1u;
+            if (emitted + B <= it) {
+                mbar_wait(&sm.bases[b], parity);
+            } else {
+                uint32_t ready = lane == 0 ? (uint32_t)mbar_test(&sm.bases[b], parity) : 0u;
+                ready = __shfl_sync(kFullMask, ready, 0);
+                if (!ready) break;
+            }
+            emit_next();
         }
-        if (stage) base_of1 = tile_base; else base_of0 = tile_base;
+        __syncwarp();
         uint32_t len_lo[kItems], len_hi[kItems];
 #pragma unroll
         for (int j = 0; j < kItems; ++j) {
-            sm.slot[stage][e0 + 32 * j] = slot[j];
+            sm.slot[buf][e0 + 32 * j] = slot[j];
             const uint32_t len = __ldg(args.lod_tab + slot[j]).x;
             len_lo[j] = len & 0xffffu;
             len_hi[j] = len >> 16;
@@ -505,27 +525,23 @@ __global__ void __maxnreg__(112)
             lo = __reduce_add_sync(kFullMask, lo);  // 128 x 16-bit pieces: no overflow
             hi = __reduce_add_sync(kFullMask, hi);
             if (lane == 0) {
-                sm.wcnt[stage][k][warp] = wc;
-                sm.wlen[stage][k][warp] = (uint64_t)lo + ((uint64_t)hi << 16);
+                sm.wcnt[buf][k][warp] = wc;
+                sm.wlen[buf][k][warp] = (uint64_t)lo + ((uint64_t)hi << 16);
             }
             woff += wc;
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.done[stage]);
+        if (lane == 0) mbar_arrive(&sm.done[buf]);
     }
-    // up to two tiles of this CTA are still pending: iterations it-2 and it-1, in that order
-#pragma unroll
-    for (int back = 2; back >= 1; --back) {
-        if (it >= (uint32_t)back) {
-            const uint32_t pit = it - back, b = pit & 1u;
-            mbar_wait(&sm.bases[b], (pit >> 1) & 1u);
-            emit_pending<V>(args, sm, wlist_base + b * (V * kTile), b, b ? base_of1 : base_of0, warp, lane);
-        }
+    // the last tiles of this CTA are still pending
+    while (emitted < it) {
+        mbar_wait(&sm.bases[emitted % B], (emitted / B) & 1u);
+        emit_next();
     }
     // pass the end marker on to the scan warp (after the waits above, so that this barrier
     // never runs two phases ahead of its reader)
     __syncwarp();
-    if (lane == 0) mbar_arrive(&sm.done[it & 1u]);
+    if (lane == 0) mbar_arrive(&sm.done[it % B]);
     if (lane == 0) bulk_wait_read0();
 }
 
