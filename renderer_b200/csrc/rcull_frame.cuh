@@ -489,8 +489,9 @@ __global__ void __maxnreg__(112)
         }
 
         // A3 per view: planes outer, the thread's 4 entities inner
+        // (the view loop stays rolled: unrolled, the kernel outgrows the instruction cache)
         uint32_t woff = 0;  // start of view k in the warp's combined list
-#pragma unroll
+#pragma unroll 1
         for (int k = 0; k < V; ++k) {
             bool outside[kItems];
 #pragma unroll
