@@ -367,8 +367,17 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
         a.flags[v] = o.flags[v];
         a.cmds[v] = o.cmds[v];
         a.visible[v] = o.visible[v];
-        for (int p = 0; p < 6; ++p)
-            a.planes[v][p] = make_float4(views[v].planes[p][0], views[v].planes[p][1], views[v].planes[p][2], views[v].planes[p][3]);
+        for (int p = 0; p < 6; ++p) {
+            const float* pl = views[v].planes[p];
+            PlaneC& pc = a.planes[v][p];
+            pc.ax = make_float2(fabsf(pl[0]), fabsf(pl[0]));
+            pc.ay = make_float2(fabsf(pl[1]), fabsf(pl[1]));
+            pc.az = make_float2(fabsf(pl[2]), fabsf(pl[2]));
+            pc.px = make_float2(pl[0], pl[0]);
+            pc.py = make_float2(pl[1], pl[1]);
+            pc.pz = make_float2(pl[2], pl[2]);
+            pc.pw = pl[3];
+        }
     }
     a.counts = o.counts;
     a.totals = o.totals;

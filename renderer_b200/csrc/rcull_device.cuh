@@ -137,6 +137,22 @@ __device__ __forceinline__ uint32_t warp_incl_scan_u32(uint32_t v, uint32_t lane
     return v;
 }
 
+// ---- packed FP32 (Blackwell FMUL2 / FADD2): two IEEE-rounded operations per instruction ----
+__device__ __forceinline__ float2 mul2_rn(float2 a, float2 b) {
+    unsigned long long r;
+    asm("mul.rn.f32x2 %0, %1, %2;"
+        : "=l"(r)
+        : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)));
+    return *reinterpret_cast<float2*>(&r);
+}
+__device__ __forceinline__ float2 add2_rn(float2 a, float2 b) {
+    unsigned long long r;
+    asm("add.rn.f32x2 %0, %1, %2;"
+        : "=l"(r)
+        : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)));
+    return *reinterpret_cast<float2*>(&r);
+}
+
 // ---- per-entity arithmetic (operation order = SURVEY 8a; compiled -fmad=false) ----
 struct Mat34 {  // upper 3 rows of the column-major model matrix; row 3 is (0,0,0,1)
     float m00, m10, m20;  // column 0

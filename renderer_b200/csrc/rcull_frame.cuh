@@ -36,6 +36,14 @@ constexpr int kMatBoxBytes = 32 * 64;                    // 32 model matrices = 
 // Tile descriptor: x = epoch:30 | flag:2 | count:32, y = index sum.
 constexpr uint64_t kFlagAgg = 1, kFlagIncl = 2;
 
+// One frustum plane, laid out for the packed (two entities per instruction) products:
+// every multiplicand is stored twice so that a 64-bit uniform load yields the pair.
+struct PlaneC {
+    float2 ax, ay, az;  // |p.x|, |p.y|, |p.z|
+    float2 px, py, pz;
+    float pw, pad0, pad1, pad2;
+};
+
 struct FrameArgs {
     const float4* pos_scale;
     const float4* rot;
@@ -60,7 +68,7 @@ struct FrameArgs {
     uint32_t cap_visible;
     float cam[3];
     float lod_d2_max;  // lod 1 iff |cam-pos|^2 > lod_d2_max  (== sqrt(d2) > lod_distance)
-    float4 planes[kMaxViews][6];
+    PlaneC planes[kMaxViews][6];
 };
 
 struct FrameSmem {
@@ -465,6 +473,14 @@ __global__ void __maxnreg__(112)
             slot[j] = mid[j] * kMaxLods + ((d2 > args.lod_d2_max && n_lods > 1u) ? 1u : 0u);
         }
 
+        float2 c2x[kItems / 2], c2y[kItems / 2], c2z[kItems / 2], h2x[kItems / 2], h2y[kItems / 2], h2z[kItems / 2];
+#pragma unroll
+        for (int i = 0; i < kItems / 2; ++i) {
+            c2x[i] = make_float2(cx[2 * i], cx[2 * i + 1]); h2x[i] = make_float2(hx[2 * i], hx[2 * i + 1]);
+            c2y[i] = make_float2(cy[2 * i], cy[2 * i + 1]); h2y[i] = make_float2(hy[2 * i], hy[2 * i + 1]);
+            c2z[i] = make_float2(cz[2 * i], cz[2 * i + 1]); h2z[i] = make_float2(hz[2 * i], hz[2 * i + 1]);
+        }
+
         // Emit the commands of earlier tiles whose output offsets the scan warp has resolved
         // by now; only the tile that owns this iteration's bookkeeping buffer is waited for.
         while (emitted < it) {
@@ -498,16 +514,23 @@ __global__ void __maxnreg__(112)
             for (int j = 0; j < kItems; ++j) outside[j] = false;
 #pragma unroll
             for (int p = 0; p < 6; ++p) {
-                const float4 pl = args.planes[k][p];
-                const float ax = fabsf(pl.x), ay = fabsf(pl.y), az = fabsf(pl.z);
+                const PlaneC& pc = args.planes[k][p];
 #pragma unroll
-                for (int j = 0; j < kItems; ++j) {
-                    const float ee = __fadd_rn(__fadd_rn(__fmul_rn(hx[j], ax), __fmul_rn(hy[j], ay)), __fmul_rn(hz[j], az));
-                    const float s = __fadd_rn(__fadd_rn(__fmul_rn(pl.x, cx[j]), __fmul_rn(pl.z, cz[j])),
-                                              __fadd_rn(__fmul_rn(pl.y, cy[j]), pl.w));
+                for (int i = 0; i < kItems / 2; ++i) {
+                    // Products of two entities per FMUL2; every sum that consumes a packed product
+                    // is a scalar FADD, so ptxas has no packed mul+add pair to contract into FFMA2
+                    // (it does that even under --fmad=false; tests/test_sass.py checks the SASS).
+                    const float2 m1 = mul2_rn(h2x[i], pc.ax), m2 = mul2_rn(h2y[i], pc.ay), m3 = mul2_rn(h2z[i], pc.az);
+                    const float e0 = __fadd_rn(__fadd_rn(m1.x, m2.x), m3.x);
+                    const float e1 = __fadd_rn(__fadd_rn(m1.y, m2.y), m3.y);
+                    const float2 p1 = mul2_rn(c2x[i], pc.px), p3 = mul2_rn(c2z[i], pc.pz), p2 = mul2_rn(c2y[i], pc.py);
+                    const float2 a = make_float2(__fadd_rn(p1.x, p3.x), __fadd_rn(p1.y, p3.y));
+                    const float2 b = make_float2(__fadd_rn(p2.x, pc.pw), __fadd_rn(p2.y, pc.pw));
+                    const float2 s = add2_rn(a, b);
                     // (s - e > 0.0) == (s > e): the rounded difference of two floats keeps its sign,
                     // and both forms are false for NaN and for inf - inf
-                    outside[j] = outside[j] || (s > ee);
+                    outside[2 * i] = outside[2 * i] || (s.x > e0);
+                    outside[2 * i + 1] = outside[2 * i + 1] || (s.y > e1);
                 }
             }
             uint32_t wc = 0, lo = 0, hi = 0;
