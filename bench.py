@@ -44,24 +44,46 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons DURING the timed region."""
+    """SM clock and throttle reasons DURING the timed region.  NVML is polled in-process
+    (the timed region of the 16 M workload lasts tens of milliseconds: too short for an
+    nvidia-smi subprocess); nvidia-smi is the fallback if NVML cannot be loaded."""
 
-    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, index: int):
         self.index, self.samples, self._stop = index, [], threading.Event()
         self._t = threading.Thread(target=self._run, daemon=True)
+        self.max_mhz = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+            self.how = "nvml"
+        except Exception:
+            self._nv = None
+            self.how = "nvidia-smi"
 
     def _run(self):
         while not self._stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([x.strip() for x in out.split(",")])
+                if self._nv is not None:
+                    mhz = float(self._nv.nvmlDeviceGetClockInfo(self._h, self._nv.NVML_CLOCK_SM))
+                    mask = int(self._nv.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+                    self.samples.append((mhz, mask))
+                    self._stop.wait(0.0005)
+                else:
+                    q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+                    out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                         capture_output=True, text=True, timeout=5).stdout.strip().split(",")
+                    bits = [0x8, 0x40, 0x20, 0x4]
+                    mask = sum(b for b, x in zip(bits, out[2:6]) if x.strip().lower().startswith("active"))
+                    self.max_mhz = float(out[1])
+                    self.samples.append((float(out[0]), mask))
             except Exception:
-                pass
-            self._stop.wait(0.05)
+                self._stop.wait(0.01)
 
     def __enter__(self):
         self._t.start()
@@ -72,12 +94,12 @@ class ClockSampler:
         self._t.join(timeout=6)
 
     def summary(self):
-        sm = [float(s[0]) for s in self.samples if s and s[0].replace(".", "").isdigit()]
-        mx = [float(s[1]) for s in self.samples if len(s) > 1 and s[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for s in self.samples for i in range(4) if len(s) > 2 + i and s[2 + i].lower().startswith("active")})
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.samples)}
+        sm = [s[0] for s in self.samples]
+        mask = 0
+        for s in self.samples:
+            mask |= s[1]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(v for k, v in self.REASONS.items() if mask & k), "samples": len(self.samples), "how": self.how}
 
 
 def cpu_baseline(wl, steps: int, warmup: int, threads: int):

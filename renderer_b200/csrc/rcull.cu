@@ -18,6 +18,7 @@ using namespace rcull;
 
 static_assert(sizeof(rcull_mesh) == 80, "rcull_mesh layout");
 static_assert(sizeof(rcull_draw_cmd) == 20, "VkDrawIndexedIndirectCommand stride");
+static_assert(sizeof(rcull_config) == 48 && sizeof(rcull_view) == 96, "rcull_config / rcull_view layout");
 static_assert(RCULL_MAX_VIEWS == kMaxViews && RCULL_MAX_LODS == kMaxLods, "header/kernel constants");
 
 namespace {

@@ -68,7 +68,8 @@ class ShardMerger:
         self.merged_cmds = [torch.empty(capacity * 5, dtype=torch.int32, device=device) for _ in range(n_views)]
         self.merged_visible = [torch.empty(capacity, dtype=torch.int32, device=device) for _ in range(n_views)]
         self._meta = torch.zeros(2 * n_views, dtype=torch.int64, device=device)
-        self._meta_all = torch.zeros(self.world, 2 * n_views, dtype=torch.int64, device=device)
+        self._meta_flat = torch.zeros(self.world * 2 * n_views, dtype=torch.int64, device=device)  # gloo wants a flat output
+        self._meta_all = self._meta_flat.view(self.world, 2 * n_views)
         self.plan: MergePlan | None = None
         self.bytes_received = 0
 
@@ -79,7 +80,7 @@ class ShardMerger:
         v = self.n_views
         self._meta[:v] = torch.as_tensor(counts_dev, device=self.device)[:v].to(torch.int64)
         self._meta[v:] = torch.as_tensor(totals_dev, device=self.device)[:v].to(torch.int64)
-        self.dist.all_gather_into_tensor(self._meta_all, self._meta, group=self.group)
+        self.dist.all_gather_into_tensor(self._meta_flat, self._meta, group=self.group)
         m = self._meta_all.cpu().numpy().astype(np.uint64)
         self.plan = plan_merge(m[:, :v], m[:, v:])
         if int(self.plan.counts.max(initial=0)) > self.capacity:

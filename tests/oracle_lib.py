@@ -52,49 +52,59 @@ def f32(a):
     return np.ascontiguousarray(a, dtype=np.float32)
 
 
+# NOTE: p() takes a raw address; every temporary is bound to a name first so that it
+# stays alive across the call.
 def model_matrix(pos, quat, scale):
     m = np.empty(16, np.float32)
-    lib().oracle_model_matrix(p(f32(pos)), p(f32(quat)), float(scale), p(m))
+    a, b = f32(pos), f32(quat)
+    lib().oracle_model_matrix(p(a), p(b), float(scale), p(m))
     return m
 
 
 def aabb(m, mesh_min, mesh_max):
     lo, hi = np.empty(3, np.float32), np.empty(3, np.float32)
-    lib().oracle_aabb(p(f32(m)), p(f32(mesh_min)), p(f32(mesh_max)), p(lo), p(hi))
+    a, b, c = f32(m), f32(mesh_min), f32(mesh_max)
+    lib().oracle_aabb(p(a), p(b), p(c), p(lo), p(hi))
     return lo, hi
 
 
 def coarse_culled(mins, maxs, planes):
-    return bool(lib().oracle_coarse_culled(p(f32(mins)), p(f32(maxs)), p(f32(planes))))
+    a, b, c = f32(mins), f32(maxs), f32(planes)
+    return bool(lib().oracle_coarse_culled(p(a), p(b), p(c)))
 
 
 def pick_lod(cam, pos, n_lods, lod_distance=10.0):
-    return int(lib().oracle_pick_lod(p(f32(cam)), p(f32(pos)), n_lods, lod_distance))
+    a, b = f32(cam), f32(pos)
+    return int(lib().oracle_pick_lod(p(a), p(b), n_lods, lod_distance))
 
 
 def frustum_planes(pv):
     out = np.empty((6, 4), np.float32)
-    lib().oracle_frustum_planes(p(f32(pv)), p(out))
+    a = f32(pv)
+    lib().oracle_frustum_planes(p(a), p(out))
     return out
 
 
 def project_camera(aspect, pos, rot):
     proj, view, pv = (np.empty(16, np.float32) for _ in range(3))
     planes = np.empty((6, 4), np.float32)
-    lib().oracle_project_camera(aspect, p(f32(pos)), p(f32(rot)), p(proj), p(view), p(pv), p(planes))
+    a, b = f32(pos), f32(rot)
+    lib().oracle_project_camera(aspect, p(a), p(b), p(proj), p(view), p(pv), p(planes))
     return proj, view, pv, planes
 
 
 def light_view(pos, rot):
     proj, view, pv = (np.empty(16, np.float32) for _ in range(3))
     planes = np.empty((6, 4), np.float32)
-    lib().oracle_light_view(p(f32(pos)), p(f32(rot)), p(proj), p(view), p(pv), p(planes))
+    a, b = f32(pos), f32(rot)
+    lib().oracle_light_view(p(a), p(b), p(proj), p(view), p(pv), p(planes))
     return proj, view, pv, planes
 
 
 def quat_look_at_lh(direction, up=(0, 1, 0)):
     q = np.empty(4, np.float32)
-    lib().oracle_quat_look_at_lh(p(f32(direction)), p(f32(up)), p(q))
+    a, b = f32(direction), f32(up)
+    lib().oracle_quat_look_at_lh(p(a), p(b), p(q))
     return q
 
 
@@ -121,8 +131,9 @@ def frame(pos, quat, scale, mesh_id, meshes, planes, cam_pos, lod_distance=10.0,
         "visible": np.empty((v, max(n, 1)), np.uint32) if "visible" in want else None,
     }
     counts, totals = np.zeros(v, np.uint32), np.zeros(v, np.uint64)
+    cam = f32(cam_pos)
     rc = lib().oracle_frame(p(pos), p(quat), p(scale), p(mesh_id), n, p(meshes), len(meshes), p(planes), v,
-                            p(f32(cam_pos)), lod_distance, draw_index_base, p(out["model"]), p(out["aabb"]),
+                            p(cam), lod_distance, draw_index_base, p(out["model"]), p(out["aabb"]),
                             p(out["flags"]), p(out["cmds"]), p(out["visible"]), p(counts), p(totals), n_threads)
     if rc != 0:
         raise ValueError("oracle_frame: mesh id out of range")
@@ -141,8 +152,9 @@ def emit_per_mesh(pos, mesh_id, flags, meshes, cam_pos, lod_distance=10.0, draw_
     cmds = np.empty(len(meshes) * 6, CMD_DTYPE)
     visible = np.empty(max(n, 1), np.uint32)
     count, inst = _u32(0), _u64(0)
-    rc = lib().oracle_emit_per_mesh(p(pos), p(np.ascontiguousarray(mesh_id, np.uint32)), p(np.ascontiguousarray(flags, np.uint8)),
-                                    n, p(meshes), len(meshes), p(f32(cam_pos)), lod_distance, draw_index_base,
+    mesh_id, flags, cam = np.ascontiguousarray(mesh_id, np.uint32), np.ascontiguousarray(flags, np.uint8), f32(cam_pos)
+    rc = lib().oracle_emit_per_mesh(p(pos), p(mesh_id), p(flags),
+                                    n, p(meshes), len(meshes), p(cam), lod_distance, draw_index_base,
                                     p(cmds), p(visible), C.byref(count), C.byref(inst))
     if rc != 0:
         raise ValueError("oracle_emit_per_mesh failed")

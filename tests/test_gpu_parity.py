@@ -186,3 +186,111 @@ def test_device_generator_matches_host_twin():
         cb, tb = b.counts()
         assert ca[0] == cb[0] and ta[0] == tb[0]
         assert np.array_equal(a.cmds(0, int(ca[0])), b.cmds(0, int(cb[0])))
+
+
+def test_golden_vectors_config1():
+    """The committed fixture (tests/golden/config1_10k.npz, made by make_golden.py)."""
+    import os
+
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "config1_10k.npz"))
+    n, n_views = int(g["n"]), len(g["views"])
+    ps, rot, mesh = scene.synth_entities(int(g["seed"]), 0, n, float(g["half_box"]))
+    with CullContext(n, max_views=n_views, max_meshes=len(g["meshes"]), materialize_aabb=True, materialize_flags=True) as ctx:
+        ctx.set_mesh_table(g["meshes"])
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(g["views"], g["cam_pos"])
+        counts, totals = ctx.counts()
+        assert np.array_equal(counts[:n_views], g["counts"]) and np.array_equal(totals[:n_views], g["totals"])
+        assert np.array_equal(ctx.model(64), g["model_head"]) and np.array_equal(ctx.aabb(64), g["aabb_head"])
+        flags = np.stack([ctx.flags(k, n) for k in range(n_views)])
+        assert np.array_equal(np.packbits(flags, axis=1), g["flags_packed"])
+        for k in range(n_views):
+            assert np.array_equal(ctx.visible(k, int(counts[k])), g[f"visible_{k}"])
+            assert np.array_equal(ctx.cmds(k, int(counts[k])), g[f"cmds_{k}"])
+
+
+def _list_properties(ctx, k, count, total, meshes, base=0):
+    """Size-independent checks of one view's draw list (used where the oracle is too slow)."""
+    vis = ctx.visible(k, count)
+    cmds = ctx.cmds(k, count)
+    assert np.all(np.diff(vis.astype(np.int64)) > 0), "visible indices not strictly ascending"
+    assert np.array_equal(cmds["firstInstance"], vis)
+    assert np.all(cmds["instanceCount"] == 1)
+    ic = cmds["indexCount"].astype(np.uint64)
+    first = np.concatenate([[0], np.cumsum(ic)[:-1]]).astype(np.uint64) & np.uint64(0xFFFFFFFF)
+    assert np.array_equal(cmds["firstIndex"], first.astype(np.uint32)), "firstIndex is not the running sum of indexCount"
+    assert int(ic.sum()) == int(total)
+    lens = set(int(x) for x in meshes["lod"][:, :, 1].reshape(-1))
+    assert set(np.unique(cmds["indexCount"]).tolist()) <= lens
+    return vis
+
+
+def test_config3_16m_five_views_properties_and_sampled_oracle():
+    """BASELINE configs[2] at full size: list properties + exact oracle comparison on slices."""
+    n, n_views = 16 * 1024 * 1024, 5
+    views = scene.scene_views(n_views)
+    with CullContext(n, max_views=n_views, max_meshes=len(MESHES)) as ctx:
+        ctx.set_mesh_table(MESHES)
+        ctx.synth_entities(scene.SEED, 0, n, 600.0, len(MESHES))
+        ctx.frame(views, scene.CAMERA_POS)
+        counts, totals = ctx.counts()
+        vis = [_list_properties(ctx, k, int(counts[k]), totals[k], MESHES) for k in range(n_views)]
+        # second frame on the same context: identical (idempotence, epoch/ticket reuse)
+        ctx.frame(views, scene.CAMERA_POS)
+        c2, t2 = ctx.counts()
+        assert np.array_equal(c2, counts) and np.array_equal(t2, totals)
+        # exact visible sets on three slices, against the oracle
+        for lo in (0, 7_654_321, n - 300_000):
+            m = 300_000
+            ps, rot, mesh = scene.synth_entities(scene.SEED, lo, m, 600.0)
+            pos, quat, scale = scene.to_components(ps, rot)
+            ref = O.frame(pos, quat, scale, mesh, MESHES, views, scene.CAMERA_POS, draw_index_base=lo, n_threads=8,
+                          want=("model", "visible"))
+            assert np.array_equal(ctx.model(m, first=lo), ref["model"])
+            for k in range(n_views):
+                got = vis[k][(vis[k] >= lo) & (vis[k] < lo + m)]
+                assert np.array_equal(got, ref["visible"][k]), (lo, k)
+
+
+def test_range_shards_merge_to_the_single_gpu_lists():
+    """SURVEY 8e on one device: two contexts own the two halves of the scene, each rebases
+    its lists into its slot of a merged buffer (rcull_rebase_into); merged == unsharded."""
+    import torch
+
+    from renderer_b200.shard import plan_merge, shard_range
+
+    n, n_views, world = 200_001, 3, 2
+    views = scene.scene_views(n_views)
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, 60.0)
+    with CullContext(n, max_views=n_views, max_meshes=len(MESHES)) as whole:
+        whole.set_mesh_table(MESHES)
+        whole.upload_entities(ps, rot, mesh)
+        whole.frame(views, scene.CAMERA_POS)
+        wc, wt = whole.counts()
+        want_cmds = [whole.cmds(k, int(wc[k])) for k in range(n_views)]
+        want_vis = [whole.visible(k, int(wc[k])) for k in range(n_views)]
+    ctxs, counts, totals = [], [], []
+    try:
+        for r in range(world):
+            lo, hi = shard_range(n, world, r)
+            c = CullContext(hi - lo, max_views=n_views, max_meshes=len(MESHES))
+            c.set_mesh_table(MESHES)
+            c.upload_entities(ps[lo:hi], rot[lo:hi], mesh[lo:hi])
+            c.frame(views, scene.CAMERA_POS, draw_index_base=lo)
+            cc, tt = c.counts()
+            ctxs.append(c), counts.append(cc[:n_views]), totals.append(tt[:n_views])
+        plan = plan_merge(np.stack(counts), np.stack(totals))
+        assert np.array_equal(plan.counts, wc[:n_views]) and np.array_equal(plan.totals, wt[:n_views])
+        for k in range(n_views):
+            m_cmds = torch.zeros(int(plan.counts[k]) * 5 + 5, dtype=torch.int32, device="cuda")
+            m_vis = torch.zeros(int(plan.counts[k]) + 1, dtype=torch.int32, device="cuda")
+            for r in range(world):
+                off = int(plan.count_prefix[r, k])
+                ctxs[r].rebase_into(k, int(plan.index_prefix[r, k]) & 0xFFFFFFFF, m_cmds.data_ptr() + off * 20, m_vis.data_ptr() + off * 4)
+            torch.cuda.synchronize()
+            got_cmds = m_cmds.cpu().numpy()[: int(plan.counts[k]) * 5].view(np.uint32)
+            assert np.array_equal(got_cmds, want_cmds[k].view(np.uint32).reshape(-1)), k
+            assert np.array_equal(m_vis.cpu().numpy()[: int(plan.counts[k])].view(np.uint32), want_vis[k]), k
+    finally:
+        for c in ctxs:
+            c.destroy()

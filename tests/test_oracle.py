@@ -1,0 +1,181 @@
+"""CPU tests of the oracle (oracle/rcull_oracle.c): hand-checkable known answers,
+an independent numpy restatement of the same operation order, and the committed
+golden vectors.  The reference holds no test or fixture for this path,
+so these are what pins the oracle; see DESIGN.md "parity unpinned"."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from renderer_b200 import scene
+
+F = np.float32
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "config1_10k.npz")
+
+
+# ---- A1: model matrix (src/ecs.rs:61-62) -------------------------------------------
+def test_model_matrix_identity_rotation_is_scale_and_translation():
+    m = O.model_matrix([1.5, -2.0, 3.25], [0, 0, 0, 1], 2.0).reshape(4, 4).T  # row, col
+    want = np.array([[2, 0, 0, 1.5], [0, 2, 0, -2.0], [0, 0, 2, 3.25], [0, 0, 0, 1]], F)
+    assert np.array_equal(m, want)
+
+
+def test_model_matrix_quarter_turn_about_y():
+    h = F(np.sqrt(0.5))
+    m = O.model_matrix([0, 0, 0], [0, h, 0, h], 1.0).reshape(4, 4).T
+    # +90 degrees about Y maps x -> -z and z -> x
+    assert np.allclose(m @ np.array([1, 0, 0, 1], F), [0, 0, -1, 1], atol=1e-6)
+    assert np.allclose(m @ np.array([0, 0, 1, 1], F), [1, 0, 0, 1], atol=1e-6)
+    assert np.array_equal(m[3], [0, 0, 0, 1])
+
+
+def _np_model(ps, q):
+    """Independent numpy float32 restatement of row A1 (vectorised over entities)."""
+    i, j, k, w, s = q[:, 0], q[:, 1], q[:, 2], q[:, 3], ps[:, 3]
+    ww, ii, jj, kk = w * w, i * i, j * j, k * k
+    ij, wk, wj = i * j * F(2), w * k * F(2), w * j * F(2)
+    ik, jk, wi = i * k * F(2), j * k * F(2), w * i * F(2)
+    m = np.zeros((len(s), 16), F)
+    m[:, 0] = (ww + ii - jj - kk) * s; m[:, 4] = (ij - wk) * s; m[:, 8] = (wj + ik) * s
+    m[:, 1] = (wk + ij) * s; m[:, 5] = (ww - ii + jj - kk) * s; m[:, 9] = (jk - wi) * s
+    m[:, 2] = (ik - wj) * s; m[:, 6] = (wi + jk) * s; m[:, 10] = (ww - ii - jj + kk) * s
+    m[:, 12:15] = ps[:, :3]
+    m[:, 15] = 1
+    return m
+
+
+def _np_aabb(m, mn, mx):
+    """Row A2 with all 8 corners, corner order of src/ecs.rs:151-159."""
+    lo = np.full((len(m), 3), np.finfo(F).max, F)
+    hi = np.full((len(m), 3), np.finfo(F).min, F)
+    for cy in (mn[:, 1], mx[:, 1]):
+        for cz in (mn[:, 2], mx[:, 2]):
+            for cx in (mn[:, 0], mx[:, 0]):
+                for a in range(3):
+                    v = m[:, a] * cx
+                    v = m[:, 4 + a] * cy + v
+                    v = m[:, 8 + a] * cz + v
+                    v = m[:, 12 + a] * F(1) + v
+                    v = v / F(1)
+                    lo[:, a] = np.minimum(lo[:, a], v)
+                    hi[:, a] = np.maximum(hi[:, a], v)
+    c, h = (hi + lo) / F(2), (hi - lo) / F(2)
+    return c - h, c + h
+
+
+def _np_culled(mins, maxs, planes):
+    h, c = (maxs - mins) * F(0.5), (mins + maxs) * F(0.5)
+    out = np.zeros(len(h), bool)
+    for p in planes:
+        a = np.abs(p[:3])
+        e = (h[:, 0] * a[0] + h[:, 1] * a[1]) + h[:, 2] * a[2]
+        s = (p[0] * c[:, 0] + p[2] * c[:, 2]) + (p[1] * c[:, 1] + p[3] * F(1))
+        out |= (s - e) > 0
+    return out
+
+
+def test_numpy_restatement_matches_c_oracle_on_config1():
+    n = 10_000
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, 60.0)
+    meshes = scene.synth_mesh_table()
+    views = scene.scene_views(5)
+    pos, quat, scale = scene.to_components(ps, rot)
+    ref = O.frame(pos, quat, scale, mesh, meshes, views, scene.CAMERA_POS)
+    m = _np_model(ps, rot)
+    assert np.array_equal(m, ref["model"])
+    mins, maxs = _np_aabb(m, meshes["aabb_min"][mesh], meshes["aabb_max"][mesh])
+    assert np.array_equal(np.concatenate([mins, maxs], axis=1), ref["aabb"])
+    for k in range(5):
+        culled = _np_culled(mins, maxs, views[k])
+        assert np.array_equal(culled.astype(np.uint8), ref["flags"][k])
+        vis = np.nonzero(~culled)[0].astype(np.uint32)
+        assert np.array_equal(vis, ref["visible"][k])
+        d = scene.CAMERA_POS[None, :] - ps[vis, :3]
+        dist = np.sqrt((d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2])
+        lod = ((dist > F(10.0)) & (meshes["n_lods"][mesh[vis]] > 1)).astype(np.int64)
+        length = meshes["lod"][mesh[vis], lod, 1].astype(np.uint64)
+        cmds = ref["cmds"][k]
+        assert np.array_equal(cmds["indexCount"], length.astype(np.uint32))
+        first = np.concatenate([[0], np.cumsum(length)[:-1]]).astype(np.uint64) & np.uint64(0xFFFFFFFF)
+        assert np.array_equal(cmds["firstIndex"], first.astype(np.uint32))
+        assert np.array_equal(cmds["firstInstance"], vis)
+        assert np.all(cmds["instanceCount"] == 1)
+        assert np.array_equal(cmds["vertexOffset"], meshes["vertex_offset"][mesh[vis]])
+        assert ref["totals"][k] == length.sum()
+
+
+# ---- A3: plane test boundary (cull_pipeline.rs:113, strict >) ------------------------
+def test_box_touching_a_plane_is_visible():
+    planes = np.zeros((6, 4), F)
+    planes[:, 3] = -1.0  # five planes that never cull
+    planes[0] = [1, 0, 0, -2]  # outside iff x - 2 > e
+    assert not O.coarse_culled([0, -1, -1], [2, 1, 1], planes)  # s - e = -1 - 1
+    assert not O.coarse_culled([2, -1, -1], [4, 1, 1], planes)  # s - e = 1 - 1 = 0: NOT culled
+    assert O.coarse_culled(np.nextafter(F(2), F(3)) + np.array([0, -1, -1], F), [4, 1, 1], planes)
+
+
+def test_pick_lod_threshold_is_strict():
+    cam = [0, 0, 0]
+    assert O.pick_lod(cam, [10, 0, 0], 3) == 0  # distance == 10: LOD 0 (helpers.rs:6 uses >)
+    assert O.pick_lod(cam, [np.nextafter(F(10), F(11)), 0, 0], 3) == 1
+    assert O.pick_lod(cam, [500, 0, 0], 1) == 0  # single LOD
+
+
+# ---- A5: planes ---------------------------------------------------------------------
+def test_default_camera_sees_forward_only():
+    planes = scene.camera_view()
+    inside = lambda p: not O.coarse_culled(np.array(p, F) - F(0.1), np.array(p, F) + F(0.1), planes)
+    assert inside([0, 1, 12])  # in front of (0,1,2) looking down +z
+    assert not inside([0, 1, -10])  # behind
+    assert not inside([0, 1, 150])  # past far = 100
+    assert not inside([200, 1, 12])  # far off to the side
+
+
+def test_library_host_helpers_match_oracle_planes():
+    _, _, pv, planes = O.project_camera(16 / 9, scene.CAMERA_POS, scene.CAMERA_ROT)
+    assert np.array_equal(scene.camera_view(), planes)
+    assert np.array_equal(O.frustum_planes(pv), planes)
+    for lp in scene.LIGHT_POS:
+        rot = scene.quat_look_at_lh(-lp.astype(np.float64))
+        assert np.array_equal(scene.light_view(lp), O.light_view(lp, rot)[3])
+
+
+# ---- generators and golden vectors ----------------------------------------------------
+def test_scene_generator_twins_agree():
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 777, 5000, 250.0)
+    pos, quat, scale, mesh2 = O.synth_entities(scene.SEED, 777, 5000, 250.0, scene.N_MESHES)
+    assert np.array_equal(ps[:, :3], pos) and np.array_equal(ps[:, 3], scale)
+    assert np.array_equal(rot, quat) and np.array_equal(mesh, mesh2)
+
+
+def test_golden_vectors_config1():
+    import sys
+    sys.path.insert(0, os.path.dirname(GOLDEN))
+    import make_golden
+
+    g = np.load(GOLDEN)
+    now = make_golden.build()
+    for key in g.files:
+        assert np.array_equal(g[key], now[key]), key
+
+
+def test_empty_and_bad_inputs():
+    meshes = scene.synth_mesh_table()
+    views = scene.scene_views(2)
+    e = np.zeros((0, 3), F)
+    r = O.frame(e, np.zeros((0, 4), F), np.zeros(0, F), np.zeros(0, np.uint32), meshes, views, scene.CAMERA_POS)
+    assert r["counts"].tolist() == [0, 0] and r["totals"].tolist() == [0, 0]
+    with pytest.raises(ValueError):
+        O.frame(np.zeros((1, 3), F), np.array([[0, 0, 0, 1]], F), np.ones(1, F), np.array([99], np.uint32), meshes, views, scene.CAMERA_POS)
+
+
+def test_threads_do_not_change_results():
+    ps, rot, mesh = scene.synth_entities(3, 0, 20_000, 80.0)
+    pos, quat, scale = scene.to_components(ps, rot)
+    meshes, views = scene.synth_mesh_table(), scene.scene_views(3)
+    a = O.frame(pos, quat, scale, mesh, meshes, views, scene.CAMERA_POS, n_threads=1)
+    b = O.frame(pos, quat, scale, mesh, meshes, views, scene.CAMERA_POS, n_threads=5)
+    assert np.array_equal(a["model"], b["model"]) and np.array_equal(a["flags"], b["flags"])
+    for k in range(3):
+        assert np.array_equal(a["cmds"][k], b["cmds"][k])
