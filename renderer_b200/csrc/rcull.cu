@@ -20,6 +20,12 @@ static_assert(sizeof(rcull_mesh) == 80, "rcull_mesh layout");
 static_assert(sizeof(rcull_draw_cmd) == 20, "VkDrawIndexedIndirectCommand stride");
 static_assert(sizeof(rcull_config) == 48 && sizeof(rcull_view) == 96, "rcull_config / rcull_view layout");
 static_assert(RCULL_MAX_VIEWS == kMaxViews && RCULL_MAX_LODS == kMaxLods, "header/kernel constants");
+// two CTAs per SM: 228 KB of shared memory per SM, 1 KB reserved per CTA
+constexpr size_t kSmemPerCta = (228 * 1024 - 2 * 1024) / 2;
+static_assert(frame_smem_bytes<1>() <= kSmemPerCta && frame_smem_bytes<2>() <= kSmemPerCta &&
+              frame_smem_bytes<3>() <= kSmemPerCta && frame_smem_bytes<4>() <= kSmemPerCta &&
+              frame_smem_bytes<5>() <= kSmemPerCta && frame_smem_bytes<6>() <= kSmemPerCta &&
+              frame_smem_bytes<7>() <= kSmemPerCta && frame_smem_bytes<8>() <= kSmemPerCta, "frame kernel must fit two CTAs per SM");
 
 namespace {
 
@@ -65,6 +71,7 @@ struct rcull_ctx {
     float4* mesh_aabb = nullptr;
     uint4* lod_tab = nullptr;
     uint32_t n_meshes = 0;
+    uint32_t len_small = 0;
     OutputSet out[3];
     ulonglong2* status = nullptr;
     size_t status_bytes = 0;
@@ -275,6 +282,7 @@ int rcull_set_mesh_table(rcull_ctx* c, const rcull_mesh* meshes, uint32_t n) {
     if (n == 0 || n > c->cfg.max_meshes) return fail(RCULL_ERR_INVALID, "mesh count %u exceeds max_meshes %u", n, c->cfg.max_meshes);
     std::vector<float4> aabb(2 * (size_t)n);
     std::vector<uint4> lods((size_t)n * kMaxLods, make_uint4(0, 0, 0, 0));
+    uint32_t max_len = 0;
     for (uint32_t i = 0; i < n; ++i) {
         const rcull_mesh& m = meshes[i];
         // pick_lod .expect("empty index buffer LODs") (helpers.rs:7-9)
@@ -283,13 +291,16 @@ int rcull_set_mesh_table(rcull_ctx* c, const rcull_mesh* meshes, uint32_t n) {
         memcpy(&nl, &m.n_lods, 4);
         aabb[2 * i] = make_float4(m.aabb_min[0], m.aabb_min[1], m.aabb_min[2], nl);
         aabb[2 * i + 1] = make_float4(m.aabb_max[0], m.aabb_max[1], m.aabb_max[2], 0.f);
-        for (uint32_t l = 0; l < m.n_lods; ++l)
+        for (uint32_t l = 0; l < m.n_lods; ++l) {
+            if (m.lod[l].index_len > max_len) max_len = m.lod[l].index_len;
             lods[(size_t)i * kMaxLods + l] = make_uint4(m.lod[l].index_len, m.lod[l].first_index, (uint32_t)m.vertex_offset, 0);
+        }
     }
     CU(cudaSetDevice(c->cfg.device));
     CU(cudaMemcpy(c->mesh_aabb, aabb.data(), aabb.size() * sizeof(float4), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(c->lod_tab, lods.data(), lods.size() * sizeof(uint4), cudaMemcpyHostToDevice));
     c->n_meshes = n;
+    c->len_small = max_len < (1u << 25) ? 1u : 0u;
     return RCULL_OK;
 }
 
@@ -390,6 +401,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     a.n = (uint32_t)n;
     a.n_tiles = n_tiles;
     a.n_meshes = c->n_meshes;
+    a.len_small = c->len_small;
     a.draw_index_base = draw_index_base;
     a.cap_visible = (uint32_t)(c->cap_vis > 0xffffffffull ? 0xffffffffull : c->cap_vis);
     a.cam[0] = cam_pos[0];

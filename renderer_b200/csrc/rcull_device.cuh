@@ -46,8 +46,10 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // the warps that are computing on the same scheduler.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
+    uint32_t ns = 32;
     do {
-        __nanosleep(64);
+        __nanosleep(ns);
+        if (ns < 256) ns *= 2;
     } while (!mbar_try_wait(bar, parity));
 }
 // non-blocking: has the phase with this parity completed?

@@ -66,6 +66,7 @@ struct FrameArgs {
     uint32_t n_meshes;
     uint32_t draw_index_base;
     uint32_t cap_visible;
+    uint32_t len_small;  // every index_len in the mesh table is < 2^25: 128 of them add up in 32 bits
     float cam[3];
     float lod_d2_max;  // lod 1 iff |cam-pos|^2 > lod_d2_max  (== sqrt(d2) > lod_distance)
     PlaneC planes[kMaxViews][6];
@@ -79,7 +80,6 @@ struct FrameSmem {
     uint32_t mesh[kStages][kTile];
     // Survivor bookkeeping is a ring of frame_bufs<V>() tiles (buffer = iteration % bufs): the
     // scan warp resolves the offsets of tile i while the compute warps run several tiles ahead.
-    uint32_t slot[kMaxBufs][kTile];  // (mesh, lod) slot of every entity
     uint64_t full[kStages];
     uint64_t empty[kStages];
     uint64_t done[kMaxBufs];   // compute warps -> scan warp: lists and aggregates of a tile are written
@@ -91,18 +91,21 @@ struct FrameSmem {
     uint64_t agg_len[kMaxBufs][kMaxViews];  // tile aggregates kept between publish and resolve
     uint32_t agg_cnt[kMaxBufs][kMaxViews];
     uint32_t tile_ring[kRing];  // tile id of iteration it at [it % kRing]
-    // followed by: uint8_t wlist[bufs][kComputeWarps][V * kWarpSpan] -- per-warp combined
+    uint32_t dummy[kComputeWarps];  // where culled lanes 'store' their list entry (keeps the list code branch-free)
+    // followed by: PlaneC planes[V][6] (a shared-memory copy: LDS.128 instead of indexed LDC), then
+    // uint32_t slot[bufs][kTile] -- (mesh, lod) slot of every entity -- and
+    // uint8_t wlist[bufs][kComputeWarps][V * kWarpSpan] -- per-warp combined
     // survivor list, view-major, entry = slot in the warp's span (the view follows
     // from the entry's position and the per-view counts)
 };
 
 template <int V>
 __host__ __device__ constexpr int frame_bufs() {
-    return V <= 4 ? 4 : V <= 7 ? 3 : 2;  // what still lets two CTAs share an SM's shared memory
+    return V <= 4 ? 4 : V <= 6 ? 3 : 2;  // what still lets two CTAs share an SM's shared memory
 }
 template <int V>
 constexpr size_t frame_smem_bytes() {
-    return sizeof(FrameSmem) + frame_bufs<V>() * V * kTile + 1024;  // + slack to align the base
+    return sizeof(FrameSmem) + V * 6 * sizeof(PlaneC) + frame_bufs<V>() * (4 + V) * kTile + 1024;  // + slack to align the base
 }
 
 __device__ __forceinline__ FrameSmem& frame_smem(unsigned char* raw) {
@@ -264,7 +267,7 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
         } else if (ended) {
             break;
         }
-        if (!progress) __nanosleep(200);
+        if (!progress) __nanosleep(400);
     }
 }
 
@@ -272,7 +275,7 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
 // warp's combined (all views) list, stable within every view.
 template <int V>
 __device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameSmem& sm, const uint8_t* wlist,
-                                             uint32_t buf, uint32_t tile_base, uint32_t warp, uint32_t lane) {
+                                             const uint32_t* slot_of, uint32_t buf, uint32_t tile_base, uint32_t warp, uint32_t lane) {
     uint32_t vend[V];  // end of view k in the combined list
     uint32_t total = 0;
 #pragma unroll
@@ -290,7 +293,7 @@ __device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameS
 #pragma unroll
             for (int kk = 0; kk < V - 1; ++kk) k += i >= vend[kk] ? 1u : 0u;
             e = warp * kWarpSpan + wlist[i];
-            L = __ldg(args.lod_tab + sm.slot[buf][e]);
+            L = __ldg(args.lod_tab + slot_of[e]);
         }
         const uint32_t incl = warp_incl_scan_u32(L.x, lane);
         const uint32_t excl = carry + incl - L.x;
@@ -339,6 +342,8 @@ __global__ void __maxnreg__(112)
         }
         fence_mbar_init();
     }
+    float4* const sm_planes = reinterpret_cast<float4*>(reinterpret_cast<unsigned char*>(&sm) + sizeof(FrameSmem));
+    for (uint32_t i = tid; i < V * 6 * 4; i += kThreads) sm_planes[i] = reinterpret_cast<const float4*>(&args.planes[0][0])[i];
     __syncthreads();
 
     if (warp == kComputeWarps) {
@@ -347,7 +352,8 @@ __global__ void __maxnreg__(112)
     }
 
     // ================================= compute warps =================================
-    uint8_t* const wlist_base = reinterpret_cast<uint8_t*>(&sm) + sizeof(FrameSmem) + warp * (V * kWarpSpan);
+    uint32_t* const slot_base = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(&sm) + sizeof(FrameSmem) + V * 6 * sizeof(PlaneC));
+    uint8_t* const wlist_base = reinterpret_cast<uint8_t*>(slot_base + frame_bufs<V>() * kTile) + warp * (V * kWarpSpan);
     const uint32_t lt = (1u << lane) - 1u;
     // swizzled (128-B pattern) byte offsets of this lane's four matrix columns in the warp's store box
     unsigned char* const box = reinterpret_cast<unsigned char*>(sm.mat[warp]);
@@ -385,7 +391,7 @@ __global__ void __maxnreg__(112)
     uint32_t emitted = 0;  // iterations [emitted, it) of this CTA still have their commands pending
     auto emit_next = [&]() {
         const uint32_t b = emitted % B;
-        emit_pending<V>(args, sm, wlist_base + b * (V * kTile), b, sm.tile_ring[emitted % kRing] * kTile, warp, lane);
+        emit_pending<V>(args, sm, wlist_base + b * (V * kTile), slot_base + b * kTile, b, sm.tile_ring[emitted % kRing] * kTile, warp, lane);
         ++emitted;
     };
     for (;; ++it) {
@@ -495,14 +501,13 @@ __global__ void __maxnreg__(112)
             emit_next();
         }
         __syncwarp();
-        uint32_t len_lo[kItems], len_hi[kItems];
+        uint32_t len[kItems];
 #pragma unroll
         for (int j = 0; j < kItems; ++j) {
-            sm.slot[buf][e0 + 32 * j] = slot[j];
-            const uint32_t len = __ldg(args.lod_tab + slot[j]).x;
-            len_lo[j] = len & 0xffffu;
-            len_hi[j] = len >> 16;
+            slot_base[buf * kTile + e0 + 32 * j] = slot[j];
+            len[j] = __ldg(args.lod_tab + slot[j]).x;
         }
+        uint8_t* const dummy = reinterpret_cast<uint8_t*>(&sm.dummy[warp]);
 
         // A3 per view: planes outer, the thread's 4 entities inner
         // (the view loop stays rolled: unrolled, the kernel outgrows the instruction cache)
@@ -511,21 +516,25 @@ __global__ void __maxnreg__(112)
         for (int k = 0; k < V; ++k) {
             bool outside[kItems];
 #pragma unroll
-            for (int j = 0; j < kItems; ++j) outside[j] = false;
+            for (int j = 0; j < kItems; ++j) outside[j] = !valid[j];  // padding slots are never visible
 #pragma unroll
             for (int p = 0; p < 6; ++p) {
-                const PlaneC& pc = args.planes[k][p];
+                const float4* pp = sm_planes + (k * 6 + p) * 4;
+                const float4 q0 = pp[0], q1 = pp[1], q2 = pp[2];  // (ax ax ay ay) (az az px px) (py py pz pz)
+                const float pw = pp[3].x;
+                const float2 ax = make_float2(q0.x, q0.y), ay = make_float2(q0.z, q0.w), az = make_float2(q1.x, q1.y);
+                const float2 px = make_float2(q1.z, q1.w), py = make_float2(q2.x, q2.y), pz = make_float2(q2.z, q2.w);
 #pragma unroll
                 for (int i = 0; i < kItems / 2; ++i) {
                     // Products of two entities per FMUL2; every sum that consumes a packed product
                     // is a scalar FADD, so ptxas has no packed mul+add pair to contract into FFMA2
-                    // (it does that even under --fmad=false; tests/test_sass.py checks the SASS).
-                    const float2 m1 = mul2_rn(h2x[i], pc.ax), m2 = mul2_rn(h2y[i], pc.ay), m3 = mul2_rn(h2z[i], pc.az);
+                    // (it does that even under --fmad=false; tests/test_abi.py checks the SASS).
+                    const float2 m1 = mul2_rn(h2x[i], ax), m2 = mul2_rn(h2y[i], ay), m3 = mul2_rn(h2z[i], az);
                     const float e0 = __fadd_rn(__fadd_rn(m1.x, m2.x), m3.x);
                     const float e1 = __fadd_rn(__fadd_rn(m1.y, m2.y), m3.y);
-                    const float2 p1 = mul2_rn(c2x[i], pc.px), p3 = mul2_rn(c2z[i], pc.pz), p2 = mul2_rn(c2y[i], pc.py);
+                    const float2 p1 = mul2_rn(c2x[i], px), p3 = mul2_rn(c2z[i], pz), p2 = mul2_rn(c2y[i], py);
                     const float2 a = make_float2(__fadd_rn(p1.x, p3.x), __fadd_rn(p1.y, p3.y));
-                    const float2 b = make_float2(__fadd_rn(p2.x, pc.pw), __fadd_rn(p2.y, pc.pw));
+                    const float2 b = make_float2(__fadd_rn(p2.x, pw), __fadd_rn(p2.y, pw));
                     const float2 s = add2_rn(a, b);
                     // (s - e > 0.0) == (s > e): the rounded difference of two floats keeps its sign,
                     // and both forms are false for NaN and for inf - inf
@@ -533,24 +542,34 @@ __global__ void __maxnreg__(112)
                     outside[2 * i + 1] = outside[2 * i + 1] || (s.y > e1);
                 }
             }
+            // ballot compaction, branch-free: culled lanes store to a dummy byte
             uint32_t wc = 0, lo = 0, hi = 0;
 #pragma unroll
             for (int j = 0; j < kItems; ++j) {
-                const bool vis = valid[j] && !outside[j];
+                const bool vis = !outside[j];
                 if (kMat && args.flags[k] != nullptr && valid[j]) args.flags[k][tile_base + e0 + 32 * j] = outside[j] ? 1 : 0;
                 const uint32_t b = __ballot_sync(kFullMask, vis);
-                if (vis) {
-                    wlist[woff + wc + __popc(b & lt)] = (uint8_t)(lane + 32 * j);
-                    lo += len_lo[j];
-                    hi += len_hi[j];
+                uint8_t* const dst = vis ? wlist + (woff + wc + __popc(b & lt)) : dummy;
+                *dst = (uint8_t)(lane + 32 * j);
+                if (args.len_small) {
+                    lo += vis ? len[j] : 0u;
+                } else {
+                    lo += vis ? (len[j] & 0xffffu) : 0u;
+                    hi += vis ? (len[j] >> 16) : 0u;
                 }
                 wc += __popc(b);
             }
-            lo = __reduce_add_sync(kFullMask, lo);  // 128 x 16-bit pieces: no overflow
-            hi = __reduce_add_sync(kFullMask, hi);
+            uint64_t wl;
+            if (args.len_small) {
+                wl = __reduce_add_sync(kFullMask, lo);  // 128 values below 2^25
+            } else {
+                lo = __reduce_add_sync(kFullMask, lo);  // 128 x 16-bit pieces: no overflow
+                hi = __reduce_add_sync(kFullMask, hi);
+                wl = (uint64_t)lo + ((uint64_t)hi << 16);
+            }
             if (lane == 0) {
                 sm.wcnt[buf][k][warp] = wc;
-                sm.wlen[buf][k][warp] = (uint64_t)lo + ((uint64_t)hi << 16);
+                sm.wlen[buf][k][warp] = wl;
             }
             woff += wc;
         }
