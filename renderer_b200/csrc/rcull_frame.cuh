@@ -507,7 +507,8 @@ __global__ void __maxnreg__(112)
             slot_base[buf * kTile + e0 + 32 * j] = slot[j];
             len[j] = __ldg(args.lod_tab + slot[j]).x;
         }
-        uint8_t* const dummy = reinterpret_cast<uint8_t*>(&sm.dummy[warp]);
+        const uint32_t dummy = smem_u32(&sm.dummy[warp]);
+        const uint32_t wlist_s = smem_u32(wlist);
 
         // A3 per view: planes outer, the thread's 4 entities inner
         // (the view loop stays rolled: unrolled, the kernel outgrows the instruction cache)
@@ -549,8 +550,7 @@ __global__ void __maxnreg__(112)
                 const bool vis = !outside[j];
                 if (kMat && args.flags[k] != nullptr && valid[j]) args.flags[k][tile_base + e0 + 32 * j] = outside[j] ? 1 : 0;
                 const uint32_t b = __ballot_sync(kFullMask, vis);
-                uint8_t* const dst = vis ? wlist + (woff + wc + __popc(b & lt)) : dummy;
-                *dst = (uint8_t)(lane + 32 * j);
+                sts_u8(vis ? wlist_s + woff + wc + __popc(b & lt) : dummy, lane + 32 * j);
                 if (args.len_small) {
                     lo += vis ? len[j] : 0u;
                 } else {
