@@ -131,7 +131,7 @@ def gpu_arm(args, wl):
     import torch.distributed as dist
 
     from renderer_b200 import CullContext, scene
-    from renderer_b200.shard import ShardMerger, _wrap_device
+    from renderer_b200.shard import PeerMerger, ShardMerger, _wrap_device
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -163,12 +163,19 @@ def gpu_arm(args, wl):
         c0, _ = ctx.counts()
         tot = torch.tensor([int(c0[:n_views].max())], dtype=torch.int64, device=dev)
         dist.all_reduce(tot)
-        merger = ShardMerger(n_views, int(tot.item() * 1.05) + 1024, dev)
+        cap = int(tot.item() * 1.05) + 1024
+        merger = PeerMerger(ctx, n_views, cap, dev) if args.merge == "p2p" else ShardMerger(n_views, cap, dev)
 
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev) if n * 36 < 256e6 else None
 
     def step():
         ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, stream=sh)
+
+    def do_merge():
+        if args.merge == "p2p":
+            merger.merge()
+        else:
+            merger.merge_from_context(ctx, stream=sh)
 
     def sync_all():
         if world > 1:
@@ -179,7 +186,7 @@ def gpu_arm(args, wl):
         for _ in range(args.warmup):
             step()
             if merger:
-                merger.merge_from_context(ctx, stream=sh)
+                do_merge()
             if flush is not None:
                 flush.zero_()
         sync_all()
@@ -191,7 +198,7 @@ def gpu_arm(args, wl):
                 step()
                 ev[i][1].record(stream)
                 if merger:
-                    merger.merge_from_context(ctx, stream=sh)
+                    do_merge()
                 ev[i][2].record(stream)
                 if flush is not None:
                     flush.zero_()
@@ -217,7 +224,7 @@ def gpu_arm(args, wl):
     def e2e_step():
         c, _ = ctx.frame_host(a_ps, a_rot, a_mesh, views, scene.CAMERA_POS, draw_index_base=lo)
         if merger:
-            merger.merge_from_context(ctx)
+            do_merge()
             torch.cuda.synchronize()
         return c
 
@@ -255,13 +262,18 @@ def gpu_arm(args, wl):
                 "workload": args.workload, "entities_per_gpu": n, "entities_total": n_total, "n_views": n_views,
                 "half_box": wl["half_box"], "visible_fraction_per_view": [round(float(x), 6) for x in vis / float(n_total)],
                 "sharding": "contiguous range per rank" if world > 1 else "none",
-                "merge": "NCCL all_gather(counts) + in-place broadcast allgatherv" if world > 1 else "none",
+                "merge": ("NCCL all_gather(meta) + one peer-store kernel per rank (NVLink P2P) + 1-word all_reduce" if args.merge == "p2p" else "NCCL all_gather(counts) + in-place broadcast allgatherv") if world > 1 else "none",
                 "l2": "flushed between iterations (256 MB write)" if flush is not None else "inputs (36 B x n) exceed L2",
             },
             "e2e": {"value": n_total * e2e_steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": n * 36,
                     "d2h_bytes_per_step": 96, "steps": e2e_steps, "ms_per_step": t_e2e / e2e_steps * 1e3,
                     "api": "rcull_frame_host (pinned host columns in, counts + index totals out)"},
             "gpu_launches": int(launches),
+            "merge": None if world == 1 else {
+                "ms_per_step": (t_step - t_frame) / args.steps * 1e3,
+                "bytes_stored_to_peers_per_gpu": int(24 * int(counts.sum()) * (world - 1)),
+                "nvlink_gbs_per_gpu": 24.0 * float(counts.sum()) * (world - 1) / max((t_step - t_frame) / args.steps, 1e-9) / 1e9,
+                "nvlink_peak_gbs": 770.0, "note": "rank 0's own lists stored into every peer; peak = measured peer copy per direction"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_kind": peak_kind, "kernel": f"transform_cull_compact<{n_views}>",
                          "bytes_per_entity": bytes_per_entity, "ms_per_launch": t_launch * 1e3},
@@ -276,6 +288,8 @@ def gpu_arm(args, wl):
             except Exception:
                 pass
         print(json.dumps(line), flush=True)
+    if merger is not None and hasattr(merger, "destroy"):
+        merger.destroy()
     ctx.destroy()
     if world > 1:
         dist.barrier()
@@ -306,6 +320,7 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--merge", default="p2p", choices=["p2p", "nccl"], help="N > 1: peer-store merge kernel or NCCL broadcasts")
     ap.add_argument("--workload", default="16m_5view", choices=sorted(WORKLOADS))
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -154,6 +154,34 @@ int rcull_download_visible(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t view, ui
 int rcull_rebase_into(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t view, uint64_t index_prefix,
                       rcull_draw_cmd *dst_cmds, uint32_t *dst_visible, void *stream);
 
+/* ---- Range-shard merge over peer memory (NVLink P2P stores) ---------------
+ * Every rank owns one MERGED allocation of identical layout (max_views draw lists of
+ * `capacity` commands + their visible-index lists).  Per frame: rcull_merge_pack_meta,
+ * an all_gather of the meta words (the caller's collective: 2*max_views u64 per rank),
+ * then rcull_merge_scatter -- ONE kernel that computes this rank's slot from the gathered
+ * words and stores its rebased lists into that slot of EVERY rank's allocation, its own
+ * and the peers' (peer-mapped pointers).  A barrier on the caller's side tells when all
+ * peers have written.  The merged list equals the single-GPU list byte for byte. */
+typedef struct rcull_merge rcull_merge;
+#define RCULL_MAX_RANKS 8
+#define RCULL_IPC_HANDLE_BYTES 64
+int rcull_merge_create(rcull_ctx *ctx, uint32_t world, uint32_t rank, uint64_t capacity, rcull_merge **out);
+void rcull_merge_destroy(rcull_merge *m);
+/* cudaIpcMemHandle_t of this rank's merged allocation, to be sent to the other processes. */
+int rcull_merge_ipc_handle(rcull_merge *m, void *handle_out);
+/* Maps a peer process' allocation (cudaIpcOpenMemHandle). */
+int rcull_merge_open_peer(rcull_merge *m, uint32_t peer, const void *handle);
+/* Same-process peers (tests, single-process multi-GPU): the peer's base pointer itself. */
+int rcull_merge_set_peer_ptr(rcull_merge *m, uint32_t peer, void *base);
+int rcull_merge_base(rcull_merge *m, void **base);
+/* Device buffers of the exchange: meta_local [2*max_views] u64, meta_all [world][2*max_views] u64. */
+int rcull_merge_meta_ptrs(rcull_merge *m, uint64_t **meta_local, uint64_t **meta_all);
+int rcull_merge_pack_meta(rcull_merge *m, uint32_t buffer_ix, void *stream);
+int rcull_merge_scatter(rcull_merge *m, uint32_t buffer_ix, uint32_t n_views, void *stream);
+/* Device pointers of the merged lists of one view and of the merged counts / index totals. */
+int rcull_merge_lists(rcull_merge *m, uint32_t view, rcull_draw_cmd **cmds, uint32_t **visible,
+                      uint32_t **counts, uint64_t **index_totals);
+
 /* Harness utility: fills the input columns on the device with the counter-based
  * synthetic scene (entity i of the global scene = first_global + slot), bit-
  * identical to renderer_b200/scene.py; avoids shipping 128 M entities from host. */

@@ -553,3 +553,160 @@ int rcull_synth_entities(rcull_ctx* c, uint64_t seed, uint64_t first_global, uin
 uint64_t rcull_launch_count(rcull_ctx* c) { return c ? c->launches : 0; }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------
+// range-shard merge over peer memory
+// ---------------------------------------------------------------------------------
+struct rcull_merge {
+    rcull_ctx* ctx = nullptr;
+    uint32_t world = 0, rank = 0;
+    uint64_t cap = 0;
+    size_t bytes = 0;
+    unsigned char* base = nullptr;
+    unsigned char* peer[kMaxRanks] = {};
+    bool opened[kMaxRanks] = {};
+    unsigned long long* meta_local = nullptr;
+    unsigned long long* meta_all = nullptr;
+    uint32_t* counts = nullptr;
+    unsigned long long* totals = nullptr;
+};
+
+static_assert(RCULL_MAX_RANKS == kMaxRanks && RCULL_IPC_HANDLE_BYTES == sizeof(cudaIpcMemHandle_t), "merge ABI constants");
+
+extern "C" {
+
+void rcull_merge_destroy(rcull_merge* m) {
+    if (!m) return;
+    cudaSetDevice(m->ctx->cfg.device);
+    cudaDeviceSynchronize();
+    for (uint32_t p = 0; p < m->world; ++p)
+        if (m->opened[p]) cudaIpcCloseMemHandle(m->peer[p]);
+    cudaFree(m->base);
+    cudaFree(m->meta_local);
+    cudaFree(m->meta_all);
+    cudaFree(m->counts);
+    cudaFree(m->totals);
+    delete m;
+}
+
+int rcull_merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t capacity, rcull_merge** out) {
+    if (!c || !out) return fail(RCULL_ERR_INVALID, "rcull_merge_create: null argument");
+    *out = nullptr;
+    if (world < 1 || world > kMaxRanks || rank >= world) return fail(RCULL_ERR_INVALID, "rank %u of world %u (max %d)", rank, world, kMaxRanks);
+    if (capacity == 0 || capacity > 0xffffffffull) return fail(RCULL_ERR_INVALID, "merged capacity must be 1..2^32-1 commands");
+    CU(cudaSetDevice(c->cfg.device));
+    rcull_merge* m = new rcull_merge();
+    m->ctx = c;
+    m->world = world;
+    m->rank = rank;
+    m->cap = capacity;
+    m->bytes = (size_t)c->cfg.max_views * capacity * 24;
+    const uint32_t mv = c->cfg.max_views;
+    if (cudaMalloc((void**)&m->base, m->bytes) != cudaSuccess || cudaMalloc((void**)&m->meta_local, 2 * mv * 8) != cudaSuccess ||
+        cudaMalloc((void**)&m->meta_all, (size_t)world * 2 * mv * 8) != cudaSuccess ||
+        cudaMalloc((void**)&m->counts, mv * 4) != cudaSuccess || cudaMalloc((void**)&m->totals, mv * 8) != cudaSuccess) {
+        rcull_merge_destroy(m);
+        return fail(RCULL_ERR_CUDA, "rcull_merge_create: cudaMalloc of %zu bytes failed", m->bytes);
+    }
+    cudaMemset(m->meta_local, 0, 2 * mv * 8);
+    cudaMemset(m->meta_all, 0, (size_t)world * 2 * mv * 8);
+    cudaMemset(m->counts, 0, mv * 4);
+    cudaMemset(m->totals, 0, mv * 8);
+    m->peer[rank] = m->base;
+    *out = m;
+    return RCULL_OK;
+}
+
+int rcull_merge_ipc_handle(rcull_merge* m, void* handle_out) {
+    if (!m || !handle_out) return fail(RCULL_ERR_INVALID, "rcull_merge_ipc_handle: null argument");
+    CU(cudaSetDevice(m->ctx->cfg.device));
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, m->base));
+    memcpy(handle_out, &h, sizeof h);
+    return RCULL_OK;
+}
+
+int rcull_merge_open_peer(rcull_merge* m, uint32_t peer, const void* handle) {
+    if (!m || !handle) return fail(RCULL_ERR_INVALID, "rcull_merge_open_peer: null argument");
+    if (peer >= m->world || peer == m->rank) return fail(RCULL_ERR_INVALID, "peer %u is not another rank of world %u", peer, m->world);
+    CU(cudaSetDevice(m->ctx->cfg.device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof h);
+    void* p = nullptr;
+    CU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    m->peer[peer] = static_cast<unsigned char*>(p);
+    m->opened[peer] = true;
+    return RCULL_OK;
+}
+
+int rcull_merge_set_peer_ptr(rcull_merge* m, uint32_t peer, void* base) {
+    if (!m || !base) return fail(RCULL_ERR_INVALID, "rcull_merge_set_peer_ptr: null argument");
+    if (peer >= m->world) return fail(RCULL_ERR_INVALID, "peer %u of world %u", peer, m->world);
+    m->peer[peer] = static_cast<unsigned char*>(base);
+    return RCULL_OK;
+}
+
+int rcull_merge_base(rcull_merge* m, void** base) {
+    if (!m || !base) return fail(RCULL_ERR_INVALID, "rcull_merge_base: null argument");
+    *base = m->base;
+    return RCULL_OK;
+}
+
+int rcull_merge_meta_ptrs(rcull_merge* m, uint64_t** meta_local, uint64_t** meta_all) {
+    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_meta_ptrs: null argument");
+    if (meta_local) *meta_local = reinterpret_cast<uint64_t*>(m->meta_local);
+    if (meta_all) *meta_all = reinterpret_cast<uint64_t*>(m->meta_all);
+    return RCULL_OK;
+}
+
+int rcull_merge_pack_meta(rcull_merge* m, uint32_t buffer_ix, void* stream) {
+    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_pack_meta: null argument");
+    rcull_ctx* c = m->ctx;
+    if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
+    CU(cudaSetDevice(c->cfg.device));
+    pack_meta<<<1, 32, 0, (cudaStream_t)stream>>>(c->out[buffer_ix].counts, c->out[buffer_ix].totals, c->cfg.max_views, m->meta_local);
+    CU(cudaGetLastError());
+    c->launches += 1;
+    return RCULL_OK;
+}
+
+int rcull_merge_scatter(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, void* stream) {
+    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_scatter: null argument");
+    rcull_ctx* c = m->ctx;
+    if (buffer_ix >= c->cfg.n_buffers || n_views < 1 || n_views > c->cfg.max_views) return fail(RCULL_ERR_INVALID, "rcull_merge_scatter: bad buffer/view count");
+    for (uint32_t p = 0; p < m->world; ++p)
+        if (!m->peer[p]) return fail(RCULL_ERR_INVALID, "peer %u has not been mapped (rcull_merge_open_peer / rcull_merge_set_peer_ptr)", p);
+    CU(cudaSetDevice(c->cfg.device));
+    MergeArgs a;
+    memset(&a, 0, sizeof a);
+    for (uint32_t p = 0; p < m->world; ++p) a.peer[p] = m->peer[p];
+    for (uint32_t k = 0; k < n_views; ++k) {
+        a.src_cmds[k] = c->out[buffer_ix].cmds[k];
+        a.src_visible[k] = c->out[buffer_ix].visible[k];
+    }
+    a.meta_all = m->meta_all;
+    a.merged_counts = m->counts;
+    a.merged_totals = m->totals;
+    a.world = m->world;
+    a.rank = m->rank;
+    a.n_views = n_views;
+    a.max_views = c->cfg.max_views;
+    a.cap = (uint32_t)m->cap;
+    scatter_rebased<<<c->sm_count * 4, 256, 0, (cudaStream_t)stream>>>(a);
+    CU(cudaGetLastError());
+    c->launches += 1;
+    return RCULL_OK;
+}
+
+int rcull_merge_lists(rcull_merge* m, uint32_t view, rcull_draw_cmd** cmds, uint32_t** visible, uint32_t** counts, uint64_t** index_totals) {
+    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_lists: null argument");
+    const uint32_t mv = m->ctx->cfg.max_views;
+    if (view >= mv) return fail(RCULL_ERR_INVALID, "view %u of %u", view, mv);
+    if (cmds) *cmds = reinterpret_cast<rcull_draw_cmd*>(m->base + (size_t)view * m->cap * 20);
+    if (visible) *visible = reinterpret_cast<uint32_t*>(m->base + (size_t)mv * m->cap * 20 + (size_t)view * m->cap * 4);
+    if (counts) *counts = m->counts;
+    if (index_totals) *index_totals = reinterpret_cast<uint64_t*>(m->totals);
+    return RCULL_OK;
+}
+
+}  // extern "C"

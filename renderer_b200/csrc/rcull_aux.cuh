@@ -28,6 +28,77 @@ __global__ void __launch_bounds__(256) rebase_into(const uint32_t* __restrict__ 
         dst_visible[i] = src_visible[i];
 }
 
+// ---- range-shard merge over peer memory (NVLink P2P) ----------------------
+// Every rank holds a MERGED allocation with the same layout:
+//   cmds of view k at  k * cap * 20 bytes,  visible of view k at  V * cap * 20 + k * cap * 4.
+// After an all_gather of the per-rank (count, index_total) words, ONE kernel per rank
+// computes its slot from the gathered words and stores its rebased list into that slot
+// of every rank's allocation -- its own and, through peer-mapped pointers, the others'.
+// The stores are the transfer: no staging copy, no per-slice collective, no host round trip.
+constexpr int kMaxRanks = 8;
+
+struct MergeArgs {
+    unsigned char* peer[kMaxRanks];         // merged allocation of every rank (peer-mapped)
+    const uint32_t* src_cmds[8];            // this rank's lists, per view
+    const uint32_t* src_visible[8];
+    const unsigned long long* meta_all;     // [world][2 * max_views]: counts then index totals (u64)
+    uint32_t* merged_counts;                // [max_views] outputs in the local allocation's header
+    unsigned long long* merged_totals;
+    uint32_t world, rank, n_views, max_views;
+    uint32_t cap;                           // merged list capacity (commands per view)
+    __host__ __device__ size_t n_views_cap_bytes() const { return (size_t)max_views * cap * 20; }
+};
+
+__global__ void __launch_bounds__(256) pack_meta(const uint32_t* __restrict__ counts,
+                                                 const unsigned long long* __restrict__ totals, uint32_t max_views,
+                                                 unsigned long long* __restrict__ meta_local) {
+    const uint32_t i = threadIdx.x;
+    if (i < max_views) {
+        meta_local[i] = counts[i];
+        meta_local[max_views + i] = totals[i];
+    }
+}
+
+__global__ void __launch_bounds__(256) scatter_rebased(const __grid_constant__ MergeArgs a) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const size_t t0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (uint32_t k = 0; k < a.n_views; ++k) {
+        unsigned long long cnt_prefix = 0, len_prefix = 0, cnt_all = 0, len_all = 0;
+        for (uint32_t r = 0; r < a.world; ++r) {
+            const unsigned long long c = a.meta_all[(size_t)r * 2 * a.max_views + k];
+            const unsigned long long l = a.meta_all[(size_t)r * 2 * a.max_views + a.max_views + k];
+            if (r < a.rank) {
+                cnt_prefix += c;
+                len_prefix += l;
+            }
+            cnt_all += c;
+            len_all += l;
+        }
+        if (t0 == 0) {
+            a.merged_counts[k] = (uint32_t)cnt_all;
+            a.merged_totals[k] = len_all;
+        }
+        unsigned long long count = a.meta_all[(size_t)a.rank * 2 * a.max_views + k];
+        if (cnt_prefix >= a.cap) continue;
+        if (cnt_prefix + count > a.cap) count = a.cap - cnt_prefix;  // clamp writes, like cap_visible
+        const size_t words = (size_t)count * 5;
+        const uint32_t add = (uint32_t)len_prefix;
+        const uint32_t* __restrict__ sc = a.src_cmds[k];
+        const uint32_t* __restrict__ sv = a.src_visible[k];
+        const size_t cmd_off = ((size_t)k * a.cap + cnt_prefix) * 20;
+        const size_t vis_off = (size_t)a.n_views_cap_bytes() + ((size_t)k * a.cap + cnt_prefix) * 4;
+        for (size_t w = t0; w < words; w += stride) {
+            uint32_t v = sc[w];
+            if (w % 5 == 2) v += add;  // firstIndex
+            for (uint32_t p = 0; p < a.world; ++p) reinterpret_cast<uint32_t*>(a.peer[p] + cmd_off)[w] = v;
+        }
+        for (size_t i = t0; i < count; i += stride) {
+            const uint32_t v = sv[i];
+            for (uint32_t p = 0; p < a.world; ++p) reinterpret_cast<uint32_t*>(a.peer[p] + vis_off)[i] = v;
+        }
+    }
+}
+
 // ---- synthetic scene (twin of renderer_b200/scene.py and oracle_synth_entities) ----
 __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;

@@ -146,3 +146,88 @@ def _wrap_device(torch, ptr: int, n: int, dtype, device):
         }
 
     return torch.as_tensor(_Holder(), device=device)
+
+
+class PeerMerger:
+    """The merge over peer memory (rcull_merge_*): per frame, one tiny all_gather of the
+    per-rank (count, index_total) words, then ONE kernel per rank that stores its rebased
+    lists into its slot of every rank's merged allocation through NVLink peer pointers,
+    then a one-word all_reduce as the "everyone has written" barrier.  Nothing in the
+    step touches the host: all of it is enqueued on the current torch stream."""
+
+    def __init__(self, ctx, n_views: int, capacity: int, device, group=None):
+        import ctypes as C
+
+        import torch
+        import torch.distributed as dist
+
+        from . import _lib
+
+        self.torch, self.dist, self.C, self._lib = torch, dist, C, _lib.load()
+        self.ctx, self.group, self.n_views, self.capacity, self.device = ctx, group, n_views, capacity, device
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self._h = C.c_void_p()
+        _lib.check(self._lib.rcull_merge_create(ctx._h, self.world, self.rank, capacity, C.byref(self._h)))
+        mv = ctx.cfg.max_views
+        a, b = C.c_void_p(), C.c_void_p()
+        _lib.check(self._lib.rcull_merge_meta_ptrs(self._h, C.byref(a), C.byref(b)))
+        self.meta_local = _wrap_device(torch, a.value, 2 * mv, torch.int64, device)
+        self.meta_all = _wrap_device(torch, b.value, self.world * 2 * mv, torch.int64, device)
+        self._flag = torch.zeros(1, dtype=torch.int32, device=device)
+        if self.world > 1:  # one-time exchange of the IPC handles of the merged allocations
+            handle = (C.c_ubyte * 64)()
+            _lib.check(self._lib.rcull_merge_ipc_handle(self._h, handle))
+            handles = [None] * self.world
+            dist.all_gather_object(handles, bytes(handle), group=group)
+            for p, h in enumerate(handles):
+                if p != self.rank:
+                    buf = (C.c_ubyte * 64).from_buffer_copy(h)
+                    _lib.check(self._lib.rcull_merge_open_peer(self._h, p, buf))
+            dist.barrier(group=group)
+        self.bytes_sent = 0
+
+    def destroy(self):
+        if self._h:
+            if self.world > 1:
+                self.dist.barrier(group=self.group)  # nobody may still be storing into this allocation
+            self._lib.rcull_merge_destroy(self._h)
+            self._h = self.C.c_void_p()
+
+    def merge(self, buffer_ix: int = 0) -> None:
+        """Enqueue one merge on the current torch stream (after the frame on the same stream)."""
+        from ._lib import check
+
+        s = self.C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
+        check(self._lib.rcull_merge_pack_meta(self._h, buffer_ix, s))
+        if self.world > 1:
+            self.dist.all_gather_into_tensor(self.meta_all, self.meta_local, group=self.group)
+        else:
+            self.meta_all.copy_(self.meta_local)
+        check(self._lib.rcull_merge_scatter(self._h, buffer_ix, self.n_views, s))
+        if self.world > 1:
+            self.dist.all_reduce(self._flag, group=self.group)  # every rank has stored its slices
+
+    def lists(self, view: int):
+        """(cmds_ptr, visible_ptr, counts_ptr, totals_ptr) device addresses of the merged outputs."""
+        from ._lib import check
+
+        C = self.C
+        a, b, c, d = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+        check(self._lib.rcull_merge_lists(self._h, view, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
+        return a.value, b.value, c.value, d.value
+
+    def download(self, view: int):
+        """Blocking read-back of one merged view (tests)."""
+        torch = self.torch
+        from ._lib import CMD_DTYPE
+
+        cp, vp, np_, tp = self.lists(view)
+        torch.cuda.synchronize(self.device)
+        mv = self.ctx.cfg.max_views
+        counts = _wrap_device(torch, np_, mv, torch.int32, self.device).cpu().numpy().view(np.uint32)
+        totals = _wrap_device(torch, tp, mv, torch.int64, self.device).cpu().numpy().view(np.uint64)
+        n = int(min(counts[view], self.capacity))
+        cmds = _wrap_device(torch, cp, max(n, 1) * 5, torch.int32, self.device).cpu().numpy()[: n * 5].view(CMD_DTYPE)
+        vis = _wrap_device(torch, vp, max(n, 1), torch.int32, self.device).cpu().numpy()[:n].view(np.uint32)
+        return cmds, vis, int(counts[view]), int(totals[view])

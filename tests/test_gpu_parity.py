@@ -294,3 +294,76 @@ def test_range_shards_merge_to_the_single_gpu_lists():
     finally:
         for c in ctxs:
             c.destroy()
+
+
+def test_peer_store_merge_two_ranks_in_one_process():
+    """rcull_merge_* with world = 2 emulated in one process (peer pointers set directly):
+    after both ranks scatter, BOTH merged allocations equal the unsharded lists."""
+    import ctypes as C
+
+    import torch
+
+    from renderer_b200 import _lib
+    from renderer_b200.shard import _wrap_device, shard_range
+
+    lib = _lib.load()
+    n, n_views, world = 150_003, 3, 2
+    views = scene.scene_views(n_views)
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, 50.0)
+    with CullContext(n, max_views=n_views, max_meshes=len(MESHES)) as whole:
+        whole.set_mesh_table(MESHES)
+        whole.upload_entities(ps, rot, mesh)
+        whole.frame(views, scene.CAMERA_POS)
+        wc, wt = whole.counts()
+        want_cmds = [whole.cmds(k, int(wc[k])) for k in range(n_views)]
+        want_vis = [whole.visible(k, int(wc[k])) for k in range(n_views)]
+    cap = int(wc.max()) + 7
+    ctxs, merges = [], []
+    dev = torch.device("cuda", 0)
+    try:
+        for r in range(world):
+            lo, hi = shard_range(n, world, r)
+            c = CullContext(hi - lo, max_views=n_views, max_meshes=len(MESHES))
+            c.set_mesh_table(MESHES)
+            c.upload_entities(ps[lo:hi], rot[lo:hi], mesh[lo:hi])
+            c.frame(views, scene.CAMERA_POS, draw_index_base=lo)
+            h = C.c_void_p()
+            _lib.check(lib.rcull_merge_create(c._h, world, r, cap, C.byref(h)))
+            ctxs.append(c), merges.append(h)
+        bases = []
+        for h in merges:
+            b = C.c_void_p()
+            _lib.check(lib.rcull_merge_base(h, C.byref(b)))
+            bases.append(b)
+        metas = []
+        for r, h in enumerate(merges):
+            for p in range(world):
+                _lib.check(lib.rcull_merge_set_peer_ptr(h, p, bases[p]))
+            _lib.check(lib.rcull_merge_pack_meta(h, 0, None))
+            a, b = C.c_void_p(), C.c_void_p()
+            _lib.check(lib.rcull_merge_meta_ptrs(h, C.byref(a), C.byref(b)))
+            metas.append((_wrap_device(torch, a.value, 2 * n_views, torch.int64, dev), _wrap_device(torch, b.value, world * 2 * n_views, torch.int64, dev)))
+        torch.cuda.synchronize()
+        gathered = torch.cat([m[0] for m in metas])  # what the all_gather delivers
+        for m in metas:
+            m[1].copy_(gathered)
+        torch.cuda.synchronize()
+        for h in merges:
+            _lib.check(lib.rcull_merge_scatter(h, 0, n_views, None))
+        torch.cuda.synchronize()
+        for h in merges:
+            for k in range(n_views):
+                a, b, c_, d = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+                _lib.check(lib.rcull_merge_lists(h, k, C.byref(a), C.byref(b), C.byref(c_), C.byref(d)))
+                counts = _wrap_device(torch, c_.value, n_views, torch.int32, dev).cpu().numpy().view(np.uint32)
+                totals = _wrap_device(torch, d.value, n_views, torch.int64, dev).cpu().numpy().view(np.uint64)
+                assert counts[k] == wc[k] and totals[k] == wt[k]
+                got = _wrap_device(torch, a.value, int(wc[k]) * 5, torch.int32, dev).cpu().numpy().view(np.uint32)
+                assert np.array_equal(got, want_cmds[k].view(np.uint32).reshape(-1)), k
+                got = _wrap_device(torch, b.value, int(wc[k]), torch.int32, dev).cpu().numpy().view(np.uint32)
+                assert np.array_equal(got, want_vis[k]), k
+    finally:
+        for h in merges:
+            lib.rcull_merge_destroy(h)
+        for c in ctxs:
+            c.destroy()
