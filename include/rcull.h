@@ -176,6 +176,7 @@ int rcull_merge_set_peer_ptr(rcull_merge *m, uint32_t peer, void *base);
 int rcull_merge_base(rcull_merge *m, void **base);
 /* Device buffers of the exchange: meta_local [2*max_views] u64, meta_all [world][2*max_views] u64. */
 int rcull_merge_meta_ptrs(rcull_merge *m, uint64_t **meta_local, uint64_t **meta_all);
+/* Only needed for a frame issued BEFORE rcull_merge_create: later frames write meta_local themselves. */
 int rcull_merge_pack_meta(rcull_merge *m, uint32_t buffer_ix, void *stream);
 int rcull_merge_scatter(rcull_merge *m, uint32_t buffer_ix, uint32_t n_views, void *stream);
 /* Device pointers of the merged lists of one view and of the merged counts / index totals. */

@@ -11,6 +11,8 @@
 #include <cstring>
 #include <vector>
 
+#include <cub/device/device_radix_sort.cuh>  // per-mesh mode only: stable bucketing of the survivor pairs
+
 #include "rcull_aux.cuh"
 #include "rcull_frame.cuh"
 
@@ -53,6 +55,8 @@ struct OutputSet {
     uint8_t* flags[kMaxViews] = {};
     uint32_t* cmds[kMaxViews] = {};
     uint32_t* visible[kMaxViews] = {};
+    uint32_t* keys[kMaxViews] = {};     // per-mesh mode: slot key of every survivor, draw_index order
+    uint32_t* vis_tmp[kMaxViews] = {};  // per-mesh mode: draw_index of every survivor before bucketing
     uint32_t* counts = nullptr;
     unsigned long long* totals = nullptr;
     CUtensorMap model_map;  // model buffer as [cap/2 rows][32 floats], 16-row boxes, 128-B swizzle
@@ -72,6 +76,11 @@ struct rcull_ctx {
     uint4* lod_tab = nullptr;
     uint32_t n_meshes = 0;
     uint32_t len_small = 0;
+    uint32_t* keys_sorted = nullptr;  // per-mesh mode scratch
+    void* sort_tmp = nullptr;
+    size_t sort_tmp_bytes = 0;
+    uint64_t cap_cmds = 0;  // command capacity per view: cap_vis, or max_meshes * 6 in per-mesh mode
+    unsigned long long* meta_out = nullptr;  // set by rcull_merge_create: the frame kernel writes the exchange words itself
     OutputSet out[3];
     ulonglong2* status = nullptr;
     size_t status_bytes = 0;
@@ -209,6 +218,7 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
     c->cap = (cfg->capacity_entities + kTile - 1) / kTile * kTile;
     c->cap_vis = cfg->capacity_visible ? cfg->capacity_visible : cfg->capacity_entities;
     c->lod_d2_max = lod_threshold(cfg->lod_distance);
+    c->cap_cmds = cfg->output_mode == RCULL_PER_MESH_INSTANCED ? (uint64_t)cfg->max_meshes * kMaxLods : c->cap_vis;
     int rc = 0;
 #define TRY(x)                \
     if ((rc = (x)) != 0) {    \
@@ -233,8 +243,12 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
         if (cfg->materialize_aabb) TRY(dev_alloc(c, &o.aabb, c->cap * 6));
         for (uint32_t v = 0; v < cfg->max_views; ++v) {
             if (cfg->materialize_flags) TRY(dev_alloc(c, &o.flags[v], c->cap));
-            TRY(dev_alloc(c, &o.cmds[v], c->cap_vis * 5));
+            TRY(dev_alloc(c, &o.cmds[v], c->cap_cmds * 5));
             TRY(dev_alloc(c, &o.visible[v], c->cap_vis));
+            if (cfg->output_mode == RCULL_PER_MESH_INSTANCED) {
+                TRY(dev_alloc(c, &o.keys[v], c->cap_vis));
+                TRY(dev_alloc(c, &o.vis_tmp[v], c->cap_vis));
+            }
         }
         TRY(dev_alloc(c, &o.counts, kMaxViews));
         TRY(dev_alloc(c, &o.totals, kMaxViews));
@@ -245,6 +259,18 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
     c->status_bytes = max_tiles * cfg->max_views * sizeof(ulonglong2);
     TRY(dev_alloc(c, &c->status, max_tiles * cfg->max_views));
     TRY(dev_alloc(c, &c->ticket, 2));
+    if (cfg->output_mode == RCULL_PER_MESH_INSTANCED) {
+        if (c->cap_vis > 0x7fffffffull) {
+            rcull_destroy(c);
+            return fail(RCULL_ERR_INVALID, "per-mesh mode sorts at most 2^31-1 survivors per view");
+        }
+        TRY(dev_alloc(c, &c->keys_sorted, c->cap_vis));
+        cub::DeviceRadixSort::SortPairs(nullptr, c->sort_tmp_bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr,
+                                        (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)c->cap_vis, 0, 32);
+        unsigned char* tmp = nullptr;
+        TRY(dev_alloc(c, &tmp, c->sort_tmp_bytes));
+        c->sort_tmp = tmp;
+    }
     if (cudaMemset(c->status, 0, c->status_bytes) != cudaSuccess || cudaMemset(c->ticket, 0, 8) != cudaSuccess) {
         rcull_destroy(c);
         return fail(RCULL_ERR_CUDA, "cudaMemset of scan state failed");
@@ -353,13 +379,14 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     if (n_views < 1 || n_views > c->cfg.max_views) return fail(RCULL_ERR_INVALID, "n_views %u not in 1..%u", n_views, c->cfg.max_views);
     if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
     if (c->n_meshes == 0) return fail(RCULL_ERR_INVALID, "rcull_set_mesh_table has not been called");
-    if (c->cfg.output_mode != RCULL_PER_ENTITY) return fail(RCULL_ERR_INVALID, "output mode %u not available in this build", c->cfg.output_mode);
+    const bool per_mesh = c->cfg.output_mode == RCULL_PER_MESH_INSTANCED;
     CU(cudaSetDevice(c->cfg.device));
     cudaStream_t s = (cudaStream_t)stream;
     OutputSet& o = c->out[buffer_ix];
     if (n == 0) {  // empty query: cull_pass still clears the buffers (cull_pipeline.rs:498-511)
         CU(cudaMemsetAsync(o.counts, 0, kMaxViews * 4, s));
         CU(cudaMemsetAsync(o.totals, 0, kMaxViews * 8, s));
+        if (c->meta_out) CU(cudaMemsetAsync(c->meta_out, 0, 2 * c->cfg.max_views * 8, s));
         return RCULL_OK;
     }
     const uint32_t n_tiles = (uint32_t)((n + kTile - 1) / kTile);
@@ -377,8 +404,8 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     a.aabb = o.aabb;
     for (uint32_t v = 0; v < n_views; ++v) {
         a.flags[v] = o.flags[v];
-        a.cmds[v] = o.cmds[v];
-        a.visible[v] = o.visible[v];
+        a.cmds[v] = per_mesh ? o.keys[v] : o.cmds[v];
+        a.visible[v] = per_mesh ? o.vis_tmp[v] : o.visible[v];
         for (int p = 0; p < 6; ++p) {
             const float* pl = views[v].planes[p];
             PlaneC& pc = a.planes[v][p];
@@ -393,6 +420,8 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     }
     a.counts = o.counts;
     a.totals = o.totals;
+    a.meta_out = c->meta_out;
+    a.max_views = c->cfg.max_views;
     a.status = c->status;
     a.ticket = c->ticket;
     a.error_flag = c->ticket + 1;
@@ -402,12 +431,21 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     a.n_tiles = n_tiles;
     a.n_meshes = c->n_meshes;
     a.len_small = c->len_small;
+    a.per_mesh = per_mesh ? 1u : 0u;
     a.draw_index_base = draw_index_base;
     a.cap_visible = (uint32_t)(c->cap_vis > 0xffffffffull ? 0xffffffffull : c->cap_vis);
     a.cam[0] = cam_pos[0];
     a.cam[1] = cam_pos[1];
     a.cam[2] = cam_pos[2];
     a.lod_d2_max = c->lod_d2_max;
+    if (per_mesh) {
+        const uint64_t n_sorted = n < c->cap_vis ? n : c->cap_vis;
+        for (uint32_t v = 0; v < n_views; ++v) {
+            fill_u32<<<c->sm_count * 2, 256, 0, s>>>(o.keys[v], (size_t)n_sorted, c->n_meshes * kMaxLods);
+            CU(cudaGetLastError());
+            c->launches += 1;
+        }
+    }
     const bool mat = c->cfg.materialize_aabb || c->cfg.materialize_flags;
     int grid = c->sm_count * c->blocks_per_sm[n_views][mat];
     if ((uint32_t)grid > n_tiles) grid = (int)n_tiles;
@@ -425,6 +463,35 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     if (e != cudaSuccess) return fail(RCULL_ERR_CUDA, "transform_cull_compact launch failed: %s", cudaGetErrorString(e));
     c->ticket_base += n_tiles + (uint32_t)grid;  // every CTA draws exactly one ticket past the end
     c->launches += 1;
+    if (per_mesh) {
+        // Stable bucketing by (mesh, lod) slot: radix sort of the (slot, draw_index) pairs on the
+        // key bits only (CUB), then one command per non-empty slot.  Pairs past the survivor
+        // count carry the padding key n_slots (filled below, before the frame kernel ran... the
+        // fill is ordered on the same stream ahead of the launch above).
+        const uint32_t n_slots = c->n_meshes * kMaxLods;
+        int end_bit = 1;
+        while ((1u << end_bit) <= n_slots) ++end_bit;
+        const uint64_t n_sorted = n < c->cap_vis ? n : c->cap_vis;
+        BucketArgs b;
+        memset(&b, 0, sizeof b);
+        for (uint32_t v = 0; v < n_views; ++v) {
+            size_t bytes = c->sort_tmp_bytes;
+            CU(cub::DeviceRadixSort::SortPairs(c->sort_tmp, bytes, (const uint32_t*)o.keys[v], c->keys_sorted,
+                                               (const uint32_t*)o.vis_tmp[v], o.visible[v], (int)n_sorted, 0, end_bit, s));
+            // the sorted keys of this view are consumed before the next view's sort reuses keys_sorted
+            BucketArgs one = b;
+            one.keys[0] = c->keys_sorted;
+            one.cmds[0] = o.cmds[v];
+            one.counts = o.counts + v;
+            one.totals = o.totals + v;
+            one.lod_tab = c->lod_tab;
+            one.n_slots = n_slots;
+            one.n_sorted = (uint32_t)n_sorted;
+            mesh_buckets<<<1, 1024, 0, s>>>(one);
+            CU(cudaGetLastError());
+            c->launches += 1;
+        }
+    }
     return RCULL_OK;
 }
 
@@ -511,7 +578,7 @@ int rcull_download_flags(rcull_ctx* c, uint32_t buffer_ix, uint32_t view, uint64
 int rcull_download_cmds(rcull_ctx* c, uint32_t buffer_ix, uint32_t view, uint64_t first, uint64_t n, rcull_draw_cmd* dst) {
     DL_PROLOGUE("rcull_download_cmds");
     if (view >= c->cfg.max_views) return fail(RCULL_ERR_INVALID, "view %u of %u", view, c->cfg.max_views);
-    if (first + n > c->cap_vis) return fail(RCULL_ERR_INVALID, "command range out of bounds");
+    if (first + n > c->cap_cmds) return fail(RCULL_ERR_INVALID, "command range out of bounds");
     CU(cudaMemcpy(dst, c->out[buffer_ix].cmds[view] + first * 5, n * 20, cudaMemcpyDeviceToHost));
     return RCULL_OK;
 }
@@ -579,6 +646,7 @@ void rcull_merge_destroy(rcull_merge* m) {
     if (!m) return;
     cudaSetDevice(m->ctx->cfg.device);
     cudaDeviceSynchronize();
+    if (m->ctx->meta_out == m->meta_local) m->ctx->meta_out = nullptr;
     for (uint32_t p = 0; p < m->world; ++p)
         if (m->opened[p]) cudaIpcCloseMemHandle(m->peer[p]);
     cudaFree(m->base);
@@ -613,6 +681,7 @@ int rcull_merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t cap
     cudaMemset(m->counts, 0, mv * 4);
     cudaMemset(m->totals, 0, mv * 8);
     m->peer[rank] = m->base;
+    c->meta_out = m->meta_local;  // frames issued from now on write the exchange words directly
     *out = m;
     return RCULL_OK;
 }

@@ -99,6 +99,78 @@ __global__ void __launch_bounds__(256) scatter_rebased(const __grid_constant__ M
     }
 }
 
+// ---- per-mesh instanced emission (BASELINE config 4; compact_draw_stream.comp:41 keep-rule on
+// instanceCount) ----------------------------------------------------------------------
+// The frame kernel leaves, per view, the survivors in draw_index order as (slot key,
+// draw_index) pairs; a stable radix sort by key buckets them; this kernel turns the sorted
+// keys into one command per NON-EMPTY (mesh, lod) slot, in slot order.
+struct BucketArgs {
+    const uint32_t* keys[8];   // sorted slot keys per view (padding key = n_slots)
+    uint32_t* cmds[8];         // out: 5 words per command
+    uint32_t* counts;          // in: survivors per view; out: commands per view
+    unsigned long long* totals;  // out: instances per view
+    const uint4* lod_tab;      // index_len, first_index, vertex_offset
+    uint32_t n_slots, n_sorted;  // n_sorted: number of pairs that went through the sort
+};
+
+__device__ __forceinline__ uint32_t lower_bound_u32(const uint32_t* __restrict__ a, uint32_t n, uint32_t key) {
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(a + mid) < key) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(1024) mesh_buckets(const __grid_constant__ BucketArgs a) {
+    __shared__ uint32_t warp_tot[32];
+    __shared__ uint32_t run_base;
+    const uint32_t view = blockIdx.x, tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint32_t* keys = a.keys[view];
+    uint32_t n_surv = a.counts[view];
+    if (n_surv > a.n_sorted) n_surv = a.n_sorted;
+    if (tid == 0) run_base = 0;
+    __syncthreads();
+    for (uint32_t s0 = 0; s0 < a.n_slots; s0 += blockDim.x) {
+        const uint32_t s = s0 + tid;
+        uint32_t first = 0, cnt = 0;
+        if (s < a.n_slots) {
+            first = lower_bound_u32(keys, n_surv, s);
+            cnt = lower_bound_u32(keys, n_surv, s + 1) - first;
+        }
+        const uint32_t b = __ballot_sync(kFullMask, cnt > 0);
+        if (lane == 0) warp_tot[warp] = __popc(b);
+        __syncthreads();
+        uint32_t before = run_base;
+        for (uint32_t w = 0; w < warp; ++w) before += warp_tot[w];
+        if (cnt > 0) {
+            const uint4 L = __ldg(a.lod_tab + s);
+            uint32_t* c = a.cmds[view] + (size_t)(before + __popc(b & ((1u << lane) - 1u))) * 5;
+            c[0] = L.x;    // indexCount
+            c[1] = cnt;    // instanceCount
+            c[2] = L.y;    // firstIndex: the LOD's own first_index
+            c[3] = L.z;    // vertexOffset
+            c[4] = first;  // firstInstance: bucket start in the bucketed visible list
+        }
+        __syncthreads();
+        if (tid == 0) {
+            uint32_t t = run_base;
+            for (uint32_t w = 0; w < (blockDim.x >> 5); ++w) t += warp_tot[w];
+            run_base = t;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        a.counts[view] = run_base;
+        a.totals[view] = n_surv;
+    }
+}
+
+__global__ void __launch_bounds__(256) fill_u32(uint32_t* __restrict__ p, size_t n, uint32_t v) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) p[i] = v;
+}
+
 // ---- synthetic scene (twin of renderer_b200/scene.py and oracle_synth_entities) ----
 __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;

@@ -56,6 +56,8 @@ struct FrameArgs {
     uint32_t* visible[kMaxViews];
     uint32_t* counts;
     unsigned long long* totals;
+    unsigned long long* meta_out;  // optional [2 * max_views]: counts then totals as u64 (merge exchange words)
+    uint32_t max_views;
     ulonglong2* status;  // [views][n_tiles]
     uint32_t* ticket;
     uint32_t* error_flag;
@@ -66,6 +68,7 @@ struct FrameArgs {
     uint32_t n_meshes;
     uint32_t draw_index_base;
     uint32_t cap_visible;
+    uint32_t per_mesh;   // RCULL_PER_MESH_INSTANCED: emit (slot key, draw_index) pairs for the bucketing passes
     uint32_t len_small;  // every index_len in the mesh table is < 2^25: 128 of them add up in 32 bits
     float cam[3];
     float lod_d2_max;  // lod 1 iff |cam-pos|^2 > lod_d2_max  (== sqrt(d2) > lod_distance)
@@ -255,6 +258,10 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
                             if (tile == n_tiles - 1) {
                                 args.counts[k] = ic;
                                 args.totals[k] = il;
+                                if (args.meta_out != nullptr) {
+                                    args.meta_out[k] = ic;
+                                    args.meta_out[args.max_views + k] = il;
+                                }
                             }
                         }
                     }
@@ -287,13 +294,14 @@ __device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameS
     for (uint32_t i0 = 0; i0 < total; i0 += 32) {
         const uint32_t i = i0 + lane;
         const bool act = i < total;
-        uint32_t k = 0, e = 0;
+        uint32_t k = 0, e = 0, slot = 0;
         uint4 L = make_uint4(0, 0, 0, 0);
         if (act) {
 #pragma unroll
             for (int kk = 0; kk < V - 1; ++kk) k += i >= vend[kk] ? 1u : 0u;
             e = warp * kWarpSpan + wlist[i];
-            L = __ldg(args.lod_tab + slot_of[e]);
+            slot = slot_of[e];
+            L = __ldg(args.lod_tab + slot);
         }
         const uint32_t incl = warp_incl_scan_u32(L.x, lane);
         const uint32_t excl = carry + incl - L.x;
@@ -302,13 +310,17 @@ __device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameS
             const uint32_t pos = sm.adj_cnt[buf][k][warp] + i;
             if (pos < args.cap_visible) {
                 const uint32_t draw_index = args.draw_index_base + tile_base + e;
+                args.visible[k][pos] = draw_index;
+                if (args.per_mesh) {  // per-mesh mode: the survivor's (mesh, lod) slot is the sort key
+                    args.cmds[k][pos] = slot;
+                    continue;
+                }
                 uint32_t* c = args.cmds[k] + (size_t)pos * 5;
                 c[0] = L.x;                               // indexCount (entity-level upper bound)
                 c[1] = 1u;                                // instanceCount
                 c[2] = sm.adj_len[buf][k][warp] + excl;   // firstIndex: running sum of earlier survivors' index_len
                 c[3] = L.z;                               // vertexOffset
                 c[4] = draw_index;                        // firstInstance
-                args.visible[k][pos] = draw_index;
             }
         }
     }

@@ -166,3 +166,49 @@ def scene_views(n_views: int = 1) -> np.ndarray:
     for k in range(n_views - 1):
         vs.append(light_view(LIGHT_POS[k % len(LIGHT_POS)] * (1.0 + 0.25 * (k // len(LIGHT_POS)))))
     return np.stack(vs).astype(np.float32)
+
+
+# ---- BASELINE config 4: Sponza instanced, per-mesh compaction -------------------------
+def sponza_mesh_table(path: str | None = None):
+    """Mesh table from the committed extract of the reference's Sponza.gltf
+    (tests/golden/sponza_meshes.json, made by tests/golden/make_sponza_table.py).
+    Returns (table, node_scale)."""
+    import json
+    import os
+
+    if path is None:
+        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "sponza_meshes.json")
+    d = json.load(open(path))
+    t = np.zeros(len(d["meshes"]), MESH_DTYPE)
+    for i, m in enumerate(d["meshes"]):
+        t[i]["aabb_min"], t[i]["aabb_max"] = m["aabb_min"], m["aabb_max"]
+        t[i]["n_lods"] = len(m["lods"])
+        for l, (first, length) in enumerate(m["lods"]):
+            t[i]["lod"][l] = (first, length)
+        t[i]["vertex_offset"] = m["vertex_offset"]
+    return t, float(d["node_scale"])
+
+
+def sponza_instances(n_entities: int, n_meshes: int, node_scale: float, spacing: float = 40.0, seed: int = SEED):
+    """n_entities = copies x n_meshes primitives (the last copy may be cut short): every
+    primitive of a copy is its own entity, as scene_loader.rs:588-599 spawns them, sharing the
+    copy's transform.  Copies sit on a jittered 3-D grid centred on the origin, random yaw,
+    uniform scale = the glTF node scale (scene_loader.rs:760-765 takes scale[0])."""
+    copies = -(-n_entities // n_meshes)
+    side = int(np.ceil(copies ** (1.0 / 3.0)))
+    c = np.arange(copies, dtype=np.uint64)
+    grid = np.stack([c % side, (c // side) % side, c // (side * side)], axis=1).astype(np.float32)
+    jitter = np.stack([_unit24(_chan(seed, c, a)) for a in range(3)], axis=1) - _F(0.5)
+    pos = ((grid - _F((side - 1) / 2.0)) + jitter * _F(0.5)) * _F(spacing)
+    yaw = _unit24(_chan(seed, c, 3)).astype(np.float64) * 2.0 * np.pi
+    q = np.zeros((copies, 4), np.float64)
+    q[:, 1], q[:, 3] = np.sin(yaw / 2), np.cos(yaw / 2)
+    q = (q / np.linalg.norm(q, axis=1, keepdims=True)).astype(np.float32)
+    nn = np.sqrt((q[:, 0] * q[:, 0] + q[:, 2] * q[:, 2]) + (q[:, 1] * q[:, 1] + q[:, 3] * q[:, 3])).astype(np.float32)
+    q = (q / nn[:, None]).astype(np.float32)  # UnitQuaternion::new_normalize (scene_loader.rs:590)
+    e = np.arange(n_entities, dtype=np.int64)
+    copy_of, mesh = e // n_meshes, (e % n_meshes).astype(np.uint32)
+    ps = np.empty((n_entities, 4), np.float32)
+    ps[:, :3] = pos[copy_of]
+    ps[:, 3] = _F(node_scale)
+    return ps, np.ascontiguousarray(q[copy_of]), mesh

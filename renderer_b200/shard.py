@@ -199,7 +199,8 @@ class PeerMerger:
         from ._lib import check
 
         s = self.C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
-        check(self._lib.rcull_merge_pack_meta(self._h, buffer_ix, s))
+        # no pack step: a context with a merge attached writes the exchange words from the
+        # frame kernel itself (frames must be issued after this object was created)
         if self.world > 1:
             self.dist.all_gather_into_tensor(self.meta_all, self.meta_local, group=self.group)
         else:

@@ -367,3 +367,39 @@ def test_peer_store_merge_two_ranks_in_one_process():
             lib.rcull_merge_destroy(h)
         for c in ctxs:
             c.destroy()
+
+
+def _per_mesh_compare(ps, rot, mesh, meshes, views, n_views, lod_distance=10.0, base=0):
+    from renderer_b200 import PER_MESH_INSTANCED
+
+    n = len(mesh)
+    pos, quat, scale = scene.to_components(ps, rot)
+    ref = O.frame(pos, quat, scale, mesh, meshes, views, scene.CAMERA_POS, lod_distance=lod_distance, n_threads=8, want=("flags",))
+    with CullContext(n, max_views=n_views, max_meshes=len(meshes), output_mode=PER_MESH_INSTANCED, lod_distance=lod_distance) as ctx:
+        ctx.set_mesh_table(meshes)
+        ctx.upload_entities(ps, rot, mesh)
+        for _ in range(2):  # twice: scratch reuse across frames
+            ctx.frame(views, scene.CAMERA_POS, draw_index_base=base)
+        counts, totals = ctx.counts()
+        for k in range(n_views):
+            want_cmds, want_vis = O.emit_per_mesh(pos, mesh, ref["flags"][k], meshes, scene.CAMERA_POS, lod_distance, base)
+            assert counts[k] == len(want_cmds) and totals[k] == len(want_vis), (k, counts[k], len(want_cmds))
+            assert np.array_equal(ctx.cmds(k, len(want_cmds)), want_cmds), f"view {k} per-mesh commands"
+            assert np.array_equal(ctx.visible(k, len(want_vis)), want_vis), f"view {k} bucketed visible list"
+            assert int(want_cmds["instanceCount"].sum()) == len(want_vis)
+    return counts
+
+
+@pytest.mark.parametrize("n", [1, 900, 50_000])
+def test_per_mesh_instanced_mode_synthetic(n):
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, 30.0)
+    _per_mesh_compare(ps, rot, mesh, MESHES, scene.scene_views(3), 3, base=17)
+
+
+def test_config4_sponza_instanced_per_mesh():
+    """BASELINE configs[3] (reduced to 300 k entities so the oracle stays fast; bench.py has 4 M)."""
+    table, node_scale = scene.sponza_mesh_table()
+    assert len(table) == 87
+    ps, rot, mesh = scene.sponza_instances(300_000, len(table), node_scale)
+    counts = _per_mesh_compare(ps, rot, mesh, table, scene.scene_views(2), 2)
+    assert 0 < counts[0] <= len(table) * 2
