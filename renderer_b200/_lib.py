@@ -17,7 +17,7 @@ MAX_LODS = 6
 PER_ENTITY = 0
 PER_MESH_INSTANCED = 1
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "librcull.so")
+LIB_PATH = os.environ.get("RCULL_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "librcull.so")  # RCULL_LIB: A/B builds of the same ABI
 
 
 class RcullError(RuntimeError):

@@ -22,12 +22,8 @@ static_assert(sizeof(rcull_mesh) == 80, "rcull_mesh layout");
 static_assert(sizeof(rcull_draw_cmd) == 20, "VkDrawIndexedIndirectCommand stride");
 static_assert(sizeof(rcull_config) == 48 && sizeof(rcull_view) == 96, "rcull_config / rcull_view layout");
 static_assert(RCULL_MAX_VIEWS == kMaxViews && RCULL_MAX_LODS == kMaxLods, "header/kernel constants");
-// two CTAs per SM: 228 KB of shared memory per SM, 1 KB reserved per CTA
-constexpr size_t kSmemPerCta = (228 * 1024 - 2 * 1024) / 2;
-static_assert(frame_smem_bytes<1>() <= kSmemPerCta && frame_smem_bytes<2>() <= kSmemPerCta &&
-              frame_smem_bytes<3>() <= kSmemPerCta && frame_smem_bytes<4>() <= kSmemPerCta &&
-              frame_smem_bytes<5>() <= kSmemPerCta && frame_smem_bytes<6>() <= kSmemPerCta &&
-              frame_smem_bytes<7>() <= kSmemPerCta && frame_smem_bytes<8>() <= kSmemPerCta, "frame kernel must fit two CTAs per SM");
+static_assert(frame_smem_bytes<1>() <= kSmemPerCta && frame_smem_bytes<5>() <= kSmemPerCta && frame_smem_bytes<8>() <= kSmemPerCta,
+              "frame kernel must fit kCtasPerSm CTAs per SM");
 
 namespace {
 
@@ -83,6 +79,7 @@ struct rcull_ctx {
     unsigned long long* meta_out = nullptr;  // set by rcull_merge_create: the frame kernel writes the exchange words itself
     OutputSet out[3];
     ulonglong2* status = nullptr;
+    ulonglong2* gstatus = nullptr;
     size_t status_bytes = 0;
     uint32_t* ticket = nullptr;  // [0] = tile ticket, [1] = error flag
     uint32_t ticket_base = 0;
@@ -256,8 +253,10 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
         cudaMemset(o.totals, 0, kMaxViews * 8);
     }
     const size_t max_tiles = c->cap / kTile;
-    c->status_bytes = max_tiles * cfg->max_views * sizeof(ulonglong2);
-    TRY(dev_alloc(c, &c->status, max_tiles * cfg->max_views));
+    const size_t max_groups = (max_tiles + kGroup - 1) / kGroup;  // group descriptors follow the tile descriptors
+    c->status_bytes = (max_tiles + max_groups) * cfg->max_views * sizeof(ulonglong2);
+    TRY(dev_alloc(c, &c->status, (max_tiles + max_groups) * cfg->max_views));
+    c->gstatus = c->status + max_tiles * cfg->max_views;
     TRY(dev_alloc(c, &c->ticket, 2));
     if (cfg->output_mode == RCULL_PER_MESH_INSTANCED) {
         if (c->cap_vis > 0x7fffffffull) {
@@ -415,7 +414,8 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
             pc.px = make_float2(pl[0], pl[0]);
             pc.py = make_float2(pl[1], pl[1]);
             pc.pz = make_float2(pl[2], pl[2]);
-            pc.pw = pl[3];
+            pc.pw = make_float2(pl[3], pl[3]);
+            pc.one = make_float2(1.0f, 1.0f);
         }
     }
     a.counts = o.counts;
@@ -423,6 +423,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     a.meta_out = c->meta_out;
     a.max_views = c->cfg.max_views;
     a.status = c->status;
+    a.gstatus = c->gstatus;
     a.ticket = c->ticket;
     a.error_flag = c->ticket + 1;
     a.ticket_base = c->ticket_base;
@@ -618,6 +619,17 @@ int rcull_synth_entities(rcull_ctx* c, uint64_t seed, uint64_t first_global, uin
 }
 
 uint64_t rcull_launch_count(rcull_ctx* c) { return c ? c->launches : 0; }
+
+#ifdef RCULL_SCAN_STATS  // diagnostic build only, not part of include/rcull.h
+int rcull_debug_stats(uint64_t out[16], int reset) {
+    if (cudaMemcpyFromSymbol(out, rcull::g_scan_stats, 16 * 8) != cudaSuccess) return -1;
+    if (reset) {
+        uint64_t z[16] = {0};
+        if (cudaMemcpyToSymbol(rcull::g_scan_stats, z, 16 * 8) != cudaSuccess) return -1;
+    }
+    return 0;
+}
+#endif
 
 }  // extern "C"
 

@@ -20,7 +20,12 @@
 
 namespace rcull {
 
-constexpr int kComputeWarps = 7;  // + 1 scan warp = 8 warps: two CTAs fill an SM's register file at 112 regs
+#ifndef RCULL_COMPUTE_WARPS
+#define RCULL_COMPUTE_WARPS 15
+#endif
+constexpr int kComputeWarps = RCULL_COMPUTE_WARPS;  // + 1 scan warp; 7 + 1: two CTAs fill an SM's register file at 112 regs, 15 + 1: one CTA does
+constexpr int kCtasPerSm = kComputeWarps <= 7 ? 2 : 1;
+constexpr size_t kSmemPerCta = (228 * 1024 - kCtasPerSm * 1024) / kCtasPerSm;  // 228 KB per SM, 1 KB reserved per CTA
 constexpr int kThreads = (kComputeWarps + 1) * 32;  // + scan warp
 constexpr int kItems = 4;                           // entities per thread per tile
 constexpr int kTile = kComputeWarps * 32 * kItems;  // 896 entities
@@ -30,8 +35,18 @@ constexpr int kMaxBufs = 4;   // survivor bookkeeping ring (tiles whose commands
 constexpr int kRing = 8;      // tile-id ring: bookkeeping ring + the tile being loaded + slack
 constexpr int kMaxViews = 8;
 constexpr int kMaxLods = 6;
+constexpr int kGroup = 64;   // tiles per look-back group (two windows of 32 lanes)
 constexpr uint32_t kStageBytes = kTile * (16 + 16 + 4);  // pos_scale + rot + mesh
 constexpr int kMatBoxBytes = 32 * 64;                    // 32 model matrices = one TMA store box
+
+#ifdef RCULL_SCAN_STATS  // diagnostic build only (profiles/scan_stats.py): where the scan and the waits spend their time
+__device__ unsigned long long g_scan_stats[16];
+#define RCULL_STAT(i, v) atomicAdd(&rcull::g_scan_stats[i], (unsigned long long)(v))
+#define RCULL_CLOCK() clock64()
+#else
+#define RCULL_STAT(i, v) ((void)0)
+#define RCULL_CLOCK() 0ll
+#endif
 
 // Tile descriptor: x = epoch:30 | flag:2 | count:32, y = index sum.
 constexpr uint64_t kFlagAgg = 1, kFlagIncl = 2;
@@ -41,7 +56,8 @@ constexpr uint64_t kFlagAgg = 1, kFlagIncl = 2;
 struct PlaneC {
     float2 ax, ay, az;  // |p.x|, |p.y|, |p.z|
     float2 px, py, pz;
-    float pw, pad0, pad1, pad2;
+    float2 pw;   // p.w twice
+    float2 one;  // 1.0 twice: the multiplier that turns the packed FMA into an exactly rounded add
 };
 
 struct FrameArgs {
@@ -58,7 +74,8 @@ struct FrameArgs {
     unsigned long long* totals;
     unsigned long long* meta_out;  // optional [2 * max_views]: counts then totals as u64 (merge exchange words)
     uint32_t max_views;
-    ulonglong2* status;  // [views][n_tiles]
+    ulonglong2* status;   // [views][n_tiles]
+    ulonglong2* gstatus;  // [views][ceil(n_tiles / kGroup)] group descriptors of the two-level look-back
     uint32_t* ticket;
     uint32_t* error_flag;
     uint32_t ticket_base;
@@ -103,13 +120,16 @@ struct FrameSmem {
 };
 
 template <int V>
-__host__ __device__ constexpr int frame_bufs() {
-    return V <= 4 ? 4 : V <= 6 ? 3 : 2;  // what still lets two CTAs share an SM's shared memory
+__host__ __device__ constexpr int frame_bufs() {  // what still lets kCtasPerSm CTAs share an SM's shared memory
+    constexpr size_t fixed = sizeof(FrameSmem) + V * 6 * sizeof(PlaneC) + 1024, per_buf = (4 + V) * kTile;
+    constexpr size_t b = (kSmemPerCta - fixed) / per_buf;
+    return b > (size_t)kMaxBufs ? kMaxBufs : (int)b;
 }
 template <int V>
 constexpr size_t frame_smem_bytes() {
     return sizeof(FrameSmem) + V * 6 * sizeof(PlaneC) + frame_bufs<V>() * (4 + V) * kTile + 1024;  // + slack to align the base
 }
+static_assert(frame_bufs<1>() >= 2 && frame_bufs<kMaxViews>() >= 2, "at least two tiles of survivor bookkeeping");
 
 __device__ __forceinline__ FrameSmem& frame_smem(unsigned char* raw) {
     const uint32_t a = smem_u32(raw);
@@ -129,25 +149,34 @@ __device__ __forceinline__ bool desc_ready(const ulonglong2& d, uint32_t epoch) 
 //   publish  -- as soon as the compute warps are done with a tile, reduce their
 //               per-warp counts / index sums and publish the tile AGGREGATE; this only
 //               depends on the CTA's own work, so aggregates appear without delay;
-//   resolve  -- for the oldest unresolved tile, one look-back round per pass: all views
-//               together, 32*U predecessors per view with every load in flight at
-//               once (CTAs run in waves, so the last tile of a wave walks back over a
-//               whole wave of aggregates).  A window that is not fully published yet
-//               is simply retried on the next pass.
+//   resolve  -- for the oldest unresolved tile, one look-back round per pass, all views
+//               together, every load in flight at once.  A window that is not fully
+//               published yet is simply retried on the next pass.
+// The look-back is TWO-LEVEL.  Tiles form groups of kGroup = 64 consecutive tiles.  Round 1
+// walks the tile's own group (at most 63 predecessors = one window of 2 x 32 lanes); if no
+// inclusive prefix turns up there, the following rounds walk GROUP descriptors, 64 groups
+// (4096 tiles) per window.  The last tile of a group is its milestone: what its round 1 sums
+// up, plus its own aggregate, is the group aggregate, and its inclusive prefix is the group's.
+// A flat look-back resolves at most (window / round latency) tiles per microsecond along the
+// chain of inclusive prefixes -- with 5 views and 64-wide windows that was slower than the
+// streaming part of the kernel; with groups the chain has one link per 64 tiles.
 template <int V>
 __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, uint32_t lane) {
-    constexpr int U = V <= 4 ? 4 : 2;
+    constexpr int U = kGroup / 32;
     constexpr uint32_t B = frame_bufs<V>();
-    const uint32_t epoch = args.epoch, n_tiles = args.n_tiles;
+    const uint32_t epoch = args.epoch, n_tiles = args.n_tiles, n_groups = (n_tiles + kGroup - 1) / kGroup;
     const uint64_t tag = (uint64_t)epoch << 34;
-    const ulonglong2 virt = make_ulonglong2(tag | (kFlagIncl << 32), 0ull);  // tile -1: inclusive prefix 0
+    const ulonglong2 virt = make_ulonglong2(tag | (kFlagIncl << 32), 0ull);  // before the first group: inclusive prefix 0
+    const ulonglong2 none = make_ulonglong2(tag | (kFlagAgg << 32), 0ull);   // lanes past the group's first tile
     ulonglong2* const status = args.status;
+    ulonglong2* const gstatus = args.gstatus;
     uint32_t pub = 0, res = 0;  // tiles published / resolved so far (iteration numbers)
-    bool ended = false, active = false;
-    uint32_t acc_c[V], tile = 0;
+    bool ended = false, active = false, groups = false;
+    uint32_t acc_c[V], tile = 0, in_group = 0, grp = 0;
     uint64_t acc_l[V];
     bool open[V];
     int base = 0;
+    long long t_pub[kMaxBufs] = {0, 0, 0, 0}, t_act = 0;
     while (true) {
         bool progress = false;
         // ---- publish ----
@@ -188,6 +217,192 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
                     vstart_l += (uint32_t)l;
                 }
                 __syncwarp();
+                t_pub[pub % B] = RCULL_CLOCK();
+                ++pub;
+            }
+        }
+        // ---- resolve ----
+        if (res < pub) {
+            if (!active) {
+                tile = sm.tile_ring[res % kRing];
+                in_group = tile % kGroup;
+                grp = tile / kGroup;
+                groups = false;
+#pragma unroll
+                for (int k = 0; k < V; ++k) {
+                    acc_c[k] = 0;
+                    acc_l[k] = 0;
+                    open[k] = tile != 0;
+                }
+                active = true;
+                t_act = RCULL_CLOCK();
+            }
+            if (lane == 0) RCULL_STAT(2, 1);
+            ulonglong2 d[V][U];
+#pragma unroll
+            for (int k = 0; k < V; ++k)
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    if (!groups) {  // predecessors inside the tile's own group
+                        const uint32_t back = lane + 32u * u;
+                        d[k][u] = (open[k] && back < in_group) ? ld_relaxed_v2(status + (size_t)k * n_tiles + (tile - 1u - back)) : none;
+                    } else {  // earlier groups
+                        const int g = base - 32 * u;
+                        d[k][u] = (open[k] && g >= 0) ? ld_relaxed_v2(gstatus + (size_t)k * n_groups + g) : virt;
+                    }
+                }
+            // all views walk the same windows: a round only counts when every open view can use it
+            bool ok = true;
+#pragma unroll
+            for (int k = 0; k < V; ++k)
+#pragma unroll
+                for (int u = 0; u < U; ++u) ok = ok && desc_ready(d[k][u], epoch);
+            if (__all_sync(kFullMask, ok)) {
+                progress = true;
+                if (lane == 0) RCULL_STAT(3, 1);
+                bool any_open = false;
+#pragma unroll
+                for (int k = 0; k < V; ++k) {
+                    if (!open[k]) continue;
+                    bool stopped = false;
+#pragma unroll
+                    for (int u = 0; u < U; ++u) {
+                        const uint32_t incl_mask = __ballot_sync(kFullMask, ((uint32_t)(d[k][u].x >> 32) & 3u) == kFlagIncl);
+                        if (!stopped) {
+                            const uint32_t stop = incl_mask ? (uint32_t)__ffs(incl_mask) - 1u : 31u;
+                            if (lane <= stop) {
+                                acc_c[k] += (uint32_t)d[k][u].x;
+                                acc_l[k] += d[k][u].y;
+                            }
+                            stopped = incl_mask != 0u;
+                        }
+                    }
+                    open[k] = !stopped;
+                    any_open = any_open || !stopped;
+                }
+                if (!groups) {
+                    // Milestone tile: its in-group predecessors plus itself are the group.  Views that
+                    // already met an inclusive prefix publish the group's inclusive value further down.
+                    if (in_group == kGroup - 1) {
+                        const uint32_t buf = res % B;
+#pragma unroll
+                        for (int k = 0; k < V; ++k) {
+                            if (!open[k]) continue;
+                            const uint32_t gc = __reduce_add_sync(kFullMask, acc_c[k]);
+                            const uint64_t gl = warp_sum_u64(acc_l[k]);
+                            acc_c[k] = lane == 0 ? gc : 0u;
+                            acc_l[k] = lane == 0 ? gl : 0ull;
+                            if (lane == 0)
+                                st_relaxed_v2(gstatus + (size_t)k * n_groups + grp, tag | (kFlagAgg << 32) | (gc + sm.agg_cnt[buf][k]),
+                                              gl + sm.agg_len[buf][k]);
+                        }
+                    }
+                    groups = true;
+                    base = (int)grp - 1 - (int)lane;  // this lane's nearest earlier group
+                } else {
+                    base -= 32 * U;
+                }
+                if (!any_open) {  // resolved: publish inclusive values, hand the offsets to the compute warps
+                    const uint32_t buf = res % B;
+#pragma unroll
+                    for (int k = 0; k < V; ++k) {
+                        const uint32_t ec = __reduce_add_sync(kFullMask, acc_c[k]);
+                        const uint64_t el = warp_sum_u64(acc_l[k]);
+                        if (lane < kComputeWarps) {
+                            sm.adj_cnt[buf][k][lane] += ec;
+                            sm.adj_len[buf][k][lane] += (uint32_t)el;  // firstIndex is u32 and wraps like the reference's
+                        }
+                        if (lane == 0) {
+                            const uint32_t ic = ec + sm.agg_cnt[buf][k];
+                            const uint64_t il = el + sm.agg_len[buf][k];
+                            if (tile != 0) st_relaxed_v2(status + (size_t)k * n_tiles + tile, tag | (kFlagIncl << 32) | ic, il);
+                            if (in_group == kGroup - 1) st_relaxed_v2(gstatus + (size_t)k * n_groups + grp, tag | (kFlagIncl << 32) | ic, il);
+                            if (tile == n_tiles - 1) {
+                                args.counts[k] = ic;
+                                args.totals[k] = il;
+                                if (args.meta_out != nullptr) {
+                                    args.meta_out[k] = ic;
+                                    args.meta_out[args.max_views + k] = il;
+                                }
+                            }
+                        }
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&sm.bases[buf]);
+                    if (lane == 0) {
+                        const long long now = RCULL_CLOCK();
+                        RCULL_STAT(0, 1);
+                        RCULL_STAT(1, now - t_pub[res % B]);
+                        RCULL_STAT(9, now - t_act);
+                    }
+                    ++res;
+                    active = false;
+                }
+            }
+        } else if (ended) {
+            break;
+        }
+        if (!progress) __nanosleep(200);
+    }
+}
+
+#ifndef RCULL_TWO_LEVEL
+template <int V>
+__device__ __forceinline__ void scan_warp_flat(const FrameArgs& args, FrameSmem& sm, uint32_t lane) {
+    constexpr int U = V <= 4 ? 4 : 2;
+    constexpr uint32_t B = frame_bufs<V>();
+    const uint32_t epoch = args.epoch, n_tiles = args.n_tiles;
+    const uint64_t tag = (uint64_t)epoch << 34;
+    const ulonglong2 virt = make_ulonglong2(tag | (kFlagIncl << 32), 0ull);  // tile -1: inclusive prefix 0
+    ulonglong2* const status = args.status;
+    uint32_t pub = 0, res = 0;  // tiles published / resolved so far (iteration numbers)
+    bool ended = false, active = false;
+    uint32_t acc_c[V], tile = 0;
+    uint64_t acc_l[V];
+    bool open[V];
+    int base = 0;
+    long long t_pub[kMaxBufs] = {0, 0, 0, 0}, t_act = 0;
+    while (true) {
+        bool progress = false;
+        // ---- publish ----
+        if (!ended && pub - res < B && mbar_test(&sm.done[pub % B], (pub / B) & 1u)) {
+            const uint32_t buf = pub % B, t = sm.tile_ring[pub % kRing];
+            progress = true;
+            if (t >= n_tiles) {
+                ended = true;  // end marker, passed on by the compute warps
+            } else {
+                uint32_t vstart_c = 0, vstart_l = 0;
+#pragma unroll
+                for (int k = 0; k < V; ++k) {  // lanes 0..6 stand for the compute warps
+                    const uint32_t c = lane < kComputeWarps ? sm.wcnt[buf][k][lane] : 0u;
+                    const uint64_t l = lane < kComputeWarps ? sm.wlen[buf][k][lane] : 0ull;
+                    uint32_t ic = c;
+                    uint64_t il = l;
+#pragma unroll
+                    for (int o = 1; o < kComputeWarps; o <<= 1) {
+                        const uint32_t tc = __shfl_up_sync(kFullMask, ic, o);
+                        const uint64_t tl = __shfl_up_sync(kFullMask, il, o);
+                        if (lane >= (uint32_t)o) {
+                            ic += tc;
+                            il += tl;
+                        }
+                    }
+                    if (lane < kComputeWarps) {
+                        // (prefix over lower warps) - (start of view k in the warp's combined list);
+                        // the tile's exclusive prefix is added when it is resolved
+                        sm.adj_cnt[buf][k][lane] = (ic - c) - vstart_c;
+                        sm.adj_len[buf][k][lane] = (uint32_t)(il - l) - vstart_l;
+                    }
+                    if (lane == kComputeWarps - 1) {
+                        sm.agg_cnt[buf][k] = ic;
+                        sm.agg_len[buf][k] = il;
+                        st_relaxed_v2(status + (size_t)k * n_tiles + t, tag | ((t == 0 ? kFlagIncl : kFlagAgg) << 32) | ic, il);
+                    }
+                    vstart_c += c;
+                    vstart_l += (uint32_t)l;
+                }
+                __syncwarp();
+                t_pub[pub % B] = RCULL_CLOCK();
                 ++pub;
             }
         }
@@ -203,7 +418,9 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
                     open[k] = tile != 0;
                 }
                 active = true;
+                t_act = RCULL_CLOCK();
             }
+            if (lane == 0) RCULL_STAT(2, 1);
             ulonglong2 d[V][U];
 #pragma unroll
             for (int k = 0; k < V; ++k)
@@ -220,6 +437,7 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
                 for (int u = 0; u < U; ++u) ok = ok && desc_ready(d[k][u], epoch);
             if (__all_sync(kFullMask, ok)) {
                 progress = true;
+                if (lane == 0) RCULL_STAT(3, 1);
                 bool any_open = false;
 #pragma unroll
                 for (int k = 0; k < V; ++k) {
@@ -267,6 +485,12 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
                     }
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&sm.bases[buf]);
+                    if (lane == 0) {
+                        const long long now = RCULL_CLOCK();
+                        RCULL_STAT(0, 1);
+                        RCULL_STAT(1, now - t_pub[res % B]);
+                        RCULL_STAT(9, now - t_act);
+                    }
                     ++res;
                     active = false;
                 }
@@ -277,6 +501,8 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
         if (!progress) __nanosleep(400);
     }
 }
+
+#endif
 
 // Compute-warp emission of its own survivors of a pending tile: one pass over the
 // warp's combined (all views) list, stable within every view.
@@ -359,7 +585,11 @@ __global__ void __maxnreg__(112)
     __syncthreads();
 
     if (warp == kComputeWarps) {
+#ifndef RCULL_TWO_LEVEL
+        scan_warp_flat<V>(args, sm, lane);
+#else
         scan_warp<V>(args, sm, lane);
+#endif
         return;
     }
 
@@ -400,6 +630,7 @@ __global__ void __maxnreg__(112)
 
     uint32_t it = 0;
     constexpr uint32_t B = frame_bufs<V>();
+    const long long k0 = RCULL_CLOCK();
     uint32_t emitted = 0;  // iterations [emitted, it) of this CTA still have their commands pending
     auto emit_next = [&]() {
         const uint32_t b = emitted % B;
@@ -413,7 +644,9 @@ __global__ void __maxnreg__(112)
             if (it >= 1) mbar_wait(&sm.empty[stage ^ 1u], ((it - 1) >> 1) & 1u);
             claim_tile(it + 1);
         }
+        const long long f0 = RCULL_CLOCK();
         mbar_wait(&sm.full[stage], (it >> 1) & 1u);
+        if (tid == 0) RCULL_STAT(6, RCULL_CLOCK() - f0);
         const uint32_t tile = sm.tile_ring[it % kRing];
         if (tile >= args.n_tiles) break;
         const uint32_t tile_base = tile * kTile;
@@ -504,7 +737,12 @@ __global__ void __maxnreg__(112)
         while (emitted < it) {
             const uint32_t b = emitted % B, parity = (emitted / B) & 1u;
             if (emitted + B <= it) {
+                const long long w0 = RCULL_CLOCK();
                 mbar_wait(&sm.bases[b], parity);
+                if (tid == 0) {
+                    RCULL_STAT(5, RCULL_CLOCK() - w0);
+                    RCULL_STAT(8, 1);
+                }
             } else {
                 uint32_t ready = lane == 0 ? (uint32_t)mbar_test(&sm.bases[b], parity) : 0u;
                 ready = __shfl_sync(kFullMask, ready, 0);
@@ -533,6 +771,7 @@ __global__ void __maxnreg__(112)
 #pragma unroll
             for (int p = 0; p < 6; ++p) {
                 const float4* pp = sm_planes + (k * 6 + p) * 4;
+#ifndef RCULL_PLANE_FFMA2
                 const float4 q0 = pp[0], q1 = pp[1], q2 = pp[2];  // (ax ax ay ay) (az az px px) (py py pz pz)
                 const float pw = pp[3].x;
                 const float2 ax = make_float2(q0.x, q0.y), ay = make_float2(q0.z, q0.w), az = make_float2(q1.x, q1.y);
@@ -555,6 +794,29 @@ __global__ void __maxnreg__(112)
                     outside[2 * i + 1] = outside[2 * i + 1] || (s.y > e1);
                 }
             }
+#else
+                const float4 q0 = pp[0], q1 = pp[1], q2 = pp[2], q3 = pp[3];  // (ax ax ay ay) (az az px px) (py py pz pz) (pw pw 1 1)
+                const float2 ax = make_float2(q0.x, q0.y), ay = make_float2(q0.z, q0.w), az = make_float2(q1.x, q1.y);
+                const float2 px = make_float2(q1.z, q1.w), py = make_float2(q2.x, q2.y), pz = make_float2(q2.z, q2.w);
+                const float2 pw = make_float2(q3.x, q3.y), one = make_float2(q3.z, q3.w);
+#pragma unroll
+                for (int i = 0; i < kItems / 2; ++i) {
+                    // Two entities per instruction.  Products are FMUL2; every sum is x * 1 + y on the
+                    // packed FMA (FFMA2), which rounds exactly like the add (x * 1 is exact).  The 1.0
+                    // comes out of shared memory, so ptxas cannot see through it: a plain packed add of
+                    // packed products would be contracted into a fused a * b + c even under
+                    // --fmad=false (tests/test_abi.py checks the SASS for the multiplier operand).
+                    const float2 m1 = mul2_rn(h2x[i], ax), m2 = mul2_rn(h2y[i], ay), m3 = mul2_rn(h2z[i], az);
+                    const float2 e = fma2_rn(fma2_rn(m1, one, m2), one, m3);
+                    const float2 p1 = mul2_rn(c2x[i], px), p3 = mul2_rn(c2z[i], pz), p2 = mul2_rn(c2y[i], py);
+                    const float2 s = fma2_rn(fma2_rn(p1, one, p3), one, fma2_rn(p2, one, pw));
+                    // (s - e > 0.0) == (s > e): the rounded difference of two floats keeps its sign,
+                    // and both forms are false for NaN and for inf - inf
+                    outside[2 * i] = outside[2 * i] || (s.x > e.x);
+                    outside[2 * i + 1] = outside[2 * i + 1] || (s.y > e.y);
+                }
+            }
+#endif
             // ballot compaction, branch-free: culled lanes store to a dummy byte
             uint32_t wc = 0, lo = 0, hi = 0;
 #pragma unroll
@@ -598,6 +860,10 @@ __global__ void __maxnreg__(112)
     __syncwarp();
     if (lane == 0) mbar_arrive(&sm.done[it % B]);
     if (lane == 0) bulk_wait_read0();
+    if (tid == 0) {
+        RCULL_STAT(7, RCULL_CLOCK() - k0);
+        RCULL_STAT(10, 1);
+    }
 }
 
 }  // namespace rcull
