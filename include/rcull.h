@@ -58,6 +58,8 @@ typedef struct {
     uint32_t materialize_aabb;  /* write the AABB component (debug_aabb consumer) */
     uint32_t materialize_flags; /* write CoarseCulled per view */
     float lod_distance;         /* helpers.rs:6 uses 10.0 */
+    uint64_t capacity_tri_indices; /* CulledIndexBuffer capacity in indices (generate_work.comp:40-42 has
+                                      20 M triples); 0 = no per-triangle stage */
 } rcull_config;
 
 /* GltfMesh (src/renderer.rs:117-126) + consolidate_mesh_buffers offsets
@@ -146,6 +148,35 @@ int rcull_download_aabb(rcull_ctx *ctx, uint32_t buffer_ix, uint64_t first, uint
 int rcull_download_flags(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t view, uint64_t first, uint64_t n, uint8_t *flags);
 int rcull_download_cmds(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t view, uint64_t first, uint64_t n, rcull_draw_cmd *cmds);
 int rcull_download_visible(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t view, uint64_t first, uint64_t n, uint32_t *visible);
+
+/* ---- Stage 2: per-triangle cull + command compaction -------------
+ * Consolidated position / index buffers (ConsolidatedMeshBuffers.position_buffer / index_buffer,
+ * consolidate_mesh_buffers.rs:26-35; vec3 and u32, scalar layout).  Host pointers, copied
+ * synchronously.  rcull_mesh.lod[].first_index and .vertex_offset index into them. */
+int rcull_set_geometry(rcull_ctx *ctx, const float *positions, uint64_t n_vertices,
+                       const uint32_t *indices, uint64_t n_indices);
+/* One call replaces cull_pass' dispatch loop over generate_work.comp (cull_pipeline.rs:534-577,
+ * one vkCmdDispatch per visible entity) and the compact_draw_stream dispatch (:589-605): every
+ * triangle of every survivor of the CAMERA view (view 0 of the last rcull_frame on buffer_ix;
+ * the reference culls triangles against the camera only) is tested with
+ * pv * (model * vec4(v, 1)) -- back-face determinant and the four NDC side tests of
+ * generate_work.comp:139-155 -- kept index triples are written to the culled index buffer at
+ * the command's firstIndex in ascending triangle order, indexCount becomes 3 * kept, and the
+ * commands with indexCount > 0 are packed to the front of the triangle-stage command list.
+ * pv = projection * view, column-major (CameraMatrices.pv, generate_work.comp:33).
+ * draw_index_base must be the value given to rcull_frame.  Asynchronous on stream. */
+int rcull_tri_cull(rcull_ctx *ctx, const float pv[16], uint32_t draw_index_base, uint32_t buffer_ix, void *stream);
+typedef struct {
+    rcull_draw_cmd *cmds;   /* compacted IndirectCommandsBuffer after stage 2 */
+    uint32_t *count;        /* IndirectCommandsCount */
+    uint32_t *indices;      /* CulledIndexBuffer: triples at [firstIndex, firstIndex + indexCount) */
+    uint64_t *kept_indices; /* sum of the refined indexCount */
+} rcull_tri_outputs;
+int rcull_get_tri_outputs(rcull_ctx *ctx, rcull_tri_outputs *out);
+/* Blocking copies for tests: count and kept_indices always; cmds[0..n_cmds) and
+ * indices[first_index .. first_index + n_indices) when the pointers are not NULL. */
+int rcull_download_tri(rcull_ctx *ctx, uint32_t *count, uint64_t *kept_indices, rcull_draw_cmd *cmds, uint64_t n_cmds,
+                       uint32_t *indices, uint64_t first_index, uint64_t n_indices);
 
 /* Range-shard merge step: writes this rank's draw list of one view
  * into dst_cmds/dst_visible (device pointers into the MERGED lists, already

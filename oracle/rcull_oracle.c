@@ -434,3 +434,142 @@ void oracle_synth_entities(uint64_t seed, uint64_t first, uint64_t n, float half
         mesh_id[k] = (uint32_t)(((chan(seed, i, 8) >> 32) * (uint64_t)n_meshes) >> 32);
     }
 }
+
+/* ------------------------------------------------------------------------------------
+ * A8: per-triangle cull (src/shaders/generate_work.comp:60-201) + A7 on the refined
+ * commands (src/shaders/compact_draw_stream.comp:34-63).
+ * ---------------------------------------------------------------------------------- */
+
+/* GLSL `mat4 * vec4`: linear combination of the columns, left to right
+ * (generate_work.comp:139-141 applies it twice: pv * (model * vec4(v, 1.0))). */
+static void glsl_mat4_mul_vec4(const float m[16], const float v[4], float out[4]) {
+    for (int r = 0; r < 4; r++) {
+        float a = m[0 + r] * v[0];
+        a = a + m[4 + r] * v[1];
+        a = a + m[8 + r] * v[2];
+        a = a + m[12 + r] * v[3];
+        out[r] = a;
+    }
+}
+
+/* generate_work.comp:139-155 for one triangle; returns 1 when culled. */
+static int tri_culled(const float model[16], const float pv[16], const float *p0, const float *p1, const float *p2) {
+    const float *p[3] = {p0, p1, p2};
+    float c[3][4];
+    for (int k = 0; k < 3; k++) {
+        const float v[4] = {p[k][0], p[k][1], p[k][2], 1.0f};
+        float w[4];
+        glsl_mat4_mul_vec4(model, v, w);
+        glsl_mat4_mul_vec4(pv, w, c[k]);
+    }
+    /* determinant(mat3(c0.xyw, c1.xyw, c2.xyw)) > 0 (:143): columns a, b, d */
+    const float ax = c[0][0], ay = c[0][1], az = c[0][3];
+    const float bx = c[1][0], by = c[1][1], bz = c[1][3];
+    const float dx = c[2][0], dy = c[2][1], dz = c[2][3];
+    const float t0 = by * dz - dy * bz;
+    const float t1 = ay * dz - dy * az;
+    const float t2 = ay * bz - by * az;
+    const float det = (ax * t0 - bx * t1) + dx * t2;
+    if (det > 0.0f) return 1;
+    /* ndc = xyz / w (:145-147); only x and y are tested (:152-155) */
+    const float x0 = c[0][0] / c[0][3], y0 = c[0][1] / c[0][3];
+    const float x1 = c[1][0] / c[1][3], y1 = c[1][1] / c[1][3];
+    const float x2 = c[2][0] / c[2][3], y2 = c[2][1] / c[2][3];
+    if (x0 < -1.0f && x1 < -1.0f && x2 < -1.0f) return 1;
+    if (x0 > 1.0f && x1 > 1.0f && x2 > 1.0f) return 1;
+    if (y0 < -1.0f && y1 < -1.0f && y2 < -1.0f) return 1;
+    if (y0 > 1.0f && y1 > 1.0f && y2 > 1.0f) return 1;
+    return 0; /* the area test (:159-167) is overwritten by `cull = false` at :166 */
+}
+
+typedef struct {
+    const oracle_cmd *cmds;
+    const uint32_t *src_first_index;
+    uint32_t lo, hi;
+    const float *model;
+    uint32_t draw_index_base;
+    const float *pv;
+    const float *positions;
+    uint64_t n_vertices;
+    const uint32_t *indices;
+    uint64_t n_indices;
+    uint32_t *out_indices;
+    uint64_t out_capacity;
+    uint32_t *kept; /* [count]: refined indexCount */
+    int err;
+} tri_job;
+
+static void *tri_thread(void *arg) {
+    tri_job *j = (tri_job *)arg;
+    for (uint32_t c = j->lo; c < j->hi; c++) {
+        const oracle_cmd *cmd = &j->cmds[c];
+        const uint32_t n_tri = cmd->indexCount / 3;           /* :73 indexCount / 3 */
+        const uint64_t src = j->src_first_index[c] / 3;       /* :74 indexOffset / 3 */
+        const float *model = j->model + 16 * (uint64_t)(cmd->firstInstance - j->draw_index_base);
+        uint32_t kept = 0;
+        for (uint32_t t = 0; t < n_tri; t++) {
+            const uint64_t at = 3 * (src + t);
+            if (at + 2 >= j->n_indices) { j->err = 1; break; }
+            const uint32_t *ix = j->indices + at;
+            uint64_t v[3];
+            int bad = 0;
+            for (int k = 0; k < 3; k++) {
+                v[k] = (uint64_t)((int64_t)cmd->vertexOffset + (int64_t)ix[k]);
+                if (v[k] >= j->n_vertices) bad = 1;
+            }
+            if (bad) { j->err = 1; break; }
+            if (tri_culled(model, j->pv, j->positions + 3 * v[0], j->positions + 3 * v[1], j->positions + 3 * v[2])) continue;
+            const uint64_t dst = ((uint64_t)cmd->firstIndex + 3ull * kept) / 3 * 3; /* :190-196: (ix + indexOffsetInOutput) / 3 */
+            if (dst + 2 < j->out_capacity) {
+                j->out_indices[dst] = ix[0];
+                j->out_indices[dst + 1] = ix[1];
+                j->out_indices[dst + 2] = ix[2];
+            }
+            kept++;
+        }
+        j->kept[c] = 3 * kept;
+    }
+    return NULL;
+}
+
+int oracle_tri_cull(const oracle_cmd *cmds, const uint32_t *src_first_index, uint32_t count,
+                    const float *model, uint32_t draw_index_base, const float pv[16],
+                    const float *positions, uint64_t n_vertices, const uint32_t *indices, uint64_t n_indices,
+                    uint32_t *out_indices, uint64_t out_capacity,
+                    oracle_cmd *out_cmds, uint32_t *out_count, uint64_t *kept_indices, int n_threads) {
+    uint32_t *kept = (uint32_t *)calloc(count ? count : 1, sizeof(uint32_t));
+    if (!kept) return -1;
+    if (n_threads < 1) n_threads = 1;
+    if (count < 64) n_threads = 1;
+    pthread_t *th = (pthread_t *)malloc(sizeof(pthread_t) * n_threads);
+    tri_job *jobs = (tri_job *)malloc(sizeof(tri_job) * n_threads);
+    for (int t = 0; t < n_threads; t++) {
+        tri_job j = {cmds, src_first_index, (uint32_t)((uint64_t)count * t / n_threads),
+                     (uint32_t)((uint64_t)count * (t + 1) / n_threads), model, draw_index_base, pv, positions,
+                     n_vertices, indices, n_indices, out_indices, out_capacity, kept, 0};
+        jobs[t] = j;
+        if (n_threads == 1) tri_thread(&jobs[t]);
+        else pthread_create(&th[t], NULL, tri_thread, &jobs[t]);
+    }
+    int err = 0;
+    for (int t = 0; t < n_threads; t++) {
+        if (n_threads > 1) pthread_join(th[t], NULL);
+        err |= jobs[t].err;
+    }
+    /* compact_draw_stream.comp:40-62: keep indexCount > 0, pack to the front, in order */
+    uint32_t n_out = 0;
+    uint64_t total = 0;
+    for (uint32_t c = 0; c < count; c++) {
+        if (kept[c] == 0) continue;
+        if (out_cmds) {
+            out_cmds[n_out] = cmds[c];
+            out_cmds[n_out].indexCount = kept[c];
+        }
+        total += kept[c];
+        n_out++;
+    }
+    if (out_count) *out_count = n_out;
+    if (kept_indices) *kept_indices = total;
+    free(kept); free(th); free(jobs);
+    return err ? -1 : 0;
+}

@@ -95,6 +95,31 @@ int oracle_emit_per_mesh(const float *pos, const uint32_t *mesh_id, const uint8_
                          float lod_distance, uint32_t draw_index_base,
                          oracle_cmd *cmds, uint32_t *visible, uint32_t *count, uint64_t *n_instances);
 
+/*
+ * A8 + A7: per-triangle cull of one view's survivors and compaction of the
+ * commands that kept a triangle (src/shaders/generate_work.comp:60-201,
+ * src/shaders/compact_draw_stream.comp:34-63; dispatch loop cull_pipeline.rs:534-605).
+ * For command c (as written by oracle_frame: indexCount = index_len, firstIndex =
+ * indexOffsetInOutput, firstInstance = gltfIndex): triangle t reads
+ * index_buffer[src_first_index[c] / 3 + t] (uvec3), vertices
+ * vertex_buffer[vertexOffset + ix] (vec3), clip = pv * (model[gltfIndex] * vec4(v, 1))
+ * (GLSL mat * vec = ((col0 * x + col1 * y) + col2 * z) + col3 * w, every product and
+ * sum rounded, no contraction); culled iff determinant(mat3(c0.xyw, c1.xyw, c2.xyw)) > 0
+ * (cofactors along the first column of GLSL's column-major mat3, glm order) or all
+ * three ndc.x < -1 / > 1 / ndc.y < -1 / > 1 (ndc = xyz / w, IEEE division).  The area
+ * test of :159-167 is computed and then disabled in the reference (:166) -- no effect.
+ * Kept triples go to out_indices[(firstIndex + 3 * rank) ...] in ascending triangle
+ * order (the reference's order inside a mesh is atomic-arrival order; this is one of
+ * its legal outcomes), indexCount becomes 3 * kept.  Commands with indexCount > 0 are
+ * packed to the front of out_cmds in order; *out_count = how many.
+ * model is indexed by firstInstance - draw_index_base.  Returns 0, -1 on bad input.
+ */
+int oracle_tri_cull(const oracle_cmd *cmds, const uint32_t *src_first_index, uint32_t count,
+                    const float *model, uint32_t draw_index_base, const float pv[16],
+                    const float *positions, uint64_t n_vertices, const uint32_t *indices, uint64_t n_indices,
+                    uint32_t *out_indices, uint64_t out_capacity,
+                    oracle_cmd *out_cmds, uint32_t *out_count, uint64_t *kept_indices, int n_threads);
+
 /* Deterministic scene generator twin (see renderer_b200/scene.py): entity i of
  * the global scene, counter-based so shards regenerate their slice. */
 void oracle_synth_entities(uint64_t seed, uint64_t first, uint64_t n, float half_box, uint32_t n_meshes,

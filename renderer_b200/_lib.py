@@ -40,11 +40,16 @@ class Config(C.Structure):
         ("materialize_aabb", C.c_uint32),
         ("materialize_flags", C.c_uint32),
         ("lod_distance", C.c_float),
+        ("capacity_tri_indices", C.c_uint64),
     ]
 
 
 class View(C.Structure):
     _fields_ = [("planes", (C.c_float * 4) * 6)]
+
+
+class TriOutputs(C.Structure):
+    _fields_ = [("cmds", C.c_void_p), ("count", C.c_void_p), ("indices", C.c_void_p), ("kept_indices", C.c_void_p)]
 
 
 class Outputs(C.Structure):
@@ -101,6 +106,10 @@ SYMBOLS = {
     "rcull_download_flags": (C.c_int, [_P, _u32, _u32, _u64, _u64, _P]),
     "rcull_download_cmds": (C.c_int, [_P, _u32, _u32, _u64, _u64, _P]),
     "rcull_download_visible": (C.c_int, [_P, _u32, _u32, _u64, _u64, _P]),
+    "rcull_set_geometry": (C.c_int, [_P, _P, _u64, _P, _u64]),
+    "rcull_tri_cull": (C.c_int, [_P, _P, _u32, _u32, _P]),
+    "rcull_get_tri_outputs": (C.c_int, [_P, C.POINTER(TriOutputs)]),
+    "rcull_download_tri": (C.c_int, [_P, _P, _P, _P, _u64, _P, _u64, _u64]),
     "rcull_rebase_into": (C.c_int, [_P, _u32, _u32, _u64, _P, _P, _P]),
     "rcull_merge_create": (C.c_int, [_P, _u32, _u32, _u64, C.POINTER(_P)]),
     "rcull_merge_destroy": (None, [_P]),

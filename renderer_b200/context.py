@@ -13,7 +13,7 @@ from typing import Sequence
 import numpy as np
 
 from . import _lib
-from ._lib import CMD_DTYPE, MESH_DTYPE, Config, Outputs, RcullError, View, check, ptr
+from ._lib import CMD_DTYPE, MESH_DTYPE, Config, Outputs, RcullError, TriOutputs, View, check, ptr
 
 
 def views_array(views: Sequence[np.ndarray] | np.ndarray) -> np.ndarray:
@@ -43,6 +43,7 @@ class CullContext:
         materialize_aabb: bool = False,
         materialize_flags: bool = False,
         lod_distance: float = 10.0,
+        capacity_tri_indices: int = 0,
     ):
         self._lib = _lib.load()
         cfg = Config(
@@ -56,6 +57,7 @@ class CullContext:
             materialize_aabb=int(materialize_aabb),
             materialize_flags=int(materialize_flags),
             lod_distance=lod_distance,
+            capacity_tri_indices=capacity_tri_indices,
         )
         self.cfg = cfg
         self._h = C.c_void_p()
@@ -178,6 +180,41 @@ class CullContext:
     def visible(self, view: int, n: int, first: int = 0, buffer_ix: int = 0) -> np.ndarray:
         out = np.empty(n, np.uint32)
         check(self._lib.rcull_download_visible(self._h, buffer_ix, view, first, n, ptr(out)))
+        return out
+
+    # -- stage 2: per-triangle cull (generate_work.comp) + compact_draw_stream ------------
+    def set_geometry(self, positions: np.ndarray, indices: np.ndarray) -> None:
+        """Consolidated position (vec3) and index (u32) buffers (consolidate_mesh_buffers.rs:26-35)."""
+        pos = np.ascontiguousarray(positions, dtype=np.float32).reshape(-1, 3)
+        idx = np.ascontiguousarray(indices, dtype=np.uint32).reshape(-1)
+        check(self._lib.rcull_set_geometry(self._h, ptr(pos), len(pos), ptr(idx), len(idx)))
+
+    def tri_cull(self, pv: np.ndarray, draw_index_base: int = 0, buffer_ix: int = 0, stream: int = 0) -> None:
+        """One call = cull_pass' generate_work dispatch loop + the compact_draw_stream dispatch."""
+        m = np.ascontiguousarray(pv, dtype=np.float32).reshape(16)
+        check(self._lib.rcull_tri_cull(self._h, ptr(m), draw_index_base, buffer_ix, C.c_void_p(stream)))
+
+    def tri_outputs(self) -> TriOutputs:
+        o = TriOutputs()
+        check(self._lib.rcull_get_tri_outputs(self._h, C.byref(o)))
+        return o
+
+    def tri_counts(self) -> tuple[int, int]:
+        count = np.zeros(1, np.uint32)
+        kept = np.zeros(1, np.uint64)
+        check(self._lib.rcull_download_tri(self._h, ptr(count), ptr(kept), None, 0, None, 0, 0))
+        return int(count[0]), int(kept[0])
+
+    def tri_cmds(self, n: int) -> np.ndarray:
+        count = np.zeros(1, np.uint32)
+        out = np.zeros(n, CMD_DTYPE)
+        check(self._lib.rcull_download_tri(self._h, ptr(count), None, ptr(out), n, None, 0, 0))
+        return out
+
+    def tri_indices(self, first: int, n: int) -> np.ndarray:
+        count = np.zeros(1, np.uint32)
+        out = np.zeros(n, np.uint32)
+        check(self._lib.rcull_download_tri(self._h, ptr(count), None, None, 0, ptr(out), first, n))
         return out
 
     def rebase_into(self, view: int, index_prefix: int, dst_cmds_ptr: int, dst_visible_ptr: int, buffer_ix: int = 0, stream: int = 0) -> None:

@@ -15,12 +15,13 @@
 
 #include "rcull_aux.cuh"
 #include "rcull_frame.cuh"
+#include "rcull_tri.cuh"
 
 using namespace rcull;
 
 static_assert(sizeof(rcull_mesh) == 80, "rcull_mesh layout");
 static_assert(sizeof(rcull_draw_cmd) == 20, "VkDrawIndexedIndirectCommand stride");
-static_assert(sizeof(rcull_config) == 48 && sizeof(rcull_view) == 96, "rcull_config / rcull_view layout");
+static_assert(sizeof(rcull_config) == 56 && sizeof(rcull_view) == 96, "rcull_config / rcull_view layout");
 static_assert(RCULL_MAX_VIEWS == kMaxViews && RCULL_MAX_LODS == kMaxLods, "header/kernel constants");
 static_assert(frame_smem_bytes<1>() <= kSmemPerCta && frame_smem_bytes<5>() <= kSmemPerCta && frame_smem_bytes<8>() <= kSmemPerCta,
               "frame kernel must fit kCtasPerSm CTAs per SM");
@@ -55,6 +56,7 @@ struct OutputSet {
     uint32_t* vis_tmp[kMaxViews] = {};  // per-mesh mode: draw_index of every survivor before bucketing
     uint32_t* counts = nullptr;
     unsigned long long* totals = nullptr;
+    uint32_t* src_first = nullptr;  // triangle stage: indexOffset of every camera-view command
     CUtensorMap model_map;  // model buffer as [cap/2 rows][32 floats], 16-row boxes, 128-B swizzle
 };
 
@@ -90,6 +92,17 @@ struct rcull_ctx {
     cudaStream_t own_stream = nullptr;
     uint32_t* h_counts = nullptr;  // pinned
     unsigned long long* h_totals = nullptr;
+    // stage 2 (rcull_tri.cuh); single-buffered like CullPassData (cull_pipeline.rs:74-84)
+    float* positions = nullptr;
+    uint32_t* indices = nullptr;
+    uint64_t n_vertices = 0, n_indices = 0;
+    uint32_t* tri_cmds = nullptr;
+    uint32_t* tri_count = nullptr;
+    uint64_t* tri_kept = nullptr;
+    uint32_t* tri_refined = nullptr;
+    uint32_t* tri_indices = nullptr;
+    uint64_t* tri_status = nullptr;  // [4 * tiles] + 2 ticket words at the end
+    size_t tri_status_bytes = 0;
     std::vector<void*> allocs;
 };
 
@@ -174,13 +187,15 @@ int make_model_map(CUtensorMap* map, float4* model, uint64_t cap) {
 extern "C" {
 
 const char* rcull_last_error(void) { return g_err; }
-uint32_t rcull_version(void) { return (0u << 16) | 1u; }
+uint32_t rcull_version(void) { return (0u << 16) | 2u; }  // 0.2: triangle stage, rcull_config.capacity_tri_indices
 
 void rcull_destroy(rcull_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     cudaDeviceSynchronize();
     for (void* p : c->allocs) cudaFree(p);
+    if (c->positions) cudaFree(c->positions);
+    if (c->indices) cudaFree(c->indices);
     if (c->h_counts) cudaFreeHost(c->h_counts);
     if (c->h_totals) cudaFreeHost(c->h_totals);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -247,6 +262,7 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
                 TRY(dev_alloc(c, &o.vis_tmp[v], c->cap_vis));
             }
         }
+        if (cfg->capacity_tri_indices) TRY(dev_alloc(c, &o.src_first, c->cap_vis));
         TRY(dev_alloc(c, &o.counts, kMaxViews));
         TRY(dev_alloc(c, &o.totals, kMaxViews));
         cudaMemset(o.counts, 0, kMaxViews * 4);
@@ -269,6 +285,22 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
         unsigned char* tmp = nullptr;
         TRY(dev_alloc(c, &tmp, c->sort_tmp_bytes));
         c->sort_tmp = tmp;
+    }
+    if (cfg->capacity_tri_indices) {
+        if (cfg->output_mode != RCULL_PER_ENTITY) {
+            rcull_destroy(c);
+            return fail(RCULL_ERR_INVALID, "the per-triangle stage works on per-entity commands");
+        }
+        const size_t tiles = (c->cap_cmds + kCompactTile - 1) / kCompactTile;
+        c->tri_status_bytes = (4 * tiles + 2) * 8;
+        TRY(dev_alloc(c, &c->tri_cmds, c->cap_cmds * 5));
+        TRY(dev_alloc(c, &c->tri_refined, c->cap_cmds));
+        TRY(dev_alloc(c, &c->tri_count, 2));
+        TRY(dev_alloc(c, &c->tri_kept, 1));
+        TRY(dev_alloc(c, &c->tri_indices, cfg->capacity_tri_indices));
+        TRY(dev_alloc(c, &c->tri_status, 4 * tiles + 2));
+        cudaMemset(c->tri_count, 0, 8);
+        cudaMemset(c->tri_kept, 0, 8);
     }
     if (cudaMemset(c->status, 0, c->status_bytes) != cudaSuccess || cudaMemset(c->ticket, 0, 8) != cudaSuccess) {
         rcull_destroy(c);
@@ -418,6 +450,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
             pc.one = make_float2(1.0f, 1.0f);
         }
     }
+    a.src_first = o.src_first;
     a.counts = o.counts;
     a.totals = o.totals;
     a.meta_out = c->meta_out;
@@ -501,7 +534,10 @@ static int check_device_error(rcull_ctx* c) {
     CU(cudaMemcpy(&flag, c->ticket + 1, 4, cudaMemcpyDeviceToHost));
     if (flag) {
         cudaMemset(c->ticket + 1, 0, 4);
-        return fail(RCULL_ERR_INVALID, "mesh id out of range of the mesh table (Vertex/Index buffer not consolidated, cull_pipeline.rs:543)");
+        if (flag & 1u)
+            return fail(RCULL_ERR_INVALID, "mesh id out of range of the mesh table (Vertex/Index buffer not consolidated, cull_pipeline.rs:543)");
+        if (flag & 2u) return fail(RCULL_ERR_INVALID, "triangle stage: index or vertex outside the consolidated buffers");
+        return fail(RCULL_ERR_INVALID, "triangle stage: culled index buffer too small (capacity_tri_indices)");
     }
     return RCULL_OK;
 }
@@ -619,6 +655,104 @@ int rcull_synth_entities(rcull_ctx* c, uint64_t seed, uint64_t first_global, uin
 }
 
 uint64_t rcull_launch_count(rcull_ctx* c) { return c ? c->launches : 0; }
+
+int rcull_set_geometry(rcull_ctx* c, const float* positions, uint64_t n_vertices, const uint32_t* indices, uint64_t n_indices) {
+    if (!c || !positions || !indices) return fail(RCULL_ERR_INVALID, "rcull_set_geometry: null argument");
+    if (!c->cfg.capacity_tri_indices) return fail(RCULL_ERR_INVALID, "context created without capacity_tri_indices");
+    if (n_vertices == 0 || n_indices == 0 || n_indices > 0xffffffffull) return fail(RCULL_ERR_INVALID, "rcull_set_geometry: empty or oversized buffers");
+    CU(cudaSetDevice(c->cfg.device));
+    CU(cudaDeviceSynchronize());
+    if (c->positions) cudaFree(c->positions);
+    if (c->indices) cudaFree(c->indices);
+    c->positions = nullptr;
+    c->indices = nullptr;
+    CU(cudaMalloc((void**)&c->positions, n_vertices * 12 + 256));
+    CU(cudaMalloc((void**)&c->indices, n_indices * 4 + 256));
+    CU(cudaMemcpy(c->positions, positions, n_vertices * 12, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(c->indices, indices, n_indices * 4, cudaMemcpyHostToDevice));
+    c->n_vertices = n_vertices;
+    c->n_indices = n_indices;
+    return RCULL_OK;
+}
+
+int rcull_tri_cull(rcull_ctx* c, const float pv[16], uint32_t draw_index_base, uint32_t buffer_ix, void* stream) {
+    if (!c || !pv) return fail(RCULL_ERR_INVALID, "rcull_tri_cull: null argument");
+    if (!c->cfg.capacity_tri_indices) return fail(RCULL_ERR_INVALID, "context created without capacity_tri_indices");
+    if (!c->positions) return fail(RCULL_ERR_INVALID, "rcull_set_geometry has not been called");
+    if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
+    CU(cudaSetDevice(c->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    OutputSet& o = c->out[buffer_ix];
+    CU(cudaMemsetAsync(c->tri_status, 0, c->tri_status_bytes, s));  // descriptors + the two tickets behind them
+    const size_t tiles = (c->cap_cmds + kCompactTile - 1) / kCompactTile;
+    uint32_t* tickets = reinterpret_cast<uint32_t*>(c->tri_status + 4 * tiles);
+    TriArgs t;
+    memset(&t, 0, sizeof t);
+    t.cmds = o.cmds[0];
+    t.src_first = o.src_first;
+    t.count = o.counts;
+    t.model = reinterpret_cast<const float*>(o.model);
+    t.positions = c->positions;
+    t.indices = c->indices;
+    t.out_indices = c->tri_indices;
+    t.refined = c->tri_refined;
+    t.ticket = tickets;
+    t.error_flag = c->ticket + 1;
+    t.n_vertices = c->n_vertices;
+    t.n_indices = c->n_indices;
+    t.out_capacity = c->cfg.capacity_tri_indices;
+    t.cap_cmds = (uint32_t)(c->cap_cmds > 0xffffffffull ? 0xffffffffull : c->cap_cmds);
+    t.draw_index_base = draw_index_base;
+    memcpy(t.pv, pv, sizeof t.pv);
+    tri_cull<<<c->sm_count * 8, kTriThreads, 0, s>>>(t);
+    CU(cudaGetLastError());
+    CompactArgs k;
+    memset(&k, 0, sizeof k);
+    k.cmds = o.cmds[0];
+    k.refined = c->tri_refined;
+    k.count = o.counts;
+    k.out_cmds = c->tri_cmds;
+    k.out_count = c->tri_count;
+    k.kept_indices = c->tri_kept;
+    k.status = c->tri_status;
+    k.ticket = tickets + 2;
+    k.cap_cmds = t.cap_cmds;
+    compact_draw_stream<<<c->sm_count * 2, kCompactThreads, 0, s>>>(k);
+    CU(cudaGetLastError());
+    c->launches += 2;
+    return RCULL_OK;
+}
+
+int rcull_get_tri_outputs(rcull_ctx* c, rcull_tri_outputs* out) {
+    if (!c || !out) return fail(RCULL_ERR_INVALID, "rcull_get_tri_outputs: null argument");
+    if (!c->cfg.capacity_tri_indices) return fail(RCULL_ERR_INVALID, "context created without capacity_tri_indices");
+    out->cmds = reinterpret_cast<rcull_draw_cmd*>(c->tri_cmds);
+    out->count = c->tri_count;
+    out->indices = c->tri_indices;
+    out->kept_indices = c->tri_kept;
+    return RCULL_OK;
+}
+
+int rcull_download_tri(rcull_ctx* c, uint32_t* count, uint64_t* kept_indices, rcull_draw_cmd* cmds, uint64_t n_cmds,
+                       uint32_t* indices, uint64_t first_index, uint64_t n_indices) {
+    if (!c || !count) return fail(RCULL_ERR_INVALID, "rcull_download_tri: null argument");
+    if (!c->cfg.capacity_tri_indices) return fail(RCULL_ERR_INVALID, "context created without capacity_tri_indices");
+    CU(cudaSetDevice(c->cfg.device));
+    CU(cudaDeviceSynchronize());
+    int rc = check_device_error(c);
+    if (rc) return rc;
+    CU(cudaMemcpy(count, c->tri_count, 4, cudaMemcpyDeviceToHost));
+    if (kept_indices) CU(cudaMemcpy(kept_indices, c->tri_kept, 8, cudaMemcpyDeviceToHost));
+    if (cmds) {
+        if (n_cmds > c->cap_cmds) return fail(RCULL_ERR_INVALID, "command range out of bounds");
+        CU(cudaMemcpy(cmds, c->tri_cmds, n_cmds * 20, cudaMemcpyDeviceToHost));
+    }
+    if (indices) {
+        if (first_index + n_indices > c->cfg.capacity_tri_indices) return fail(RCULL_ERR_INVALID, "index range out of bounds");
+        CU(cudaMemcpy(indices, c->tri_indices + first_index, n_indices * 4, cudaMemcpyDeviceToHost));
+    }
+    return RCULL_OK;
+}
 
 #ifdef RCULL_SCAN_STATS  // diagnostic build only, not part of include/rcull.h
 int rcull_debug_stats(uint64_t out[16], int reset) {

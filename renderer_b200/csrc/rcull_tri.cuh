@@ -1,0 +1,264 @@
+// rcull_tri.cuh -- stage 2 of the cull pipeline (SURVEY 8a row A8 + row A7 on its output):
+// per-triangle cull of the camera view's survivors and compaction of the commands that kept
+// a triangle.  Replaces the reference's one-vkCmdDispatch-per-visible-entity loop
+// (cull_pipeline.rs:534-577 driving src/shaders/generate_work.comp) and the
+// compact_draw_stream dispatch (cull_pipeline.rs:589-605) with two launches per frame.
+//
+// Arithmetic is pinned to the GLSL source: `mat4 * vec4` is the left-to-right combination
+// of the columns with every product and sum rounded (no contraction: the library is built
+// with -fmad=false and uses explicit _rn intrinsics), `/` is IEEE division.
+#pragma once
+#include "rcull_device.cuh"
+
+namespace rcull {
+
+constexpr int kTriThreads = 128;  // triangles per step of one command
+constexpr int kCompactThreads = 256;
+constexpr int kCompactItems = 4;
+constexpr int kCompactTile = kCompactThreads * kCompactItems;
+
+struct TriArgs {
+    const uint32_t* cmds;        // view's draw list from the frame kernel, 5 words per command
+    const uint32_t* src_first;   // indexOffset push constant of each command (first_index of the chosen LOD)
+    const uint32_t* count;       // how many commands (device)
+    const float* model;          // mat4 column-major, slot = firstInstance - draw_index_base
+    const float* positions;      // ConsolidatedMeshBuffers.position_buffer, vec3 scalar layout
+    const uint32_t* indices;     // ConsolidatedMeshBuffers.index_buffer
+    uint32_t* out_indices;       // CulledIndexBuffer (uvec3 out_index_buffer[], generate_work.comp:40-42)
+    uint32_t* refined;           // [count] refined indexCount of every command
+    uint32_t* ticket;            // [0] command ticket of the cull kernel, [1] tile ticket of the compaction
+    uint32_t* error_flag;
+    uint64_t n_vertices, n_indices, out_capacity;
+    uint32_t cap_cmds, draw_index_base;
+    float pv[16];
+};
+
+// GLSL mat4 * vec4 with w == 1 known only for the first product; kept generic so that the
+// rounding sequence is the shader's: ((c0 * x + c1 * y) + c2 * z) + c3 * w per row.
+__device__ __forceinline__ float4 glsl_mul(const float* __restrict__ m, float4 v) {
+    float4 r;
+    r.x = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m[0], v.x), __fmul_rn(m[4], v.y)), __fmul_rn(m[8], v.z)), __fmul_rn(m[12], v.w));
+    r.y = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m[1], v.x), __fmul_rn(m[5], v.y)), __fmul_rn(m[9], v.z)), __fmul_rn(m[13], v.w));
+    r.z = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m[2], v.x), __fmul_rn(m[6], v.y)), __fmul_rn(m[10], v.z)), __fmul_rn(m[14], v.w));
+    r.w = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m[3], v.x), __fmul_rn(m[7], v.y)), __fmul_rn(m[11], v.z)), __fmul_rn(m[15], v.w));
+    return r;
+}
+
+// generate_work.comp:139-155.  true = culled.
+__device__ __forceinline__ bool tri_culled(const float* __restrict__ model, const float* __restrict__ pv, float4 p0, float4 p1,
+                                           float4 p2) {
+    const float4 c0 = glsl_mul(pv, glsl_mul(model, p0));
+    const float4 c1 = glsl_mul(pv, glsl_mul(model, p1));
+    const float4 c2 = glsl_mul(pv, glsl_mul(model, p2));
+    // determinant(mat3(c0.xyw, c1.xyw, c2.xyw)) > 0: cofactors along the first row of columns
+    const float t0 = __fsub_rn(__fmul_rn(c1.y, c2.w), __fmul_rn(c2.y, c1.w));
+    const float t1 = __fsub_rn(__fmul_rn(c0.y, c2.w), __fmul_rn(c2.y, c0.w));
+    const float t2 = __fsub_rn(__fmul_rn(c0.y, c1.w), __fmul_rn(c1.y, c0.w));
+    const float det = __fadd_rn(__fsub_rn(__fmul_rn(c0.x, t0), __fmul_rn(c1.x, t1)), __fmul_rn(c2.x, t2));
+    if (det > 0.0f) return true;
+    const float x0 = __fdiv_rn(c0.x, c0.w), y0 = __fdiv_rn(c0.y, c0.w);
+    const float x1 = __fdiv_rn(c1.x, c1.w), y1 = __fdiv_rn(c1.y, c1.w);
+    const float x2 = __fdiv_rn(c2.x, c2.w), y2 = __fdiv_rn(c2.y, c2.w);
+    return (x0 < -1.0f && x1 < -1.0f && x2 < -1.0f) || (x0 > 1.0f && x1 > 1.0f && x2 > 1.0f) ||
+           (y0 < -1.0f && y1 < -1.0f && y2 < -1.0f) || (y0 > 1.0f && y1 > 1.0f && y2 > 1.0f);
+    // the area test of :159-167 is overwritten by `cull = false` (:166): nothing to compute
+}
+
+// One CTA per command at a time (ticket order): the command's triangles in steps of 128,
+// ballot compaction with a running base, so the kept triples land in ascending triangle
+// order at out_index_buffer[firstIndex / 3 + rank] (the reference's order inside a mesh is
+// atomic-arrival order; ascending is one of its outcomes).
+__global__ void __launch_bounds__(kTriThreads) tri_cull(const __grid_constant__ TriArgs a) {
+    __shared__ float s_model[16], s_pv[16];
+    __shared__ uint32_t s_cmd, s_warp[kTriThreads / 32];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    uint32_t count = *a.count;
+    if (count > a.cap_cmds) count = a.cap_cmds;
+    if (tid < 16) s_pv[tid] = a.pv[tid];
+    for (;;) {
+        if (tid == 0) s_cmd = atomicAdd(a.ticket, 1u);
+        __syncthreads();
+        const uint32_t c = s_cmd;
+        if (c >= count) break;
+        const uint32_t* cmd = a.cmds + (size_t)c * 5;
+        const uint32_t n_tri = cmd[0] / 3u, out_first = cmd[2] / 3u, first_instance = cmd[4];
+        const int32_t vertex_offset = (int32_t)cmd[3];
+        const uint64_t src = a.src_first[c] / 3u;
+        if (tid < 16) s_model[tid] = __ldg(a.model + (size_t)(first_instance - a.draw_index_base) * 16 + tid);
+        __syncthreads();
+        uint32_t running = 0;
+        for (uint32_t t0 = 0; t0 < n_tri; t0 += kTriThreads) {
+            const uint32_t t = t0 + tid;
+            bool keep = false;
+            uint32_t i0 = 0, i1 = 0, i2 = 0;
+            if (t < n_tri) {
+                const uint64_t at = 3ull * (src + t);
+                if (at + 2 < a.n_indices) {
+                    i0 = __ldg(a.indices + at);
+                    i1 = __ldg(a.indices + at + 1);
+                    i2 = __ldg(a.indices + at + 2);
+                    const uint64_t v0 = (uint64_t)((int64_t)vertex_offset + i0), v1 = (uint64_t)((int64_t)vertex_offset + i1),
+                                   v2 = (uint64_t)((int64_t)vertex_offset + i2);
+                    if (v0 < a.n_vertices && v1 < a.n_vertices && v2 < a.n_vertices) {
+                        const float* q0 = a.positions + 3 * v0;
+                        const float* q1 = a.positions + 3 * v1;
+                        const float* q2 = a.positions + 3 * v2;
+                        keep = !tri_culled(s_model, s_pv, make_float4(__ldg(q0), __ldg(q0 + 1), __ldg(q0 + 2), 1.0f),
+                                           make_float4(__ldg(q1), __ldg(q1 + 1), __ldg(q1 + 2), 1.0f),
+                                           make_float4(__ldg(q2), __ldg(q2 + 1), __ldg(q2 + 2), 1.0f));
+                    } else {
+                        atomicOr(a.error_flag, 2u);
+                    }
+                } else {
+                    atomicOr(a.error_flag, 2u);
+                }
+            }
+            const uint32_t b = __ballot_sync(kFullMask, keep);
+            if (lane == 0) s_warp[warp] = __popc(b);
+            __syncthreads();
+            uint32_t before = 0, total = 0;
+#pragma unroll
+            for (int w = 0; w < kTriThreads / 32; ++w) {
+                const uint32_t x = s_warp[w];
+                before += (uint32_t)w < warp ? x : 0u;
+                total += x;
+            }
+            if (keep) {
+                const uint64_t dst = 3ull * ((uint64_t)out_first + running + before + __popc(b & ((1u << lane) - 1u)));
+                if (dst + 2 < a.out_capacity) {
+                    a.out_indices[dst] = i0;
+                    a.out_indices[dst + 1] = i1;
+                    a.out_indices[dst + 2] = i2;
+                } else {
+                    atomicOr(a.error_flag, 4u);  // CulledIndexBuffer too small
+                }
+            }
+            running += total;
+            __syncthreads();
+        }
+        if (tid == 0) a.refined[c] = 3u * running;
+    }
+}
+
+// compact_draw_stream.comp:34-63 on the refined commands: keep indexCount > 0, stable, dense
+// from slot 0, count written by the last tile.  Single pass, decoupled look-back over tiles of
+// 1024 commands; a descriptor is four u64 {flag:2 | kept commands:32, aggregate index sum,
+// inclusive index sum, pad}, cleared by the host beforehand.
+struct CompactArgs {
+    const uint32_t* cmds;      // 5 words per command (input list)
+    const uint32_t* refined;   // refined indexCount per command
+    const uint32_t* count;     // input count (device)
+    uint32_t* out_cmds;        // compacted list
+    uint32_t* out_count;
+    uint64_t* kept_indices;  // sum of refined indexCount
+    uint64_t* status;        // [4 * n_tiles] zeroed
+    uint32_t* ticket;
+    uint32_t cap_cmds;
+};
+
+__global__ void __launch_bounds__(kCompactThreads) compact_draw_stream(const __grid_constant__ CompactArgs a) {
+    __shared__ uint32_t s_tile, s_warp[kCompactThreads / 32], s_base;
+    __shared__ uint64_t s_sum[kCompactThreads / 32];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    uint32_t count = *a.count;
+    if (count > a.cap_cmds) count = a.cap_cmds;
+    const uint32_t n_tiles = (count + kCompactTile - 1) / kCompactTile;
+    if (n_tiles == 0) {
+        if (blockIdx.x == 0 && tid == 0) {
+            *a.out_count = 0;
+            *a.kept_indices = 0;
+        }
+        return;
+    }
+    for (;;) {
+        if (tid == 0) s_tile = atomicAdd(a.ticket, 1u);
+        __syncthreads();
+        const uint32_t tile = s_tile;
+        if (tile >= n_tiles) break;
+        // blocked arrangement: thread owns kCompactItems consecutive commands (stable order)
+        const uint32_t first = tile * kCompactTile + tid * kCompactItems;
+        uint32_t len[kCompactItems], mine = 0;
+        uint64_t sum = 0;
+#pragma unroll
+        for (int j = 0; j < kCompactItems; ++j) {
+            len[j] = first + j < count ? a.refined[first + j] : 0u;
+            mine += len[j] > 0u ? 1u : 0u;
+            sum += len[j];
+        }
+        const uint32_t incl = warp_incl_scan_u32(mine, lane);
+        const uint64_t wsum = warp_sum_u64(sum);
+        if (lane == 31) s_warp[warp] = incl;
+        if (lane == 0) s_sum[warp] = wsum;
+        __syncthreads();
+        uint32_t before = 0, total = 0;
+        uint64_t tsum = 0;
+#pragma unroll
+        for (int w = 0; w < kCompactThreads / 32; ++w) {
+            before += (uint32_t)w < warp ? s_warp[w] : 0u;
+            total += s_warp[w];
+            tsum += s_sum[w];
+        }
+        // look-back (warp 0): value = kept commands (32 bits); the index sum rides in a second word
+        if (warp == 0) {
+            uint64_t* st = a.status + 4ull * tile;
+            if (lane == 0) {
+                st_relaxed(st + (tile == 0 ? 2 : 1), tsum);
+                __threadfence();
+                st_relaxed(st, ((tile == 0 ? 2ull : 1ull) << 32) | total);
+            }
+            uint32_t excl = 0;
+            uint64_t excl_sum = 0;
+            int p = (int)tile - 1 - (int)lane;
+            bool done = tile == 0;
+            while (!done) {
+                uint64_t d = p >= 0 ? ld_relaxed(a.status + 4ull * p) : (2ull << 32);
+                while (__any_sync(kFullMask, (d >> 32) == 0ull)) {
+                    __nanosleep(100);
+                    d = p >= 0 ? ld_relaxed(a.status + 4ull * p) : (2ull << 32);
+                }
+                __threadfence();
+                const uint32_t incl_mask = __ballot_sync(kFullMask, (d >> 32) == 2ull);
+                const uint32_t stop = incl_mask ? (uint32_t)__ffs(incl_mask) - 1u : 31u;
+                if (lane <= stop) {
+                    excl += (uint32_t)d;
+                    // word 1 = aggregate index sum, word 2 = inclusive index sum (written before its flag)
+                    excl_sum += p >= 0 ? ld_relaxed(a.status + 4ull * p + ((d >> 32) == 2ull ? 2 : 1)) : 0ull;
+                }
+                done = incl_mask != 0u;
+                p -= 32;
+            }
+            excl = __reduce_add_sync(kFullMask, excl);
+            excl_sum = warp_sum_u64(excl_sum);
+            if (lane == 0) {
+                s_base = excl;
+                if (tile != 0) {
+                    st_relaxed(st + 2, excl_sum + tsum);
+                    __threadfence();
+                    st_relaxed(st, (2ull << 32) | (excl + total));
+                }
+                if (tile == n_tiles - 1) {
+                    *a.out_count = excl + total;
+                    *a.kept_indices = excl_sum + tsum;
+                }
+            }
+        }
+        __syncthreads();
+        uint32_t pos = s_base + before + incl - mine;
+#pragma unroll
+        for (int j = 0; j < kCompactItems; ++j) {
+            if (len[j] > 0u) {
+                const uint32_t* src = a.cmds + (size_t)(first + j) * 5;
+                uint32_t* dst = a.out_cmds + (size_t)pos * 5;
+                dst[0] = len[j];
+                dst[1] = src[1];
+                dst[2] = src[2];
+                dst[3] = src[3];
+                dst[4] = src[4];
+                ++pos;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace rcull

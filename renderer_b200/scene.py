@@ -90,6 +90,27 @@ def synth_mesh_table(n_meshes: int = N_MESHES, seed: int = SEED) -> np.ndarray:
     return t
 
 
+def synth_geometry(meshes: np.ndarray, seed: int = SEED, last_vertices: int = 4096):
+    """Consolidated position / index buffers for a synthetic mesh table: mesh m owns vertices
+    [vertex_offset[m], vertex_offset[m+1]) placed uniformly inside its AABB, and every LOD's
+    index range [first_index, first_index + index_len) holds random triangles over them
+    (indices relative to vertex_offset, as generate_work.comp:122 adds it back)."""
+    rng = np.random.Generator(np.random.PCG64(seed ^ 0x9E3779B9))
+    voff = meshes["vertex_offset"].astype(np.int64)
+    n_vert = np.append(voff[1:], voff[-1] + last_vertices) - voff
+    positions = np.empty((int(voff[-1] + last_vertices), 3), np.float32)
+    n_idx = int(max(int(m["lod"][l][0]) + int(m["lod"][l][1]) for m in meshes for l in range(int(m["n_lods"]))))
+    indices = np.zeros(n_idx, np.uint32)
+    for m, mesh in enumerate(meshes):
+        lo, hi = mesh["aabb_min"].astype(np.float64), mesh["aabb_max"].astype(np.float64)
+        nv = int(n_vert[m])
+        positions[voff[m] : voff[m] + nv] = (lo + rng.random((nv, 3)) * (hi - lo)).astype(np.float32)
+        for l in range(int(mesh["n_lods"])):
+            first, length = int(mesh["lod"][l][0]), int(mesh["lod"][l][1])
+            indices[first : first + length] = rng.integers(0, nv, length, dtype=np.uint32)
+    return positions, indices
+
+
 def to_components(pos_scale: np.ndarray, rot: np.ndarray):
     """SoA columns -> the reference's AoS components (Position, Rotation, Scale)."""
     return (
@@ -124,6 +145,17 @@ def camera_view(aspect: float = 16.0 / 9.0, pos=CAMERA_POS, rot=CAMERA_ROT) -> n
     rot = np.ascontiguousarray(rot, np.float32)
     lib.rcull_project_camera(aspect, _fp(pos), _fp(rot), None, None, None, C.byref(v))
     return np.ctypeslib.as_array(v.planes).copy().astype(np.float32)
+
+
+def camera_pv(aspect: float = 16.0 / 9.0, pos=CAMERA_POS, rot=CAMERA_ROT) -> np.ndarray:
+    """projection * view of the camera, column-major (CameraMatrices.pv, generate_work.comp:33)."""
+    lib = _lib.load()
+    v = View()
+    pos = np.ascontiguousarray(pos, np.float32)
+    rot = np.ascontiguousarray(rot, np.float32)
+    pv = np.zeros(16, np.float32)
+    lib.rcull_project_camera(aspect, _fp(pos), _fp(rot), None, None, _fp(pv), C.byref(v))
+    return pv
 
 
 def quat_look_at_lh(direction, up=(0.0, 1.0, 0.0)) -> np.ndarray:

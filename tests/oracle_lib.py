@@ -39,6 +39,8 @@ def lib():
         L.oracle_frame.restype = C.c_int
         L.oracle_emit_per_mesh.argtypes = [_P, _P, _P, _u64, _P, _u32, _P, _f, _u32, _P, _P, _P, _P]
         L.oracle_emit_per_mesh.restype = C.c_int
+        L.oracle_tri_cull.argtypes = [_P, _P, _u32, _P, _u32, _P, _P, _u64, _P, _u64, _P, _u64, _P, _P, _P, C.c_int]
+        L.oracle_tri_cull.restype = C.c_int
         L.oracle_synth_entities.argtypes = [_u64, _u64, _u64, _f, _u32, _P, _P, _P, _P]
         _lib = L
     return _lib
@@ -159,3 +161,36 @@ def emit_per_mesh(pos, mesh_id, flags, meshes, cam_pos, lod_distance=10.0, draw_
     if rc != 0:
         raise ValueError("oracle_emit_per_mesh failed")
     return cmds[: count.value], visible[: inst.value]
+
+
+def src_first_index(pos, mesh_id, cmds, meshes, cam_pos, lod_distance=10.0, draw_index_base=0):
+    """indexOffset push constant of every command (cull_pipeline.rs:544-548): first_index of the
+    LOD pick_lod chooses for the command's entity."""
+    pos = f32(pos)
+    cam = f32(cam_pos)
+    out = np.empty(len(cmds), np.uint32)
+    for c, cmd in enumerate(cmds):
+        e = int(cmd["firstInstance"]) - draw_index_base
+        m = meshes[int(mesh_id[e])]
+        lod = pick_lod(cam, pos[e], int(m["n_lods"]), lod_distance)
+        out[c] = m["lod"][lod][0]
+    return out
+
+
+def tri_cull(cmds, src_first, model, pv, positions, indices, out_capacity, draw_index_base=0, n_threads=1):
+    """A8 + A7 for one view's command list.  Returns dict(indices, cmds, count, kept_indices)."""
+    cmds = np.ascontiguousarray(cmds, dtype=CMD_DTYPE)
+    src_first = np.ascontiguousarray(src_first, dtype=np.uint32)
+    model, pvv = f32(model), f32(pv).reshape(16)
+    positions = f32(positions)
+    indices = np.ascontiguousarray(indices, dtype=np.uint32)
+    out_idx = np.zeros(int(out_capacity), np.uint32)
+    out_cmds = np.zeros(len(cmds), CMD_DTYPE)
+    count = np.zeros(1, np.uint32)
+    kept = np.zeros(1, np.uint64)
+    rc = lib().oracle_tri_cull(p(cmds), p(src_first), len(cmds), p(model), draw_index_base, p(pvv), p(positions),
+                               len(positions) // 3 if positions.ndim == 1 else len(positions), p(indices), len(indices),
+                               p(out_idx), int(out_capacity), p(out_cmds), p(count), p(kept), int(n_threads))
+    if rc != 0:
+        raise ValueError("oracle_tri_cull: index or vertex out of range")
+    return dict(indices=out_idx, cmds=out_cmds[: int(count[0])], count=int(count[0]), kept_indices=int(kept[0]))

@@ -37,7 +37,8 @@ def test_struct_layouts_match_the_header():
     assert _lib.MESH_DTYPE.itemsize == 80  # rcull_mesh
     assert _lib.CMD_DTYPE.itemsize == 20  # VkDrawIndexedIndirectCommand stride (generate_work.comp:9-15)
     assert C.sizeof(_lib.View) == 96
-    assert C.sizeof(_lib.Config) == 48
+    assert C.sizeof(_lib.Config) == 56
+    assert C.sizeof(_lib.TriOutputs) == 32
     assert C.sizeof(_lib.Outputs) == 8 * (2 + 3 * _lib.MAX_VIEWS + 2)
 
 

@@ -1,0 +1,94 @@
+"""GPU parity of stage 2 (SURVEY 8a rows A8 + A7): per-triangle cull of the camera view's
+survivors and compaction of the commands that kept a triangle, against the CPU oracle's
+restatement of generate_work.comp / compact_draw_stream.comp.  Commands, counts and the
+culled index buffer must be bit-exact (ascending-triangle order is the canonical order of
+both; the reference's own order inside a mesh is atomic-arrival order)."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from renderer_b200 import CullContext, RcullError, scene
+
+pytestmark = pytest.mark.gpu
+
+MESHES = scene.synth_mesh_table()
+POSITIONS, INDICES = scene.synth_geometry(MESHES)
+
+
+def run_tri(n, half_box, *, base=0, cam_pos=scene.CAMERA_POS, capacity=None, threads=8, seed=scene.SEED):
+    ps, rot, mesh = scene.synth_entities(seed, 0, n, half_box, len(MESHES))
+    views = scene.camera_view(pos=cam_pos)[None]
+    pv = scene.camera_pv(pos=cam_pos)
+    pos, quat, scale = scene.to_components(ps, rot)
+    ref = O.frame(pos, quat, scale, mesh, MESHES, views, cam_pos, draw_index_base=base, n_threads=threads)
+    total = int(ref["totals"][0])
+    cap = capacity if capacity is not None else max(total, 3)
+    with CullContext(max(n, 1), max_views=1, max_meshes=len(MESHES), capacity_tri_indices=cap) as ctx:
+        ctx.set_mesh_table(MESHES)
+        ctx.set_geometry(POSITIONS, INDICES)
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(views, cam_pos, n=n, draw_index_base=base)
+        ctx.tri_cull(pv, draw_index_base=base)
+        count, kept = ctx.tri_counts()
+        src = O.src_first_index(pos, mesh, ref["cmds"][0], MESHES, cam_pos, draw_index_base=base)
+        want = O.tri_cull(ref["cmds"][0], src, ref["model"], pv, POSITIONS, INDICES, cap, draw_index_base=base, n_threads=threads)
+        assert count == want["count"]
+        assert kept == want["kept_indices"]
+        got_cmds = ctx.tri_cmds(count)
+        assert np.array_equal(got_cmds, want["cmds"])
+        got_idx = ctx.tri_indices(0, cap)
+        for c in want["cmds"]:  # only the ranges the commands own are defined
+            a, b = int(c["firstIndex"]), int(c["firstIndex"]) + int(c["indexCount"])
+            assert np.array_equal(got_idx[a:b], want["indices"][a:b])
+        assert ctx.launch_count == 3  # frame + tri_cull + compact_draw_stream
+        return count, kept, total, int(ref["counts"][0])
+
+
+def test_tri_cull_small_scene():
+    count, kept, total, visible = run_tri(20_000, 40.0)
+    assert 0 < count <= visible and 0 < kept < total
+
+
+@pytest.mark.parametrize("n", [1, 33, 1500])
+def test_tri_cull_ragged(n):
+    run_tri(n, 15.0)
+
+
+def test_tri_cull_draw_index_base():
+    run_tri(5_000, 30.0, base=1_000_000)
+
+
+def test_tri_cull_nothing_visible():
+    count, kept, total, visible = run_tri(2_000, 40.0, cam_pos=np.array([5000.0, 0.0, 0.0], np.float32))
+    assert (count, kept, visible) == (0, 0, 0)
+
+
+def test_tri_cull_config2_1m_camera():
+    count, kept, total, visible = run_tri(1_000_000, 250.0, threads=16)
+    assert visible > 10_000 and count > 0 and kept % 3 == 0
+
+
+def test_tri_cull_errors_are_loud():
+    with CullContext(100, max_views=1, max_meshes=len(MESHES)) as ctx:
+        with pytest.raises(RcullError):  # context created without the stage
+            ctx.set_geometry(POSITIONS, INDICES)
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, 2000, 15.0, len(MESHES))
+    views = scene.camera_view()[None]
+    with CullContext(2000, max_views=1, max_meshes=len(MESHES), capacity_tri_indices=300) as ctx:
+        ctx.set_mesh_table(MESHES)
+        with pytest.raises(RcullError):  # no geometry yet
+            ctx.tri_cull(scene.camera_pv())
+        ctx.set_geometry(POSITIONS, INDICES)
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(views, scene.CAMERA_POS)
+        ctx.tri_cull(scene.camera_pv())
+        with pytest.raises(RcullError):  # culled index buffer too small
+            ctx.tri_counts()
+    with CullContext(2000, max_views=1, max_meshes=len(MESHES), capacity_tri_indices=1 << 22) as ctx:
+        ctx.set_mesh_table(MESHES)
+        ctx.set_geometry(POSITIONS[:100], INDICES)  # vertices missing
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(views, scene.CAMERA_POS)
+        ctx.tri_cull(scene.camera_pv())
+        with pytest.raises(RcullError):
+            ctx.tri_counts()

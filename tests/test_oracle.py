@@ -179,3 +179,105 @@ def test_threads_do_not_change_results():
     assert np.array_equal(a["model"], b["model"]) and np.array_equal(a["flags"], b["flags"])
     for k in range(3):
         assert np.array_equal(a["cmds"][k], b["cmds"][k])
+
+
+# ---- stage 2: per-triangle cull (generate_work.comp) + compact_draw_stream ------------------
+def _one_cmd(index_len, first_instance=0, first_index=0):
+    c = np.zeros(1, O.CMD_DTYPE)
+    c[0] = (index_len, 1, first_index, 0, first_instance)
+    return c
+
+
+def test_tri_cull_kats():
+    """Identity model and pv: clip == vertex (w = 1).  The determinant of (v0.xyw, v1.xyw, v2.xyw)
+    is twice the signed area in xy: > 0 is culled (generate_work.comp:143), a triangle with all
+    three x > 1 is culled (:152-155), one straddling the edge is kept."""
+    eye = np.eye(4, dtype=np.float32).reshape(-1)
+    pos = np.array([
+        [0, 0, 0.5], [0, 0.5, 0.5], [0.5, 0, 0.5],     # det < 0 -> kept
+        [2, 0, 0.5], [2, 0.5, 0.5], [2.5, 0, 0.5],     # same winding, all x > 1 -> culled
+        [0.9, 0, 0.5], [0.9, 0.5, 0.5], [1.5, 0, 0.5],  # straddles x = 1 -> kept
+    ], np.float32)
+    idx = np.array([0, 1, 2,  0, 2, 1,  3, 4, 5,  6, 7, 8], np.uint32)  # second triangle: flipped winding -> det > 0 -> culled
+    r = O.tri_cull(_one_cmd(12), np.zeros(1, np.uint32), eye, eye, pos, idx, 12)
+    assert r["count"] == 1 and r["kept_indices"] == 6
+    assert r["cmds"][0]["indexCount"] == 6 and r["cmds"][0]["firstIndex"] == 0
+    assert r["indices"][:6].tolist() == [0, 1, 2, 6, 7, 8]
+
+
+def test_tri_cull_compacts_empty_commands_and_keeps_order():
+    eye = np.eye(4, dtype=np.float32).reshape(-1)
+    pos = np.array([[0, 0, 0.5], [0, 0.5, 0.5], [0.5, 0, 0.5]], np.float32)
+    idx = np.array([0, 1, 2,  0, 2, 1], np.uint32)  # kept, culled
+    cmds = np.zeros(3, O.CMD_DTYPE)
+    cmds[0] = (3, 1, 0, 0, 10)  # kept triangle
+    cmds[1] = (3, 1, 3, 0, 11)  # culled triangle -> indexCount 0 -> dropped (compact_draw_stream.comp:41)
+    cmds[2] = (6, 1, 6, 0, 12)  # both -> one kept
+    src = np.array([0, 3, 0], np.uint32)
+    model = np.tile(eye, 3)
+    r = O.tri_cull(cmds, src, model, eye, pos, idx, 12, draw_index_base=10)
+    assert r["count"] == 2 and r["kept_indices"] == 6
+    assert r["cmds"]["firstInstance"].tolist() == [10, 12]
+    assert r["cmds"]["indexCount"].tolist() == [3, 3]
+    assert r["indices"][0:3].tolist() == [0, 1, 2] and r["indices"][6:9].tolist() == [0, 1, 2]
+
+
+def test_tri_cull_matches_numpy_restatement():
+    """Independent numpy restatement of the shader arithmetic (float32, same operation order)
+    over a random scene through the whole frame -> tri pipeline."""
+    from renderer_b200 import scene as S
+    meshes = S.synth_mesh_table()
+    positions, indices = S.synth_geometry(meshes)
+    n = 300
+    ps, rot, mesh = S.synth_entities(S.SEED, 0, n, 12.0, len(meshes))
+    pos, quat, scale = S.to_components(ps, rot)
+    _, _, pv, planes = O.project_camera(16.0 / 9.0, S.CAMERA_POS, S.CAMERA_ROT)
+    ref = O.frame(pos, quat, scale, mesh, meshes, planes[None], S.CAMERA_POS)
+    cmds = ref["cmds"][0]
+    src = O.src_first_index(pos, mesh, cmds, meshes, S.CAMERA_POS)
+    total = int(ref["totals"][0])
+    r = O.tri_cull(cmds, src, ref["model"], pv, positions, indices, max(total, 3))
+    f = np.float32
+
+    def mul(m, v):  # GLSL mat4 * vec4, columns left to right; m column-major [16], v [k][4]
+        out = np.empty_like(v)
+        for row in range(4):
+            a = f(m[0 + row]) * v[:, 0]
+            a = a + f(m[4 + row]) * v[:, 1]
+            a = a + f(m[8 + row]) * v[:, 2]
+            a = a + f(m[12 + row]) * v[:, 3]
+            out[:, row] = a
+        return out
+
+    kept_total, n_out = 0, 0
+    with np.errstate(all="ignore"):
+        for c, cmd in enumerate(cmds):
+            nt = int(cmd["indexCount"]) // 3
+            tri = indices[int(src[c]) : int(src[c]) + 3 * nt].reshape(nt, 3)
+            model = ref["model"].reshape(-1, 16)[int(cmd["firstInstance"])]
+            clip = []
+            for k in range(3):
+                v = positions[int(cmd["vertexOffset"]) + tri[:, k].astype(np.int64)]
+                v4 = np.concatenate([v, np.ones((nt, 1), np.float32)], axis=1)
+                clip.append(mul(pv, mul(model, v4)))
+            a, b, d = clip
+            t0 = b[:, 1] * d[:, 3] - d[:, 1] * b[:, 3]
+            t1 = a[:, 1] * d[:, 3] - d[:, 1] * a[:, 3]
+            t2 = a[:, 1] * b[:, 3] - b[:, 1] * a[:, 3]
+            det = (a[:, 0] * t0 - b[:, 0] * t1) + d[:, 0] * t2
+            x = [q[:, 0] / q[:, 3] for q in clip]
+            y = [q[:, 1] / q[:, 3] for q in clip]
+            culled = det > 0
+            culled |= (x[0] < -1) & (x[1] < -1) & (x[2] < -1)
+            culled |= (x[0] > 1) & (x[1] > 1) & (x[2] > 1)
+            culled |= (y[0] < -1) & (y[1] < -1) & (y[2] < -1)
+            culled |= (y[0] > 1) & (y[1] > 1) & (y[2] > 1)
+            keep = tri[~culled].reshape(-1)
+            if len(keep):
+                assert r["cmds"][n_out]["firstInstance"] == cmd["firstInstance"]
+                assert r["cmds"][n_out]["indexCount"] == len(keep)
+                fi = int(cmd["firstIndex"])
+                assert np.array_equal(r["indices"][fi : fi + len(keep)], keep)
+                n_out += 1
+                kept_total += len(keep)
+    assert n_out == r["count"] and kept_total == r["kept_indices"] and n_out > 0
