@@ -29,6 +29,9 @@ WORKLOADS = {
     "16m_5view": dict(n=16 * 1024 * 1024, n_views=5, half_box=600.0),
     "16m_1view": dict(n=16 * 1024 * 1024, n_views=1, half_box=600.0),
     "1m_1view": dict(n=1_000_000, n_views=1, half_box=250.0),
+    # BASELINE configs[1] through BOTH stages of the reference's cull pass: the frame kernel, then the
+    # per-triangle cull (generate_work.comp) of the camera survivors and compact_draw_stream
+    "1m_tri": dict(n=1_000_000, n_views=1, half_box=250.0, tri=True),
 }
 METRIC = "entities/sec transformed+culled+compacted"
 UNIT = "entities/s"
@@ -149,8 +152,20 @@ def gpu_arm(args, wl):
     lo = rank * n  # weak scaling: every rank owns n entities of an (n * world)-entity scene
     meshes = scene.synth_mesh_table()
     views = scene.scene_views(n_views)
-    ctx = CullContext(n, max_views=n_views, max_meshes=len(meshes), device=local_rank)
+    tri = bool(wl.get("tri")) and world == 1
+    tri_cap = 0
+    if tri:  # size the culled index buffer from the scene itself (the reference fixes it at 20 M triples)
+        with CullContext(n, max_views=n_views, max_meshes=len(meshes), device=local_rank) as probe:
+            probe.set_mesh_table(meshes)
+            probe.synth_entities(scene.SEED, lo, n, wl["half_box"], len(meshes))
+            probe.frame(views, scene.CAMERA_POS, draw_index_base=lo)
+            tri_cap = int(probe.counts()[1][0]) + 3
+    ctx = CullContext(n, max_views=n_views, max_meshes=len(meshes), device=local_rank, capacity_tri_indices=tri_cap)
     ctx.set_mesh_table(meshes)
+    pv = None
+    if tri:
+        ctx.set_geometry(*scene.synth_geometry(meshes))
+        pv = scene.camera_pv()
     stream = torch.cuda.Stream(device=dev)
     sh = stream.cuda_stream
     ctx.synth_entities(scene.SEED, lo, n, wl["half_box"], len(meshes), stream=sh)
@@ -187,6 +202,8 @@ def gpu_arm(args, wl):
             step()
             if merger:
                 do_merge()
+            if tri:
+                ctx.tri_cull(pv, draw_index_base=lo, stream=sh)
             if flush is not None:
                 flush.zero_()
         sync_all()
@@ -199,6 +216,8 @@ def gpu_arm(args, wl):
                 ev[i][1].record(stream)
                 if merger:
                     do_merge()
+                if tri:
+                    ctx.tri_cull(pv, draw_index_base=lo, stream=sh)
                 ev[i][2].record(stream)
                 if flush is not None:
                     flush.zero_()
@@ -279,6 +298,16 @@ def gpu_arm(args, wl):
                          "bytes_per_entity": bytes_per_entity, "ms_per_launch": t_launch * 1e3},
             "clocks": clocks.summary(),
         }
+        if tri:
+            n_cmd, kept = ctx.tri_counts()
+            t_tri = (t_step - t_frame) / args.steps
+            tris = int(totals[0]) // 3
+            line["tri_stage"] = {
+                "kernels": "tri_cull + compact_draw_stream", "ms_per_step": t_tri * 1e3, "triangles_in": tris, "triangles_kept": kept // 3,
+                "commands_in": int(counts[0]), "commands_out": n_cmd, "gtri_per_s": tris / t_tri / 1e9,
+                # 12 B index triple read per triangle, 12 B written per kept one, 20 + 4 B command in, 20 B out
+                "algorithmic_gbs": (12.0 * tris + 4.0 * kept + 24.0 * int(counts[0]) + 20.0 * n_cmd) / t_tri / 1e9,
+                "note": "e2e and cpu_baseline cover the frame stage only"}
         if world == 1:
             line["cpu_baseline"] = cpu_baseline(wl, steps=3, warmup=1, threads=os.cpu_count() or 1)
         prof = os.path.join(ROOT, "profiles", "r01_traffic.json")

@@ -72,6 +72,7 @@ struct rcull_ctx {
     uint32_t* mesh = nullptr;
     float4* mesh_aabb = nullptr;
     uint4* lod_tab = nullptr;
+    uint32_t* mesh_len1 = nullptr;
     uint32_t n_meshes = 0;
     uint32_t len_small = 0;
     uint32_t* keys_sorted = nullptr;  // per-mesh mode scratch
@@ -81,7 +82,6 @@ struct rcull_ctx {
     unsigned long long* meta_out = nullptr;  // set by rcull_merge_create: the frame kernel writes the exchange words itself
     OutputSet out[3];
     ulonglong2* status = nullptr;
-    ulonglong2* gstatus = nullptr;
     size_t status_bytes = 0;
     uint32_t* ticket = nullptr;  // [0] = tile ticket, [1] = error flag
     uint32_t ticket_base = 0;
@@ -242,6 +242,7 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
     TRY(dev_alloc(c, &c->mesh, c->cap));
     TRY(dev_alloc(c, &c->mesh_aabb, (size_t)cfg->max_meshes * 2));
     TRY(dev_alloc(c, &c->lod_tab, (size_t)cfg->max_meshes * kMaxLods));
+    TRY(dev_alloc(c, &c->mesh_len1, (size_t)cfg->max_meshes));
     // padding slots of the last tile are staged by TMA like real ones: keep them defined
     if (cudaMemset(c->pos_scale, 0, c->cap * 16) != cudaSuccess || cudaMemset(c->rot, 0, c->cap * 16) != cudaSuccess ||
         cudaMemset(c->mesh, 0, c->cap * 4) != cudaSuccess) {
@@ -269,10 +270,8 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
         cudaMemset(o.totals, 0, kMaxViews * 8);
     }
     const size_t max_tiles = c->cap / kTile;
-    const size_t max_groups = (max_tiles + kGroup - 1) / kGroup;  // group descriptors follow the tile descriptors
-    c->status_bytes = (max_tiles + max_groups) * cfg->max_views * sizeof(ulonglong2);
-    TRY(dev_alloc(c, &c->status, (max_tiles + max_groups) * cfg->max_views));
-    c->gstatus = c->status + max_tiles * cfg->max_views;
+    c->status_bytes = max_tiles * cfg->max_views * sizeof(ulonglong2);
+    TRY(dev_alloc(c, &c->status, max_tiles * cfg->max_views));
     TRY(dev_alloc(c, &c->ticket, 2));
     if (cfg->output_mode == RCULL_PER_MESH_INSTANCED) {
         if (c->cap_vis > 0x7fffffffull) {
@@ -339,6 +338,7 @@ int rcull_set_mesh_table(rcull_ctx* c, const rcull_mesh* meshes, uint32_t n) {
     if (n == 0 || n > c->cfg.max_meshes) return fail(RCULL_ERR_INVALID, "mesh count %u exceeds max_meshes %u", n, c->cfg.max_meshes);
     std::vector<float4> aabb(2 * (size_t)n);
     std::vector<uint4> lods((size_t)n * kMaxLods, make_uint4(0, 0, 0, 0));
+    std::vector<uint32_t> len1(n);
     uint32_t max_len = 0;
     for (uint32_t i = 0; i < n; ++i) {
         const rcull_mesh& m = meshes[i];
@@ -347,7 +347,10 @@ int rcull_set_mesh_table(rcull_ctx* c, const rcull_mesh* meshes, uint32_t n) {
         float nl;
         memcpy(&nl, &m.n_lods, 4);
         aabb[2 * i] = make_float4(m.aabb_min[0], m.aabb_min[1], m.aabb_min[2], nl);
-        aabb[2 * i + 1] = make_float4(m.aabb_max[0], m.aabb_max[1], m.aabb_max[2], 0.f);
+        float l0;  // index_len of lod 0 rides in the spare word; lod 1's (the only other one pick_lod returns) in len1
+        memcpy(&l0, &m.lod[0].index_len, 4);
+        aabb[2 * i + 1] = make_float4(m.aabb_max[0], m.aabb_max[1], m.aabb_max[2], l0);
+        len1[i] = m.n_lods > 1 ? m.lod[1].index_len : m.lod[0].index_len;
         for (uint32_t l = 0; l < m.n_lods; ++l) {
             if (m.lod[l].index_len > max_len) max_len = m.lod[l].index_len;
             lods[(size_t)i * kMaxLods + l] = make_uint4(m.lod[l].index_len, m.lod[l].first_index, (uint32_t)m.vertex_offset, 0);
@@ -356,6 +359,7 @@ int rcull_set_mesh_table(rcull_ctx* c, const rcull_mesh* meshes, uint32_t n) {
     CU(cudaSetDevice(c->cfg.device));
     CU(cudaMemcpy(c->mesh_aabb, aabb.data(), aabb.size() * sizeof(float4), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(c->lod_tab, lods.data(), lods.size() * sizeof(uint4), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(c->mesh_len1, len1.data(), len1.size() * 4, cudaMemcpyHostToDevice));
     c->n_meshes = n;
     c->len_small = max_len < (1u << 25) ? 1u : 0u;
     return RCULL_OK;
@@ -432,6 +436,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     a.mesh = c->mesh;
     a.mesh_aabb = c->mesh_aabb;
     a.lod_tab = c->lod_tab;
+    a.mesh_len1 = c->mesh_len1;
     a.aabb = o.aabb;
     for (uint32_t v = 0; v < n_views; ++v) {
         a.flags[v] = o.flags[v];
@@ -446,8 +451,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
             pc.px = make_float2(pl[0], pl[0]);
             pc.py = make_float2(pl[1], pl[1]);
             pc.pz = make_float2(pl[2], pl[2]);
-            pc.pw = make_float2(pl[3], pl[3]);
-            pc.one = make_float2(1.0f, 1.0f);
+            pc.pw = pl[3];
         }
     }
     a.src_first = o.src_first;
@@ -456,7 +460,6 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     a.meta_out = c->meta_out;
     a.max_views = c->cfg.max_views;
     a.status = c->status;
-    a.gstatus = c->gstatus;
     a.ticket = c->ticket;
     a.error_flag = c->ticket + 1;
     a.ticket_base = c->ticket_base;
@@ -703,7 +706,7 @@ int rcull_tri_cull(rcull_ctx* c, const float pv[16], uint32_t draw_index_base, u
     t.out_capacity = c->cfg.capacity_tri_indices;
     t.cap_cmds = (uint32_t)(c->cap_cmds > 0xffffffffull ? 0xffffffffull : c->cap_cmds);
     t.draw_index_base = draw_index_base;
-    memcpy(t.pv, pv, sizeof t.pv);
+    memcpy(t.pv.m, pv, sizeof t.pv.m);
     tri_cull<<<c->sm_count * 8, kTriThreads, 0, s>>>(t);
     CU(cudaGetLastError());
     CompactArgs k;

@@ -160,16 +160,6 @@ __device__ __forceinline__ float2 add2_rn(float2 a, float2 b) {
     return *reinterpret_cast<float2*>(&r);
 }
 
-// a * b + c with ONE rounding per lane -- only ever used with b == 1.0 (an exactly rounded add)
-__device__ __forceinline__ float2 fma2_rn(float2 a, float2 b, float2 c) {
-    unsigned long long r;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;"
-        : "=l"(r)
-        : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)),
-          "l"(*reinterpret_cast<unsigned long long*>(&c)));
-    return *reinterpret_cast<float2*>(&r);
-}
-
 // ---- per-entity arithmetic (operation order = SURVEY 8a; compiled -fmad=false) ----
 struct Mat34 {  // upper 3 rows of the column-major model matrix; row 3 is (0,0,0,1)
     float m00, m10, m20;  // column 0

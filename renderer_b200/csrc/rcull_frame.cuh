@@ -35,7 +35,6 @@ constexpr int kMaxBufs = 4;   // survivor bookkeeping ring (tiles whose commands
 constexpr int kRing = 8;      // tile-id ring: bookkeeping ring + the tile being loaded + slack
 constexpr int kMaxViews = 8;
 constexpr int kMaxLods = 6;
-constexpr int kGroup = 64;   // tiles per look-back group (two windows of 32 lanes)
 constexpr uint32_t kStageBytes = kTile * (16 + 16 + 4);  // pos_scale + rot + mesh
 constexpr int kMatBoxBytes = 32 * 64;                    // 32 model matrices = one TMA store box
 
@@ -56,15 +55,15 @@ constexpr uint64_t kFlagAgg = 1, kFlagIncl = 2;
 struct PlaneC {
     float2 ax, ay, az;  // |p.x|, |p.y|, |p.z|
     float2 px, py, pz;
-    float2 pw;   // p.w twice
-    float2 one;  // 1.0 twice: the multiplier that turns the packed FMA into an exactly rounded add
+    float pw, pad0, pad1, pad2;
 };
 
 struct FrameArgs {
     const float4* pos_scale;
     const float4* rot;
     const uint32_t* mesh;
-    const float4* mesh_aabb;  // [M][2]: (min.xyz, n_lods), (max.xyz, -)
+    const float4* mesh_aabb;  // [M][2]: (min.xyz, n_lods), (max.xyz, index_len of lod 0)
+    const uint32_t* mesh_len1;  // [M]: index_len of lod 1 (pick_lod only ever returns lod 0 or 1)
     const uint4* lod_tab;     // [M*kMaxLods]: index_len, first_index, vertex_offset, 0
     float* aabb;              // optional [n][6]
     uint8_t* flags[kMaxViews];  // optional [n]
@@ -76,7 +75,6 @@ struct FrameArgs {
     unsigned long long* meta_out;  // optional [2 * max_views]: counts then totals as u64 (merge exchange words)
     uint32_t max_views;
     ulonglong2* status;   // [views][n_tiles]
-    ulonglong2* gstatus;  // [views][ceil(n_tiles / kGroup)] group descriptors of the two-level look-back
     uint32_t* ticket;
     uint32_t* error_flag;
     uint32_t ticket_base;
@@ -114,21 +112,30 @@ struct FrameSmem {
     uint32_t tile_ring[kRing];  // tile id of iteration it at [it % kRing]
     uint32_t dummy[kComputeWarps];  // where culled lanes 'store' their list entry (keeps the list code branch-free)
     // followed by: PlaneC planes[V][6] (a shared-memory copy: LDS.128 instead of indexed LDC), then
-    // uint32_t slot[bufs][kTile] -- (mesh, lod) slot of every entity -- and
-    // uint8_t wlist[bufs][kComputeWarps][V * kWarpSpan] -- per-warp combined
-    // survivor list, view-major, entry = slot in the warp's span (the view follows
-    // from the entry's position and the per-view counts)
+    // uint8_t wlist[bufs][kComputeWarps][V * kWarpSpan] -- per-warp combined survivor list,
+    // view-major, entry = lod << 7 | slot in the warp's span (the view follows from the entry's
+    // position and the per-view counts) -- and, when it fits, a copy of the mesh table
+    // (float4 aabb[M][2], uint32_t len1[M]: 36 bytes per mesh)
 };
 
 template <int V>
 __host__ __device__ constexpr int frame_bufs() {  // what still lets kCtasPerSm CTAs share an SM's shared memory
-    constexpr size_t fixed = sizeof(FrameSmem) + V * 6 * sizeof(PlaneC) + 1024, per_buf = (4 + V) * kTile;
+    constexpr size_t fixed = sizeof(FrameSmem) + V * 6 * sizeof(PlaneC) + 1024, per_buf = V * kTile;
     constexpr size_t b = (kSmemPerCta - fixed) / per_buf;
     return b > (size_t)kMaxBufs ? kMaxBufs : (int)b;
 }
 template <int V>
+__host__ __device__ constexpr size_t frame_lists_end() {  // offset of the first byte behind the survivor lists
+    return (sizeof(FrameSmem) + V * 6 * sizeof(PlaneC) + frame_bufs<V>() * V * kTile + 15) / 16 * 16;
+}
+template <int V>
+__host__ __device__ constexpr uint32_t frame_mesh_cap() {  // meshes whose table fits behind the lists (36 bytes each)
+    constexpr size_t left = kSmemPerCta - 1024 - frame_lists_end<V>();
+    return left / 36 > 1024 ? 1024u : (uint32_t)(left / 36) / 4 * 4;
+}
+template <int V>
 constexpr size_t frame_smem_bytes() {
-    return sizeof(FrameSmem) + V * 6 * sizeof(PlaneC) + frame_bufs<V>() * (4 + V) * kTile + 1024;  // + slack to align the base
+    return frame_lists_end<V>() + frame_mesh_cap<V>() * 36 + 1024;  // + slack to align the base
 }
 static_assert(frame_bufs<1>() >= 2 && frame_bufs<kMaxViews>() >= 2, "at least two tiles of survivor bookkeeping");
 
@@ -150,206 +157,15 @@ __device__ __forceinline__ bool desc_ready(const ulonglong2& d, uint32_t epoch) 
 //   publish  -- as soon as the compute warps are done with a tile, reduce their
 //               per-warp counts / index sums and publish the tile AGGREGATE; this only
 //               depends on the CTA's own work, so aggregates appear without delay;
-//   resolve  -- for the oldest unresolved tile, one look-back round per pass, all views
-//               together, every load in flight at once.  A window that is not fully
-//               published yet is simply retried on the next pass.
-// The look-back is TWO-LEVEL.  Tiles form groups of kGroup = 64 consecutive tiles.  Round 1
-// walks the tile's own group (at most 63 predecessors = one window of 2 x 32 lanes); if no
-// inclusive prefix turns up there, the following rounds walk GROUP descriptors, 64 groups
-// (4096 tiles) per window.  The last tile of a group is its milestone: what its round 1 sums
-// up, plus its own aggregate, is the group aggregate, and its inclusive prefix is the group's.
-// A flat look-back resolves at most (window / round latency) tiles per microsecond along the
-// chain of inclusive prefixes -- with 5 views and 64-wide windows that was slower than the
-// streaming part of the kernel; with groups the chain has one link per 64 tiles.
+//   resolve  -- for the oldest unresolved tile, one look-back round per pass: all views
+//               together, 32*U predecessors per view with every load in flight at
+//               once (CTAs run in waves, so the last tile of a wave walks back over a
+//               whole wave of aggregates).  A window that is not fully published yet
+//               is simply retried on the next pass.
+// (A two-level variant -- groups of 64 tiles with milestone descriptors -- was measured
+// slower: every tile then needs two dependent rounds; see DESIGN.md.)
 template <int V>
 __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, uint32_t lane) {
-    constexpr int U = kGroup / 32;
-    constexpr uint32_t B = frame_bufs<V>();
-    const uint32_t epoch = args.epoch, n_tiles = args.n_tiles, n_groups = (n_tiles + kGroup - 1) / kGroup;
-    const uint64_t tag = (uint64_t)epoch << 34;
-    const ulonglong2 virt = make_ulonglong2(tag | (kFlagIncl << 32), 0ull);  // before the first group: inclusive prefix 0
-    const ulonglong2 none = make_ulonglong2(tag | (kFlagAgg << 32), 0ull);   // lanes past the group's first tile
-    ulonglong2* const status = args.status;
-    ulonglong2* const gstatus = args.gstatus;
-    uint32_t pub = 0, res = 0;  // tiles published / resolved so far (iteration numbers)
-    bool ended = false, active = false, groups = false;
-    uint32_t acc_c[V], tile = 0, in_group = 0, grp = 0;
-    uint64_t acc_l[V];
-    bool open[V];
-    int base = 0;
-    long long t_pub[kMaxBufs] = {0, 0, 0, 0}, t_act = 0;
-    while (true) {
-        bool progress = false;
-        // ---- publish ----
-        if (!ended && pub - res < B && mbar_test(&sm.done[pub % B], (pub / B) & 1u)) {
-            const uint32_t buf = pub % B, t = sm.tile_ring[pub % kRing];
-            progress = true;
-            if (t >= n_tiles) {
-                ended = true;  // end marker, passed on by the compute warps
-            } else {
-                uint32_t vstart_c = 0, vstart_l = 0;
-#pragma unroll
-                for (int k = 0; k < V; ++k) {  // lanes 0..6 stand for the compute warps
-                    const uint32_t c = lane < kComputeWarps ? sm.wcnt[buf][k][lane] : 0u;
-                    const uint64_t l = lane < kComputeWarps ? sm.wlen[buf][k][lane] : 0ull;
-                    uint32_t ic = c;
-                    uint64_t il = l;
-#pragma unroll
-                    for (int o = 1; o < kComputeWarps; o <<= 1) {
-                        const uint32_t tc = __shfl_up_sync(kFullMask, ic, o);
-                        const uint64_t tl = __shfl_up_sync(kFullMask, il, o);
-                        if (lane >= (uint32_t)o) {
-                            ic += tc;
-                            il += tl;
-                        }
-                    }
-                    if (lane < kComputeWarps) {
-                        // (prefix over lower warps) - (start of view k in the warp's combined list);
-                        // the tile's exclusive prefix is added when it is resolved
-                        sm.adj_cnt[buf][k][lane] = (ic - c) - vstart_c;
-                        sm.adj_len[buf][k][lane] = (uint32_t)(il - l) - vstart_l;
-                    }
-                    if (lane == kComputeWarps - 1) {
-                        sm.agg_cnt[buf][k] = ic;
-                        sm.agg_len[buf][k] = il;
-                        st_relaxed_v2(status + (size_t)k * n_tiles + t, tag | ((t == 0 ? kFlagIncl : kFlagAgg) << 32) | ic, il);
-                    }
-                    vstart_c += c;
-                    vstart_l += (uint32_t)l;
-                }
-                __syncwarp();
-                t_pub[pub % B] = RCULL_CLOCK();
-                ++pub;
-            }
-        }
-        // ---- resolve ----
-        if (res < pub) {
-            if (!active) {
-                tile = sm.tile_ring[res % kRing];
-                in_group = tile % kGroup;
-                grp = tile / kGroup;
-                groups = false;
-#pragma unroll
-                for (int k = 0; k < V; ++k) {
-                    acc_c[k] = 0;
-                    acc_l[k] = 0;
-                    open[k] = tile != 0;
-                }
-                active = true;
-                t_act = RCULL_CLOCK();
-            }
-            if (lane == 0) RCULL_STAT(2, 1);
-            ulonglong2 d[V][U];
-#pragma unroll
-            for (int k = 0; k < V; ++k)
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    if (!groups) {  // predecessors inside the tile's own group
-                        const uint32_t back = lane + 32u * u;
-                        d[k][u] = (open[k] && back < in_group) ? ld_relaxed_v2(status + (size_t)k * n_tiles + (tile - 1u - back)) : none;
-                    } else {  // earlier groups
-                        const int g = base - 32 * u;
-                        d[k][u] = (open[k] && g >= 0) ? ld_relaxed_v2(gstatus + (size_t)k * n_groups + g) : virt;
-                    }
-                }
-            // all views walk the same windows: a round only counts when every open view can use it
-            bool ok = true;
-#pragma unroll
-            for (int k = 0; k < V; ++k)
-#pragma unroll
-                for (int u = 0; u < U; ++u) ok = ok && desc_ready(d[k][u], epoch);
-            if (__all_sync(kFullMask, ok)) {
-                progress = true;
-                if (lane == 0) RCULL_STAT(3, 1);
-                bool any_open = false;
-#pragma unroll
-                for (int k = 0; k < V; ++k) {
-                    if (!open[k]) continue;
-                    bool stopped = false;
-#pragma unroll
-                    for (int u = 0; u < U; ++u) {
-                        const uint32_t incl_mask = __ballot_sync(kFullMask, ((uint32_t)(d[k][u].x >> 32) & 3u) == kFlagIncl);
-                        if (!stopped) {
-                            const uint32_t stop = incl_mask ? (uint32_t)__ffs(incl_mask) - 1u : 31u;
-                            if (lane <= stop) {
-                                acc_c[k] += (uint32_t)d[k][u].x;
-                                acc_l[k] += d[k][u].y;
-                            }
-                            stopped = incl_mask != 0u;
-                        }
-                    }
-                    open[k] = !stopped;
-                    any_open = any_open || !stopped;
-                }
-                if (!groups) {
-                    // Milestone tile: its in-group predecessors plus itself are the group.  Views that
-                    // already met an inclusive prefix publish the group's inclusive value further down.
-                    if (in_group == kGroup - 1) {
-                        const uint32_t buf = res % B;
-#pragma unroll
-                        for (int k = 0; k < V; ++k) {
-                            if (!open[k]) continue;
-                            const uint32_t gc = __reduce_add_sync(kFullMask, acc_c[k]);
-                            const uint64_t gl = warp_sum_u64(acc_l[k]);
-                            acc_c[k] = lane == 0 ? gc : 0u;
-                            acc_l[k] = lane == 0 ? gl : 0ull;
-                            if (lane == 0)
-                                st_relaxed_v2(gstatus + (size_t)k * n_groups + grp, tag | (kFlagAgg << 32) | (gc + sm.agg_cnt[buf][k]),
-                                              gl + sm.agg_len[buf][k]);
-                        }
-                    }
-                    groups = true;
-                    base = (int)grp - 1 - (int)lane;  // this lane's nearest earlier group
-                } else {
-                    base -= 32 * U;
-                }
-                if (!any_open) {  // resolved: publish inclusive values, hand the offsets to the compute warps
-                    const uint32_t buf = res % B;
-#pragma unroll
-                    for (int k = 0; k < V; ++k) {
-                        const uint32_t ec = __reduce_add_sync(kFullMask, acc_c[k]);
-                        const uint64_t el = warp_sum_u64(acc_l[k]);
-                        if (lane < kComputeWarps) {
-                            sm.adj_cnt[buf][k][lane] += ec;
-                            sm.adj_len[buf][k][lane] += (uint32_t)el;  // firstIndex is u32 and wraps like the reference's
-                        }
-                        if (lane == 0) {
-                            const uint32_t ic = ec + sm.agg_cnt[buf][k];
-                            const uint64_t il = el + sm.agg_len[buf][k];
-                            if (tile != 0) st_relaxed_v2(status + (size_t)k * n_tiles + tile, tag | (kFlagIncl << 32) | ic, il);
-                            if (in_group == kGroup - 1) st_relaxed_v2(gstatus + (size_t)k * n_groups + grp, tag | (kFlagIncl << 32) | ic, il);
-                            if (tile == n_tiles - 1) {
-                                args.counts[k] = ic;
-                                args.totals[k] = il;
-                                if (args.meta_out != nullptr) {
-                                    args.meta_out[k] = ic;
-                                    args.meta_out[args.max_views + k] = il;
-                                }
-                            }
-                        }
-                    }
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&sm.bases[buf]);
-                    if (lane == 0) {
-                        const long long now = RCULL_CLOCK();
-                        RCULL_STAT(0, 1);
-                        RCULL_STAT(1, now - t_pub[res % B]);
-                        RCULL_STAT(9, now - t_act);
-                    }
-                    ++res;
-                    active = false;
-                }
-            }
-        } else if (ended) {
-            break;
-        }
-        if (!progress) __nanosleep(200);
-    }
-}
-
-#ifndef RCULL_TWO_LEVEL
-template <int V>
-__device__ __forceinline__ void scan_warp_flat(const FrameArgs& args, FrameSmem& sm, uint32_t lane) {
     constexpr int U = V <= 4 ? 4 : 2;
     constexpr uint32_t B = frame_bufs<V>();
     const uint32_t epoch = args.epoch, n_tiles = args.n_tiles;
@@ -503,13 +319,11 @@ __device__ __forceinline__ void scan_warp_flat(const FrameArgs& args, FrameSmem&
     }
 }
 
-#endif
-
 // Compute-warp emission of its own survivors of a pending tile: one pass over the
 // warp's combined (all views) list, stable within every view.
 template <int V>
 __device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameSmem& sm, const uint8_t* wlist,
-                                             const uint32_t* slot_of, uint32_t buf, uint32_t tile_base, uint32_t warp, uint32_t lane) {
+                                             uint32_t buf, uint32_t tile_base, uint32_t warp, uint32_t lane) {
     uint32_t vend[V];  // end of view k in the combined list
     uint32_t total = 0;
 #pragma unroll
@@ -526,8 +340,11 @@ __device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameS
         if (act) {
 #pragma unroll
             for (int kk = 0; kk < V - 1; ++kk) k += i >= vend[kk] ? 1u : 0u;
-            e = warp * kWarpSpan + wlist[i];
-            slot = slot_of[e];
+            const uint32_t entry = wlist[i];  // lod << 7 | slot in the warp's span
+            e = warp * kWarpSpan + (entry & 127u);
+            uint32_t mid = __ldg(args.mesh + tile_base + e);  // survivors only: the column is still in L2
+            if (mid >= args.n_meshes) mid = 0;                // same clamp as the compute pass (error already flagged)
+            slot = mid * kMaxLods + (entry >> 7);
             L = __ldg(args.lod_tab + slot);
         }
         const uint32_t incl = warp_incl_scan_u32(L.x, lane);
@@ -584,20 +401,27 @@ __global__ void __maxnreg__(112)
     }
     float4* const sm_planes = reinterpret_cast<float4*>(reinterpret_cast<unsigned char*>(&sm) + sizeof(FrameSmem));
     for (uint32_t i = tid; i < V * 6 * 4; i += kThreads) sm_planes[i] = reinterpret_cast<const float4*>(&args.planes[0][0])[i];
+    // Mesh table: a shared-memory copy when it fits (the L1 left beside ~220 KB of shared memory
+    // is a few KB: table lines kept falling out of it), else the global one through generic loads.
+    const float4* mesh_tab = args.mesh_aabb;
+    const uint32_t* len1_tab = args.mesh_len1;
+    if (args.n_meshes <= frame_mesh_cap<V>()) {
+        float4* sm_mesh = reinterpret_cast<float4*>(reinterpret_cast<unsigned char*>(&sm) + frame_lists_end<V>());
+        uint32_t* sm_len1 = reinterpret_cast<uint32_t*>(sm_mesh + 2 * frame_mesh_cap<V>());
+        for (uint32_t i = tid; i < 2 * args.n_meshes; i += kThreads) sm_mesh[i] = args.mesh_aabb[i];
+        for (uint32_t i = tid; i < args.n_meshes; i += kThreads) sm_len1[i] = args.mesh_len1[i];
+        mesh_tab = sm_mesh;
+        len1_tab = sm_len1;
+    }
     __syncthreads();
 
     if (warp == kComputeWarps) {
-#ifndef RCULL_TWO_LEVEL
-        scan_warp_flat<V>(args, sm, lane);
-#else
         scan_warp<V>(args, sm, lane);
-#endif
         return;
     }
 
     // ================================= compute warps =================================
-    uint32_t* const slot_base = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(&sm) + sizeof(FrameSmem) + V * 6 * sizeof(PlaneC));
-    uint8_t* const wlist_base = reinterpret_cast<uint8_t*>(slot_base + frame_bufs<V>() * kTile) + warp * (V * kWarpSpan);
+    uint8_t* const wlist_base = reinterpret_cast<unsigned char*>(&sm) + sizeof(FrameSmem) + V * 6 * sizeof(PlaneC) + warp * (V * kWarpSpan);
     const uint32_t lt = (1u << lane) - 1u;
     // swizzled (128-B pattern) byte offsets of this lane's four matrix columns in the warp's store box
     unsigned char* const box = reinterpret_cast<unsigned char*>(sm.mat[warp]);
@@ -636,7 +460,7 @@ __global__ void __maxnreg__(112)
     uint32_t emitted = 0;  // iterations [emitted, it) of this CTA still have their commands pending
     auto emit_next = [&]() {
         const uint32_t b = emitted % B;
-        emit_pending<V>(args, sm, wlist_base + b * (V * kTile), slot_base + b * kTile, b, sm.tile_ring[emitted % kRing] * kTile, warp, lane);
+        emit_pending<V>(args, sm, wlist_base + b * (V * kTile), b, sm.tile_ring[emitted % kRing] * kTile, warp, lane);
         ++emitted;
     };
     for (;; ++it) {
@@ -666,7 +490,7 @@ __global__ void __maxnreg__(112)
         if (lane == 0) mbar_arrive(&sm.empty[stage]);  // inputs are in registers: the stage can be refilled
 
         float cx[kItems], cy[kItems], cz[kItems], hx[kItems], hy[kItems], hz[kItems];
-        uint32_t slot[kItems];
+        uint32_t len[kItems], entry[kItems];
         bool valid[kItems];
 #pragma unroll
         for (int j = 0; j < kItems; ++j) {
@@ -698,8 +522,8 @@ __global__ void __maxnreg__(112)
             }
 
             // A2: world AABB
-            const float4 mn = __ldg(args.mesh_aabb + 2 * mid[j]);
-            const float4 mx = __ldg(args.mesh_aabb + 2 * mid[j] + 1);
+            const float4 mn = mesh_tab[2 * mid[j]];
+            const float4 mx = mesh_tab[2 * mid[j] + 1];
             float lox, hix, loy, hiy, loz, hiz;
             row_extent(m.m00, m.m01, m.m02, m.tx, mn, mx, lox, hix);
             row_extent(m.m10, m.m11, m.m12, m.ty, mn, mx, loy, hiy);
@@ -723,7 +547,9 @@ __global__ void __maxnreg__(112)
                         dz = __fsub_rn(args.cam[2], ps[j].z);
             const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
             const uint32_t n_lods = __float_as_uint(mn.w);
-            slot[j] = mid[j] * kMaxLods + ((d2 > args.lod_d2_max && n_lods > 1u) ? 1u : 0u);
+            const bool lod1 = d2 > args.lod_d2_max && n_lods > 1u;
+            len[j] = lod1 ? len1_tab[mid[j]] : __float_as_uint(mx.w);  // index_len of the chosen lod
+            entry[j] = (lod1 ? 128u : 0u) + lane + 32u * j;            // survivor-list entry: lod << 7 | slot in span
         }
 
         float2 c2x[kItems / 2], c2y[kItems / 2], c2z[kItems / 2], h2x[kItems / 2], h2y[kItems / 2], h2z[kItems / 2];
@@ -753,12 +579,6 @@ __global__ void __maxnreg__(112)
             emit_next();
         }
         __syncwarp();
-        uint32_t len[kItems];
-#pragma unroll
-        for (int j = 0; j < kItems; ++j) {
-            slot_base[buf * kTile + e0 + 32 * j] = slot[j];
-            len[j] = __ldg(args.lod_tab + slot[j]).x;
-        }
         const uint32_t dummy = smem_u32(&sm.dummy[warp]);
         const uint32_t wlist_s = smem_u32(wlist);
 
@@ -773,7 +593,6 @@ __global__ void __maxnreg__(112)
 #pragma unroll
             for (int p = 0; p < 6; ++p) {
                 const float4* pp = sm_planes + (k * 6 + p) * 4;
-#ifndef RCULL_PLANE_FFMA2
                 const float4 q0 = pp[0], q1 = pp[1], q2 = pp[2];  // (ax ax ay ay) (az az px px) (py py pz pz)
                 const float pw = pp[3].x;
                 const float2 ax = make_float2(q0.x, q0.y), ay = make_float2(q0.z, q0.w), az = make_float2(q1.x, q1.y);
@@ -796,29 +615,6 @@ __global__ void __maxnreg__(112)
                     outside[2 * i + 1] = outside[2 * i + 1] || (s.y > e1);
                 }
             }
-#else
-                const float4 q0 = pp[0], q1 = pp[1], q2 = pp[2], q3 = pp[3];  // (ax ax ay ay) (az az px px) (py py pz pz) (pw pw 1 1)
-                const float2 ax = make_float2(q0.x, q0.y), ay = make_float2(q0.z, q0.w), az = make_float2(q1.x, q1.y);
-                const float2 px = make_float2(q1.z, q1.w), py = make_float2(q2.x, q2.y), pz = make_float2(q2.z, q2.w);
-                const float2 pw = make_float2(q3.x, q3.y), one = make_float2(q3.z, q3.w);
-#pragma unroll
-                for (int i = 0; i < kItems / 2; ++i) {
-                    // Two entities per instruction.  Products are FMUL2; every sum is x * 1 + y on the
-                    // packed FMA (FFMA2), which rounds exactly like the add (x * 1 is exact).  The 1.0
-                    // comes out of shared memory, so ptxas cannot see through it: a plain packed add of
-                    // packed products would be contracted into a fused a * b + c even under
-                    // --fmad=false (tests/test_abi.py checks the SASS for the multiplier operand).
-                    const float2 m1 = mul2_rn(h2x[i], ax), m2 = mul2_rn(h2y[i], ay), m3 = mul2_rn(h2z[i], az);
-                    const float2 e = fma2_rn(fma2_rn(m1, one, m2), one, m3);
-                    const float2 p1 = mul2_rn(c2x[i], px), p3 = mul2_rn(c2z[i], pz), p2 = mul2_rn(c2y[i], py);
-                    const float2 s = fma2_rn(fma2_rn(p1, one, p3), one, fma2_rn(p2, one, pw));
-                    // (s - e > 0.0) == (s > e): the rounded difference of two floats keeps its sign,
-                    // and both forms are false for NaN and for inf - inf
-                    outside[2 * i] = outside[2 * i] || (s.x > e.x);
-                    outside[2 * i + 1] = outside[2 * i + 1] || (s.y > e.y);
-                }
-            }
-#endif
             // ballot compaction, branch-free: culled lanes store to a dummy byte
             uint32_t wc = 0, lo = 0, hi = 0;
 #pragma unroll
@@ -826,7 +622,7 @@ __global__ void __maxnreg__(112)
                 const bool vis = !outside[j];
                 if (kMat && args.flags[k] != nullptr && valid[j]) args.flags[k][tile_base + e0 + 32 * j] = outside[j] ? 1 : 0;
                 const uint32_t b = __ballot_sync(kFullMask, vis);
-                sts_u8(vis ? wlist_s + woff + wc + __popc(b & lt) : dummy, lane + 32 * j);
+                sts_u8(vis ? wlist_s + woff + wc + __popc(b & lt) : dummy, entry[j]);
                 if (args.len_small) {
                     lo += vis ? len[j] : 0u;
                 } else {

@@ -17,6 +17,10 @@ constexpr int kCompactThreads = 256;
 constexpr int kCompactItems = 4;
 constexpr int kCompactTile = kCompactThreads * kCompactItems;
 
+struct Mat4 {
+    float m[16];  // column-major
+};
+
 struct TriArgs {
     const uint32_t* cmds;        // view's draw list from the frame kernel, 5 words per command
     const uint32_t* src_first;   // indexOffset push constant of each command (first_index of the chosen LOD)
@@ -30,12 +34,12 @@ struct TriArgs {
     uint32_t* error_flag;
     uint64_t n_vertices, n_indices, out_capacity;
     uint32_t cap_cmds, draw_index_base;
-    float pv[16];
+    Mat4 pv;  // read straight out of the constant bank (kernel parameter): no loads
 };
 
-// GLSL mat4 * vec4 with w == 1 known only for the first product; kept generic so that the
-// rounding sequence is the shader's: ((c0 * x + c1 * y) + c2 * z) + c3 * w per row.
-__device__ __forceinline__ float4 glsl_mul(const float* __restrict__ m, float4 v) {
+// GLSL mat4 * vec4: ((c0 * x + c1 * y) + c2 * z) + c3 * w per row, every product and sum rounded.
+__device__ __forceinline__ float4 glsl_mul(const Mat4& a, float4 v) {
+    const float* m = a.m;
     float4 r;
     r.x = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m[0], v.x), __fmul_rn(m[4], v.y)), __fmul_rn(m[8], v.z)), __fmul_rn(m[12], v.w));
     r.y = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m[1], v.x), __fmul_rn(m[5], v.y)), __fmul_rn(m[9], v.z)), __fmul_rn(m[13], v.w));
@@ -43,13 +47,24 @@ __device__ __forceinline__ float4 glsl_mul(const float* __restrict__ m, float4 v
     r.w = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m[3], v.x), __fmul_rn(m[7], v.y)), __fmul_rn(m[11], v.z)), __fmul_rn(m[15], v.w));
     return r;
 }
+// the same with v.w == 1.0: c3 * 1.0 is c3 itself, bit for bit, so the four products are skipped
+__device__ __forceinline__ float4 glsl_mul_w1(const Mat4& a, float x, float y, float z) {
+    const float* m = a.m;
+    float4 r;
+    r.x = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m[0], x), __fmul_rn(m[4], y)), __fmul_rn(m[8], z)), m[12]);
+    r.y = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m[1], x), __fmul_rn(m[5], y)), __fmul_rn(m[9], z)), m[13]);
+    r.z = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m[2], x), __fmul_rn(m[6], y)), __fmul_rn(m[10], z)), m[14]);
+    r.w = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m[3], x), __fmul_rn(m[7], y)), __fmul_rn(m[11], z)), m[15]);
+    return r;
+}
 
-// generate_work.comp:139-155.  true = culled.
-__device__ __forceinline__ bool tri_culled(const float* __restrict__ model, const float* __restrict__ pv, float4 p0, float4 p1,
-                                           float4 p2) {
-    const float4 c0 = glsl_mul(pv, glsl_mul(model, p0));
-    const float4 c1 = glsl_mul(pv, glsl_mul(model, p1));
-    const float4 c2 = glsl_mul(pv, glsl_mul(model, p2));
+// generate_work.comp:139-155.  true = culled.  q0..q2 point at the three vec3 positions.
+template <typename PV>
+__device__ __forceinline__ bool tri_culled(const Mat4& model, const PV& pv, const float* __restrict__ q0,
+                                           const float* __restrict__ q1, const float* __restrict__ q2) {
+    const float4 c0 = glsl_mul(pv, glsl_mul_w1(model, __ldg(q0), __ldg(q0 + 1), __ldg(q0 + 2)));
+    const float4 c1 = glsl_mul(pv, glsl_mul_w1(model, __ldg(q1), __ldg(q1 + 1), __ldg(q1 + 2)));
+    const float4 c2 = glsl_mul(pv, glsl_mul_w1(model, __ldg(q2), __ldg(q2 + 1), __ldg(q2 + 2)));
     // determinant(mat3(c0.xyw, c1.xyw, c2.xyw)) > 0: cofactors along the first row of columns
     const float t0 = __fsub_rn(__fmul_rn(c1.y, c2.w), __fmul_rn(c2.y, c1.w));
     const float t1 = __fsub_rn(__fmul_rn(c0.y, c2.w), __fmul_rn(c2.y, c0.w));
@@ -69,12 +84,10 @@ __device__ __forceinline__ bool tri_culled(const float* __restrict__ model, cons
 // order at out_index_buffer[firstIndex / 3 + rank] (the reference's order inside a mesh is
 // atomic-arrival order; ascending is one of its outcomes).
 __global__ void __launch_bounds__(kTriThreads) tri_cull(const __grid_constant__ TriArgs a) {
-    __shared__ float s_model[16], s_pv[16];
     __shared__ uint32_t s_cmd, s_warp[kTriThreads / 32];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     uint32_t count = *a.count;
     if (count > a.cap_cmds) count = a.cap_cmds;
-    if (tid < 16) s_pv[tid] = a.pv[tid];
     for (;;) {
         if (tid == 0) s_cmd = atomicAdd(a.ticket, 1u);
         __syncthreads();
@@ -84,8 +97,16 @@ __global__ void __launch_bounds__(kTriThreads) tri_cull(const __grid_constant__ 
         const uint32_t n_tri = cmd[0] / 3u, out_first = cmd[2] / 3u, first_instance = cmd[4];
         const int32_t vertex_offset = (int32_t)cmd[3];
         const uint64_t src = a.src_first[c] / 3u;
-        if (tid < 16) s_model[tid] = __ldg(a.model + (size_t)(first_instance - a.draw_index_base) * 16 + tid);
-        __syncthreads();
+        Mat4 model;  // the command's model matrix in registers: one load per command, not per product
+        {
+            const float4* mp = reinterpret_cast<const float4*>(a.model + (size_t)(first_instance - a.draw_index_base) * 16);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float4 col = __ldg(mp + i);
+                model.m[4 * i] = col.x; model.m[4 * i + 1] = col.y; model.m[4 * i + 2] = col.z; model.m[4 * i + 3] = col.w;
+            }
+        }
+        __syncthreads();  // everyone has read s_cmd
         uint32_t running = 0;
         for (uint32_t t0 = 0; t0 < n_tri; t0 += kTriThreads) {
             const uint32_t t = t0 + tid;
@@ -100,12 +121,7 @@ __global__ void __launch_bounds__(kTriThreads) tri_cull(const __grid_constant__ 
                     const uint64_t v0 = (uint64_t)((int64_t)vertex_offset + i0), v1 = (uint64_t)((int64_t)vertex_offset + i1),
                                    v2 = (uint64_t)((int64_t)vertex_offset + i2);
                     if (v0 < a.n_vertices && v1 < a.n_vertices && v2 < a.n_vertices) {
-                        const float* q0 = a.positions + 3 * v0;
-                        const float* q1 = a.positions + 3 * v1;
-                        const float* q2 = a.positions + 3 * v2;
-                        keep = !tri_culled(s_model, s_pv, make_float4(__ldg(q0), __ldg(q0 + 1), __ldg(q0 + 2), 1.0f),
-                                           make_float4(__ldg(q1), __ldg(q1 + 1), __ldg(q1 + 2), 1.0f),
-                                           make_float4(__ldg(q2), __ldg(q2 + 1), __ldg(q2 + 2), 1.0f));
+                        keep = !tri_culled(model, a.pv, a.positions + 3 * v0, a.positions + 3 * v1, a.positions + 3 * v2);
                     } else {
                         atomicOr(a.error_flag, 2u);
                     }
