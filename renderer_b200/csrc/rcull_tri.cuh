@@ -12,7 +12,8 @@
 
 namespace rcull {
 
-constexpr int kTriThreads = 128;  // triangles per step of one command
+constexpr int kTriThreads = 128;
+constexpr int kTriItems = 2;  // triangles per thread per step: 256 triangles of one command per barrier
 constexpr int kCompactThreads = 256;
 constexpr int kCompactItems = 4;
 constexpr int kCompactTile = kCompactThreads * kCompactItems;
@@ -79,12 +80,12 @@ __device__ __forceinline__ bool tri_culled(const Mat4& model, const PV& pv, cons
     // the area test of :159-167 is overwritten by `cull = false` (:166): nothing to compute
 }
 
-// One CTA per command at a time (ticket order): the command's triangles in steps of 128,
+// One CTA per command at a time (ticket order): the command's triangles in steps of 256,
 // ballot compaction with a running base, so the kept triples land in ascending triangle
 // order at out_index_buffer[firstIndex / 3 + rank] (the reference's order inside a mesh is
 // atomic-arrival order; ascending is one of its outcomes).
 __global__ void __launch_bounds__(kTriThreads) tri_cull(const __grid_constant__ TriArgs a) {
-    __shared__ uint32_t s_cmd, s_warp[kTriThreads / 32];
+    __shared__ uint32_t s_cmd, s_warp[2][kTriItems][kTriThreads / 32];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     uint32_t count = *a.count;
     if (count > a.cap_cmds) count = a.cap_cmds;
@@ -107,50 +108,64 @@ __global__ void __launch_bounds__(kTriThreads) tri_cull(const __grid_constant__ 
             }
         }
         __syncthreads();  // everyone has read s_cmd
-        uint32_t running = 0;
-        for (uint32_t t0 = 0; t0 < n_tri; t0 += kTriThreads) {
-            const uint32_t t = t0 + tid;
-            bool keep = false;
-            uint32_t i0 = 0, i1 = 0, i2 = 0;
-            if (t < n_tri) {
-                const uint64_t at = 3ull * (src + t);
-                if (at + 2 < a.n_indices) {
-                    i0 = __ldg(a.indices + at);
-                    i1 = __ldg(a.indices + at + 1);
-                    i2 = __ldg(a.indices + at + 2);
-                    const uint64_t v0 = (uint64_t)((int64_t)vertex_offset + i0), v1 = (uint64_t)((int64_t)vertex_offset + i1),
-                                   v2 = (uint64_t)((int64_t)vertex_offset + i2);
-                    if (v0 < a.n_vertices && v1 < a.n_vertices && v2 < a.n_vertices) {
-                        keep = !tri_culled(model, a.pv, a.positions + 3 * v0, a.positions + 3 * v1, a.positions + 3 * v2);
+        uint32_t running = 0, step = 0;
+        for (uint32_t t0 = 0; t0 < n_tri; t0 += kTriThreads * kTriItems, ++step) {
+            bool keep[kTriItems];
+            uint32_t ix[kTriItems][3], b[kTriItems];
+#pragma unroll
+            for (int j = 0; j < kTriItems; ++j) {  // item-major: triangle t0 + j * 128 + tid (coalesced index loads)
+                const uint32_t t = t0 + j * kTriThreads + tid;
+                keep[j] = false;
+                ix[j][0] = ix[j][1] = ix[j][2] = 0;
+                if (t < n_tri) {
+                    const uint64_t at = 3ull * (src + t);
+                    if (at + 2 < a.n_indices) {
+                        ix[j][0] = __ldg(a.indices + at);
+                        ix[j][1] = __ldg(a.indices + at + 1);
+                        ix[j][2] = __ldg(a.indices + at + 2);
+                        const uint64_t v0 = (uint64_t)((int64_t)vertex_offset + ix[j][0]), v1 = (uint64_t)((int64_t)vertex_offset + ix[j][1]),
+                                       v2 = (uint64_t)((int64_t)vertex_offset + ix[j][2]);
+                        if (v0 < a.n_vertices && v1 < a.n_vertices && v2 < a.n_vertices) {
+                            keep[j] = !tri_culled(model, a.pv, a.positions + 3 * v0, a.positions + 3 * v1, a.positions + 3 * v2);
+                        } else {
+                            atomicOr(a.error_flag, 2u);
+                        }
                     } else {
                         atomicOr(a.error_flag, 2u);
                     }
-                } else {
-                    atomicOr(a.error_flag, 2u);
                 }
             }
-            const uint32_t b = __ballot_sync(kFullMask, keep);
-            if (lane == 0) s_warp[warp] = __popc(b);
-            __syncthreads();
-            uint32_t before = 0, total = 0;
+            // per-warp kept counts, double-buffered by step parity: one barrier per step is enough
+            uint32_t (*sw)[kTriThreads / 32] = s_warp[step & 1u];
 #pragma unroll
-            for (int w = 0; w < kTriThreads / 32; ++w) {
-                const uint32_t x = s_warp[w];
-                before += (uint32_t)w < warp ? x : 0u;
-                total += x;
+            for (int j = 0; j < kTriItems; ++j) {
+                b[j] = __ballot_sync(kFullMask, keep[j]);
+                if (lane == 0) sw[j][warp] = __popc(b[j]);
             }
-            if (keep) {
-                const uint64_t dst = 3ull * ((uint64_t)out_first + running + before + __popc(b & ((1u << lane) - 1u)));
-                if (dst + 2 < a.out_capacity) {
-                    a.out_indices[dst] = i0;
-                    a.out_indices[dst + 1] = i1;
-                    a.out_indices[dst + 2] = i2;
-                } else {
-                    atomicOr(a.error_flag, 4u);  // CulledIndexBuffer too small
-                }
-            }
-            running += total;
             __syncthreads();
+            uint32_t base = running;
+#pragma unroll
+            for (int j = 0; j < kTriItems; ++j) {
+                uint32_t before = 0, total = 0;
+#pragma unroll
+                for (int w = 0; w < kTriThreads / 32; ++w) {
+                    const uint32_t x = sw[j][w];
+                    before += (uint32_t)w < warp ? x : 0u;
+                    total += x;
+                }
+                if (keep[j]) {
+                    const uint64_t dst = 3ull * ((uint64_t)out_first + base + before + __popc(b[j] & ((1u << lane) - 1u)));
+                    if (dst + 2 < a.out_capacity) {
+                        a.out_indices[dst] = ix[j][0];
+                        a.out_indices[dst + 1] = ix[j][1];
+                        a.out_indices[dst + 2] = ix[j][2];
+                    } else {
+                        atomicOr(a.error_flag, 4u);  // CulledIndexBuffer too small
+                    }
+                }
+                base += total;
+            }
+            running = base;
         }
         if (tid == 0) a.refined[c] = 3u * running;
     }
