@@ -178,6 +178,21 @@ int rcull_get_tri_outputs(rcull_ctx *ctx, rcull_tri_outputs *out);
 int rcull_download_tri(rcull_ctx *ctx, uint32_t *count, uint64_t *kept_indices, rcull_draw_cmd *cmds, uint64_t n_cmds,
                        uint32_t *indices, uint64_t first_index, uint64_t n_indices);
 
+/* ---- Acceleration-structure instance records ---------------------------
+ * The data-parallel half of build_acceleration_structures (acceleration_strucures.rs:419-445):
+ * one 64-byte VkAccelerationStructureInstanceKHR per entity -- rows 0..2 of the model matrix
+ * row-major, instance_custom_index = draw_index | mask 0xFF << 24, SBT offset 0 | flags
+ * TRIANGLE_FACING_CULL_DISABLE << 24, BLAS device address of the entity's mesh.  The BLAS/TLAS
+ * builds themselves are Vulkan ray-tracing calls and stay with the caller.
+ * blas_addresses: one u64 per mesh of the mesh table (host pointer, copied synchronously). */
+int rcull_set_blas_table(rcull_ctx *ctx, const uint64_t *blas_addresses, uint32_t n);
+/* Packs records [0, n) from the model buffer the last rcull_frame wrote into output set
+ * buffer_ix; asynchronous on stream. */
+int rcull_as_instances(rcull_ctx *ctx, uint64_t n, uint32_t draw_index_base, uint32_t buffer_ix, void *stream);
+/* Device pointer of the instance buffer (capacity_entities records of 64 bytes). */
+int rcull_get_as_instances(rcull_ctx *ctx, void **instances);
+int rcull_download_as_instances(rcull_ctx *ctx, uint64_t first, uint64_t n, void *dst);
+
 /* Range-shard merge step: writes this rank's draw list of one view
  * into dst_cmds/dst_visible (device pointers into the MERGED lists, already
  * offset to this rank's slot), adding index_prefix to every firstIndex.  The

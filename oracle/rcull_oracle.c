@@ -573,3 +573,22 @@ int oracle_tri_cull(const oracle_cmd *cmds, const uint32_t *src_first_index, uin
     free(kept); free(th); free(jobs);
     return err ? -1 : 0;
 }
+
+/* F4: acceleration_strucures.rs:419-449. */
+void oracle_as_instances(const float *model, const uint32_t *mesh_id, const uint64_t *blas, uint64_t n,
+                         uint32_t draw_index_base, void *out) {
+    unsigned char *o = (unsigned char *)out;
+    for (uint64_t i = 0; i < n; i++, o += 64) {
+        const float *m = model + 16 * i;
+        float rows[12];
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 4; c++) rows[4 * r + c] = m[4 * c + r]; /* model_matrix.rows(0, 3).transpose().as_slice() (:427) */
+        const uint32_t custom = (((uint32_t)(draw_index_base + i)) & 0xffffffu) | (0xffu << 24); /* Packed24_8::new(draw_index, 0xFF) */
+        const uint32_t sbt = 0u | (1u << 24); /* Packed24_8::new(0, TRIANGLE_FACING_CULL_DISABLE) */
+        const uint64_t addr = blas[mesh_id[i]];
+        memcpy(o, rows, 48);
+        memcpy(o + 48, &custom, 4);
+        memcpy(o + 52, &sbt, 4);
+        memcpy(o + 56, &addr, 8);
+    }
+}

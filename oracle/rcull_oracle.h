@@ -120,6 +120,13 @@ int oracle_tri_cull(const oracle_cmd *cmds, const uint32_t *src_first_index, uin
                     uint32_t *out_indices, uint64_t out_capacity,
                     oracle_cmd *out_cmds, uint32_t *out_count, uint64_t *kept_indices, int n_threads);
 
+/* F4: VkAccelerationStructureInstanceKHR records (acceleration_strucures.rs:419-449): rows 0..2
+ * of the column-major model matrix transposed into 12 row-major floats, custom index = draw_index
+ * (24 bits) | mask 0xFF << 24, SBT offset 0 | TRIANGLE_FACING_CULL_DISABLE (1) << 24, BLAS address
+ * of the entity's mesh.  out: 64 bytes per entity. */
+void oracle_as_instances(const float *model, const uint32_t *mesh_id, const uint64_t *blas, uint64_t n,
+                         uint32_t draw_index_base, void *out);
+
 /* Deterministic scene generator twin (see renderer_b200/scene.py): entity i of
  * the global scene, counter-based so shards regenerate their slice. */
 void oracle_synth_entities(uint64_t seed, uint64_t first, uint64_t n, float half_box, uint32_t n_meshes,

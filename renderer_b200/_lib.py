@@ -83,7 +83,11 @@ CMD_DTYPE = np.dtype(
         ("firstInstance", "<u4"),
     ]
 )
-assert MESH_DTYPE.itemsize == 80 and CMD_DTYPE.itemsize == 20
+# VkAccelerationStructureInstanceKHR (acceleration_strucures.rs:439-449)
+AS_INSTANCE_DTYPE = np.dtype(
+    [("transform", "<f4", (3, 4)), ("custom_index_and_mask", "<u4"), ("sbt_offset_and_flags", "<u4"), ("blas", "<u8")]
+)
+assert MESH_DTYPE.itemsize == 80 and CMD_DTYPE.itemsize == 20 and AS_INSTANCE_DTYPE.itemsize == 64
 
 # every symbol include/rcull.h declares: name -> (restype, argtypes)
 _P = C.c_void_p
@@ -110,6 +114,10 @@ SYMBOLS = {
     "rcull_tri_cull": (C.c_int, [_P, _P, _u32, _u32, _P]),
     "rcull_get_tri_outputs": (C.c_int, [_P, C.POINTER(TriOutputs)]),
     "rcull_download_tri": (C.c_int, [_P, _P, _P, _P, _u64, _P, _u64, _u64]),
+    "rcull_set_blas_table": (C.c_int, [_P, _P, _u32]),
+    "rcull_as_instances": (C.c_int, [_P, _u64, _u32, _u32, _P]),
+    "rcull_get_as_instances": (C.c_int, [_P, C.POINTER(_P)]),
+    "rcull_download_as_instances": (C.c_int, [_P, _u64, _u64, _P]),
     "rcull_rebase_into": (C.c_int, [_P, _u32, _u32, _u64, _P, _P, _P]),
     "rcull_merge_create": (C.c_int, [_P, _u32, _u32, _u64, C.POINTER(_P)]),
     "rcull_merge_destroy": (None, [_P]),

@@ -217,6 +217,19 @@ class CullContext:
         check(self._lib.rcull_download_tri(self._h, ptr(count), None, None, 0, ptr(out), first, n))
         return out
 
+    # -- acceleration-structure instance records (acceleration_strucures.rs:419-445) -------
+    def set_blas_table(self, addresses: np.ndarray) -> None:
+        a = np.ascontiguousarray(addresses, dtype=np.uint64)
+        check(self._lib.rcull_set_blas_table(self._h, ptr(a), len(a)))
+
+    def as_instances(self, n: int | None = None, draw_index_base: int = 0, buffer_ix: int = 0, stream: int = 0) -> None:
+        check(self._lib.rcull_as_instances(self._h, self.n if n is None else n, draw_index_base, buffer_ix, C.c_void_p(stream)))
+
+    def download_as_instances(self, n: int, first: int = 0) -> np.ndarray:
+        out = np.zeros(n, _lib.AS_INSTANCE_DTYPE)
+        check(self._lib.rcull_download_as_instances(self._h, first, n, ptr(out)))
+        return out
+
     def rebase_into(self, view: int, index_prefix: int, dst_cmds_ptr: int, dst_visible_ptr: int, buffer_ix: int = 0, stream: int = 0) -> None:
         check(self._lib.rcull_rebase_into(self._h, buffer_ix, view, index_prefix, C.c_void_p(dst_cmds_ptr), C.c_void_p(dst_visible_ptr), C.c_void_p(stream)))
 

@@ -103,6 +103,8 @@ struct rcull_ctx {
     uint32_t* tri_indices = nullptr;
     uint64_t* tri_status = nullptr;  // [4 * tiles] + 2 ticket words at the end
     size_t tri_status_bytes = 0;
+    unsigned long long* blas = nullptr;  // F4: BLAS address per mesh
+    uint4* instances = nullptr;          // F4: VkAccelerationStructureInstanceKHR [cap]
     std::vector<void*> allocs;
 };
 
@@ -658,6 +660,52 @@ int rcull_synth_entities(rcull_ctx* c, uint64_t seed, uint64_t first_global, uin
 }
 
 uint64_t rcull_launch_count(rcull_ctx* c) { return c ? c->launches : 0; }
+
+int rcull_set_blas_table(rcull_ctx* c, const uint64_t* blas, uint32_t n) {
+    if (!c || !blas) return fail(RCULL_ERR_INVALID, "rcull_set_blas_table: null argument");
+    if (n == 0 || n > c->cfg.max_meshes) return fail(RCULL_ERR_INVALID, "blas table of %u entries, max_meshes %u", n, c->cfg.max_meshes);
+    CU(cudaSetDevice(c->cfg.device));
+    if (!c->blas) {
+        int rc = dev_alloc(c, &c->blas, c->cfg.max_meshes);
+        if (rc) return rc;
+        rc = dev_alloc(c, &c->instances, c->cap * 4);
+        if (rc) return rc;
+    }
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(c->blas, blas, (size_t)n * 8, cudaMemcpyHostToDevice));
+    return RCULL_OK;
+}
+
+int rcull_as_instances(rcull_ctx* c, uint64_t n, uint32_t draw_index_base, uint32_t buffer_ix, void* stream) {
+    if (!c) return fail(RCULL_ERR_INVALID, "rcull_as_instances: null context");
+    if (!c->blas) return fail(RCULL_ERR_INVALID, "rcull_set_blas_table has not been called");
+    if (n > c->cfg.capacity_entities) return fail(RCULL_ERR_INVALID, "n exceeds capacity_entities");
+    if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
+    if (n == 0) return RCULL_OK;
+    CU(cudaSetDevice(c->cfg.device));
+    as_instances<<<c->sm_count * 8, 256, 0, (cudaStream_t)stream>>>(c->out[buffer_ix].model, c->mesh, c->blas, c->n_meshes, (uint32_t)n,
+                                                                    draw_index_base, c->instances);
+    CU(cudaGetLastError());
+    c->launches += 1;
+    return RCULL_OK;
+}
+
+int rcull_get_as_instances(rcull_ctx* c, void** instances) {
+    if (!c || !instances) return fail(RCULL_ERR_INVALID, "rcull_get_as_instances: null argument");
+    if (!c->instances) return fail(RCULL_ERR_INVALID, "rcull_set_blas_table has not been called");
+    *instances = c->instances;
+    return RCULL_OK;
+}
+
+int rcull_download_as_instances(rcull_ctx* c, uint64_t first, uint64_t n, void* dst) {
+    if (!c || !dst) return fail(RCULL_ERR_INVALID, "rcull_download_as_instances: null argument");
+    if (!c->instances) return fail(RCULL_ERR_INVALID, "rcull_set_blas_table has not been called");
+    if (first + n > c->cap) return fail(RCULL_ERR_INVALID, "instance range out of bounds");
+    CU(cudaSetDevice(c->cfg.device));
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(dst, c->instances + first * 4, n * 64, cudaMemcpyDeviceToHost));
+    return RCULL_OK;
+}
 
 int rcull_set_geometry(rcull_ctx* c, const float* positions, uint64_t n_vertices, const uint32_t* indices, uint64_t n_indices) {
     if (!c || !positions || !indices) return fail(RCULL_ERR_INVALID, "rcull_set_geometry: null argument");

@@ -219,4 +219,27 @@ __global__ void __launch_bounds__(256) synth_entities(uint64_t seed, uint64_t fi
     mesh[k] = (uint32_t)(((chan(seed, i, 8) >> 32) * (uint64_t)n_meshes) >> 32);
 }
 
+// ---- acceleration-structure instance records ------------------------------
+// build_acceleration_structures' CPU loop (acceleration_strucures.rs:419-445) writes one
+// VkAccelerationStructureInstanceKHR per entity: the upper 3 rows of the model matrix row-major,
+// instance_custom_index = draw_index (24 bits) | mask 0xFF, SBT offset 0 | flags
+// TRIANGLE_FACING_CULL_DISABLE (= 1), and the BLAS device address of the entity's mesh.
+// One thread per entity: 68 bytes in (model + mesh id), 64 bytes out.
+__global__ void __launch_bounds__(256) as_instances(const float4* __restrict__ model, const uint32_t* __restrict__ mesh,
+                                                    const unsigned long long* __restrict__ blas, uint32_t n_meshes, uint32_t n,
+                                                    uint32_t draw_index_base, uint4* __restrict__ out) {
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float4 c0 = model[4 * (size_t)i], c1 = model[4 * (size_t)i + 1], c2 = model[4 * (size_t)i + 2], c3 = model[4 * (size_t)i + 3];
+        uint32_t m = mesh[i];
+        if (m >= n_meshes) m = 0;  // the frame kernel has already flagged the error
+        const unsigned long long addr = blas[m];
+        uint4* o = out + 4 * (size_t)i;
+        o[0] = make_uint4(__float_as_uint(c0.x), __float_as_uint(c1.x), __float_as_uint(c2.x), __float_as_uint(c3.x));
+        o[1] = make_uint4(__float_as_uint(c0.y), __float_as_uint(c1.y), __float_as_uint(c2.y), __float_as_uint(c3.y));
+        o[2] = make_uint4(__float_as_uint(c0.z), __float_as_uint(c1.z), __float_as_uint(c2.z), __float_as_uint(c3.z));
+        o[3] = make_uint4(((draw_index_base + i) & 0xffffffu) | 0xff000000u, 1u << 24, (uint32_t)addr, (uint32_t)(addr >> 32));
+    }
+}
+
 }  // namespace rcull

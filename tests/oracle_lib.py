@@ -41,6 +41,7 @@ def lib():
         L.oracle_emit_per_mesh.restype = C.c_int
         L.oracle_tri_cull.argtypes = [_P, _P, _u32, _P, _u32, _P, _P, _u64, _P, _u64, _P, _u64, _P, _P, _P, C.c_int]
         L.oracle_tri_cull.restype = C.c_int
+        L.oracle_as_instances.argtypes = [_P, _P, _P, _u64, _u32, _P]
         L.oracle_synth_entities.argtypes = [_u64, _u64, _u64, _f, _u32, _P, _P, _P, _P]
         _lib = L
     return _lib
@@ -194,3 +195,17 @@ def tri_cull(cmds, src_first, model, pv, positions, indices, out_capacity, draw_
     if rc != 0:
         raise ValueError("oracle_tri_cull: index or vertex out of range")
     return dict(indices=out_idx, cmds=out_cmds[: int(count[0])], count=int(count[0]), kept_indices=int(kept[0]))
+
+
+AS_INSTANCE_DTYPE = np.dtype(
+    [("transform", "<f4", (3, 4)), ("custom_index_and_mask", "<u4"), ("sbt_offset_and_flags", "<u4"), ("blas", "<u8")]
+)
+
+
+def as_instances(model, mesh_id, blas, draw_index_base=0):
+    model = f32(model)
+    mesh_id = np.ascontiguousarray(mesh_id, dtype=np.uint32)
+    blas = np.ascontiguousarray(blas, dtype=np.uint64)
+    out = np.zeros(len(mesh_id), AS_INSTANCE_DTYPE)
+    lib().oracle_as_instances(p(model), p(mesh_id), p(blas), len(mesh_id), draw_index_base, p(out))
+    return out

@@ -403,3 +403,21 @@ def test_config4_sponza_instanced_per_mesh():
     ps, rot, mesh = scene.sponza_instances(300_000, len(table), node_scale)
     counts = _per_mesh_compare(ps, rot, mesh, table, scene.scene_views(2), 2)
     assert 0 < counts[0] <= len(table) * 2
+
+
+def test_as_instance_records_match_oracle():
+    """F4 (acceleration_strucures.rs:419-449): byte-exact VkAccelerationStructureInstanceKHR records."""
+    n, base = 70_001, 123_456
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, 80.0, len(MESHES))
+    blas = (np.arange(len(MESHES), dtype=np.uint64) + 1) * np.uint64(0x1_0000_0100)
+    with CullContext(n, max_views=1, max_meshes=len(MESHES)) as ctx:
+        ctx.set_mesh_table(MESHES)
+        with pytest.raises(RcullError):
+            ctx.as_instances(n)  # no BLAS table yet
+        ctx.set_blas_table(blas)
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(scene.scene_views(1), scene.CAMERA_POS, draw_index_base=base)
+        ctx.as_instances(n, draw_index_base=base)
+        got = ctx.download_as_instances(n)
+        want = O.as_instances(ctx.model(n), mesh, blas, draw_index_base=base)
+        assert got.tobytes() == want.tobytes()

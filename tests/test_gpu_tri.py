@@ -15,7 +15,8 @@ MESHES = scene.synth_mesh_table()
 POSITIONS, INDICES = scene.synth_geometry(MESHES)
 
 
-def run_tri(n, half_box, *, base=0, cam_pos=scene.CAMERA_POS, capacity=None, threads=8, seed=scene.SEED):
+def run_tri(n, half_box, *, base=0, cam_pos=scene.CAMERA_POS, capacity=None, threads=8, seed=scene.SEED, geometry=None):
+    MESHES, POSITIONS, INDICES = geometry if geometry is not None else (globals()['MESHES'], globals()['POSITIONS'], globals()['INDICES'])
     ps, rot, mesh = scene.synth_entities(seed, 0, n, half_box, len(MESHES))
     views = scene.camera_view(pos=cam_pos)[None]
     pv = scene.camera_pv(pos=cam_pos)
@@ -92,3 +93,13 @@ def test_tri_cull_errors_are_loud():
         ctx.tri_cull(scene.camera_pv())
         with pytest.raises(RcullError):
             ctx.tri_counts()
+
+
+def test_tri_cull_on_gltf_geometry():
+    """Meshes and consolidated buffers from the glTF loader (tests/golden/grid.gltf: real connected
+    triangle grids, two LODs, u16 indices widened) through frame -> tri_cull -> compact."""
+    import os
+    from renderer_b200 import gltf
+    g = gltf.load_gltf(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "grid.gltf"), synthetic_lod1=True)
+    count, kept, total, visible = run_tri(3_000, 14.0, geometry=(g.meshes, g.positions, g.indices))
+    assert visible > 100 and 0 < kept < total

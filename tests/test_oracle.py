@@ -281,3 +281,13 @@ def test_tri_cull_matches_numpy_restatement():
                 n_out += 1
                 kept_total += len(keep)
     assert n_out == r["count"] and kept_total == r["kept_indices"] and n_out > 0
+
+
+def test_as_instance_records():
+    """acceleration_strucures.rs:419-449: 3x4 row-major transform, custom index | 0xFF mask, flags, BLAS address."""
+    m = O.model_matrix([1.0, 2.0, 3.0], [0.0, 0.0, 0.0, 1.0], 2.0)
+    r = O.as_instances(np.tile(m, 2), [1, 0], np.array([0x1111, 0x2222_0000_0000], np.uint64), draw_index_base=0x1000005)
+    assert r["transform"][0].tolist() == [[2, 0, 0, 1], [0, 2, 0, 2], [0, 0, 2, 3]]
+    assert r["custom_index_and_mask"].tolist() == [0xFF000005, 0xFF000006]  # 24-bit draw index, mask 0xFF
+    assert r["sbt_offset_and_flags"].tolist() == [1 << 24, 1 << 24]
+    assert r["blas"].tolist() == [0x2222_0000_0000, 0x1111]
