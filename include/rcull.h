@@ -132,6 +132,13 @@ int rcull_pack_components(uint64_t n, const float *position, const float *rotati
 int rcull_frame(rcull_ctx *ctx, uint64_t n, const rcull_view *views, uint32_t n_views,
                 const float cam_pos[3], uint32_t draw_index_base, uint32_t buffer_ix, void *stream);
 
+/* A frame with RuntimeConfiguration.freeze_culling on (cull_pass_bypass, cull_pipeline.rs:331-421):
+ * the reference keeps the draw lists, count and culled index buffer of the last unfrozen frame
+ * (it copies the buffers onto themselves) while model_matrix_calculation and
+ * model_matrices_upload still run.  Writes the model matrices of entities [0, n) into output set
+ * buffer_ix and nothing else; the lists to draw from stay those of the last rcull_frame. */
+int rcull_frame_frozen(rcull_ctx *ctx, uint64_t n, uint32_t buffer_ix, void *stream);
+
 /* Host-buffer convenience used by the end-to-end path: upload the columns,
  * run the frame, read back counts and index totals; blocks until done. */
 int rcull_frame_host(rcull_ctx *ctx, uint64_t n, const float *pos_scale, const float *rot,

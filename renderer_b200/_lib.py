@@ -102,6 +102,7 @@ SYMBOLS = {
     "rcull_entity_ptrs": (C.c_int, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)]),
     "rcull_pack_components": (C.c_int, [_u64, _P, _P, _P, _P, _P]),
     "rcull_frame": (C.c_int, [_P, _u64, _P, _u32, _P, _u32, _u32, _P]),
+    "rcull_frame_frozen": (C.c_int, [_P, _u64, _u32, _P]),
     "rcull_frame_host": (C.c_int, [_P, _u64, _P, _P, _P, _P, _u32, _P, _u32, _u32, _P, _P]),
     "rcull_get_outputs": (C.c_int, [_P, _u32, C.POINTER(Outputs)]),
     "rcull_download_counts": (C.c_int, [_P, _u32, _P, _P]),

@@ -125,6 +125,10 @@ class CullContext:
         check(self._lib.rcull_frame(self._h, n, ptr(v), len(v), ptr(cam), draw_index_base, buffer_ix, C.c_void_p(stream)))
         self._last = (n, len(v))
 
+    def frame_frozen(self, n: int | None = None, buffer_ix: int = 0, stream: int = 0) -> None:
+        """FREEZE_CULLING frame (cull_pass_bypass): model matrices only, draw lists untouched."""
+        check(self._lib.rcull_frame_frozen(self._h, self.n if n is None else n, buffer_ix, C.c_void_p(stream)))
+
     def frame_host(self, pos_scale, rot, mesh, views, cam_pos, draw_index_base: int = 0, buffer_ix: int = 0):
         """Host buffers in, counts out (the end-to-end call)."""
         v = views_array(views)

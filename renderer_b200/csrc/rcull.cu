@@ -661,6 +661,18 @@ int rcull_synth_entities(rcull_ctx* c, uint64_t seed, uint64_t first_global, uin
 
 uint64_t rcull_launch_count(rcull_ctx* c) { return c ? c->launches : 0; }
 
+int rcull_frame_frozen(rcull_ctx* c, uint64_t n, uint32_t buffer_ix, void* stream) {
+    if (!c) return fail(RCULL_ERR_INVALID, "rcull_frame_frozen: null context");
+    if (n > c->cfg.capacity_entities) return fail(RCULL_ERR_INVALID, "n = %llu exceeds capacity_entities", (unsigned long long)n);
+    if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
+    if (n == 0) return RCULL_OK;
+    CU(cudaSetDevice(c->cfg.device));
+    model_only<<<c->sm_count * 8, 256, 0, (cudaStream_t)stream>>>(c->pos_scale, c->rot, (uint32_t)n, c->out[buffer_ix].model);
+    CU(cudaGetLastError());
+    c->launches += 1;
+    return RCULL_OK;
+}
+
 int rcull_set_blas_table(rcull_ctx* c, const uint64_t* blas, uint32_t n) {
     if (!c || !blas) return fail(RCULL_ERR_INVALID, "rcull_set_blas_table: null argument");
     if (n == 0 || n > c->cfg.max_meshes) return fail(RCULL_ERR_INVALID, "blas table of %u entries, max_meshes %u", n, c->cfg.max_meshes);

@@ -242,4 +242,20 @@ __global__ void __launch_bounds__(256) as_instances(const float4* __restrict__ m
     }
 }
 
+// ---- FREEZE_CULLING frames (cull_pass_bypass, cull_pipeline.rs:331-421) ---------------------
+// With culling frozen the reference keeps the last draw lists and still runs
+// model_matrix_calculation + model_matrices_upload: model matrices only, 32 bytes in, 64 out.
+__global__ void __launch_bounds__(256) model_only(const float4* __restrict__ pos_scale, const float4* __restrict__ rot, uint32_t n,
+                                                  float4* __restrict__ model) {
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const Mat34 m = model_matrix(pos_scale[i], rot[i]);
+        float4* o = model + 4 * (size_t)i;
+        o[0] = make_float4(m.m00, m.m10, m.m20, 0.f);
+        o[1] = make_float4(m.m01, m.m11, m.m21, 0.f);
+        o[2] = make_float4(m.m02, m.m12, m.m22, 0.f);
+        o[3] = make_float4(m.tx, m.ty, m.tz, 1.f);
+    }
+}
+
 }  // namespace rcull

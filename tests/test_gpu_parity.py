@@ -421,3 +421,27 @@ def test_as_instance_records_match_oracle():
         got = ctx.download_as_instances(n)
         want = O.as_instances(ctx.model(n), mesh, blas, draw_index_base=base)
         assert got.tobytes() == want.tobytes()
+
+
+def test_frozen_culling_frame_updates_models_only():
+    """cull_pass_bypass (cull_pipeline.rs:331-421): with freeze_culling the lists of the last unfrozen
+    frame stay, model matrices follow the moved entities (double-buffered model sets)."""
+    n = 30_000
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, 60.0, len(MESHES))
+    ps2, rot2, _ = scene.synth_entities(scene.SEED + 1, 0, n, 60.0, len(MESHES))
+    views = scene.scene_views(2)
+    with CullContext(n, max_views=2, max_meshes=len(MESHES), n_buffers=2) as ctx:
+        ctx.set_mesh_table(MESHES)
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(views, scene.CAMERA_POS, buffer_ix=0)
+        counts0, totals0 = ctx.counts(0)
+        cmds0 = [ctx.cmds(k, int(counts0[k])) for k in range(2)]
+        ctx.upload_entities(ps2, rot2, mesh)  # the world moves on while culling is frozen
+        ctx.frame_frozen(n, buffer_ix=1)
+        pos, quat, scale = scene.to_components(ps2, rot2)
+        ref = O.frame(pos, quat, scale, mesh, MESHES, views, scene.CAMERA_POS, want=("model",))
+        assert np.array_equal(ctx.model(n, buffer_ix=1), ref["model"])
+        counts1, totals1 = ctx.counts(0)
+        assert np.array_equal(counts0, counts1) and np.array_equal(totals0, totals1)
+        for k in range(2):
+            assert np.array_equal(ctx.cmds(k, int(counts0[k])), cmds0[k])
