@@ -160,7 +160,10 @@ def gpu_arm(args, wl):
             probe.synth_entities(scene.SEED, lo, n, wl["half_box"], len(meshes))
             probe.frame(views, scene.CAMERA_POS, draw_index_base=lo)
             tri_cap = int(probe.counts()[1][0]) + 3
-    ctx = CullContext(n, max_views=n_views, max_meshes=len(meshes), device=local_rank, capacity_tri_indices=tri_cap)
+    # N > 1 with the peer-store merge: two output sets, so the merge of frame i (its own stream) overlaps frame i + 1
+    pipelined = world > 1 and args.merge == "p2p" and not args.no_overlap
+    ctx = CullContext(n, max_views=n_views, max_meshes=len(meshes), device=local_rank, capacity_tri_indices=tri_cap,
+                      n_buffers=2 if pipelined else 1)
     ctx.set_mesh_table(meshes)
     pv = None
     if tri:
@@ -183,11 +186,32 @@ def gpu_arm(args, wl):
 
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev) if n * 36 < 256e6 else None
 
-    def step():
-        ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, stream=sh)
+    merge_stream = torch.cuda.Stream(device=dev) if pipelined else None
+    frame_done = [torch.cuda.Event() for _ in range(2)]
+    step_no = [0]
+
+    def step(ev0=None):
+        if not pipelined:
+            if ev0 is not None:
+                ev0.record(stream)
+            ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, stream=sh)
+            return
+        b = step_no[0] & 1
+        if step_no[0] >= 2:
+            stream.wait_event(merger.ev_scatter_done[b])  # merge i-2 has read output set b
+        if ev0 is not None:
+            ev0.record(stream)
+        ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, buffer_ix=b, stream=sh)
+        frame_done[b].record(stream)
 
     def do_merge():
-        if args.merge == "p2p":
+        if pipelined:
+            b = step_no[0] & 1
+            step_no[0] += 1
+            merge_stream.wait_event(frame_done[b])
+            with torch.cuda.stream(merge_stream):
+                merger.exchange(b)
+        elif args.merge == "p2p":
             merger.merge()
         else:
             merger.merge_from_context(ctx, stream=sh)
@@ -211,20 +235,21 @@ def gpu_arm(args, wl):
         launches0 = ctx.launch_count
         with ClockSampler(local_rank) as clocks:
             for i in range(args.steps):
-                ev[i][0].record(stream)
-                step()
+                step(ev[i][0])
                 ev[i][1].record(stream)
                 if merger:
                     do_merge()
                 if tri:
                     ctx.tri_cull(pv, draw_index_base=lo, stream=sh)
+                if pipelined and i == args.steps - 1:
+                    stream.wait_stream(merge_stream)  # the timed region ends when the last merge has
                 ev[i][2].record(stream)
                 if flush is not None:
                     flush.zero_()
             sync_all()
         launches = ctx.launch_count - launches0
     t_frame = sum(e[0].elapsed_time(e[1]) for e in ev) / 1e3  # seconds, all steps
-    t_step = sum(e[0].elapsed_time(e[2]) for e in ev) / 1e3
+    t_step = (ev[0][0].elapsed_time(ev[-1][2]) if pipelined else sum(e[0].elapsed_time(e[2]) for e in ev)) / 1e3
     counts, totals = ctx.counts()
     counts = counts[:n_views].astype(np.int64)
 
@@ -243,7 +268,12 @@ def gpu_arm(args, wl):
     def e2e_step():
         c, _ = ctx.frame_host(a_ps, a_rot, a_mesh, views, scene.CAMERA_POS, draw_index_base=lo)
         if merger:
-            do_merge()
+            if pipelined:
+                merger.exchange(0)  # frame_host wrote output set 0 and has already completed
+            elif args.merge == "p2p":
+                merger.merge(0)
+            else:
+                do_merge()
             torch.cuda.synchronize()
         return c
 
@@ -281,7 +311,7 @@ def gpu_arm(args, wl):
                 "workload": args.workload, "entities_per_gpu": n, "entities_total": n_total, "n_views": n_views,
                 "half_box": wl["half_box"], "visible_fraction_per_view": [round(float(x), 6) for x in vis / float(n_total)],
                 "sharding": "contiguous range per rank" if world > 1 else "none",
-                "merge": ("NCCL all_gather(meta) + one peer-store kernel per rank (NVLink P2P) + 1-word all_reduce" if args.merge == "p2p" else "NCCL all_gather(counts) + in-place broadcast allgatherv") if world > 1 else "none",
+                "merge": ((("one fused exchange kernel per rank: counts to every peer's mailbox, rebased lists stored into every rank's allocation over NVLink, done tags; on its own stream, the exchange of frame i overlaps frame i+1 (two output sets)" if pipelined else "NCCL all_gather(meta) + one peer-store kernel per rank (NVLink P2P) + 1-word all_reduce")) if args.merge == "p2p" else "NCCL all_gather(counts) + in-place broadcast allgatherv") if world > 1 else "none",
                 "l2": "flushed between iterations (256 MB write)" if flush is not None else "inputs (36 B x n) exceed L2",
             },
             "e2e": {"value": n_total * e2e_steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": n * 36,
@@ -350,6 +380,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--merge", default="p2p", choices=["p2p", "nccl"], help="N > 1: peer-store merge kernel or NCCL broadcasts")
+    ap.add_argument("--no-overlap", action="store_true", help="N > 1: run frame and merge back to back instead of pipelined")
     ap.add_argument("--workload", default="16m_5view", choices=sorted(WORKLOADS))
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

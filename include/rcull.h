@@ -227,11 +227,24 @@ int rcull_merge_open_peer(rcull_merge *m, uint32_t peer, const void *handle);
 /* Same-process peers (tests, single-process multi-GPU): the peer's base pointer itself. */
 int rcull_merge_set_peer_ptr(rcull_merge *m, uint32_t peer, void *base);
 int rcull_merge_base(rcull_merge *m, void **base);
-/* Device buffers of the exchange: meta_local [2*max_views] u64, meta_all [world][2*max_views] u64. */
+/* Device buffers of the exchange: meta_local [3 output sets][2*max_views] u64 (row = buffer_ix),
+ * meta_all [world][2*max_views] u64. */
 int rcull_merge_meta_ptrs(rcull_merge *m, uint64_t **meta_local, uint64_t **meta_all);
 /* Only needed for a frame issued BEFORE rcull_merge_create: later frames write meta_local themselves. */
 int rcull_merge_pack_meta(rcull_merge *m, uint32_t buffer_ix, void *stream);
 int rcull_merge_scatter(rcull_merge *m, uint32_t buffer_ix, uint32_t n_views, void *stream);
+/* The whole exchange in ONE kernel, no collective call: this rank's (count, index total) words go
+ * into every rank's mailbox over NVLink, the kernel waits for every rank's words of the same
+ * exchange, computes its slot and stores its rebased lists into that slot of every rank's
+ * allocation (16-byte peer stores), then raises a done tag everywhere.  Every rank must issue
+ * its exchanges in the same order.  The kernel (128 threads, 64 registers) is resident beside the
+ * frame kernel, so on its own stream the exchange of frame i overlaps frame i + 1 (use two
+ * output sets).  rcull_merge_wait enqueues a kernel that returns once every rank's slices of the
+ * exchanges issued so far have landed in THIS rank's allocation.  One process driving several
+ * ranks must enqueue every rank's exchange before any rank's wait (streams of one process may share
+ * a hardware queue). */
+int rcull_merge_exchange(rcull_merge *m, uint32_t buffer_ix, uint32_t n_views, void *stream);
+int rcull_merge_wait(rcull_merge *m, void *stream);
 /* Device pointers of the merged lists of one view and of the merged counts / index totals. */
 int rcull_merge_lists(rcull_merge *m, uint32_t view, rcull_draw_cmd **cmds, uint32_t **visible,
                       uint32_t **counts, uint64_t **index_totals);

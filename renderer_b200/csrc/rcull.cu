@@ -423,7 +423,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     if (n == 0) {  // empty query: cull_pass still clears the buffers (cull_pipeline.rs:498-511)
         CU(cudaMemsetAsync(o.counts, 0, kMaxViews * 4, s));
         CU(cudaMemsetAsync(o.totals, 0, kMaxViews * 8, s));
-        if (c->meta_out) CU(cudaMemsetAsync(c->meta_out, 0, 2 * c->cfg.max_views * 8, s));
+        if (c->meta_out) CU(cudaMemsetAsync(c->meta_out + (size_t)buffer_ix * 2 * c->cfg.max_views, 0, 2 * c->cfg.max_views * 8, s));
         return RCULL_OK;
     }
     const uint32_t n_tiles = (uint32_t)((n + kTile - 1) / kTile);
@@ -459,7 +459,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     a.src_first = o.src_first;
     a.counts = o.counts;
     a.totals = o.totals;
-    a.meta_out = c->meta_out;
+    a.meta_out = c->meta_out ? c->meta_out + (size_t)buffer_ix * 2 * c->cfg.max_views : nullptr;
     a.max_views = c->cfg.max_views;
     a.status = c->status;
     a.ticket = c->ticket;
@@ -845,6 +845,9 @@ struct rcull_merge {
     unsigned long long* meta_all = nullptr;
     uint32_t* counts = nullptr;
     unsigned long long* totals = nullptr;
+    size_t sync_off = 0;           // MergeSync mailbox at the end of the (peer-mapped) allocation
+    unsigned long long epoch = 0;  // exchanges issued so far
+    uint32_t* cta_done = nullptr;
 };
 
 static_assert(RCULL_MAX_RANKS == kMaxRanks && RCULL_IPC_HANDLE_BYTES == sizeof(cudaIpcMemHandle_t), "merge ABI constants");
@@ -863,6 +866,7 @@ void rcull_merge_destroy(rcull_merge* m) {
     cudaFree(m->meta_all);
     cudaFree(m->counts);
     cudaFree(m->totals);
+    cudaFree(m->cta_done);
     delete m;
 }
 
@@ -877,19 +881,28 @@ int rcull_merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t cap
     m->world = world;
     m->rank = rank;
     m->cap = capacity;
-    m->bytes = (size_t)c->cfg.max_views * capacity * 24;
+    m->sync_off = ((size_t)c->cfg.max_views * capacity * 24 + 255) / 256 * 256;
+    m->bytes = m->sync_off + sizeof(MergeSync);
     const uint32_t mv = c->cfg.max_views;
-    if (cudaMalloc((void**)&m->base, m->bytes) != cudaSuccess || cudaMalloc((void**)&m->meta_local, 2 * mv * 8) != cudaSuccess ||
+    // meta_local: one row of exchange words per output set, so a pipelined frame never overwrites the row a merge still reads
+    if (cudaMalloc((void**)&m->base, m->bytes) != cudaSuccess || cudaMalloc((void**)&m->meta_local, 3 * 2 * mv * 8) != cudaSuccess ||
+        cudaMalloc((void**)&m->cta_done, 4) != cudaSuccess ||
         cudaMalloc((void**)&m->meta_all, (size_t)world * 2 * mv * 8) != cudaSuccess ||
         cudaMalloc((void**)&m->counts, mv * 4) != cudaSuccess || cudaMalloc((void**)&m->totals, mv * 8) != cudaSuccess) {
         rcull_merge_destroy(m);
         return fail(RCULL_ERR_CUDA, "rcull_merge_create: cudaMalloc of %zu bytes failed", m->bytes);
     }
-    cudaMemset(m->meta_local, 0, 2 * mv * 8);
+    cudaMemset(m->meta_local, 0, 3 * 2 * mv * 8);
+    cudaMemset(m->cta_done, 0, 4);
+    cudaMemset(m->base + m->sync_off, 0, sizeof(MergeSync));
     cudaMemset(m->meta_all, 0, (size_t)world * 2 * mv * 8);
     cudaMemset(m->counts, 0, mv * 4);
     cudaMemset(m->totals, 0, mv * 8);
     m->peer[rank] = m->base;
+    // the same shared-memory carveout as the frame kernel: an SM's split cannot change while CTAs are resident,
+    // so a CTA of a kernel that prefers another split would keep the next frame's CTA off its SM until it exits
+    cudaFuncSetAttribute(merge_exchange, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(merge_wait, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     c->meta_out = m->meta_local;  // frames issued from now on write the exchange words directly
     *out = m;
     return RCULL_OK;
@@ -942,20 +955,20 @@ int rcull_merge_pack_meta(rcull_merge* m, uint32_t buffer_ix, void* stream) {
     rcull_ctx* c = m->ctx;
     if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
     CU(cudaSetDevice(c->cfg.device));
-    pack_meta<<<1, 32, 0, (cudaStream_t)stream>>>(c->out[buffer_ix].counts, c->out[buffer_ix].totals, c->cfg.max_views, m->meta_local);
+    pack_meta<<<1, 32, 0, (cudaStream_t)stream>>>(c->out[buffer_ix].counts, c->out[buffer_ix].totals, c->cfg.max_views,
+                                                  m->meta_local + (size_t)buffer_ix * 2 * c->cfg.max_views);
     CU(cudaGetLastError());
     c->launches += 1;
     return RCULL_OK;
 }
 
-int rcull_merge_scatter(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, void* stream) {
-    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_scatter: null argument");
+static int merge_args(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, MergeArgs* out) {
     rcull_ctx* c = m->ctx;
-    if (buffer_ix >= c->cfg.n_buffers || n_views < 1 || n_views > c->cfg.max_views) return fail(RCULL_ERR_INVALID, "rcull_merge_scatter: bad buffer/view count");
+    if (buffer_ix >= c->cfg.n_buffers || n_views < 1 || n_views > c->cfg.max_views) return fail(RCULL_ERR_INVALID, "merge: bad buffer/view count");
     for (uint32_t p = 0; p < m->world; ++p)
         if (!m->peer[p]) return fail(RCULL_ERR_INVALID, "peer %u has not been mapped (rcull_merge_open_peer / rcull_merge_set_peer_ptr)", p);
     CU(cudaSetDevice(c->cfg.device));
-    MergeArgs a;
+    MergeArgs& a = *out;
     memset(&a, 0, sizeof a);
     for (uint32_t p = 0; p < m->world; ++p) a.peer[p] = m->peer[p];
     for (uint32_t k = 0; k < n_views; ++k) {
@@ -970,9 +983,48 @@ int rcull_merge_scatter(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, vo
     a.n_views = n_views;
     a.max_views = c->cfg.max_views;
     a.cap = (uint32_t)m->cap;
-    scatter_rebased<<<c->sm_count * 4, 256, 0, (cudaStream_t)stream>>>(a);
+    a.meta_mine = m->meta_local + (size_t)buffer_ix * 2 * c->cfg.max_views;
+    a.sync_off = m->sync_off;
+    a.cta_done = m->cta_done;
+    return RCULL_OK;
+}
+
+int rcull_merge_scatter(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, void* stream) {
+    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_scatter: null argument");
+    MergeArgs a;
+    int rc = merge_args(m, buffer_ix, n_views, &a);
+    if (rc) return rc;
+    scatter_rebased<<<m->ctx->sm_count * 4, 256, 0, (cudaStream_t)stream>>>(a);
     CU(cudaGetLastError());
-    c->launches += 1;
+    m->ctx->launches += 1;
+    return RCULL_OK;
+}
+
+int rcull_merge_exchange(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, void* stream) {
+    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_exchange: null argument");
+    MergeArgs a;
+    int rc = merge_args(m, buffer_ix, n_views, &a);
+    if (rc) return rc;
+    a.epoch = ++m->epoch;
+    // one CTA per SM: it fits beside the frame kernel's CTA, and every CTA of the grid is resident at
+    // once (none of them waits behind a spinning sibling)
+    int ctas = m->ctx->sm_count / 2;  // measured at N = 2: 64-74 CTAs move the lists fastest while costing the co-running frame least
+    if (const char* e = getenv("RCULL_EXCHANGE_CTAS")) {  // tuning knob: fewer CTAs = fewer SMs shared with the frame kernel
+        const int v = atoi(e);
+        if (v >= 1 && v <= m->ctx->sm_count) ctas = v;
+    }
+    merge_exchange<<<ctas, 128, 0, (cudaStream_t)stream>>>(a);
+    CU(cudaGetLastError());
+    m->ctx->launches += 1;
+    return RCULL_OK;
+}
+
+int rcull_merge_wait(rcull_merge* m, void* stream) {
+    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_wait: null argument");
+    CU(cudaSetDevice(m->ctx->cfg.device));
+    merge_wait<<<1, 32, 0, (cudaStream_t)stream>>>(reinterpret_cast<const MergeSync*>(m->base + m->sync_off), m->world, m->epoch);
+    CU(cudaGetLastError());
+    m->ctx->launches += 1;
     return RCULL_OK;
 }
 

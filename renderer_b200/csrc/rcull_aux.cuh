@@ -46,6 +46,11 @@ struct MergeArgs {
     unsigned long long* merged_totals;
     uint32_t world, rank, n_views, max_views;
     uint32_t cap;                           // merged list capacity (commands per view)
+    // fused exchange (merge_exchange): no collective library on the path
+    const unsigned long long* meta_mine;    // this rank's (counts, index totals) of the frame being merged
+    size_t sync_off;                        // byte offset of the MergeSync block in every merged allocation
+    unsigned long long epoch;               // exchange number, the same on every rank
+    uint32_t* cta_done;                     // local counter: CTAs of this launch that have stored their share
     __host__ __device__ size_t n_views_cap_bytes() const { return (size_t)max_views * cap * 20; }
 };
 
@@ -56,6 +61,79 @@ __global__ void __launch_bounds__(256) pack_meta(const uint32_t* __restrict__ co
     if (i < max_views) {
         meta_local[i] = counts[i];
         meta_local[max_views + i] = totals[i];
+    }
+}
+
+// Flags other GPUs write into this GPU's memory over NVLink: system-scope release / acquire.
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// Per-rank mailbox at the end of every merged allocation; slot [r] is written by rank r only.
+struct MergeSync {
+    // two slots, by exchange parity: a rank can be one exchange ahead of a peer's late CTAs, never two
+    // (its exchange e + 2 needs the peer's words of e + 1, which the peer sends after finishing e)
+    unsigned long long meta[2][kMaxRanks][16];  // counts[8] then index totals[8] of rank r
+    unsigned long long meta_tag[2][kMaxRanks];  // epoch of the exchange meta[.][r] belongs to
+    unsigned long long done_tag[kMaxRanks];  // rank r has stored all its slices of exchange `epoch` here
+};
+
+// Copies n_words 32-bit words of one of this rank's lists to byte offset dst_off of EVERY
+// rank's merged allocation.  Stores are 16 bytes wide wherever the destination is 16-byte
+// aligned (NVLink moves full 16-byte-multiple packets: word-wide stores reached 0.3 TB/s, a third
+// of the link); the up-to-3 words before the first aligned address and after the last go out as
+// single words.  kCmds: word w of the 5-word command stream is firstIndex iff w % 5 == 2.
+template <bool kCmds>
+__device__ __forceinline__ void store_to_peers(const MergeArgs& a, const uint32_t* __restrict__ src, size_t n_words, size_t dst_off,
+                                               uint32_t add, size_t t0, size_t stride) {
+    const size_t head = ((16u - (uint32_t)(dst_off & 15u)) & 15u) / 4u;  // words until the destination is 16-byte aligned
+    const size_t h = head < n_words ? head : n_words;
+    const size_t n_vec = (n_words - h) / 4;
+    // four vectors per thread in flight: the loop is bound by the latency of the local loads, not by issue
+    constexpr int kUnroll = 4;
+    for (size_t v0 = t0; v0 < n_vec; v0 += kUnroll * stride) {
+        uint4 x[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const size_t v = v0 + u * stride;
+            if (v < n_vec) {
+                const size_t w = h + 4 * v;
+                x[u] = make_uint4(src[w], src[w + 1], src[w + 2], src[w + 3]);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const size_t v = v0 + u * stride;
+            if (v < n_vec) {
+                const size_t w = h + 4 * v;
+                if (kCmds) {
+                    const uint32_t m = (uint32_t)(w % 5);  // firstIndex sits where (w + j) % 5 == 2
+                    if (m == 2) x[u].x += add;
+                    if (m == 1) x[u].y += add;
+                    if (m == 0) x[u].z += add;
+                    if (m == 4) x[u].w += add;
+                }
+                for (uint32_t p = 0; p < a.world; ++p) *reinterpret_cast<uint4*>(a.peer[p] + dst_off + 4 * w) = x[u];
+            }
+        }
+    }
+    // head and tail words (at most 6 in total)
+    const size_t tail0 = h + 4 * n_vec;
+    for (size_t i = t0; i < h + (n_words - tail0); i += stride) {
+        const size_t w = i < h ? i : tail0 + (i - h);
+        uint32_t x = src[w];
+        if (kCmds && w % 5 == 2) x += add;
+        for (uint32_t p = 0; p < a.world; ++p) *reinterpret_cast<uint32_t*>(a.peer[p] + dst_off + 4 * w) = x;
     }
 }
 
@@ -87,15 +165,80 @@ __global__ void __launch_bounds__(256) scatter_rebased(const __grid_constant__ M
         const uint32_t* __restrict__ sv = a.src_visible[k];
         const size_t cmd_off = ((size_t)k * a.cap + cnt_prefix) * 20;
         const size_t vis_off = (size_t)a.n_views_cap_bytes() + ((size_t)k * a.cap + cnt_prefix) * 4;
-        for (size_t w = t0; w < words; w += stride) {
-            uint32_t v = sc[w];
-            if (w % 5 == 2) v += add;  // firstIndex
-            for (uint32_t p = 0; p < a.world; ++p) reinterpret_cast<uint32_t*>(a.peer[p] + cmd_off)[w] = v;
+        store_to_peers<true>(a, sc, words, cmd_off, add, t0, stride);
+        store_to_peers<false>(a, sv, (size_t)count, vis_off, 0u, t0, stride);
+    }
+}
+
+// The whole exchange step in ONE kernel, no collective library call on the path:
+//   1. CTA 0 stores this rank's (count, index total) words into every rank's mailbox and raises its tag;
+//   2. every CTA waits until all ranks' words of this epoch have arrived in the LOCAL mailbox;
+//   3. exclusive prefixes over ranks -> this rank's slot; the rebased lists are stored into that
+//      slot of every rank's merged allocation (16-byte peer stores over NVLink);
+//   4. the last CTA to finish raises this rank's done tag in every mailbox.
+// 128 threads x 64 registers (the 8192 registers the frame kernel's CTA leaves free) and no shared memory: such a CTA is resident beside
+// the frame kernel's CTA, so the exchange of frame i runs under frame i + 1.
+__global__ void __maxnreg__(64) merge_exchange(const __grid_constant__ MergeArgs a) {
+    const uint32_t tid = threadIdx.x;
+    if (blockIdx.x == 0) {
+        if (tid < 16) {
+            const uint32_t k = tid & 7u;
+            const unsigned long long v = k < a.max_views ? a.meta_mine[(tid >> 3) * a.max_views + k] : 0ull;
+            for (uint32_t p = 0; p < a.world; ++p) reinterpret_cast<MergeSync*>(a.peer[p] + a.sync_off)->meta[a.epoch & 1][a.rank][tid] = v;
         }
-        for (size_t i = t0; i < count; i += stride) {
-            const uint32_t v = sv[i];
-            for (uint32_t p = 0; p < a.world; ++p) reinterpret_cast<uint32_t*>(a.peer[p] + vis_off)[i] = v;
+        __threadfence_system();
+        __syncthreads();
+        if (tid < a.world) st_release_sys(&reinterpret_cast<MergeSync*>(a.peer[tid] + a.sync_off)->meta_tag[a.epoch & 1][a.rank], a.epoch);
+    }
+    const MergeSync* mine = reinterpret_cast<const MergeSync*>(a.peer[a.rank] + a.sync_off);
+    if (tid < a.world) {
+        while (ld_acquire_sys(&mine->meta_tag[a.epoch & 1][tid]) != a.epoch) __nanosleep(200);
+    }
+    __syncthreads();
+    const unsigned long long (*meta)[16] = mine->meta[a.epoch & 1];  // every rank's words, now in local memory
+
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const size_t t0 = (size_t)blockIdx.x * blockDim.x + tid;
+    for (uint32_t k = 0; k < a.n_views; ++k) {
+        unsigned long long cnt_prefix = 0, len_prefix = 0, cnt_all = 0, len_all = 0;
+        for (uint32_t r = 0; r < a.world; ++r) {
+            const unsigned long long c = ld_relaxed_sys(&meta[r][k]), l = ld_relaxed_sys(&meta[r][8 + k]);
+            if (r < a.rank) {
+                cnt_prefix += c;
+                len_prefix += l;
+            }
+            cnt_all += c;
+            len_all += l;
         }
+        if (t0 == 0) {
+            a.merged_counts[k] = (uint32_t)cnt_all;
+            a.merged_totals[k] = len_all;
+        }
+        unsigned long long count = ld_relaxed_sys(&meta[a.rank][k]);
+        if (cnt_prefix >= a.cap) continue;
+        if (cnt_prefix + count > a.cap) count = a.cap - cnt_prefix;  // clamp writes, like cap_visible
+        const size_t cmd_off = ((size_t)k * a.cap + cnt_prefix) * 20;
+        const size_t vis_off = (size_t)a.n_views_cap_bytes() + ((size_t)k * a.cap + cnt_prefix) * 4;
+        store_to_peers<true>(a, a.src_cmds[k], (size_t)count * 5, cmd_off, (uint32_t)len_prefix, t0, stride);
+        store_to_peers<false>(a, a.src_visible[k], (size_t)count, vis_off, 0u, t0, stride);
+    }
+    __threadfence_system();  // this thread's peer stores are visible system-wide before the CTA counts itself
+    __syncthreads();
+    if (tid == 0) {
+        const uint32_t done = atomicAdd(a.cta_done, 1u);
+        if (done == gridDim.x - 1) {
+            *a.cta_done = 0;
+            __threadfence_system();
+            for (uint32_t p = 0; p < a.world; ++p)
+                st_release_sys(&reinterpret_cast<MergeSync*>(a.peer[p] + a.sync_off)->done_tag[a.rank], a.epoch);
+        }
+    }
+}
+
+// Returns when every rank's slices of exchange `epoch` have landed in this rank's allocation.
+__global__ void merge_wait(const MergeSync* mine, uint32_t world, unsigned long long epoch) {
+    if (threadIdx.x < world) {
+        while (ld_acquire_sys(&mine->done_tag[threadIdx.x]) < epoch) __nanosleep(200);
     }
 }
 

@@ -25,7 +25,10 @@ namespace rcull {
 #endif
 constexpr int kComputeWarps = RCULL_COMPUTE_WARPS;  // + 1 scan warp; 7 + 1: two CTAs fill an SM's register file at 112 regs, 15 + 1: one CTA does
 constexpr int kCtasPerSm = kComputeWarps <= 7 ? 2 : 1;
-constexpr size_t kSmemPerCta = (228 * 1024 - kCtasPerSm * 1024) / kCtasPerSm;  // 228 KB per SM, 1 KB reserved per CTA
+// 228 KB per SM, 1 KB reserved per CTA; the one-CTA shape leaves a second reserved KB free so that a small
+// shared-memory-free CTA of another stream (the merge's peer-store kernel: 128 threads x 64 registers)
+// can be resident beside it and overlap with the frame
+constexpr size_t kSmemPerCta = (228 * 1024 - (kCtasPerSm == 1 ? 2 : kCtasPerSm) * 1024) / kCtasPerSm;
 constexpr int kThreads = (kComputeWarps + 1) * 32;  // + scan warp
 constexpr int kItems = 4;                           // entities per thread per tile
 constexpr int kTile = kComputeWarps * 32 * kItems;  // 896 entities

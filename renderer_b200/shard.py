@@ -172,9 +172,13 @@ class PeerMerger:
         mv = ctx.cfg.max_views
         a, b = C.c_void_p(), C.c_void_p()
         _lib.check(self._lib.rcull_merge_meta_ptrs(self._h, C.byref(a), C.byref(b)))
-        self.meta_local = _wrap_device(torch, a.value, 2 * mv, torch.int64, device)
+        self.meta_rows = _wrap_device(torch, a.value, 3 * 2 * mv, torch.int64, device).view(3, 2 * mv)  # row = output set
+        self.meta_local = self.meta_rows[0]
         self.meta_all = _wrap_device(torch, b.value, self.world * 2 * mv, torch.int64, device)
         self._flag = torch.zeros(1, dtype=torch.int32, device=device)
+        # pipelined use (exchange of frame i overlapping frame i + 1 on another stream): the event the
+        # caller orders the reuse of an output set by
+        self.ev_scatter_done = [torch.cuda.Event() for _ in range(3)]
         if self.world > 1:  # one-time exchange of the IPC handles of the merged allocations
             handle = (C.c_ubyte * 64)()
             _lib.check(self._lib.rcull_merge_ipc_handle(self._h, handle))
@@ -202,12 +206,26 @@ class PeerMerger:
         # no pack step: a context with a merge attached writes the exchange words from the
         # frame kernel itself (frames must be issued after this object was created)
         if self.world > 1:
-            self.dist.all_gather_into_tensor(self.meta_all, self.meta_local, group=self.group)
+            self.dist.all_gather_into_tensor(self.meta_all, self.meta_rows[buffer_ix], group=self.group)
         else:
-            self.meta_all.copy_(self.meta_local)
+            self.meta_all.copy_(self.meta_rows[buffer_ix])
         check(self._lib.rcull_merge_scatter(self._h, buffer_ix, self.n_views, s))
         if self.world > 1:
             self.dist.all_reduce(self._flag, group=self.group)  # every rank has stored its slices
+
+    def exchange(self, buffer_ix: int = 0, wait: bool = True) -> None:
+        """The fused exchange (rcull_merge_exchange): ONE kernel on the current stream -- meta words to every
+        peer's mailbox, wait for everyone's, rebased lists into every rank's allocation, done tags -- and no
+        collective call.  Records ev_scatter_done[buffer_ix] (output set buffer_ix may be overwritten);
+        wait=True appends the kernel that returns when every rank's slices have landed here."""
+        from ._lib import check
+
+        st = self.torch.cuda.current_stream(self.device)
+        s = self.C.c_void_p(st.cuda_stream)
+        check(self._lib.rcull_merge_exchange(self._h, buffer_ix, self.n_views, s))
+        self.ev_scatter_done[buffer_ix].record(st)
+        if wait:
+            check(self._lib.rcull_merge_wait(self._h, s))
 
     def lists(self, view: int):
         """(cmds_ptr, visible_ptr, counts_ptr, totals_ptr) device addresses of the merged outputs."""

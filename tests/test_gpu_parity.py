@@ -445,3 +445,76 @@ def test_frozen_culling_frame_updates_models_only():
         assert np.array_equal(counts0, counts1) and np.array_equal(totals0, totals1)
         for k in range(2):
             assert np.array_equal(ctx.cmds(k, int(counts0[k])), cmds0[k])
+
+
+def test_fused_exchange_two_ranks_in_one_process():
+    """rcull_merge_exchange with world = 2 emulated in one process on two streams: no collective call, the
+    kernels exchange their counts through the mailboxes and store into both allocations; three exchanges
+    in a row (mailbox parity slots, epoch tags, both output sets), each equal to the unsharded lists."""
+    import ctypes as C
+
+    import torch
+
+    from renderer_b200 import _lib
+    from renderer_b200.shard import _wrap_device, shard_range
+
+    lib = _lib.load()
+    n, n_views, world = 120_001, 2, 2
+    dev = torch.device("cuda", 0)
+    streams = [torch.cuda.Stream(device=dev) for _ in range(world)]
+    ctxs, merges = [], []
+    try:
+        for r in range(world):
+            lo, hi = shard_range(n, world, r)
+            c = CullContext(hi - lo, max_views=n_views, max_meshes=len(MESHES), n_buffers=2)
+            c.set_mesh_table(MESHES)
+            h = C.c_void_p()
+            _lib.check(lib.rcull_merge_create(c._h, world, r, n, C.byref(h)))
+            ctxs.append(c), merges.append(h)
+        bases = []
+        for h in merges:
+            b = C.c_void_p()
+            _lib.check(lib.rcull_merge_base(h, C.byref(b)))
+            bases.append(b)
+        for h in merges:
+            for p in range(world):
+                _lib.check(lib.rcull_merge_set_peer_ptr(h, p, bases[p]))
+        for it, (seed, half_box) in enumerate([(scene.SEED, 50.0), (scene.SEED + 7, 20.0), (scene.SEED + 9, 35.0)]):
+            views = scene.scene_views(n_views)
+            ps, rot, mesh = scene.synth_entities(seed, 0, n, half_box)
+            with CullContext(n, max_views=n_views, max_meshes=len(MESHES)) as whole:
+                whole.set_mesh_table(MESHES)
+                whole.upload_entities(ps, rot, mesh)
+                whole.frame(views, scene.CAMERA_POS)
+                wc, wt = whole.counts()
+                want_cmds = [whole.cmds(k, int(wc[k])) for k in range(n_views)]
+                want_vis = [whole.visible(k, int(wc[k])) for k in range(n_views)]
+            b = it & 1
+            for r, c in enumerate(ctxs):
+                lo, hi = shard_range(n, world, r)
+                c.upload_entities(ps[lo:hi], rot[lo:hi], mesh[lo:hi])
+                c.frame(views, scene.CAMERA_POS, draw_index_base=lo, buffer_ix=b, stream=streams[r].cuda_stream)
+            # both exchange kernels must be in flight together: two streams, and every exchange is enqueued
+            # before any wait (streams of one process can share a hardware queue: a wait queued ahead of
+            # the other rank's exchange would block it for good)
+            for r, h in enumerate(merges):
+                _lib.check(lib.rcull_merge_exchange(h, b, n_views, C.c_void_p(streams[r].cuda_stream)))
+            for r, h in enumerate(merges):
+                _lib.check(lib.rcull_merge_wait(h, C.c_void_p(streams[r].cuda_stream)))
+            torch.cuda.synchronize()
+            for h in merges:
+                for k in range(n_views):
+                    a, b_, c_, d = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+                    _lib.check(lib.rcull_merge_lists(h, k, C.byref(a), C.byref(b_), C.byref(c_), C.byref(d)))
+                    counts = _wrap_device(torch, c_.value, n_views, torch.int32, dev).cpu().numpy().view(np.uint32)
+                    totals = _wrap_device(torch, d.value, n_views, torch.int64, dev).cpu().numpy().view(np.uint64)
+                    assert counts[k] == wc[k] and totals[k] == wt[k], (it, k)
+                    got = _wrap_device(torch, a.value, max(int(wc[k]), 1) * 5, torch.int32, dev).cpu().numpy().view(np.uint32)[: int(wc[k]) * 5]
+                    assert np.array_equal(got, want_cmds[k].view(np.uint32).reshape(-1)), (it, k)
+                    got = _wrap_device(torch, b_.value, max(int(wc[k]), 1), torch.int32, dev).cpu().numpy().view(np.uint32)[: int(wc[k])]
+                    assert np.array_equal(got, want_vis[k]), (it, k)
+    finally:
+        for h in merges:
+            lib.rcull_merge_destroy(h)
+        for c in ctxs:
+            c.destroy()
