@@ -233,6 +233,14 @@ int rcull_merge_meta_ptrs(rcull_merge *m, uint64_t **meta_local, uint64_t **meta
 /* Only needed for a frame issued BEFORE rcull_merge_create: later frames write meta_local themselves. */
 int rcull_merge_pack_meta(rcull_merge *m, uint32_t buffer_ix, void *stream);
 int rcull_merge_scatter(rcull_merge *m, uint32_t buffer_ix, uint32_t n_views, void *stream);
+/* The merged allocation on caller-owned memory of rcull_merge_bytes(capacity) bytes (for instance
+ * symmetric memory that every rank has mapped, with an NVLS multicast mapping): peers are named with
+ * rcull_merge_set_peer_ptr; with rcull_merge_set_multicast_ptr the exchange stores each list ONCE
+ * through the multicast address and the NVSwitch replicates it into every rank's allocation
+ * (multimem.st), instead of one store per peer. */
+int rcull_merge_bytes(rcull_ctx *ctx, uint64_t capacity, uint64_t *bytes);
+int rcull_merge_create_on(rcull_ctx *ctx, uint32_t world, uint32_t rank, uint64_t capacity, void *base, rcull_merge **out);
+int rcull_merge_set_multicast_ptr(rcull_merge *m, void *multicast_base);
 /* The whole exchange in ONE kernel, no collective call: this rank's (count, index total) words go
  * into every rank's mailbox over NVLink, the kernel waits for every rank's words of the same
  * exchange, computes its slot and stores its rebased lists into that slot of every rank's

@@ -129,6 +129,9 @@ SYMBOLS = {
     "rcull_merge_meta_ptrs": (C.c_int, [_P, C.POINTER(_P), C.POINTER(_P)]),
     "rcull_merge_pack_meta": (C.c_int, [_P, _u32, _P]),
     "rcull_merge_scatter": (C.c_int, [_P, _u32, _u32, _P]),
+    "rcull_merge_bytes": (C.c_int, [_P, _u64, _P]),
+    "rcull_merge_create_on": (C.c_int, [_P, _u32, _u32, _u64, _P, C.POINTER(_P)]),
+    "rcull_merge_set_multicast_ptr": (C.c_int, [_P, _P]),
     "rcull_merge_exchange": (C.c_int, [_P, _u32, _u32, _P]),
     "rcull_merge_wait": (C.c_int, [_P, _P]),
     "rcull_merge_lists": (C.c_int, [_P, _u32, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)]),

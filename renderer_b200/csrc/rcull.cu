@@ -845,6 +845,8 @@ struct rcull_merge {
     unsigned long long* meta_all = nullptr;
     uint32_t* counts = nullptr;
     unsigned long long* totals = nullptr;
+    bool owns_base = true;         // false: the caller's (symmetric-memory) allocation, rcull_merge_create_on
+    unsigned char* mc_base = nullptr;  // NVLS multicast mapping of the same allocation on every rank, or null
     size_t sync_off = 0;           // MergeSync mailbox at the end of the (peer-mapped) allocation
     unsigned long long epoch = 0;  // exchanges issued so far
     uint32_t* cta_done = nullptr;
@@ -861,7 +863,7 @@ void rcull_merge_destroy(rcull_merge* m) {
     if (m->ctx->meta_out == m->meta_local) m->ctx->meta_out = nullptr;
     for (uint32_t p = 0; p < m->world; ++p)
         if (m->opened[p]) cudaIpcCloseMemHandle(m->peer[p]);
-    cudaFree(m->base);
+    if (m->owns_base) cudaFree(m->base);
     cudaFree(m->meta_local);
     cudaFree(m->meta_all);
     cudaFree(m->counts);
@@ -870,7 +872,7 @@ void rcull_merge_destroy(rcull_merge* m) {
     delete m;
 }
 
-int rcull_merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t capacity, rcull_merge** out) {
+static int merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t capacity, void* external_base, rcull_merge** out) {
     if (!c || !out) return fail(RCULL_ERR_INVALID, "rcull_merge_create: null argument");
     *out = nullptr;
     if (world < 1 || world > kMaxRanks || rank >= world) return fail(RCULL_ERR_INVALID, "rank %u of world %u (max %d)", rank, world, kMaxRanks);
@@ -885,7 +887,11 @@ int rcull_merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t cap
     m->bytes = m->sync_off + sizeof(MergeSync);
     const uint32_t mv = c->cfg.max_views;
     // meta_local: one row of exchange words per output set, so a pipelined frame never overwrites the row a merge still reads
-    if (cudaMalloc((void**)&m->base, m->bytes) != cudaSuccess || cudaMalloc((void**)&m->meta_local, 3 * 2 * mv * 8) != cudaSuccess ||
+    if (external_base) {
+        m->base = static_cast<unsigned char*>(external_base);
+        m->owns_base = false;
+    }
+    if ((!external_base && cudaMalloc((void**)&m->base, m->bytes) != cudaSuccess) || cudaMalloc((void**)&m->meta_local, 3 * 2 * mv * 8) != cudaSuccess ||
         cudaMalloc((void**)&m->cta_done, 4) != cudaSuccess ||
         cudaMalloc((void**)&m->meta_all, (size_t)world * 2 * mv * 8) != cudaSuccess ||
         cudaMalloc((void**)&m->counts, mv * 4) != cudaSuccess || cudaMalloc((void**)&m->totals, mv * 8) != cudaSuccess) {
@@ -905,6 +911,27 @@ int rcull_merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t cap
     cudaFuncSetAttribute(merge_wait, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     c->meta_out = m->meta_local;  // frames issued from now on write the exchange words directly
     *out = m;
+    return RCULL_OK;
+}
+
+int rcull_merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t capacity, rcull_merge** out) {
+    return merge_create(c, world, rank, capacity, nullptr, out);
+}
+
+int rcull_merge_bytes(rcull_ctx* c, uint64_t capacity, uint64_t* bytes) {
+    if (!c || !bytes) return fail(RCULL_ERR_INVALID, "rcull_merge_bytes: null argument");
+    *bytes = ((uint64_t)c->cfg.max_views * capacity * 24 + 255) / 256 * 256 + sizeof(MergeSync);
+    return RCULL_OK;
+}
+
+int rcull_merge_create_on(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t capacity, void* base, rcull_merge** out) {
+    if (!base) return fail(RCULL_ERR_INVALID, "rcull_merge_create_on: null base");
+    return merge_create(c, world, rank, capacity, base, out);
+}
+
+int rcull_merge_set_multicast_ptr(rcull_merge* m, void* multicast_base) {
+    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_set_multicast_ptr: null argument");
+    m->mc_base = static_cast<unsigned char*>(multicast_base);
     return RCULL_OK;
 }
 
@@ -986,6 +1013,7 @@ static int merge_args(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, Merg
     a.meta_mine = m->meta_local + (size_t)buffer_ix * 2 * c->cfg.max_views;
     a.sync_off = m->sync_off;
     a.cta_done = m->cta_done;
+    a.mc = m->mc_base;
     return RCULL_OK;
 }
 

@@ -51,6 +51,7 @@ struct MergeArgs {
     size_t sync_off;                        // byte offset of the MergeSync block in every merged allocation
     unsigned long long epoch;               // exchange number, the same on every rank
     uint32_t* cta_done;                     // local counter: CTAs of this launch that have stored their share
+    unsigned char* mc;                      // NVLS multicast mapping of every rank's merged allocation (one store, the switch replicates), or null
     __host__ __device__ size_t n_views_cap_bytes() const { return (size_t)max_views * cap * 20; }
 };
 
@@ -77,6 +78,17 @@ __device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long
     unsigned long long v;
     asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
+}
+
+// Stores through an NVLS multicast address: one store leaves the GPU, the NVSwitch writes it into every
+// member's memory (egress per rank = its own lists once, not once per peer).
+__device__ __forceinline__ void multimem_st_v4(void* mc, uint4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(__uint_as_float(v.x)),
+                 "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+                 : "memory");
+}
+__device__ __forceinline__ void multimem_st_u32(void* mc, uint32_t v) {
+    asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
 }
 
 // Per-rank mailbox at the end of every merged allocation; slot [r] is written by rank r only.
@@ -123,7 +135,11 @@ __device__ __forceinline__ void store_to_peers(const MergeArgs& a, const uint32_
                     if (m == 0) x[u].z += add;
                     if (m == 4) x[u].w += add;
                 }
-                for (uint32_t p = 0; p < a.world; ++p) *reinterpret_cast<uint4*>(a.peer[p] + dst_off + 4 * w) = x[u];
+                if (a.mc != nullptr) {
+                    multimem_st_v4(a.mc + dst_off + 4 * w, x[u]);  // NVSwitch replicates the store into every rank's allocation
+                } else {
+                    for (uint32_t p = 0; p < a.world; ++p) *reinterpret_cast<uint4*>(a.peer[p] + dst_off + 4 * w) = x[u];
+                }
             }
         }
     }
@@ -133,7 +149,11 @@ __device__ __forceinline__ void store_to_peers(const MergeArgs& a, const uint32_
         const size_t w = i < h ? i : tail0 + (i - h);
         uint32_t x = src[w];
         if (kCmds && w % 5 == 2) x += add;
-        for (uint32_t p = 0; p < a.world; ++p) *reinterpret_cast<uint32_t*>(a.peer[p] + dst_off + 4 * w) = x;
+        if (a.mc != nullptr) {
+            multimem_st_u32(a.mc + dst_off + 4 * w, x);
+        } else {
+            for (uint32_t p = 0; p < a.world; ++p) *reinterpret_cast<uint32_t*>(a.peer[p] + dst_off + 4 * w) = x;
+        }
     }
 }
 

@@ -155,7 +155,7 @@ class PeerMerger:
     then a one-word all_reduce as the "everyone has written" barrier.  Nothing in the
     step touches the host: all of it is enqueued on the current torch stream."""
 
-    def __init__(self, ctx, n_views: int, capacity: int, device, group=None):
+    def __init__(self, ctx, n_views: int, capacity: int, device, group=None, symmetric: bool = True):
         import ctypes as C
 
         import torch
@@ -168,7 +168,34 @@ class PeerMerger:
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self._h = C.c_void_p()
-        _lib.check(self._lib.rcull_merge_create(ctx._h, self.world, self.rank, capacity, C.byref(self._h)))
+        self.transport = "cuda-ipc peer stores"
+        self._symm = None
+        if symmetric and self.world > 1:
+            # Symmetric memory: every rank maps every rank's allocation AND one NVLS multicast address that
+            # stands for all of them -- the exchange then stores each list once and the NVSwitch replicates it.
+            try:
+                import torch.distributed._symmetric_memory as symm
+
+                nbytes = C.c_uint64()
+                _lib.check(self._lib.rcull_merge_bytes(ctx._h, capacity, C.byref(nbytes)))
+                buf = symm.empty(int(nbytes.value), dtype=torch.uint8, device=device)
+                g = group if group is not None else dist.group.WORLD
+                hdl = symm.rendezvous(buf, g.group_name)
+                ptrs = [int(p) for p in hdl.buffer_ptrs]
+                _lib.check(self._lib.rcull_merge_create_on(ctx._h, self.world, self.rank, capacity, C.c_void_p(ptrs[self.rank]), C.byref(self._h)))
+                for p in range(self.world):
+                    _lib.check(self._lib.rcull_merge_set_peer_ptr(self._h, p, C.c_void_p(ptrs[p])))
+                mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+                if mc:
+                    _lib.check(self._lib.rcull_merge_set_multicast_ptr(self._h, C.c_void_p(mc)))
+                self.transport = "symmetric memory, " + ("NVLS multicast stores" if mc else "peer stores")
+                self._symm = (buf, hdl)
+            except Exception as e:  # no symmetric-memory support in this torch / on this fabric: CUDA IPC below
+                self._symm = None
+                self._h = C.c_void_p()
+                self.transport = f"cuda-ipc peer stores (symmetric memory unavailable: {type(e).__name__})"
+        if not self._h:
+            _lib.check(self._lib.rcull_merge_create(ctx._h, self.world, self.rank, capacity, C.byref(self._h)))
         mv = ctx.cfg.max_views
         a, b = C.c_void_p(), C.c_void_p()
         _lib.check(self._lib.rcull_merge_meta_ptrs(self._h, C.byref(a), C.byref(b)))
@@ -179,7 +206,9 @@ class PeerMerger:
         # pipelined use (exchange of frame i overlapping frame i + 1 on another stream): the event the
         # caller orders the reuse of an output set by
         self.ev_scatter_done = [torch.cuda.Event() for _ in range(3)]
-        if self.world > 1:  # one-time exchange of the IPC handles of the merged allocations
+        if self.world > 1 and self._symm is not None:
+            dist.barrier(group=group)  # every mailbox is cleared before anyone stores into it
+        elif self.world > 1:  # one-time exchange of the IPC handles of the merged allocations
             handle = (C.c_ubyte * 64)()
             _lib.check(self._lib.rcull_merge_ipc_handle(self._h, handle))
             handles = [None] * self.world
