@@ -169,7 +169,7 @@ def gpu_arm(args, wl):
     if tri:
         ctx.set_geometry(*scene.synth_geometry(meshes))
         pv = scene.camera_pv()
-    stream = torch.cuda.Stream(device=dev)
+    stream = torch.cuda.Stream(device=dev, priority=-1)
     sh = stream.cuda_stream
     ctx.synth_entities(scene.SEED, lo, n, wl["half_box"], len(meshes), stream=sh)
     stream.synchronize()
@@ -182,11 +182,11 @@ def gpu_arm(args, wl):
         tot = torch.tensor([int(c0[:n_views].max())], dtype=torch.int64, device=dev)
         dist.all_reduce(tot)
         cap = int(tot.item() * 1.05) + 1024
-        merger = PeerMerger(ctx, n_views, cap, dev) if args.merge == "p2p" else ShardMerger(n_views, cap, dev)
+        merger = PeerMerger(ctx, n_views, cap, dev, symmetric=world >= 8) if args.merge == "p2p" else ShardMerger(n_views, cap, dev)
 
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev) if n * 36 < 256e6 else None
 
-    merge_stream = torch.cuda.Stream(device=dev) if pipelined else None
+    merge_stream = torch.cuda.Stream(device=dev, priority=0) if pipelined else None  # below the frame stream: frame CTAs are placed first
     frame_done = [torch.cuda.Event() for _ in range(2)]
     step_no = [0]
 

@@ -79,6 +79,7 @@ struct rcull_ctx {
     void* sort_tmp = nullptr;
     size_t sort_tmp_bytes = 0;
     uint64_t cap_cmds = 0;  // command capacity per view: cap_vis, or max_meshes * 6 in per-mesh mode
+    int reserved_sms = 0;  // SMs the frame kernel leaves to the exchange kernel of an attached merge (world > 1)
     unsigned long long* meta_out = nullptr;  // set by rcull_merge_create: the frame kernel writes the exchange words itself
     OutputSet out[3];
     ulonglong2* status = nullptr;
@@ -486,7 +487,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
         }
     }
     const bool mat = c->cfg.materialize_aabb || c->cfg.materialize_flags;
-    int grid = c->sm_count * c->blocks_per_sm[n_views][mat];
+    int grid = (c->sm_count - c->reserved_sms) * c->blocks_per_sm[n_views][mat];
     if ((uint32_t)grid > n_tiles) grid = (int)n_tiles;
     cudaError_t e = cudaSuccess;
     switch (n_views) {
@@ -860,7 +861,10 @@ void rcull_merge_destroy(rcull_merge* m) {
     if (!m) return;
     cudaSetDevice(m->ctx->cfg.device);
     cudaDeviceSynchronize();
-    if (m->ctx->meta_out == m->meta_local) m->ctx->meta_out = nullptr;
+    if (m->ctx->meta_out == m->meta_local) {
+        m->ctx->meta_out = nullptr;
+        m->ctx->reserved_sms = 0;
+    }
     for (uint32_t p = 0; p < m->world; ++p)
         if (m->opened[p]) cudaIpcCloseMemHandle(m->peer[p]);
     if (m->owns_base) cudaFree(m->base);
@@ -910,6 +914,14 @@ static int merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t ca
     cudaFuncSetAttribute(merge_exchange, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     cudaFuncSetAttribute(merge_wait, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     c->meta_out = m->meta_local;  // frames issued from now on write the exchange words directly
+    // Tuning knob (default off): leave RCULL_EXCHANGE_SMS SMs to the exchange kernel instead of letting its CTAs
+    // sit beside the frame's.  Measured slower at N = 2 and N = 8.
+    if (world > 1) {
+        if (const char* e = getenv("RCULL_EXCHANGE_SMS")) {
+            const int v = atoi(e);
+            if (v >= 0 && v < c->sm_count / 2) c->reserved_sms = v;
+        }
+    }
     *out = m;
     return RCULL_OK;
 }
@@ -1036,12 +1048,16 @@ int rcull_merge_exchange(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, v
     a.epoch = ++m->epoch;
     // one CTA per SM: it fits beside the frame kernel's CTA, and every CTA of the grid is resident at
     // once (none of them waits behind a spinning sibling)
-    int ctas = m->ctx->sm_count / 2;  // measured at N = 2: 64-74 CTAs move the lists fastest while costing the co-running frame least
-    if (const char* e = getenv("RCULL_EXCHANGE_CTAS")) {  // tuning knob: fewer CTAs = fewer SMs shared with the frame kernel
+    // CTAs of 128 threads x 64 registers: one fits beside the frame kernel's CTA on an SM.  How many: enough
+    // to keep NVLink busy, few enough not to slow the co-running frame (measured: 64-74 at N <= 4, 32 at N = 8,
+    // where every received byte also lands in this GPU's HBM under the frame).
+    int ctas = m->world >= 8 ? 32 : m->ctx->sm_count / 2;
+    if (const char* e = getenv("RCULL_EXCHANGE_CTAS")) {
         const int v = atoi(e);
-        if (v >= 1 && v <= m->ctx->sm_count) ctas = v;
+        if (v >= 1 && v <= 8 * m->ctx->sm_count) ctas = v;
     }
-    merge_exchange<<<ctas, 128, 0, (cudaStream_t)stream>>>(a);
+    if (m->ctx->reserved_sms > 0) ctas = m->ctx->reserved_sms * 8;  // dedicated SMs: 8 CTAs fill a register file
+    merge_exchange<<<ctas, 128, m->ctx->reserved_sms > 0 ? 2048 : 0, (cudaStream_t)stream>>>(a);
     CU(cudaGetLastError());
     m->ctx->launches += 1;
     return RCULL_OK;
