@@ -352,7 +352,7 @@ def gpu_arm(args, wl):
                 "nvlink_gbs_per_gpu": None if pipelined else 24.0 * float(counts.sum()) * (world - 1) / max((t_step - t_frame) / args.steps, 1e-9) / 1e9,
                 "nvlink_peak_gbs": 770.0, "transport": getattr(merger, "transport", "nccl"), "verified_against_nccl_allgatherv": merge_verified, "note": "rank 0's own lists delivered to every peer (one multicast store each when the transport says so); peak = measured peer copy per direction"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_kind": peak_kind, "kernel": f"transform_cull_compact<{n_views}>",
+                         "frac_of_nominal_8000": achieved / 8000.0, "traffic": None, "peak_kind": peak_kind, "kernel": f"transform_cull_compact<{n_views}>",
                          "bytes_per_entity": bytes_per_entity, "ms_per_launch": t_launch * 1e3},
             "clocks": clocks.summary(),
         }

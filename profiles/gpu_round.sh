@@ -1,15 +1,18 @@
 #!/bin/bash
-# GPU-box helper: parity tests, bench workloads, ncu launch list + full capture of the frame kernel.
+# GPU-box helper (round end): smoke, parity tests, bench lines, ncu launch list + full captures.
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.max.sm,clocks.max.mem --format=csv > gpurun_out/smi.txt; nproc >> gpurun_out/smi.txt
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -15 | tee gpurun_out/pytest_gpu.txt
-for w in 16m_5view 16m_1view 1m_1view; do
-  timeout 400 python bench.py --steps 20 --warmup 5 --workload $w > gpurun_out/bench_$w.log 2>&1
-  tail -1 gpurun_out/bench_$w.log | cut -c1-1500
+timeout 300 python __graft_entry__.py smoke 2>&1 | tail -2
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -4 | tee gpurun_out/pytest_gpu.txt
+for w in 16m_5view 16m_1view 1m_1view 1m_tri; do
+  timeout 400 python bench.py --steps 30 --warmup 5 --workload $w > gpurun_out/bench_$w.log 2>&1
+  tail -1 gpurun_out/bench_$w.log | cut -c1-300
 done
-timeout 400 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.log 2>&1; tail -1 gpurun_out/bench_ref.log
+timeout 400 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.log 2>&1; tail -1 gpurun_out/bench_ref.log | cut -c1-300
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_16m5view.csv python bench.py --steps 3 --warmup 3 > gpurun_out/ncu_launch.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:transform_cull_compact -s 3 -c 1 -o gpurun_out/frame_16m5view -f python bench.py --steps 3 --warmup 3 > gpurun_out/ncu_full.log 2>&1
-tail -3 gpurun_out/ncu_full.log
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:transform_cull_compact -s 3 -c 1 -o gpurun_out/frame_16m1view -f python bench.py --steps 3 --warmup 3 --workload 16m_1view > gpurun_out/ncu_full1.log 2>&1
-tail -3 gpurun_out/ncu_full1.log
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_1mtri.csv python bench.py --steps 3 --warmup 3 --workload 1m_tri > gpurun_out/ncu_launch_tri.log 2>&1
+for spec in "16m_5view:transform_cull_compact:frame_16m5view" "16m_1view:transform_cull_compact:frame_16m1view" "1m_tri:tri_cull:tri_1m"; do
+  IFS=: read w k tag <<< "$spec"
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:$k -s 3 -c 1 -o gpurun_out/$tag -f python bench.py --steps 3 --warmup 3 --workload $w > gpurun_out/ncu_$tag.log 2>&1
+  tail -1 gpurun_out/ncu_$tag.log | cut -c1-120
+done
