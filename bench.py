@@ -31,7 +31,8 @@ WORKLOADS = {
     "1m_1view": dict(n=1_000_000, n_views=1, half_box=250.0),
     # BASELINE configs[1] through BOTH stages of the reference's cull pass: the frame kernel, then the
     # per-triangle cull (generate_work.comp) of the camera survivors and compact_draw_stream
-    "1m_tri": dict(n=1_000_000, n_views=1, half_box=250.0, tri=True),
+    "1m_tri": dict(n=1_000_000, n_views=1, half_box=250.0, tri=True, coherent=True),
+    "1m_tri_random": dict(n=1_000_000, n_views=1, half_box=250.0, tri=True, coherent=False),  # random index triples: gather worst case
 }
 METRIC = "entities/sec transformed+culled+compacted"
 UNIT = "entities/s"
@@ -167,7 +168,7 @@ def gpu_arm(args, wl):
     ctx.set_mesh_table(meshes)
     pv = None
     if tri:
-        ctx.set_geometry(*scene.synth_geometry(meshes))
+        ctx.set_geometry(*scene.synth_geometry(meshes, coherent=bool(wl.get("coherent"))))
         pv = scene.camera_pv()
     stream = torch.cuda.Stream(device=dev, priority=-1)
     sh = stream.cuda_stream
@@ -365,6 +366,7 @@ def gpu_arm(args, wl):
                 "commands_in": int(counts[0]), "commands_out": n_cmd, "gtri_per_s": tris / t_tri / 1e9,
                 # 12 B index triple read per triangle, 12 B written per kept one, 20 + 4 B command in, 20 B out
                 "algorithmic_gbs": (12.0 * tris + 4.0 * kept + 24.0 * int(counts[0]) + 20.0 * n_cmd) / t_tri / 1e9,
+                "meshes": "grid sheets, row-major cell order (vertex reuse like an indexed glTF mesh)" if wl.get("coherent") else "random index triples (no vertex reuse)",
                 "note": "e2e and cpu_baseline cover the frame stage only"}
         if world == 1:
             line["cpu_baseline"] = cpu_baseline(wl, steps=3, warmup=1, threads=os.cpu_count() or 1)

@@ -59,13 +59,12 @@ __device__ __forceinline__ float4 glsl_mul_w1(const Mat4& a, float x, float y, f
     return r;
 }
 
-// generate_work.comp:139-155.  true = culled.  q0..q2 point at the three vec3 positions.
+// generate_work.comp:139-155.  true = culled.  v[k] = the k-th vertex position.
 template <typename PV>
-__device__ __forceinline__ bool tri_culled(const Mat4& model, const PV& pv, const float* __restrict__ q0,
-                                           const float* __restrict__ q1, const float* __restrict__ q2) {
-    const float4 c0 = glsl_mul(pv, glsl_mul_w1(model, __ldg(q0), __ldg(q0 + 1), __ldg(q0 + 2)));
-    const float4 c1 = glsl_mul(pv, glsl_mul_w1(model, __ldg(q1), __ldg(q1 + 1), __ldg(q1 + 2)));
-    const float4 c2 = glsl_mul(pv, glsl_mul_w1(model, __ldg(q2), __ldg(q2 + 1), __ldg(q2 + 2)));
+__device__ __forceinline__ bool tri_culled(const Mat4& model, const PV& pv, const float (&v)[3][3]) {
+    const float4 c0 = glsl_mul(pv, glsl_mul_w1(model, v[0][0], v[0][1], v[0][2]));
+    const float4 c1 = glsl_mul(pv, glsl_mul_w1(model, v[1][0], v[1][1], v[1][2]));
+    const float4 c2 = glsl_mul(pv, glsl_mul_w1(model, v[2][0], v[2][1], v[2][2]));
     // determinant(mat3(c0.xyw, c1.xyw, c2.xyw)) > 0: cofactors along the first row of columns
     const float t0 = __fsub_rn(__fmul_rn(c1.y, c2.w), __fmul_rn(c2.y, c1.w));
     const float t1 = __fsub_rn(__fmul_rn(c0.y, c2.w), __fmul_rn(c2.y, c0.w));
@@ -108,33 +107,46 @@ __global__ void __launch_bounds__(kTriThreads) tri_cull(const __grid_constant__ 
             }
         }
         __syncthreads();  // everyone has read s_cmd
+        // Range checks once per command, not per triangle: the command's index range must lie inside the
+        // index buffer, and an index is in range iff it is below v_limit (32-bit compare).
+        uint32_t n_steps_tri = n_tri;
+        if (3ull * (src + n_tri) > a.n_indices || vertex_offset < 0 || (uint64_t)vertex_offset >= a.n_vertices) {
+            if (tid == 0) atomicOr(a.error_flag, 2u);
+            n_steps_tri = 0;
+        }
+        const uint64_t room = a.n_vertices - (uint64_t)(vertex_offset < 0 ? 0 : vertex_offset);
+        const uint32_t v_limit = room > 0xffffffffull ? 0xffffffffu : (uint32_t)room;
+        const uint32_t* __restrict__ ib = a.indices + 3ull * src;
+        const float* __restrict__ vb = a.positions + 3ll * vertex_offset;
         uint32_t running = 0, step = 0;
-        for (uint32_t t0 = 0; t0 < n_tri; t0 += kTriThreads * kTriItems, ++step) {
+        for (uint32_t t0 = 0; t0 < n_steps_tri; t0 += kTriThreads * kTriItems, ++step) {
             bool keep[kTriItems];
             uint32_t ix[kTriItems][3], b[kTriItems];
+            float v[kTriItems][3][3];
+            // all loads of the step first (index triples, then the nine position words per triangle), then the math
 #pragma unroll
             for (int j = 0; j < kTriItems; ++j) {  // item-major: triangle t0 + j * 128 + tid (coalesced index loads)
                 const uint32_t t = t0 + j * kTriThreads + tid;
-                keep[j] = false;
-                ix[j][0] = ix[j][1] = ix[j][2] = 0;
-                if (t < n_tri) {
-                    const uint64_t at = 3ull * (src + t);
-                    if (at + 2 < a.n_indices) {
-                        ix[j][0] = __ldg(a.indices + at);
-                        ix[j][1] = __ldg(a.indices + at + 1);
-                        ix[j][2] = __ldg(a.indices + at + 2);
-                        const uint64_t v0 = (uint64_t)((int64_t)vertex_offset + ix[j][0]), v1 = (uint64_t)((int64_t)vertex_offset + ix[j][1]),
-                                       v2 = (uint64_t)((int64_t)vertex_offset + ix[j][2]);
-                        if (v0 < a.n_vertices && v1 < a.n_vertices && v2 < a.n_vertices) {
-                            keep[j] = !tri_culled(model, a.pv, a.positions + 3 * v0, a.positions + 3 * v1, a.positions + 3 * v2);
-                        } else {
-                            atomicOr(a.error_flag, 2u);
-                        }
-                    } else {
-                        atomicOr(a.error_flag, 2u);
-                    }
+                const bool act = t < n_tri;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) ix[j][k] = act ? __ldg(ib + 3u * t + k) : 0u;
+                keep[j] = act;
+            }
+#pragma unroll
+            for (int j = 0; j < kTriItems; ++j) {
+                const bool ok = ix[j][0] < v_limit && ix[j][1] < v_limit && ix[j][2] < v_limit;
+                if (keep[j] && !ok) atomicOr(a.error_flag, 2u);
+                keep[j] = keep[j] && ok;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const float* q = vb + 3ull * (keep[j] ? ix[j][k] : 0u);  // a safe address for inactive lanes
+                    v[j][k][0] = __ldg(q);
+                    v[j][k][1] = __ldg(q + 1);
+                    v[j][k][2] = __ldg(q + 2);
                 }
             }
+#pragma unroll
+            for (int j = 0; j < kTriItems; ++j) keep[j] = keep[j] && !tri_culled(model, a.pv, v[j]);
             // per-warp kept counts, double-buffered by step parity: one barrier per step is enough
             uint32_t (*sw)[kTriThreads / 32] = s_warp[step & 1u];
 #pragma unroll

@@ -90,11 +90,16 @@ def synth_mesh_table(n_meshes: int = N_MESHES, seed: int = SEED) -> np.ndarray:
     return t
 
 
-def synth_geometry(meshes: np.ndarray, seed: int = SEED, last_vertices: int = 4096):
+def synth_geometry(meshes: np.ndarray, seed: int = SEED, last_vertices: int = 4096, coherent: bool = False):
     """Consolidated position / index buffers for a synthetic mesh table: mesh m owns vertices
-    [vertex_offset[m], vertex_offset[m+1]) placed uniformly inside its AABB, and every LOD's
-    index range [first_index, first_index + index_len) holds random triangles over them
-    (indices relative to vertex_offset, as generate_work.comp:122 adds it back)."""
+    [vertex_offset[m], vertex_offset[m+1]) inside its AABB, and every LOD's index range
+    [first_index, first_index + index_len) holds triangles over them (indices relative to
+    vertex_offset, as generate_work.comp:122 adds it back).
+    coherent=False: uniformly random positions and random index triples -- no vertex reuse between
+    neighbouring triangles, the worst case for the position gathers.
+    coherent=True: a jittered W x H grid sheet folded through the AABB, triangles in row-major cell order
+    (two per cell, alternating winding by row, wrapped to fill index_len) -- consecutive triangles share
+    vertices the way an indexed, cache-optimised glTF mesh does."""
     rng = np.random.Generator(np.random.PCG64(seed ^ 0x9E3779B9))
     voff = meshes["vertex_offset"].astype(np.int64)
     n_vert = np.append(voff[1:], voff[-1] + last_vertices) - voff
@@ -104,10 +109,33 @@ def synth_geometry(meshes: np.ndarray, seed: int = SEED, last_vertices: int = 40
     for m, mesh in enumerate(meshes):
         lo, hi = mesh["aabb_min"].astype(np.float64), mesh["aabb_max"].astype(np.float64)
         nv = int(n_vert[m])
-        positions[voff[m] : voff[m] + nv] = (lo + rng.random((nv, 3)) * (hi - lo)).astype(np.float32)
+        if not coherent:
+            positions[voff[m] : voff[m] + nv] = (lo + rng.random((nv, 3)) * (hi - lo)).astype(np.float32)
+            for l in range(int(mesh["n_lods"])):
+                first, length = int(mesh["lod"][l][0]), int(mesh["lod"][l][1])
+                indices[first : first + length] = rng.integers(0, nv, length, dtype=np.uint32)
+            continue
+        w = max(2, int(np.sqrt(nv)))
+        h = max(2, nv // w)
+        u, v = np.meshgrid(np.linspace(0.0, 1.0, w), np.linspace(0.0, 1.0, h))
+        u = np.clip(u + (rng.random(u.shape) - 0.5) * 0.3 / w, 0.0, 1.0)
+        v = np.clip(v + (rng.random(v.shape) - 0.5) * 0.3 / h, 0.0, 1.0)
+        z = 0.5 + 0.5 * np.sin(6.0 * u + m) * np.cos(5.0 * v)
+        grid = np.stack([u.ravel(), v.ravel(), z.ravel()], axis=1)
+        pts = np.empty((nv, 3))
+        pts[: w * h] = grid
+        pts[w * h :] = grid[: nv - w * h]  # vertices the grid does not use repeat its first ones
+        positions[voff[m] : voff[m] + nv] = (lo + pts * (hi - lo)).astype(np.float32)
+        a = (np.arange(h - 1)[:, None] * w + np.arange(w - 1)[None, :])
+        flip = (np.arange(h - 1)[:, None] % 2 == 1)  # alternate the winding by row: both facings occur
+        t0 = np.where(flip[..., None], np.stack([a, a + w, a + 1], -1), np.stack([a, a + 1, a + w], -1))
+        t1 = np.where(flip[..., None], np.stack([a + 1, a + w, a + w + 1], -1), np.stack([a + 1, a + w + 1, a + w], -1))
+        cells = np.stack([t0, t1], axis=2).reshape(-1, 3).astype(np.uint32)  # row-major cells, two triangles each
         for l in range(int(mesh["n_lods"])):
             first, length = int(mesh["lod"][l][0]), int(mesh["lod"][l][1])
-            indices[first : first + length] = rng.integers(0, nv, length, dtype=np.uint32)
+            stride = 1 << l  # coarser LODs skip cells
+            tri = cells[(np.arange(length // 3) * stride) % len(cells)]
+            indices[first : first + length] = tri.reshape(-1)[:length]
     return positions, indices
 
 

@@ -103,3 +103,10 @@ def test_tri_cull_on_gltf_geometry():
     g = gltf.load_gltf(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "grid.gltf"), synthetic_lod1=True)
     count, kept, total, visible = run_tri(3_000, 14.0, geometry=(g.meshes, g.positions, g.indices))
     assert visible > 100 and 0 < kept < total
+
+
+def test_tri_cull_coherent_grid_meshes():
+    """The bench's mesh flavour: grid sheets with shared vertices and both windings."""
+    pos, idx = scene.synth_geometry(MESHES, coherent=True)
+    count, kept, total, visible = run_tri(20_000, 40.0, geometry=(MESHES, pos, idx))
+    assert 0 < kept < total
