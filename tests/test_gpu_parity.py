@@ -397,7 +397,7 @@ def test_per_mesh_instanced_mode_synthetic(n):
 
 
 def test_config4_sponza_instanced_per_mesh():
-    """BASELINE configs[3] (reduced to 300 k entities so the oracle stays fast; bench.py has 4 M)."""
+    """BASELINE configs[3] (reduced to 300 k entities so the oracle stays fast; a parity case, not a bench line)."""
     table, node_scale = scene.sponza_mesh_table()
     assert len(table) == 87
     ps, rot, mesh = scene.sponza_instances(300_000, len(table), node_scale)
