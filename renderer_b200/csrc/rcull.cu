@@ -11,7 +11,6 @@
 #include <cstring>
 #include <vector>
 
-#include <cub/device/device_radix_sort.cuh>  // per-mesh mode only: stable bucketing of the survivor pairs
 
 #include "rcull_aux.cuh"
 #include "rcull_frame.cuh"
@@ -75,9 +74,10 @@ struct rcull_ctx {
     uint32_t* mesh_len1 = nullptr;
     uint32_t n_meshes = 0;
     uint32_t len_small = 0;
-    uint32_t* keys_sorted = nullptr;  // per-mesh mode scratch
-    void* sort_tmp = nullptr;
-    size_t sort_tmp_bytes = 0;
+    uint32_t* bucket_hist = nullptr;  // per-mesh mode scratch: [tiles][slots] counts, see rcull_aux.cuh
+    uint32_t* slot_total = nullptr;
+    uint32_t* slot_base = nullptr;
+    size_t bucket_hist_words = 0;
     uint64_t cap_cmds = 0;  // command capacity per view: cap_vis, or max_meshes * 6 in per-mesh mode
     int reserved_sms = 0;  // SMs the frame kernel leaves to the exchange kernel of an attached merge (world > 1)
     unsigned long long* meta_out = nullptr;  // set by rcull_merge_create: the frame kernel writes the exchange words itself
@@ -277,16 +277,21 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
     TRY(dev_alloc(c, &c->status, max_tiles * cfg->max_views));
     TRY(dev_alloc(c, &c->ticket, 2));
     if (cfg->output_mode == RCULL_PER_MESH_INSTANCED) {
-        if (c->cap_vis > 0x7fffffffull) {
+        if (c->cap_vis > 0xffffffffull) {
             rcull_destroy(c);
-            return fail(RCULL_ERR_INVALID, "per-mesh mode sorts at most 2^31-1 survivors per view");
+            return fail(RCULL_ERR_INVALID, "per-mesh mode buckets at most 2^32-1 survivors per view");
         }
-        TRY(dev_alloc(c, &c->keys_sorted, c->cap_vis));
-        cub::DeviceRadixSort::SortPairs(nullptr, c->sort_tmp_bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr,
-                                        (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)c->cap_vis, 0, 32);
-        unsigned char* tmp = nullptr;
-        TRY(dev_alloc(c, &tmp, c->sort_tmp_bytes));
-        c->sort_tmp = tmp;
+        // histogram scratch: one row of slot counts per tile of pairs, capped at 128 MB over all
+        // views (the kernels lengthen the tiles to fit, rcull_aux.cuh bucket_view)
+        const size_t slots_max = (size_t)cfg->max_meshes * kMaxLods;
+        const size_t rows = (c->cap_vis + 1023) / 1024;
+        c->bucket_hist_words = rows * slots_max < (16u << 20) ? rows * slots_max : (16u << 20);
+        c->bucket_hist_words *= cfg->max_views;  // every view has its own rows
+        if (c->bucket_hist_words > (32u << 20)) c->bucket_hist_words = 32u << 20;
+        if (c->bucket_hist_words < slots_max * cfg->max_views) c->bucket_hist_words = slots_max * cfg->max_views;
+        TRY(dev_alloc(c, &c->bucket_hist, c->bucket_hist_words));
+        TRY(dev_alloc(c, &c->slot_total, slots_max * cfg->max_views));
+        TRY(dev_alloc(c, &c->slot_base, slots_max * cfg->max_views));
     }
     if (cfg->capacity_tri_indices) {
         if (cfg->output_mode != RCULL_PER_ENTITY) {
@@ -478,14 +483,6 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     a.cam[1] = cam_pos[1];
     a.cam[2] = cam_pos[2];
     a.lod_d2_max = c->lod_d2_max;
-    if (per_mesh) {
-        const uint64_t n_sorted = n < c->cap_vis ? n : c->cap_vis;
-        for (uint32_t v = 0; v < n_views; ++v) {
-            fill_u32<<<c->sm_count * 2, 256, 0, s>>>(o.keys[v], (size_t)n_sorted, c->n_meshes * kMaxLods);
-            CU(cudaGetLastError());
-            c->launches += 1;
-        }
-    }
     const bool mat = c->cfg.materialize_aabb || c->cfg.materialize_flags;
     int grid = (c->sm_count - c->reserved_sms) * c->blocks_per_sm[n_views][mat];
     if ((uint32_t)grid > n_tiles) grid = (int)n_tiles;
@@ -504,33 +501,38 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     c->ticket_base += n_tiles + (uint32_t)grid;  // every CTA draws exactly one ticket past the end
     c->launches += 1;
     if (per_mesh) {
-        // Stable bucketing by (mesh, lod) slot: radix sort of the (slot, draw_index) pairs on the
-        // key bits only (CUB), then one command per non-empty slot.  Pairs past the survivor
-        // count carry the padding key n_slots (filled below, before the frame kernel ran... the
-        // fill is ordered on the same stream ahead of the launch above).
+        // Stable bucketing by (mesh, lod) slot: counting sort over tiles of the survivor pairs
+        // (rcull_aux.cuh), then one command per non-empty slot.
         const uint32_t n_slots = c->n_meshes * kMaxLods;
-        int end_bit = 1;
-        while ((1u << end_bit) <= n_slots) ++end_bit;
-        const uint64_t n_sorted = n < c->cap_vis ? n : c->cap_vis;
+        const uint64_t n_pairs = n < c->cap_vis ? n : c->cap_vis;
         BucketArgs b;
         memset(&b, 0, sizeof b);
         for (uint32_t v = 0; v < n_views; ++v) {
-            size_t bytes = c->sort_tmp_bytes;
-            CU(cub::DeviceRadixSort::SortPairs(c->sort_tmp, bytes, (const uint32_t*)o.keys[v], c->keys_sorted,
-                                               (const uint32_t*)o.vis_tmp[v], o.visible[v], (int)n_sorted, 0, end_bit, s));
-            // the sorted keys of this view are consumed before the next view's sort reuses keys_sorted
-            BucketArgs one = b;
-            one.keys[0] = c->keys_sorted;
-            one.cmds[0] = o.cmds[v];
-            one.counts = o.counts + v;
-            one.totals = o.totals + v;
-            one.lod_tab = c->lod_tab;
-            one.n_slots = n_slots;
-            one.n_sorted = (uint32_t)n_sorted;
-            mesh_buckets<<<1, 1024, 0, s>>>(one);
-            CU(cudaGetLastError());
-            c->launches += 1;
+            b.keys[v] = o.keys[v];
+            b.draw_ix[v] = o.vis_tmp[v];
+            b.visible[v] = o.visible[v];
+            b.cmds[v] = o.cmds[v];
         }
+        b.counts = o.counts;
+        b.totals = o.totals;
+        b.hist = c->bucket_hist;
+        b.slot_total = c->slot_total;
+        b.slot_base = c->slot_base;
+        b.lod_tab = c->lod_tab;
+        b.n_slots = n_slots;
+        b.cap = (uint32_t)n_pairs;
+        const uint64_t rows_max = c->bucket_hist_words / ((uint64_t)n_slots * n_views);
+        b.rows_max = (uint32_t)(rows_max < 0xffffffffull ? rows_max : 0xffffffffull);
+        uint32_t sweep_ctas = (uint32_t)c->sm_count * 7 / n_views;  // 32 KB of counters per CTA: seven CTAs per SM
+        if (sweep_ctas == 0) sweep_ctas = 1;
+        b.rows_target = sweep_ctas * kBucketWarps;
+        const dim3 sweep_grid(sweep_ctas, n_views);
+        bucket_hist<<<sweep_grid, kBucketWarps * 32, 0, s>>>(b);
+        bucket_colscan<<<dim3((n_slots + 31) / 32, n_views), 1024, 0, s>>>(b);
+        bucket_cmds<<<dim3(1, n_views), 1024, 0, s>>>(b);
+        bucket_scatter<<<sweep_grid, kBucketWarps * 32, 0, s>>>(b);
+        CU(cudaGetLastError());
+        c->launches += 4;
     }
     return RCULL_OK;
 }

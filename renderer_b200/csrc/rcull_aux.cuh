@@ -265,50 +265,175 @@ __global__ void merge_wait(const MergeSync* mine, uint32_t world, unsigned long 
 // ---- per-mesh instanced emission (BASELINE config 4; compact_draw_stream.comp:41 keep-rule on
 // instanceCount) ----------------------------------------------------------------------
 // The frame kernel leaves, per view, the survivors in draw_index order as (slot key,
-// draw_index) pairs; a stable radix sort by key buckets them; this kernel turns the sorted
-// keys into one command per NON-EMPTY (mesh, lod) slot, in slot order.
+// draw_index) pairs.  A stable counting sort buckets them by slot:
+//   bucket_hist     one warp per tile of `tile_len` pairs: per-slot counts -> hist[tile][slot]
+//   bucket_colscan  per slot, exclusive scan down the tiles (in place) + slot totals
+//   bucket_cmds     exclusive scan over the slot totals -> bucket starts, one command per
+//                   NON-EMPTY (mesh, lod) slot in slot order
+//   bucket_scatter  same tiling as bucket_hist: rank of each pair inside its slot =
+//                   bucket start + tile offset + arrivals before it in the tile (stable)
+// Slot counters live in shared memory, kBucketChunk slots per warp at a time; tables with more
+// slots take one sweep of the tile per chunk.  The survivor count is read on the device.
+constexpr uint32_t kBucketChunk = 2048;
+constexpr uint32_t kBucketWarps = 4;
+
 struct BucketArgs {
-    const uint32_t* keys[8];   // sorted slot keys per view (padding key = n_slots)
-    uint32_t* cmds[8];         // out: 5 words per command
-    uint32_t* counts;          // in: survivors per view; out: commands per view
-    unsigned long long* totals;  // out: instances per view
-    const uint4* lod_tab;      // index_len, first_index, vertex_offset
-    uint32_t n_slots, n_sorted;  // n_sorted: number of pairs that went through the sort
+    const uint32_t* keys[8];    // per view: slot key per survivor, draw order
+    const uint32_t* draw_ix[8]; // per view: draw_index per survivor, draw order
+    uint32_t* visible[8];       // out: draw indices grouped by slot
+    uint32_t* cmds[8];          // out: 5 words per command
+    uint32_t* counts;           // [view] in: survivors; out (bucket_cmds): commands
+    unsigned long long* totals; // [view] out (bucket_cmds): instances
+    uint32_t* hist;             // [view][rows_max][n_slots]
+    uint32_t* slot_total;       // [view][n_slots]
+    uint32_t* slot_base;        // [view][n_slots]
+    const uint4* lod_tab;       // index_len, first_index, vertex_offset
+    uint32_t n_slots, cap;      // cap: pairs the lists can hold
+    uint32_t rows_max;          // histogram rows available per view
+    uint32_t rows_target;       // tiles wanted: about two per resident warp
 };
 
-__device__ __forceinline__ uint32_t lower_bound_u32(const uint32_t* __restrict__ a, uint32_t n, uint32_t key) {
-    uint32_t lo = 0, hi = n;
-    while (lo < hi) {
-        const uint32_t mid = (lo + hi) >> 1;
-        if (__ldg(a + mid) < key) lo = mid + 1; else hi = mid;
-    }
-    return lo;
+// The view this CTA works on, its survivor count and the tile length all sweeps agree on:
+// as many tiles as there are warps to run them, never more rows than the histogram holds.
+struct BucketView {
+    uint32_t view, n_surv, tile_len, n_tiles;
+    uint32_t* hist;
+};
+__device__ __forceinline__ BucketView bucket_view(const BucketArgs& a, bool after_cmds) {
+    BucketView b;
+    b.view = blockIdx.y;
+    const uint32_t n = after_cmds ? (uint32_t)a.totals[b.view] : a.counts[b.view];
+    b.n_surv = n < a.cap ? n : a.cap;
+    const uint32_t rows = a.rows_target < a.rows_max ? a.rows_target : a.rows_max;
+    const uint32_t len = ((b.n_surv + rows - 1) / rows + 31u) & ~31u;
+    b.tile_len = len < 128u ? 128u : len;
+    b.n_tiles = (b.n_surv + b.tile_len - 1) / b.tile_len;
+    b.hist = a.hist + (size_t)b.view * a.rows_max * a.n_slots;
+    return b;
 }
 
-__global__ void __launch_bounds__(1024) mesh_buckets(const __grid_constant__ BucketArgs a) {
-    __shared__ uint32_t warp_tot[32];
-    __shared__ uint32_t run_base;
-    const uint32_t view = blockIdx.x, tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    const uint32_t* keys = a.keys[view];
-    uint32_t n_surv = a.counts[view];
-    if (n_surv > a.n_sorted) n_surv = a.n_sorted;
-    if (tid == 0) run_base = 0;
+template <bool kScatter>
+__device__ __forceinline__ void bucket_sweep(const BucketArgs& a) {
+    __shared__ uint32_t s_cnt[kBucketWarps][kBucketChunk];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    uint32_t* cnt = s_cnt[warp];
+    const BucketView bv = bucket_view(a, kScatter);
+    const uint32_t* __restrict__ keys = a.keys[bv.view];
+    const uint32_t* __restrict__ draw_ix = a.draw_ix[bv.view];
+    uint32_t* __restrict__ visible = a.visible[bv.view];
+    const uint32_t* slot_base = a.slot_base + (size_t)bv.view * a.n_slots;
+    const uint32_t lt = (1u << lane) - 1u;
+    for (uint32_t tile = blockIdx.x * kBucketWarps + warp; tile < bv.n_tiles; tile += gridDim.x * kBucketWarps) {
+        const uint32_t lo = tile * bv.tile_len;
+        const uint32_t hi = min(lo + bv.tile_len, bv.n_surv);
+        uint32_t* row = bv.hist + (size_t)tile * a.n_slots;
+        for (uint32_t c0 = 0; c0 < a.n_slots; c0 += kBucketChunk) {
+            const uint32_t nc = min(kBucketChunk, a.n_slots - c0);
+            for (uint32_t j = lane; j < nc; j += 32)
+                cnt[j] = kScatter ? row[c0 + j] + slot_base[c0 + j] : 0u;
+            __syncwarp();
+            // four steps of 32 pairs at a time: their loads are issued together
+            for (uint32_t i0 = lo; i0 < hi; i0 += 128) {
+                uint32_t key[4], dix[4];
+#pragma unroll
+                for (uint32_t u = 0; u < 4; ++u) {
+                    const uint32_t i = i0 + u * 32 + lane;
+                    key[u] = i < hi ? __ldg(keys + i) - c0 : 0xffffffffu;
+                    if (kScatter) dix[u] = i < hi ? __ldg(draw_ix + i) : 0u;
+                }
+#pragma unroll
+                for (uint32_t u = 0; u < 4; ++u) {
+                    const bool in = key[u] < nc;
+                    const uint32_t peers = __match_any_sync(kFullMask, key[u]);
+                    const uint32_t leader = __ffs(peers) - 1;
+                    uint32_t old = 0;
+                    if (in && lane == leader) {
+                        old = cnt[key[u]];
+                        cnt[key[u]] = old + __popc(peers);
+                    }
+                    if (kScatter) {
+                        old = __shfl_sync(kFullMask, old, leader);
+                        if (in) visible[old + __popc(peers & lt)] = dix[u];
+                    }
+                    __syncwarp();
+                }
+            }
+            if (!kScatter)
+                for (uint32_t j = lane; j < nc; j += 32) row[c0 + j] = cnt[j];
+            __syncwarp();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kBucketWarps * 32) bucket_hist(const __grid_constant__ BucketArgs a) {
+    bucket_sweep<false>(a);
+}
+__global__ void __launch_bounds__(kBucketWarps * 32) bucket_scatter(const __grid_constant__ BucketArgs a) {
+    bucket_sweep<true>(a);
+}
+
+// CTA = 32 slots (x) by 32 runs of tiles (y): every thread sums its run of tiles for one slot,
+// the runs are scanned through shared memory, and a second walk writes the exclusive offsets.
+__global__ void __launch_bounds__(1024) bucket_colscan(const __grid_constant__ BucketArgs a) {
+    __shared__ uint32_t s_run[32][33];
+    const uint32_t x = threadIdx.x & 31u, y = threadIdx.x >> 5;
+    const uint32_t slot = blockIdx.x * 32 + x;
+    const BucketView bv = bucket_view(a, false);
+    const uint32_t n_tiles = bv.n_tiles;
+    const uint32_t per_run = (n_tiles + 31) / 32;
+    const uint32_t t0 = min(y * per_run, n_tiles), t1 = min(t0 + per_run, n_tiles);
+    uint32_t sum = 0;
+    if (slot < a.n_slots)
+        for (uint32_t t = t0; t < t1; ++t) sum += bv.hist[(size_t)t * a.n_slots + slot];
+    s_run[y][x] = sum;
+    __syncthreads();
+    uint32_t before = 0;
+    for (uint32_t r = 0; r < y; ++r) before += s_run[r][x];
+    if (slot < a.n_slots) {
+        for (uint32_t t = t0; t < t1; ++t) {
+            uint32_t* h = bv.hist + (size_t)t * a.n_slots + slot;
+            const uint32_t c = *h;
+            *h = before;
+            before += c;
+        }
+        if (y == 31) a.slot_total[(size_t)bv.view * a.n_slots + slot] = before;
+    }
+}
+
+__global__ void __launch_bounds__(1024) bucket_cmds(const __grid_constant__ BucketArgs a) {
+    __shared__ uint32_t warp_cmds[32], warp_inst[32];
+    __shared__ uint32_t run_cmds, run_inst;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const BucketView bv = bucket_view(a, false);
+    const uint32_t* slot_total = a.slot_total + (size_t)bv.view * a.n_slots;
+    uint32_t* slot_base = a.slot_base + (size_t)bv.view * a.n_slots;
+    if (tid == 0) run_cmds = run_inst = 0;
     __syncthreads();
     for (uint32_t s0 = 0; s0 < a.n_slots; s0 += blockDim.x) {
         const uint32_t s = s0 + tid;
-        uint32_t first = 0, cnt = 0;
-        if (s < a.n_slots) {
-            first = lower_bound_u32(keys, n_surv, s);
-            cnt = lower_bound_u32(keys, n_surv, s + 1) - first;
-        }
+        const uint32_t cnt = s < a.n_slots ? slot_total[s] : 0u;
         const uint32_t b = __ballot_sync(kFullMask, cnt > 0);
-        if (lane == 0) warp_tot[warp] = __popc(b);
+        uint32_t incl = cnt;  // inclusive scan of the instance counts across the warp
+#pragma unroll
+        for (uint32_t d = 1; d < 32; d <<= 1) {
+            const uint32_t up = __shfl_up_sync(kFullMask, incl, d);
+            if (lane >= d) incl += up;
+        }
+        if (lane == 31) {
+            warp_cmds[warp] = __popc(b);
+            warp_inst[warp] = incl;
+        }
         __syncthreads();
-        uint32_t before = run_base;
-        for (uint32_t w = 0; w < warp; ++w) before += warp_tot[w];
+        uint32_t cmds_before = run_cmds, inst_before = run_inst;
+        for (uint32_t w = 0; w < warp; ++w) {
+            cmds_before += warp_cmds[w];
+            inst_before += warp_inst[w];
+        }
+        const uint32_t first = inst_before + incl - cnt;
+        if (s < a.n_slots) slot_base[s] = first;
         if (cnt > 0) {
             const uint4 L = __ldg(a.lod_tab + s);
-            uint32_t* c = a.cmds[view] + (size_t)(before + __popc(b & ((1u << lane) - 1u))) * 5;
+            uint32_t* c = a.cmds[bv.view] + (size_t)(cmds_before + __popc(b & ((1u << lane) - 1u))) * 5;
             c[0] = L.x;    // indexCount
             c[1] = cnt;    // instanceCount
             c[2] = L.y;    // firstIndex: the LOD's own first_index
@@ -317,21 +442,20 @@ __global__ void __launch_bounds__(1024) mesh_buckets(const __grid_constant__ Buc
         }
         __syncthreads();
         if (tid == 0) {
-            uint32_t t = run_base;
-            for (uint32_t w = 0; w < (blockDim.x >> 5); ++w) t += warp_tot[w];
-            run_base = t;
+            uint32_t tc = run_cmds, ti = run_inst;
+            for (uint32_t w = 0; w < (blockDim.x >> 5); ++w) {
+                tc += warp_cmds[w];
+                ti += warp_inst[w];
+            }
+            run_cmds = tc;
+            run_inst = ti;
         }
         __syncthreads();
     }
     if (tid == 0) {
-        a.counts[view] = run_base;
-        a.totals[view] = n_surv;
+        a.counts[bv.view] = run_cmds;
+        a.totals[bv.view] = bv.n_surv;
     }
-}
-
-__global__ void __launch_bounds__(256) fill_u32(uint32_t* __restrict__ p, size_t n, uint32_t v) {
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) p[i] = v;
 }
 
 // ---- synthetic scene (twin of renderer_b200/scene.py and oracle_synth_entities) ----

@@ -405,6 +405,21 @@ def test_config4_sponza_instanced_per_mesh():
     assert 0 < counts[0] <= len(table) * 2
 
 
+def test_per_mesh_many_slots_take_several_counter_sweeps():
+    """1000 meshes = 6000 (mesh, lod) slots: three shared-memory counter chunks per tile (rcull_aux.cuh bucket_sweep)."""
+    table = scene.synth_mesh_table(1000)
+    ps, rot, mesh = scene.synth_entities(scene.SEED + 5, 0, 200_000, 25.0, len(table))
+    counts = _per_mesh_compare(ps, rot, mesh, table, scene.scene_views(2), 2, base=3)
+    assert counts[0] > 2048 / 6  # commands spread over more than one chunk of slots
+
+
+def test_per_mesh_histogram_cap_lengthens_tiles():
+    """4096 meshes x 1 Mi pairs would need 24 M histogram words: the 64 MB cap makes tiles longer than 1024 pairs."""
+    table = scene.synth_mesh_table(4096)
+    ps, rot, mesh = scene.synth_entities(scene.SEED + 6, 0, 1 << 20, 12.0, len(table))
+    _per_mesh_compare(ps, rot, mesh, table, scene.scene_views(1), 1)
+
+
 def test_as_instance_records_match_oracle():
     """F4 (acceleration_strucures.rs:419-449): byte-exact VkAccelerationStructureInstanceKHR records."""
     n, base = 70_001, 123_456
