@@ -370,6 +370,8 @@ def gpu_arm(args, wl):
                 "note": "e2e and cpu_baseline cover the frame stage only"}
         if world == 1:
             line["cpu_baseline"] = cpu_baseline(wl, steps=3, warmup=1, threads=os.cpu_count() or 1)
+        if world == 1 and not args.no_also:
+            line["also"] = [resident_timing(w, args.steps, local_rank) for w in ("16m_1view", "16m_5view", "1m_1view") if w != args.workload]
         prof = os.path.join(ROOT, "profiles", "r01_traffic.json")
         if os.path.exists(prof):
             try:
@@ -383,6 +385,46 @@ def gpu_arm(args, wl):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def resident_timing(name, steps, device):
+    """Kernel-resident timing of another workload of the table (no e2e / CPU legs): the same CUDA-event
+    protocol as the main line, reported under "also" so one run shows the 1-view and 5-view rooflines together."""
+    import torch
+
+    from renderer_b200 import CullContext, scene
+
+    wl = WORKLOADS[name]
+    n, n_views = wl["n"], wl["n_views"]
+    meshes = scene.synth_mesh_table()
+    views = scene.scene_views(n_views)
+    dev = torch.device("cuda", device)
+    stream = torch.cuda.Stream(device=dev)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev) if n * 36 < 256e6 else None
+    with CullContext(n, max_views=n_views, max_meshes=len(meshes), device=device) as ctx:
+        ctx.set_mesh_table(meshes)
+        ctx.synth_entities(scene.SEED, 0, n, wl["half_box"], len(meshes), stream=stream.cuda_stream)
+        ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(steps)]
+        with torch.cuda.stream(stream):
+            for _ in range(5):
+                ctx.frame(views, scene.CAMERA_POS, stream=stream.cuda_stream)
+                if flush is not None:
+                    flush.zero_()
+            torch.cuda.synchronize()
+            for i in range(steps):
+                ev[i][0].record(stream)
+                ctx.frame(views, scene.CAMERA_POS, stream=stream.cuda_stream)
+                ev[i][1].record(stream)
+                if flush is not None:
+                    flush.zero_()
+            torch.cuda.synchronize()
+        t = sum(a.elapsed_time(b) for a, b in ev) / steps / 1e3
+        counts, _ = ctx.counts()
+    peak, _ = load_peaks()
+    bpe = 36.0 + 64.0 + 24.0 * float(counts[:n_views].sum()) / n
+    return {"workload": name, "entities": n, "n_views": n_views, "ms_per_step": t * 1e3, "value": n / t, "unit": UNIT,
+            "bytes_per_entity": bpe, "achieved_gbs": n * bpe / t / 1e9, "roofline_frac": n * bpe / t / 1e9 / peak,
+            "l2": "flushed between iterations (256 MB write)" if flush is not None else "inputs (36 B x n) exceed L2"}
 
 
 def reference_arm(args, wl):
@@ -412,6 +454,7 @@ def main():
     ap.add_argument("--merge", default="p2p", choices=["p2p", "nccl"], help="N > 1: peer-store merge kernel or NCCL broadcasts")
     ap.add_argument("--no-overlap", action="store_true", help="N > 1: run frame and merge back to back instead of pipelined")
     ap.add_argument("--workload", default="16m_5view", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-also", action="store_true", help="N = 1: skip the resident timings of the other entity-stage workloads")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     wl = WORKLOADS[args.workload]

@@ -23,6 +23,13 @@ namespace rcull {
 #ifndef RCULL_COMPUTE_WARPS
 #define RCULL_COMPUTE_WARPS 15
 #endif
+#ifndef RCULL_VIEW_UNROLL
+#define RCULL_VIEW_UNROLL 1
+#endif
+#ifndef RCULL_FRAME_REGS
+#define RCULL_FRAME_REGS 112  // 512 x 112 registers leave 8 K of the SM's 64 K for a resident exchange CTA (128 x 64)
+#endif
+constexpr int kViewUnroll = RCULL_VIEW_UNROLL;  // 1: the view loop stays rolled
 constexpr int kComputeWarps = RCULL_COMPUTE_WARPS;  // + 1 scan warp; 7 + 1: two CTAs fill an SM's register file at 112 regs, 15 + 1: one CTA does
 constexpr int kCtasPerSm = kComputeWarps <= 7 ? 2 : 1;
 // 228 KB per SM, 1 KB reserved per CTA; the one-CTA shape leaves a second reserved KB free so that a small
@@ -380,7 +387,7 @@ __device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameS
 // kMat: the optional AABB / CoarseCulled outputs exist (checked per pointer); the
 // hot variant (kMat = false) carries none of that code.
 template <int V, bool kMat>
-__global__ void __maxnreg__(112)
+__global__ void __maxnreg__(RCULL_FRAME_REGS)
     transform_cull_compact(const __grid_constant__ FrameArgs args, const __grid_constant__ CUtensorMap model_map) {
     extern __shared__ unsigned char smem_raw[];
     FrameSmem& sm = frame_smem(smem_raw);
@@ -588,7 +595,7 @@ __global__ void __maxnreg__(112)
         // A3 per view: planes outer, the thread's 4 entities inner
         // (the view loop stays rolled: unrolled, the kernel outgrows the instruction cache)
         uint32_t woff = 0;  // start of view k in the warp's combined list
-#pragma unroll 1
+#pragma unroll kViewUnroll
         for (int k = 0; k < V; ++k) {
             bool outside[kItems];
 #pragma unroll
