@@ -114,7 +114,12 @@ int rcull_set_mesh_table(rcull_ctx *ctx, const rcull_mesh *meshes, uint32_t n);
 /* SoA component columns: pos_scale = (Position.xyz, Scale), rot = Rotation
  * (i,j,k,w), mesh = index into the mesh table; entity slot i IS draw_index i
  * (assign_draw_index, src/ecs.rs:117-136).  Host pointers; async on stream
- * (0 = default stream) when the host memory is pinned. */
+ * (0 = default stream) when the host memory is pinned.
+ * Domain: finite components whose model matrix is finite (zero, negative,
+ * denormal and huge scales, non-unit quaternions are all fine and bit-exact).
+ * A NaN / inf component only changes that entity's own matrix, box and
+ * visibility, and not necessarily the way the reference's generic 4x4
+ * products would (inf * 0 terms, src/ecs.rs:60-62). */
 int rcull_upload_entities(rcull_ctx *ctx, uint64_t first, uint64_t n, const float *pos_scale,
                           const float *rot, const uint32_t *mesh, void *stream);
 /* Device pointers of the input columns, for callers that fill them in place. */
