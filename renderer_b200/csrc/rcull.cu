@@ -498,7 +498,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
         case 8: e = launch<8>(mat, a, o.model_map, grid, s); break;
     }
     if (e != cudaSuccess) return fail(RCULL_ERR_CUDA, "transform_cull_compact launch failed: %s", cudaGetErrorString(e));
-    c->ticket_base += n_tiles + (uint32_t)grid;  // every CTA draws exactly one ticket past the end
+    c->ticket_base += n_tiles;  // n_tiles - grid real tickets (the first tile of a CTA is its block index) + one past the end per CTA
     c->launches += 1;
     if (per_mesh) {
         // Stable bucketing by (mesh, lod) slot: counting sort over tiles of the survivor pairs

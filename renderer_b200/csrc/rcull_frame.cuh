@@ -409,6 +409,29 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
         }
         fence_mbar_init();
     }
+    // Compute warp 0, lane 0 is also the producer: it draws tile tickets and issues the TMA
+    // loads one tile ahead, as soon as the other stage has been read by every compute warp.
+    const bool producer = tid == 0;
+    bool more = true;  // producer only: the last ticket drawn was a real tile
+    auto claim_tile = [&](uint32_t for_it) {
+        const uint32_t stage = for_it & 1u;
+        // the first tile of a CTA is its block index (every CTA of the persistent grid is resident, so
+        // tiles 0 .. grid-1 are all in flight); later ones are drawn from the ticket counter
+        const uint32_t t = for_it == 0 ? blockIdx.x : atomicAdd(args.ticket, 1u) - args.ticket_base + gridDim.x;
+        sm.tile_ring[for_it % kRing] = t;
+        uint64_t* bar = &sm.full[stage];
+        if (t < args.n_tiles) {
+            fence_proxy_async();
+            mbar_expect_tx(bar, kStageBytes);
+            bulk_g2s(sm.pos_scale[stage], args.pos_scale + (size_t)t * kTile, kTile * 16, bar);
+            bulk_g2s(sm.rot[stage], args.rot + (size_t)t * kTile, kTile * 16, bar);
+            bulk_g2s(sm.mesh[stage], args.mesh + (size_t)t * kTile, kTile * 4, bar);
+        } else {
+            mbar_arrive(bar);  // end marker: every warp reads tile_ring and leaves
+            more = false;
+        }
+    };
+    if (producer) claim_tile(0);  // in flight while the CTA copies its tables below
     float4* const sm_planes = reinterpret_cast<float4*>(reinterpret_cast<unsigned char*>(&sm) + sizeof(FrameSmem));
     for (uint32_t i = tid; i < V * 6 * 4; i += kThreads) sm_planes[i] = reinterpret_cast<const float4*>(&args.planes[0][0])[i];
     // Mesh table: a shared-memory copy when it fits (the L1 left beside ~220 KB of shared memory
@@ -442,27 +465,6 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
     const uint32_t moff3 = mrow * 128u + (((mhalf + 3u) ^ (mrow & 7u)) << 4);
     const uint32_t e0 = warp * kWarpSpan + lane;  // slot in tile of item 0; item j adds 32*j
 
-    // Compute warp 0, lane 0 is also the producer: it draws tile tickets and issues the TMA
-    // loads one tile ahead, as soon as the other stage has been read by every compute warp.
-    const bool producer = tid == 0;
-    bool more = true;  // producer only: the last ticket drawn was a real tile
-    auto claim_tile = [&](uint32_t for_it) {
-        const uint32_t stage = for_it & 1u;
-        const uint32_t t = atomicAdd(args.ticket, 1u) - args.ticket_base;
-        sm.tile_ring[for_it % kRing] = t;
-        uint64_t* bar = &sm.full[stage];
-        if (t < args.n_tiles) {
-            fence_proxy_async();
-            mbar_expect_tx(bar, kStageBytes);
-            bulk_g2s(sm.pos_scale[stage], args.pos_scale + (size_t)t * kTile, kTile * 16, bar);
-            bulk_g2s(sm.rot[stage], args.rot + (size_t)t * kTile, kTile * 16, bar);
-            bulk_g2s(sm.mesh[stage], args.mesh + (size_t)t * kTile, kTile * 4, bar);
-        } else {
-            mbar_arrive(bar);  // end marker: every warp reads tile_ring and leaves
-            more = false;
-        }
-    };
-    if (producer) claim_tile(0);
 
     uint32_t it = 0;
     constexpr uint32_t B = frame_bufs<V>();
