@@ -769,7 +769,7 @@ int rcull_tri_cull(rcull_ctx* c, const float pv[16], uint32_t draw_index_base, u
     t.out_capacity = c->cfg.capacity_tri_indices;
     t.cap_cmds = (uint32_t)(c->cap_cmds > 0xffffffffull ? 0xffffffffull : c->cap_cmds);
     t.draw_index_base = draw_index_base;
-    memcpy(t.pv.m, pv, sizeof t.pv.m);
+    for (int i = 0; i < 16; ++i) t.pv.m[i] = make_float2(pv[i], pv[i]);
     tri_cull<<<c->sm_count * 8, kTriThreads, 0, s>>>(t);
     CU(cudaGetLastError());
     CompactArgs k;

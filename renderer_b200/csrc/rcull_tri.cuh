@@ -21,6 +21,11 @@ constexpr int kCompactTile = kCompactThreads * kCompactItems;
 struct Mat4 {
     float m[16];  // column-major
 };
+// The same matrix with every entry stored twice: the multiplier of a packed (FMUL2) product
+// whose two halves belong to the two triangles a thread handles per step.
+struct Mat4x2 {
+    float2 m[16];
+};
 
 struct TriArgs {
     const uint32_t* cmds;        // view's draw list from the frame kernel, 5 words per command
@@ -35,7 +40,7 @@ struct TriArgs {
     uint32_t* error_flag;
     uint64_t n_vertices, n_indices, out_capacity;
     uint32_t cap_cmds, draw_index_base;
-    Mat4 pv;  // read straight out of the constant bank (kernel parameter): no loads
+    Mat4x2 pv;  // read straight out of the constant bank (kernel parameter): no loads
 };
 
 // GLSL mat4 * vec4: ((c0 * x + c1 * y) + c2 * z) + c3 * w per row, every product and sum rounded.
@@ -79,6 +84,70 @@ __device__ __forceinline__ bool tri_culled(const Mat4& model, const PV& pv, cons
     // the area test of :159-167 is overwritten by `cull = false` (:166): nothing to compute
 }
 
+// ---- two triangles per thread: packed products, scalar sums ------------------------------
+// Every product of the two transforms and of the determinant is an FMUL2 over the pair
+// (triangle j = 0, 1 of the step in the two halves); every sum that consumes a packed product
+// is a scalar FADD, so there is no packed mul + add pair for ptxas to contract into FFMA2
+// (it does that even under --fmad=false; tests/test_abi.py checks the SASS).  The one packed
+// add is sum + matrix entry.  Each half goes through exactly the operations of glsl_mul /
+// glsl_mul_w1 above, in the same order.
+__device__ __forceinline__ float2 sum3(float2 a, float2 b, float2 c) {
+    return make_float2(__fadd_rn(__fadd_rn(a.x, b.x), c.x), __fadd_rn(__fadd_rn(a.y, b.y), c.y));
+}
+__device__ __forceinline__ float2 sub2s(float2 a, float2 b) { return make_float2(__fsub_rn(a.x, b.x), __fsub_rn(a.y, b.y)); }
+// row r of model * vec4(v, 1)
+__device__ __forceinline__ float2 row_w1(const Mat4x2& a, int r, float2 x, float2 y, float2 z) {
+    return add2_rn(sum3(mul2_rn(a.m[r], x), mul2_rn(a.m[4 + r], y), mul2_rn(a.m[8 + r], z)), a.m[12 + r]);
+}
+// row r of pv * v
+__device__ __forceinline__ float2 row_full(const Mat4x2& a, int r, const float2 (&v)[4]) {
+    const float2 s = sum3(mul2_rn(a.m[r], v[0]), mul2_rn(a.m[4 + r], v[1]), mul2_rn(a.m[8 + r], v[2]));
+    const float2 w = mul2_rn(a.m[12 + r], v[3]);
+    return make_float2(__fadd_rn(s.x, w.x), __fadd_rn(s.y, w.y));
+}
+__device__ __forceinline__ bool ndc_culled(float c0x, float c0y, float c0w, float c1x, float c1y, float c1w, float c2x, float c2y, float c2w) {
+    const float x0 = __fdiv_rn(c0x, c0w), y0 = __fdiv_rn(c0y, c0w);
+    const float x1 = __fdiv_rn(c1x, c1w), y1 = __fdiv_rn(c1y, c1w);
+    const float x2 = __fdiv_rn(c2x, c2w), y2 = __fdiv_rn(c2y, c2w);
+    return (x0 < -1.0f && x1 < -1.0f && x2 < -1.0f) || (x0 > 1.0f && x1 > 1.0f && x2 > 1.0f) ||
+           (y0 < -1.0f && y1 < -1.0f && y2 < -1.0f) || (y0 > 1.0f && y1 > 1.0f && y2 > 1.0f);
+}
+// generate_work.comp:139-155 for triangles 0 and 1 of the step; v[j][k] = vertex k of triangle j.
+template <typename PV>
+__device__ __forceinline__ void tri_culled2(const Mat4x2& model, const PV& pv, const float (&v)[2][3][3], bool& culled0, bool& culled1) {
+    float2 cx[3], cy[3], cw[3];  // clip-space x, y, w of vertex k, one triangle per half
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float2 x = make_float2(v[0][k][0], v[1][k][0]), y = make_float2(v[0][k][1], v[1][k][1]),
+                     z = make_float2(v[0][k][2], v[1][k][2]);
+        const float2 w[4] = {row_w1(model, 0, x, y, z), row_w1(model, 1, x, y, z), row_w1(model, 2, x, y, z), row_w1(model, 3, x, y, z)};
+        cx[k] = row_full(pv, 0, w);
+        cy[k] = row_full(pv, 1, w);
+        cw[k] = row_full(pv, 3, w);
+    }
+    // determinant(mat3(c0.xyw, c1.xyw, c2.xyw)) > 0: cofactors along the first row of columns
+    const float2 t0 = sub2s(mul2_rn(cy[1], cw[2]), mul2_rn(cy[2], cw[1]));
+    const float2 t1 = sub2s(mul2_rn(cy[0], cw[2]), mul2_rn(cy[2], cw[0]));
+    const float2 t2 = sub2s(mul2_rn(cy[0], cw[1]), mul2_rn(cy[1], cw[0]));
+    const float2 d0 = mul2_rn(cx[0], t0), d1 = mul2_rn(cx[1], t1), d2 = mul2_rn(cx[2], t2);
+    const float det0 = __fadd_rn(__fsub_rn(d0.x, d1.x), d2.x), det1 = __fadd_rn(__fsub_rn(d0.y, d1.y), d2.y);
+    // The four NDC tests each need ALL three vertices beyond the same side.  A vertex with w > 0,
+    // |x| <= w and |y| <= w has x / w and y / w inside [-1, 1] after rounding too (division rounds
+    // monotonically and +-1 are representable; inf / inf = NaN compares false as well), so one such
+    // vertex decides "not culled" without the six divisions -- the common case for a mesh on screen.
+    bool in0 = false, in1 = false;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        in0 = in0 || (cw[k].x > 0.0f && fabsf(cx[k].x) <= cw[k].x && fabsf(cy[k].x) <= cw[k].x);
+        in1 = in1 || (cw[k].y > 0.0f && fabsf(cx[k].y) <= cw[k].y && fabsf(cy[k].y) <= cw[k].y);
+    }
+    culled0 = det0 > 0.0f;
+    culled1 = det1 > 0.0f;
+    if (!culled0 && !in0) culled0 = ndc_culled(cx[0].x, cy[0].x, cw[0].x, cx[1].x, cy[1].x, cw[1].x, cx[2].x, cy[2].x, cw[2].x);
+    if (!culled1 && !in1) culled1 = ndc_culled(cx[0].y, cy[0].y, cw[0].y, cx[1].y, cy[1].y, cw[1].y, cx[2].y, cy[2].y, cw[2].y);
+    // the area test of :159-167 is overwritten by `cull = false` (:166): nothing to compute
+}
+
 // One CTA per command at a time (ticket order): the command's triangles in steps of 256,
 // ballot compaction with a running base, so the kept triples land in ascending triangle
 // order at out_index_buffer[firstIndex / 3 + rank] (the reference's order inside a mesh is
@@ -97,13 +166,14 @@ __global__ void __launch_bounds__(kTriThreads) tri_cull(const __grid_constant__ 
         const uint32_t n_tri = cmd[0] / 3u, out_first = cmd[2] / 3u, first_instance = cmd[4];
         const int32_t vertex_offset = (int32_t)cmd[3];
         const uint64_t src = a.src_first[c] / 3u;
-        Mat4 model;  // the command's model matrix in registers: one load per command, not per product
+        Mat4x2 model;  // the command's model matrix in registers, every entry twice: one load per command, not per product
         {
             const float4* mp = reinterpret_cast<const float4*>(a.model + (size_t)(first_instance - a.draw_index_base) * 16);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const float4 col = __ldg(mp + i);
-                model.m[4 * i] = col.x; model.m[4 * i + 1] = col.y; model.m[4 * i + 2] = col.z; model.m[4 * i + 3] = col.w;
+                model.m[4 * i] = make_float2(col.x, col.x); model.m[4 * i + 1] = make_float2(col.y, col.y);
+                model.m[4 * i + 2] = make_float2(col.z, col.z); model.m[4 * i + 3] = make_float2(col.w, col.w);
             }
         }
         __syncthreads();  // everyone has read s_cmd
@@ -145,8 +215,13 @@ __global__ void __launch_bounds__(kTriThreads) tri_cull(const __grid_constant__ 
                     v[j][k][2] = __ldg(q + 2);
                 }
             }
-#pragma unroll
-            for (int j = 0; j < kTriItems; ++j) keep[j] = keep[j] && !tri_culled(model, a.pv, v[j]);
+            {
+                static_assert(kTriItems == 2, "tri_culled2 works on the two triangles of a step");
+                bool culled0, culled1;
+                tri_culled2(model, a.pv, v, culled0, culled1);
+                keep[0] = keep[0] && !culled0;
+                keep[1] = keep[1] && !culled1;
+            }
             // per-warp kept counts, double-buffered by step parity: one barrier per step is enough
             uint32_t (*sw)[kTriThreads / 32] = s_warp[step & 1u];
 #pragma unroll

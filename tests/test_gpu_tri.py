@@ -110,3 +110,44 @@ def test_tri_cull_coherent_grid_meshes():
     pos, idx = scene.synth_geometry(MESHES, coherent=True)
     count, kept, total, visible = run_tri(20_000, 40.0, geometry=(MESHES, pos, idx))
     assert 0 < kept < total
+
+
+def test_tri_cull_ndc_boundaries_and_nonpositive_w():
+    """Clip coordinates placed exactly on and one ulp around the NDC limits, with w > 0, tiny, zero and
+    negative: the GPU skips the six divisions when a vertex is provably inside (w > 0, |x| <= w, |y| <= w)
+    and must still agree with the shader arithmetic everywhere.  Identity model, pv = (x, y, z, w = z)."""
+    rng = np.random.default_rng(77)
+    f = np.float32
+    xy = np.array([-2, np.nextafter(f(-1), f(-2)), -1, np.nextafter(f(-1), f(0)), -0.5, 0, 0.5,
+                   np.nextafter(f(1), f(0)), 1, np.nextafter(f(1), f(2)), 2, 1e-30, -1e-30], f)
+    zs = np.array([-1, -1e-30, 0, 1e-30, 0.5, 1, 1, 1, 2], f)
+    n_tri = 6000
+    positions = np.stack([rng.choice(xy, 3 * n_tri), rng.choice(xy, 3 * n_tri), rng.choice(zs, 3 * n_tri)], axis=1).astype(f)
+    indices = np.arange(3 * n_tri, dtype=np.uint32)
+    meshes = np.zeros(1, scene.MESH_DTYPE)
+    meshes[0]["aabb_min"], meshes[0]["aabb_max"], meshes[0]["n_lods"] = (-2, -2, -1), (2, 2, 2), 1
+    meshes[0]["lod"][0] = (0, 3 * n_tri)
+    ps = np.array([[0, 0, 0, 1]], f)
+    rot = np.array([[0, 0, 0, 1]], f)
+    mesh = np.zeros(1, np.uint32)
+    views = np.zeros((1, 6, 4), f)
+    views[..., 3] = -1.0  # s = -1, e = 0: inside every plane
+    pv = np.zeros(16, f)  # column-major: x' = x, y' = y, z' = z, w' = z
+    pv[0] = pv[5] = pv[10] = pv[11] = 1.0
+    cam = scene.CAMERA_POS
+    pos, quat, scale = scene.to_components(ps, rot)
+    ref = O.frame(pos, quat, scale, mesh, meshes, views, cam)
+    assert ref["counts"][0] == 1 and np.array_equal(ref["model"].reshape(4, 4), np.eye(4, dtype=f))
+    src = O.src_first_index(pos, mesh, ref["cmds"][0], meshes, cam)
+    want = O.tri_cull(ref["cmds"][0], src, ref["model"], pv, positions, indices, 3 * n_tri)
+    with CullContext(1, max_views=1, max_meshes=1, capacity_tri_indices=3 * n_tri) as ctx:
+        ctx.set_mesh_table(meshes)
+        ctx.set_geometry(positions, indices)
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(views, cam)
+        ctx.tri_cull(pv)
+        count, kept = ctx.tri_counts()
+        assert (count, kept) == (want["count"], want["kept_indices"])
+        assert 0 < kept < 3 * n_tri
+        assert np.array_equal(ctx.tri_cmds(count), want["cmds"])
+        assert np.array_equal(ctx.tri_indices(0, kept), want["indices"][:kept])
