@@ -1,16 +1,19 @@
 // rcull_frame.cuh -- the fused transform + AABB + multi-view cull + compaction
 // kernel (SURVEY 8a rows A1-A7 in one launch).
 //
-// Shape: persistent, warp-specialised CTAs (grid = SMs x resident CTAs).
-//   * 8 COMPUTE warps: one thread per entity, 4 entities per thread per tile.
+// Shape: persistent, warp-specialised CTAs (grid = SMs x resident CTAs; one CTA of 15 + 1
+// warps per SM in the default build, tile = 1920 entities).
+//   * COMPUTE warps: one thread per entity, 4 entities per thread per tile.
 //     Inputs come out of shared memory (staged there by TMA), model matrices go
 //     back through a swizzled shared-memory box and a 2-D TMA tensor store, the
 //     plane tests run planes-outer / entities-inner so each plane is fetched once
 //     per 4 entities, survivors are ballot-compacted into per-warp lists.
-//   * 1 SCAN warp: draws tile tickets, issues the TMA loads (two stages), and for
-//     every finished tile runs the decoupled look-back (count and index sum per
-//     view in one 16-byte descriptor) and emits the draw commands while the
-//     compute warps are already working on the next tile.
+//     Thread 0 is also the producer: it draws tile tickets and issues the TMA loads
+//     (two stages).  The commands of a tile are emitted by the compute warps a few
+//     tiles later, once its output offsets are known.
+//   * 1 SCAN warp: for every finished tile, the decoupled look-back (count and index
+//     sum per view in one 16-byte descriptor) as a non-blocking state machine, while
+//     the compute warps are already working on the next tiles.
 // Warps synchronise through mbarriers only; there is no CTA-wide barrier in the
 // tile loop.
 #pragma once
@@ -38,7 +41,7 @@ constexpr int kCtasPerSm = kComputeWarps <= 7 ? 2 : 1;
 constexpr size_t kSmemPerCta = (228 * 1024 - (kCtasPerSm == 1 ? 2 : kCtasPerSm) * 1024) / kCtasPerSm;
 constexpr int kThreads = (kComputeWarps + 1) * 32;  // + scan warp
 constexpr int kItems = 4;                           // entities per thread per tile
-constexpr int kTile = kComputeWarps * 32 * kItems;  // 896 entities
+constexpr int kTile = kComputeWarps * 32 * kItems;  // 1920 entities with 15 compute warps
 constexpr int kWarpSpan = 32 * kItems;              // entities owned by one compute warp
 constexpr int kStages = 2;
 constexpr int kMaxBufs = 4;   // survivor bookkeeping ring (tiles whose commands are not emitted yet)
@@ -200,7 +203,7 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
             } else {
                 uint32_t vstart_c = 0, vstart_l = 0;
 #pragma unroll
-                for (int k = 0; k < V; ++k) {  // lanes 0..6 stand for the compute warps
+                for (int k = 0; k < V; ++k) {  // lane w stands for compute warp w
                     const uint32_t c = lane < kComputeWarps ? sm.wcnt[buf][k][lane] : 0u;
                     const uint64_t l = lane < kComputeWarps ? sm.wlen[buf][k][lane] : 0ull;
                     uint32_t ic = c;
