@@ -80,7 +80,10 @@ def test_config1_10k_five_views():
     run_and_compare(10_000, 5, 60.0)
 
 
-@pytest.mark.parametrize("n", [0, 1, 31, 32, 33, 127, 128, 129, 1023, 1024, 1025, 2047, 4097, 5000])
+# around the warp span (128), the tile (1920) and one tile per CTA of the persistent grid (148 x 1920: the
+# first ticket drawn from the counter is tile 148)
+@pytest.mark.parametrize("n", [0, 1, 31, 32, 33, 127, 128, 129, 1023, 1024, 1025, 1919, 1920, 1921, 3841, 5000,
+                               148 * 1920 - 1, 148 * 1920, 148 * 1920 + 1, 149 * 1920 + 7])
 def test_ragged_sizes(n):
     run_and_compare(n, 2, 30.0)
 
