@@ -483,7 +483,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     a.cam[1] = cam_pos[1];
     a.cam[2] = cam_pos[2];
     a.lod_d2_max = c->lod_d2_max;
-    const bool mat = c->cfg.materialize_aabb || c->cfg.materialize_flags;
+    const bool mat = c->cfg.materialize_aabb || c->cfg.materialize_flags || !c->len_small;  // the general variant
     int grid = (c->sm_count - c->reserved_sms) * c->blocks_per_sm[n_views][mat];
     if ((uint32_t)grid > n_tiles) grid = (int)n_tiles;
     cudaError_t e = cudaSuccess;

@@ -387,8 +387,9 @@ __device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameS
 // ---------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------
-// kMat: the optional AABB / CoarseCulled outputs exist (checked per pointer); the
-// hot variant (kMat = false) carries none of that code.
+// kMat: the optional AABB / CoarseCulled outputs may exist (checked per pointer) and index
+// lengths may need 64-bit warp sums (args.len_small == 0); the hot variant (kMat = false)
+// carries none of that code.
 template <int V, bool kMat>
 __global__ void __maxnreg__(RCULL_FRAME_REGS)
     transform_cull_compact(const __grid_constant__ FrameArgs args, const __grid_constant__ CUtensorMap model_map) {
@@ -638,7 +639,7 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
                 if (kMat && args.flags[k] != nullptr && valid[j]) args.flags[k][tile_base + e0 + 32 * j] = outside[j] ? 1 : 0;
                 const uint32_t b = __ballot_sync(kFullMask, vis);
                 sts_u8(vis ? wlist_s + woff + wc + __popc(b & lt) : dummy, entry[j]);
-                if (args.len_small) {
+                if (!kMat || args.len_small) {  // compile-time in the hot variant
                     lo += vis ? len[j] : 0u;
                 } else {
                     lo += vis ? (len[j] & 0xffffu) : 0u;
@@ -647,7 +648,7 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
                 wc += __popc(b);
             }
             uint64_t wl;
-            if (args.len_small) {
+            if (!kMat || args.len_small) {  // compile-time in the hot variant
                 wl = __reduce_add_sync(kFullMask, lo);  // 128 values below 2^25
             } else {
                 lo = __reduce_add_sync(kFullMask, lo);  // 128 x 16-bit pieces: no overflow

@@ -71,6 +71,17 @@ def test_extreme_finite_components():
     run_and_compare(8192, 3, 60.0, entities=_with_special_components(values, 11))
 
 
+def test_index_lengths_beyond_2_pow_25_use_wide_sums():
+    """A mesh table with index_len >= 2^25: the per-warp index sums no longer fit 32 bits (128 x 2^25), the kernel
+    takes its general variant (16-bit halves), firstIndex wraps mod 2^32 as the u32 field does and the index
+    totals stay exact in 64 bits."""
+    meshes = MESHES.copy()
+    meshes["lod"][:, 0, 1] = (np.arange(len(meshes), dtype=np.uint32) + 1) * 3 * 11_200_000  # up to 537.6 M indices
+    meshes["lod"][:, 1, 1] = 3 * 11_184_811  # just above 2^25 for every LOD 1
+    counts, _ = run_and_compare(3000, 2, 20.0, meshes=meshes)
+    assert counts[0] > 0
+
+
 def test_config1_10k_single_camera():
     counts, n = run_and_compare(10_000, 1, 60.0)
     assert 0 < counts[0] < n
