@@ -123,7 +123,6 @@ struct FrameSmem {
     uint64_t agg_len[kMaxBufs][kMaxViews];  // tile aggregates kept between publish and resolve
     uint32_t agg_cnt[kMaxBufs][kMaxViews];
     uint32_t tile_ring[kRing];  // tile id of iteration it at [it % kRing]
-    uint32_t dummy[kComputeWarps];  // where culled lanes 'store' their list entry (keeps the list code branch-free)
     // followed by: PlaneC planes[V][6] (a shared-memory copy: LDS.128 instead of indexed LDC), then
     // uint8_t wlist[bufs][kComputeWarps][V * kWarpSpan] -- per-warp combined survivor list,
     // view-major, entry = lod << 7 | slot in the warp's span (the view follows from the entry's
@@ -595,7 +594,6 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
             emit_next();
         }
         __syncwarp();
-        const uint32_t dummy = smem_u32(&sm.dummy[warp]);
         const uint32_t wlist_s = smem_u32(wlist);
 
         // A3 per view: planes outer, the thread's 4 entities inner
@@ -631,14 +629,14 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
                     outside[2 * i + 1] = outside[2 * i + 1] || (s.y > e1);
                 }
             }
-            // ballot compaction, branch-free: culled lanes store to a dummy byte
+            // ballot compaction, branch-free
             uint32_t wc = 0, lo = 0, hi = 0;
 #pragma unroll
             for (int j = 0; j < kItems; ++j) {
                 const bool vis = !outside[j];
                 if (kMat && args.flags[k] != nullptr && valid[j]) args.flags[k][tile_base + e0 + 32 * j] = outside[j] ? 1 : 0;
                 const uint32_t b = __ballot_sync(kFullMask, vis);
-                sts_u8(vis ? wlist_s + woff + wc + __popc(b & lt) : dummy, entry[j]);
+                if (vis) sts_u8(wlist_s + woff + wc + __popc(b & lt), entry[j]);  // compiles to a predicated STS
                 if (!kMat || args.len_small) {  // compile-time in the hot variant
                     lo += vis ? len[j] : 0u;
                 } else {
