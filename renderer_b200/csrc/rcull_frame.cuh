@@ -507,19 +507,33 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
         float cx[kItems], cy[kItems], cz[kItems], hx[kItems], hy[kItems], hz[kItems];
         uint32_t len[kItems], entry[kItems];
         bool valid[kItems];
+        // Input hygiene off the hot path: only the frame's last tile has padding slots (they
+        // become identity entities that are never visible), and a mesh id outside the table
+        // is an error the whole tile reports once.
+        if (tile_base + kTile > args.n) {  // uniform
+#pragma unroll
+            for (int j = 0; j < kItems; ++j) {
+                if (tile_base + e0 + 32 * j >= args.n) {
+                    ps[j] = make_float4(0.f, 0.f, 0.f, 1.f);
+                    q[j] = make_float4(0.f, 0.f, 0.f, 1.f);
+                    mid[j] = 0;
+                }
+            }
+        }
+        {
+            uint32_t worst = mid[0];
+#pragma unroll
+            for (int j = 1; j < kItems; ++j) worst = max(worst, mid[j]);
+            if (worst >= args.n_meshes) {
+                atomicOr(args.error_flag, 1u);
+#pragma unroll
+                for (int j = 0; j < kItems; ++j) mid[j] = mid[j] >= args.n_meshes ? 0u : mid[j];
+            }
+        }
 #pragma unroll
         for (int j = 0; j < kItems; ++j) {
             const uint32_t g = tile_base + e0 + 32 * j;  // slot in frame
             valid[j] = g < args.n;
-            if (!valid[j]) {
-                ps[j] = make_float4(0.f, 0.f, 0.f, 1.f);
-                q[j] = make_float4(0.f, 0.f, 0.f, 1.f);
-                mid[j] = 0;
-            }
-            if (mid[j] >= args.n_meshes) {
-                atomicOr(args.error_flag, 1u);
-                mid[j] = 0;
-            }
             const Mat34 m = model_matrix(ps[j], q[j]);
 
             // model matrix out: swizzled box in smem -> one 2 KB TMA tensor store per warp and item
