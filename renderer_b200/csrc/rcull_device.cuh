@@ -42,8 +42,23 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-// Waiting warps back off with nanosleep so that they do not take issue slots from
-// the warps that are computing on the same scheduler.
+// try_wait with a suspend-time hint: the hardware parks the warp until the phase completes
+// or the hint (ns) runs out, so a waiting warp issues one instruction per time-out instead
+// of polling.
+__device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parity, uint32_t hint_ns) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(hint_ns)
+        : "memory");
+    return ok != 0;
+}
+#ifdef RCULL_WAIT_NANOSLEEP  // the previous scheme: poll, backing off with nanosleep
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     uint32_t ns = 32;
@@ -52,6 +67,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         if (ns < 256) ns *= 2;
     } while (!mbar_try_wait(bar, parity));
 }
+#else
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait_hint(bar, parity, 4000u)) {
+    }
+}
+#endif
 // non-blocking: has the phase with this parity completed?
 __device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
     uint32_t ok;

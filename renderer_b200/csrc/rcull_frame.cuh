@@ -414,13 +414,16 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
     }
     // Compute warp 0, lane 0 is also the producer: it draws tile tickets and issues the TMA
     // loads one tile ahead, as soon as the other stage has been read by every compute warp.
+    // Tickets are drawn one tile EARLIER than they are needed (the atomic's round trip through L2
+    // would otherwise sit in warp 0's timeline every tile, and every other warp ends up paced by
+    // the warp that feeds them).  The first tile of a CTA is its block index (every CTA of the
+    // persistent grid is resident, so tiles 0 .. grid-1 are all in flight).
     const bool producer = tid == 0;
-    bool more = true;  // producer only: the last ticket drawn was a real tile
-    auto claim_tile = [&](uint32_t for_it) {
+    bool more = true;      // producer only: the last ticket used was a real tile
+    uint32_t next_t = 0;   // producer only: the ticket drawn for the tile after the one being loaded
+    auto draw_ticket = [&]() { return atomicAdd(args.ticket, 1u) - args.ticket_base + gridDim.x; };
+    auto load_tile = [&](uint32_t for_it, uint32_t t) {
         const uint32_t stage = for_it & 1u;
-        // the first tile of a CTA is its block index (every CTA of the persistent grid is resident, so
-        // tiles 0 .. grid-1 are all in flight); later ones are drawn from the ticket counter
-        const uint32_t t = for_it == 0 ? blockIdx.x : atomicAdd(args.ticket, 1u) - args.ticket_base + gridDim.x;
         sm.tile_ring[for_it % kRing] = t;
         uint64_t* bar = &sm.full[stage];
         if (t < args.n_tiles) {
@@ -434,7 +437,10 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
             more = false;
         }
     };
-    if (producer) claim_tile(0);  // in flight while the CTA copies its tables below
+    if (producer) {  // in flight while the CTA copies its tables below
+        load_tile(0, blockIdx.x);
+        next_t = draw_ticket();
+    }
     float4* const sm_planes = reinterpret_cast<float4*>(reinterpret_cast<unsigned char*>(&sm) + sizeof(FrameSmem));
     for (uint32_t i = tid; i < V * 6 * 4; i += kThreads) sm_planes[i] = reinterpret_cast<const float4*>(&args.planes[0][0])[i];
     // Mesh table: a shared-memory copy when it fits (the L1 left beside ~220 KB of shared memory
@@ -483,7 +489,9 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
         const uint32_t buf = it % B;     // bookkeeping buffer of this tile
         if (producer && more) {
             if (it >= 1) mbar_wait(&sm.empty[stage ^ 1u], ((it - 1) >> 1) & 1u);
-            claim_tile(it + 1);
+            const uint32_t t = next_t;
+            if (t < args.n_tiles) next_t = draw_ticket();  // for tile it + 2: lands while this tile is computed
+            load_tile(it + 1, t);
         }
         const long long f0 = RCULL_CLOCK();
         mbar_wait(&sm.full[stage], (it >> 1) & 1u);
