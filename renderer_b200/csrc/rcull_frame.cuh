@@ -29,6 +29,9 @@ namespace rcull {
 #ifndef RCULL_VIEW_UNROLL
 #define RCULL_VIEW_UNROLL 1
 #endif
+#ifndef RCULL_SCAN_IDLE_NS
+#define RCULL_SCAN_IDLE_NS 400  // scan warp: pause between passes that made no progress
+#endif
 #ifndef RCULL_FRAME_REGS
 #define RCULL_FRAME_REGS 112  // 512 x 112 registers leave 8 K of the SM's 64 K for a resident exchange CTA (128 x 64)
 #endif
@@ -327,7 +330,7 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
         } else if (ended) {
             break;
         }
-        if (!progress) __nanosleep(400);
+        if (!progress) __nanosleep(RCULL_SCAN_IDLE_NS);
     }
 }
 
