@@ -318,7 +318,7 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&sm.bases[buf]);
                     if (lane == 0) {
-                        const long long now = RCULL_CLOCK();
+                        [[maybe_unused]] const long long now = RCULL_CLOCK();
                         RCULL_STAT(0, 1);
                         RCULL_STAT(1, now - t_pub[res % B]);
                         RCULL_STAT(9, now - t_act);
@@ -480,7 +480,7 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
 
     uint32_t it = 0;
     constexpr uint32_t B = frame_bufs<V>();
-    const long long k0 = RCULL_CLOCK();
+    [[maybe_unused]] const long long k0 = RCULL_CLOCK();
     uint32_t emitted = 0;  // iterations [emitted, it) of this CTA still have their commands pending
     auto emit_next = [&]() {
         const uint32_t b = emitted % B;
@@ -496,7 +496,7 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
             if (t < args.n_tiles) next_t = draw_ticket();  // for tile it + 2: lands while this tile is computed
             load_tile(it + 1, t);
         }
-        const long long f0 = RCULL_CLOCK();
+        [[maybe_unused]] const long long f0 = RCULL_CLOCK();
         mbar_wait(&sm.full[stage], (it >> 1) & 1u);
         if (tid == 0) RCULL_STAT(6, RCULL_CLOCK() - f0);
         const uint32_t tile = sm.tile_ring[it % kRing];
@@ -605,7 +605,7 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
         while (emitted < it) {
             const uint32_t b = emitted % B, parity = (emitted / B) & 1u;
             if (emitted + B <= it) {
-                const long long w0 = RCULL_CLOCK();
+                [[maybe_unused]] const long long w0 = RCULL_CLOCK();
                 mbar_wait(&sm.bases[b], parity);
                 if (tid == 0) {
                     RCULL_STAT(5, RCULL_CLOCK() - w0);
