@@ -1,0 +1,169 @@
+// systems_driver.cpp -- test harness for include/rcull_systems.hpp: loads a scene file written by
+// tests/test_cpp_systems.py, runs the C++ systems (project_camera, gpu_transform_cull and, on request,
+// a frozen frame and the acceleration-structure records) and writes what they produced to a result
+// file.  The CHECK against the oracle happens in the Python test; nothing here links oracle/.
+//
+//   systems_driver planes <scene> <result>    host-only: camera + light frusta (no CUDA device needed)
+//   systems_driver frame  <scene> <result>    the full stage through librcull.so (panics without a GPU)
+//
+// Scene file (little endian): u64 n, u32 n_meshes, u32 n_lights, u32 draw_index_base, f32 aspect,
+// f32 lod_distance, Camera position[3] rotation[4], Light[n_lights] (position[3], rotation[4]),
+// rcull_mesh[n_meshes], Position[n], Rotation[n], Scale[n], GltfMesh[n].
+// Result file: u32 n_views, u32 counts[8], u64 index_totals[8], rcull_view[n_views]; then for `frame`:
+// ModelMatrix[n], AABB[n], per view: CoarseCulled[n], rcull_draw_cmd[count], DrawIndex[count];
+// ModelMatrix[n] after a frozen frame over entities whose Scale was doubled.
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <vector>
+
+#include "rcull_systems.hpp"
+
+using namespace rcull::ecs;
+
+namespace {
+
+template <class T>
+void get(std::ifstream& f, T* dst, size_t count = 1) {
+    f.read(reinterpret_cast<char*>(dst), static_cast<std::streamsize>(sizeof(T) * count));
+    if (!f) panic("scene file is truncated");
+}
+template <class T>
+void put(std::ofstream& f, const T* src, size_t count = 1) {
+    f.write(reinterpret_cast<const char*>(src), static_cast<std::streamsize>(sizeof(T) * count));
+}
+
+struct Scene {
+    uint64_t n = 0;
+    uint32_t n_meshes = 0, n_lights = 0, draw_index_base = 0;
+    float aspect = 1.f, lod_distance = 10.f;
+    Camera camera;
+    std::vector<Light> lights;
+    MeshTable meshes;
+    std::vector<Position> position;
+    std::vector<Rotation> rotation;
+    std::vector<Scale> scale;
+    std::vector<GltfMesh> gltf_mesh;
+};
+
+Scene load(const char* path) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f) panic(std::string("cannot open ") + path);
+    Scene s;
+    get(f, &s.n);
+    get(f, &s.n_meshes);
+    get(f, &s.n_lights);
+    get(f, &s.draw_index_base);
+    get(f, &s.aspect);
+    get(f, &s.lod_distance);
+    get(f, s.camera.position, 3);
+    get(f, s.camera.rotation, 4);
+    s.lights.resize(s.n_lights);
+    s.meshes.rows.resize(s.n_meshes);
+    s.position.resize(s.n);
+    s.rotation.resize(s.n);
+    s.scale.resize(s.n);
+    s.gltf_mesh.resize(s.n);
+    if (s.n_lights) get(f, s.lights.data(), s.n_lights);
+    if (s.n_meshes) get(f, s.meshes.rows.data(), s.n_meshes);
+    if (s.n) {
+        get(f, s.position.data(), s.n);
+        get(f, s.rotation.data(), s.n);
+        get(f, s.scale.data(), s.n);
+        get(f, s.gltf_mesh.data(), s.n);
+    }
+    return s;
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+    if (argc != 4 || (std::strcmp(argv[1], "planes") && std::strcmp(argv[1], "frame"))) {
+        std::fprintf(stderr, "usage: %s planes|frame <scene> <result>\n", argv[0]);
+        return 2;
+    }
+    const bool full = !std::strcmp(argv[1], "frame");
+    Scene s = load(argv[2]);
+    project_camera(s.camera, s.aspect);  // the system that runs before the cull stage (src/ecs.rs:66-91)
+    const uint32_t n_views = 1 + s.n_lights;
+
+    std::ofstream out(argv[3], std::ios::binary);
+    if (!out) panic(std::string("cannot create ") + argv[3]);
+
+    if (!full) {
+        const uint32_t zero32[RCULL_MAX_VIEWS] = {};
+        const uint64_t zero64[RCULL_MAX_VIEWS] = {};
+        put(out, &n_views);
+        put(out, zero32, RCULL_MAX_VIEWS);
+        put(out, zero64, RCULL_MAX_VIEWS);
+        put(out, &s.camera.frustum_planes);
+        for (const Light& l : s.lights) {
+            const rcull_view v = light_frustum(l);
+            put(out, &v);
+        }
+        return out.good() ? 0 : 1;
+    }
+
+    rcull_config cfg;
+    std::memset(&cfg, 0, sizeof cfg);
+    cfg.device = 0;
+    cfg.max_views = n_views;
+    cfg.capacity_entities = s.n ? s.n : 1;
+    cfg.max_meshes = s.n_meshes;
+    cfg.output_mode = RCULL_PER_ENTITY;
+    cfg.n_buffers = 2;  // DoubleBuffered: this run uses image index 1
+    cfg.materialize_aabb = 1;
+    cfg.materialize_flags = 1;
+    cfg.lod_distance = s.lod_distance;
+    RcullRes rc(cfg);  // panics (aborts) without a CUDA device: there is no CPU path
+    rc.set_mesh_table(s.meshes);
+
+    const ImageIndex image_index{1};
+    gpu_transform_cull(rc, image_index, s.camera, s.lights, s.position.data(), s.rotation.data(), s.scale.data(),
+                       s.gltf_mesh.data(), s.n, s.draw_index_base);
+
+    put(out, &rc.n_views);
+    put(out, rc.counts, RCULL_MAX_VIEWS);
+    put(out, rc.index_totals, RCULL_MAX_VIEWS);
+    put(out, &s.camera.frustum_planes);
+    for (const Light& l : s.lights) {
+        const rcull_view v = light_frustum(l);
+        put(out, &v);
+    }
+    const std::vector<ModelMatrix> model = download_model(rc, image_index);
+    const std::vector<AABB> aabb = download_aabb(rc, image_index);
+    put(out, model.data(), model.size());
+    put(out, aabb.data(), aabb.size());
+    for (uint32_t v = 0; v < rc.n_views; ++v) {
+        const std::vector<CoarseCulled> culled = download_coarse_culled(rc, image_index, v);
+        const std::vector<rcull_draw_cmd> cmds = download_commands(rc, image_index, v);
+        const std::vector<DrawIndex> visible = download_visible(rc, image_index, v);
+        put(out, culled.data(), culled.size());
+        put(out, cmds.data(), cmds.size());
+        put(out, visible.data(), visible.size());
+    }
+
+    // freeze_culling: the entities keep moving (here: every Scale doubles) but only the model
+    // matrices follow; counts and lists stay those of the frame above (cull_pipeline.rs:331-421).
+    for (Scale& sc : s.scale) sc.s *= 2.f;
+    expect(rcull_pack_components(s.n, reinterpret_cast<const float*>(s.position.data()),
+                                 reinterpret_cast<const float*>(s.rotation.data()),
+                                 reinterpret_cast<const float*>(s.scale.data()), rc.pos_scale.data(), rc.rot.data()),
+           "rcull_pack_components");
+    expect(rcull_upload_entities(rc.ctx(), 0, s.n, rc.pos_scale.data(), rc.rot.data(), rc.mesh.data(), nullptr),
+           "rcull_upload_entities");
+    RuntimeConfiguration runtime_config;
+    runtime_config.freeze_culling = true;
+    gpu_cull_triangles(rc, image_index, s.camera, runtime_config, s.draw_index_base);
+    const std::vector<ModelMatrix> frozen = download_model(rc, image_index);
+    put(out, frozen.data(), frozen.size());
+    uint32_t counts_after[RCULL_MAX_VIEWS] = {};
+    uint64_t totals_after[RCULL_MAX_VIEWS] = {};
+    expect(rcull_download_counts(rc.ctx(), image_index.ix, counts_after, totals_after), "rcull_download_counts");
+    put(out, counts_after, RCULL_MAX_VIEWS);
+
+    rc.destroy();
+    out.flush();
+    return out.good() ? 0 : 1;
+}
