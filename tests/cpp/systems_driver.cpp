@@ -1,5 +1,5 @@
 // systems_driver.cpp -- test harness for include/rcull_systems.hpp: loads a scene file written by
-// tests/test_cpp_systems.py, runs the C++ systems (project_camera, gpu_transform_cull and, on request,
+// tests/test_zz_cpp_systems.py, runs the C++ systems (project_camera, gpu_transform_cull and, on request,
 // a frozen frame and the acceleration-structure records) and writes what they produced to a result
 // file.  The CHECK against the oracle happens in the Python test; nothing here links oracle/.
 //
