@@ -336,7 +336,10 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
     TRY((configure<8, false>(c)));
     TRY((configure<8, true>(c)));
 #undef TRY
-    CU(cudaDeviceSynchronize());
+    if (cudaError_t e = cudaDeviceSynchronize(); e != cudaSuccess) {
+        rcull_destroy(c);
+        return fail(RCULL_ERR_CUDA, "rcull_create: %s", cudaGetErrorString(e));
+    }
     *out = c;
     return RCULL_OK;
 }
