@@ -214,6 +214,35 @@ inline std::vector<DrawIndex> download_visible(RcullRes& rc, ImageIndex ix, uint
     return out;
 }
 
+
+// After gpu_cull_triangles: IndirectCommandsCount, the compacted commands and the sum of the refined indexCount
+// (CullPassData.culled_commands_count_buffer / culled_commands_buffer, cull_pipeline.rs:74-84).
+struct TriangleStage {
+    uint32_t count = 0;
+    uint64_t kept_indices = 0;
+    std::vector<rcull_draw_cmd> commands;
+};
+inline TriangleStage download_triangle_stage(RcullRes& rc) {
+    TriangleStage t;
+    expect(rcull_download_tri(rc.ctx(), &t.count, &t.kept_indices, nullptr, 0, nullptr, 0, 0), "rcull_download_tri");
+    t.commands.resize(t.count);
+    if (t.count) expect(rcull_download_tri(rc.ctx(), &t.count, nullptr, t.commands.data(), t.count, nullptr, 0, 0), "rcull_download_tri");
+    return t;
+}
+// CullPassData.culled_index_buffer [first, first + n): a command's triples start at its firstIndex.
+inline std::vector<uint32_t> download_culled_indices(RcullRes& rc, uint64_t first, uint64_t n) {
+    std::vector<uint32_t> out(n);
+    uint32_t count = 0;
+    if (n) expect(rcull_download_tri(rc.ctx(), &count, nullptr, nullptr, 0, out.data(), first, n), "rcull_download_tri");
+    return out;
+}
+struct AsInstance { unsigned char bytes[64]; };  // VkAccelerationStructureInstanceKHR
+inline std::vector<AsInstance> download_as_instances(RcullRes& rc) {
+    std::vector<AsInstance> out(rc.n_entities);
+    if (!out.empty()) expect(rcull_download_as_instances(rc.ctx(), 0, out.size(), out.data()), "rcull_download_as_instances");
+    return out;
+}
+
 }  // namespace ecs
 }  // namespace rcull
 #endif

@@ -5,13 +5,18 @@
 //
 //   systems_driver planes <scene> <result>    host-only: camera + light frusta (no CUDA device needed)
 //   systems_driver frame  <scene> <result>    the full stage through librcull.so (panics without a GPU)
+//   systems_driver stage2 <scene> <result>    camera view only, then gpu_cull_triangles + gpu_as_instances
 //
 // Scene file (little endian): u64 n, u32 n_meshes, u32 n_lights, u32 draw_index_base, f32 aspect,
 // f32 lod_distance, Camera position[3] rotation[4], Light[n_lights] (position[3], rotation[4]),
 // rcull_mesh[n_meshes], Position[n], Rotation[n], Scale[n], GltfMesh[n].
 // Result file: u32 n_views, u32 counts[8], u64 index_totals[8], rcull_view[n_views]; then for `frame`:
 // ModelMatrix[n], AABB[n], per view: CoarseCulled[n], rcull_draw_cmd[count], DrawIndex[count];
-// ModelMatrix[n] after a frozen frame over entities whose Scale was doubled.
+// ModelMatrix[n] after a frozen frame over entities whose Scale was doubled, u32 counts[8] after it.
+// `stage2` scenes continue with: u64 n_vertices, u64 n_indices, u64 capacity_tri_indices, f32 positions[3 * n_vertices],
+// u32 indices[n_indices], u64 blas[n_meshes]; its result: u32 n_views (= 1), u32 counts[8], u64 index_totals[8],
+// f32 pv[16], u32 tri_count, u64 kept_indices, rcull_draw_cmd[tri_count], u32 culled_indices[index_totals[0]],
+// AsInstance[n].
 #include <cstdio>
 #include <cstring>
 #include <fstream>
@@ -41,13 +46,17 @@ struct Scene {
     Camera camera;
     std::vector<Light> lights;
     MeshTable meshes;
+    std::vector<float> positions_xyz;  // stage2: consolidated position / index buffers, BLAS addresses
+    std::vector<uint32_t> indices;
+    std::vector<uint64_t> blas;
+    uint64_t capacity_tri_indices = 0;
     std::vector<Position> position;
     std::vector<Rotation> rotation;
     std::vector<Scale> scale;
     std::vector<GltfMesh> gltf_mesh;
 };
 
-Scene load(const char* path) {
+Scene load(const char* path, bool stage2) {
     std::ifstream f(path, std::ios::binary);
     if (!f) panic(std::string("cannot open ") + path);
     Scene s;
@@ -73,23 +82,72 @@ Scene load(const char* path) {
         get(f, s.scale.data(), s.n);
         get(f, s.gltf_mesh.data(), s.n);
     }
+    if (stage2) {
+        uint64_t n_vertices = 0, n_indices = 0;
+        get(f, &n_vertices);
+        get(f, &n_indices);
+        get(f, &s.capacity_tri_indices);
+        s.positions_xyz.resize(3 * n_vertices);
+        s.indices.resize(n_indices);
+        s.blas.resize(s.n_meshes);
+        if (n_vertices) get(f, s.positions_xyz.data(), s.positions_xyz.size());
+        if (n_indices) get(f, s.indices.data(), s.indices.size());
+        if (s.n_meshes) get(f, s.blas.data(), s.blas.size());
+    }
     return s;
 }
 
 }  // namespace
 
 int main(int argc, char** argv) {
-    if (argc != 4 || (std::strcmp(argv[1], "planes") && std::strcmp(argv[1], "frame"))) {
-        std::fprintf(stderr, "usage: %s planes|frame <scene> <result>\n", argv[0]);
+    if (argc != 4 || (std::strcmp(argv[1], "planes") && std::strcmp(argv[1], "frame") && std::strcmp(argv[1], "stage2"))) {
+        std::fprintf(stderr, "usage: %s planes|frame|stage2 <scene> <result>\n", argv[0]);
         return 2;
     }
+    const bool stage2 = !std::strcmp(argv[1], "stage2");
     const bool full = !std::strcmp(argv[1], "frame");
-    Scene s = load(argv[2]);
+    Scene s = load(argv[2], stage2);
     project_camera(s.camera, s.aspect);  // the system that runs before the cull stage (src/ecs.rs:66-91)
     const uint32_t n_views = 1 + s.n_lights;
 
     std::ofstream out(argv[3], std::ios::binary);
     if (!out) panic(std::string("cannot create ") + argv[3]);
+
+    if (stage2) {
+        rcull_config cfg;
+        std::memset(&cfg, 0, sizeof cfg);
+        cfg.max_views = 1;  // the reference culls triangles against the camera only
+        cfg.capacity_entities = s.n ? s.n : 1;
+        cfg.max_meshes = s.n_meshes;
+        cfg.output_mode = RCULL_PER_ENTITY;
+        cfg.n_buffers = 1;
+        cfg.lod_distance = s.lod_distance;
+        cfg.capacity_tri_indices = s.capacity_tri_indices;
+        RcullRes rc(cfg);
+        rc.set_mesh_table(s.meshes);
+        rc.set_geometry(s.positions_xyz, s.indices);
+        rc.set_blas_table(s.blas);
+        const ImageIndex image_index{0};
+        gpu_transform_cull(rc, image_index, s.camera, {}, s.position.data(), s.rotation.data(), s.scale.data(), s.gltf_mesh.data(),
+                           s.n, s.draw_index_base);
+        gpu_cull_triangles(rc, image_index, s.camera, RuntimeConfiguration{}, s.draw_index_base);
+        const TriangleStage t = download_triangle_stage(rc);
+        const std::vector<uint32_t> culled = download_culled_indices(rc, 0, rc.index_totals[0]);
+        gpu_as_instances(rc, image_index, s.draw_index_base);
+        const std::vector<AsInstance> instances = download_as_instances(rc);
+        put(out, &rc.n_views);
+        put(out, rc.counts, RCULL_MAX_VIEWS);
+        put(out, rc.index_totals, RCULL_MAX_VIEWS);
+        put(out, s.camera.pv, 16);
+        put(out, &t.count);
+        put(out, &t.kept_indices);
+        put(out, t.commands.data(), t.commands.size());
+        put(out, culled.data(), culled.size());
+        put(out, instances.data(), instances.size());
+        rc.destroy();
+        out.flush();
+        return out.good() ? 0 : 1;
+    }
 
     if (!full) {
         const uint32_t zero32[RCULL_MAX_VIEWS] = {};

@@ -156,3 +156,58 @@ def test_gpu_transform_cull_system_matches_oracle(driver, tmp_path, n, n_lights,
     frozen = O.frame(pos, quat, scale * np.float32(2.0), mesh, MESHES, views, scene.CAMERA_POS, want=("model",))
     assert np.array_equal(r.frozen_model, frozen["model"])
     assert np.array_equal(r.counts_after_frozen[:v], ref["counts"])
+
+
+def write_stage2_tail(path, positions, indices, capacity, blas):
+    positions = np.ascontiguousarray(positions, "<f4").reshape(-1)
+    with open(path, "ab") as f:
+        f.write(struct.pack("<QQQ", len(positions) // 3, len(indices), capacity))
+        f.write(positions.tobytes())
+        f.write(np.ascontiguousarray(indices, "<u4").tobytes())
+        f.write(np.ascontiguousarray(blas, "<u8").tobytes())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,half_box,base", [(5_000, 40.0, 0), (1, 3.0, 0), (20_000, 30.0, 250_000)])
+def test_gpu_cull_triangles_and_as_instances_systems_match_oracle(driver, tmp_path, n, half_box, base):
+    """The second half of cull_pass (generate_work dispatches + compact_draw_stream) and the TLAS instance loop
+    through the C++ systems: commands, count, culled index ranges and the 64-byte records are bit-exact."""
+    positions, indices = scene.synth_geometry(MESHES)
+    blas = (np.arange(len(MESHES), dtype=np.uint64) + 1) * np.uint64(0x1_0000_0100)
+    pos, quat, scale, mesh = O.synth_entities(scene.SEED, 0, n, half_box, len(MESHES))
+    views = scene.scene_views(1)
+    ref = O.frame(pos, quat, scale, mesh, MESHES, views, scene.CAMERA_POS, draw_index_base=base, n_threads=8)
+    total = int(ref["totals"][0])
+    cap = max(total, 3)
+    write_scene(tmp_path / "s.bin", pos, quat, scale, mesh, MESHES, 0, base=base)
+    write_stage2_tail(tmp_path / "s.bin", positions, indices, cap, blas)
+    subprocess.check_call([driver, "stage2", str(tmp_path / "s.bin"), str(tmp_path / "r.bin")], timeout=300)
+
+    buf, off = open(tmp_path / "r.bin", "rb").read(), 0
+
+    def take(dtype, count):
+        nonlocal off
+        a = np.frombuffer(buf, dtype=dtype, count=count, offset=off)
+        off += a.nbytes
+        return a
+
+    assert int(take("<u4", 1)[0]) == 1
+    counts, totals, pv = take("<u4", 8), take("<u8", 8), take("<f4", 16)
+    assert counts[0] == ref["counts"][0] and totals[0] == total
+    assert np.array_equal(pv.view(np.uint32), scene.camera_pv().view(np.uint32))
+    tri_count, kept = int(take("<u4", 1)[0]), int(take("<u8", 1)[0])
+    tri_cmds, culled = take(CMD_DTYPE, tri_count), take("<u4", total)
+    instances = take(O.AS_INSTANCE_DTYPE, n)
+    assert off == len(buf), "result file has trailing bytes"
+
+    src = O.src_first_index(pos, mesh, ref["cmds"][0], MESHES, scene.CAMERA_POS, draw_index_base=base)
+    want = O.tri_cull(ref["cmds"][0], src, ref["model"], pv, positions, indices, cap, draw_index_base=base, n_threads=8)
+    assert (tri_count, kept) == (want["count"], want["kept_indices"])
+    assert np.array_equal(tri_cmds, want["cmds"])
+    for c in want["cmds"]:  # only the ranges the commands own are defined
+        a, b = int(c["firstIndex"]), int(c["firstIndex"]) + int(c["indexCount"])
+        assert np.array_equal(culled[a:b], want["indices"][a:b])
+    want_inst = O.as_instances(ref["model"], mesh, blas, draw_index_base=base)
+    assert np.array_equal(instances["transform"], want_inst["transform"])  # == on floats, like the model matrices
+    for field in ("custom_index_and_mask", "sbt_offset_and_flags", "blas"):
+        assert np.array_equal(instances[field], want_inst[field]), field
