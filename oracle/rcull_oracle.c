@@ -359,6 +359,138 @@ int oracle_frame(const float *pos, const float *quat, const float *scale, const 
     return 0;
 }
 
+/* ---- fused CPU variant (CPU baseline (ii)) ----------------------------
+ * The same per-entity functions as oracle_frame, scheduled the way a CPU implementation
+ * that cared about memory traffic would: ONE pass per entity (A1 -> A2 -> A3 for every
+ * view, matrix and box kept in registers / L1 unless the caller wants them), a per-thread
+ * count of survivors and index lengths, an exclusive prefix over the threads, and a second
+ * pass in which every thread writes its own slice of the draw lists.  Outputs are
+ * bit-identical to oracle_frame's (tests/test_oracle.py); only the schedule differs.  It is
+ * the stronger of the two CPU baselines bench.py reports, not a second definition. */
+typedef struct {
+    const float *pos, *quat, *scale;
+    const uint32_t *mesh_id;
+    const oracle_mesh *meshes;
+    const float *planes;
+    const float *cam_pos;
+    float lod_distance;
+    uint32_t n_views, draw_index_base;
+    uint64_t n, lo, hi;
+    float *model, *aabb;
+    uint8_t *flags;      /* optional output [n_views][n] */
+    uint8_t *culled_in;  /* [n]: bit v = culled in view v (n_views <= 8) */
+    oracle_cmd *cmds;
+    uint32_t *visible;
+    uint32_t count[8];      /* phase A out: survivors of this range per view */
+    uint64_t len[8];        /*              their index lengths */
+    uint32_t count_base[8]; /* phase B in: exclusive prefixes over the earlier ranges */
+    uint64_t len_base[8];
+} fused_job;
+
+static void *fused_phase_a(void *arg) {
+    fused_job *j = (fused_job *)arg;
+    for (uint32_t v = 0; v < j->n_views; v++) { j->count[v] = 0; j->len[v] = 0; }
+    for (uint64_t i = j->lo; i < j->hi; i++) {
+        float m_local[16], box_local[6];
+        float *m = j->model ? j->model + 16 * i : m_local;
+        float *box = j->aabb ? j->aabb + 6 * i : box_local;
+        const oracle_mesh *mesh = j->meshes + j->mesh_id[i];
+        oracle_model_matrix(j->pos + 3 * i, j->quat + 4 * i, j->scale[i], m);
+        oracle_aabb(m, mesh->aabb_min, mesh->aabb_max, box, box + 3);
+        uint8_t mask = 0;
+        for (uint32_t v = 0; v < j->n_views; v++) {
+            const int culled = oracle_coarse_culled(box, box + 3, (const float(*)[4])(j->planes + 24 * v));
+            if (culled) mask |= (uint8_t)(1u << v);
+            if (j->flags) j->flags[(uint64_t)v * j->n + i] = (uint8_t)culled;
+        }
+        j->culled_in[i] = mask;
+        if (mask != (uint8_t)((1u << j->n_views) - 1u)) { /* visible somewhere: pick_lod once */
+            const uint32_t lod = oracle_pick_lod(j->cam_pos, j->pos + 3 * i, mesh->n_lods, j->lod_distance);
+            const uint32_t index_len = mesh->lod[lod].index_len;
+            for (uint32_t v = 0; v < j->n_views; v++)
+                if (!(mask & (1u << v))) { j->count[v]++; j->len[v] += index_len; }
+        }
+    }
+    return NULL;
+}
+
+static void *fused_phase_b(void *arg) {
+    fused_job *j = (fused_job *)arg;
+    uint32_t at[8], first_index[8];
+    for (uint32_t v = 0; v < j->n_views; v++) { at[v] = j->count_base[v]; first_index[v] = (uint32_t)j->len_base[v]; }
+    const uint8_t all = (uint8_t)((1u << j->n_views) - 1u);
+    for (uint64_t i = j->lo; i < j->hi; i++) {
+        const uint8_t mask = j->culled_in[i];
+        if (mask == all) continue;
+        const oracle_mesh *mesh = j->meshes + j->mesh_id[i];
+        const uint32_t lod = oracle_pick_lod(j->cam_pos, j->pos + 3 * i, mesh->n_lods, j->lod_distance);
+        const uint32_t index_len = mesh->lod[lod].index_len;
+        for (uint32_t v = 0; v < j->n_views; v++) {
+            if (mask & (1u << v)) continue;
+            if (j->cmds) {
+                oracle_cmd *c = j->cmds + (uint64_t)v * j->n + at[v];
+                c->indexCount = index_len;
+                c->instanceCount = 1;
+                c->firstIndex = first_index[v];
+                c->vertexOffset = mesh->vertex_offset;
+                c->firstInstance = j->draw_index_base + (uint32_t)i;
+            }
+            if (j->visible) j->visible[(uint64_t)v * j->n + at[v]] = j->draw_index_base + (uint32_t)i;
+            first_index[v] += index_len; /* u32, wraps like oracle_frame's */
+            at[v]++;
+        }
+    }
+    return NULL;
+}
+
+static void fused_run(fused_job *jobs, int n_threads, void *(*fn)(void *)) {
+    if (n_threads == 1) { fn(&jobs[0]); return; }
+    pthread_t *th = (pthread_t *)malloc(sizeof(pthread_t) * n_threads);
+    for (int t = 0; t < n_threads; t++) pthread_create(&th[t], NULL, fn, &jobs[t]);
+    for (int t = 0; t < n_threads; t++) pthread_join(th[t], NULL);
+    free(th);
+}
+
+int oracle_frame_fused(const float *pos, const float *quat, const float *scale, const uint32_t *mesh_id,
+                       uint64_t n, const oracle_mesh *meshes, uint32_t n_meshes,
+                       const float *planes, uint32_t n_views, const float cam_pos[3], float lod_distance,
+                       uint32_t draw_index_base, float *model, float *aabb, uint8_t *flags,
+                       oracle_cmd *cmds, uint32_t *visible, uint32_t *counts, uint64_t *index_totals,
+                       int n_threads) {
+    if (n_views < 1 || n_views > 8) return -1;
+    for (uint64_t i = 0; i < n; i++)
+        if (mesh_id[i] >= n_meshes) return -1;
+    if (n_threads < 1 || n < 1024) n_threads = 1;
+    uint8_t *mask = (uint8_t *)malloc(n ? n : 1);
+    fused_job *jobs = (fused_job *)calloc((size_t)n_threads, sizeof(fused_job));
+    for (int t = 0; t < n_threads; t++) {
+        fused_job *j = &jobs[t];
+        j->pos = pos; j->quat = quat; j->scale = scale; j->mesh_id = mesh_id; j->meshes = meshes;
+        j->planes = planes; j->cam_pos = cam_pos; j->lod_distance = lod_distance;
+        j->n_views = n_views; j->draw_index_base = draw_index_base; j->n = n;
+        j->lo = n * (uint64_t)t / (uint64_t)n_threads;
+        j->hi = n * (uint64_t)(t + 1) / (uint64_t)n_threads;
+        j->model = model; j->aabb = aabb; j->flags = flags; j->culled_in = mask; j->cmds = cmds; j->visible = visible;
+    }
+    fused_run(jobs, n_threads, fused_phase_a);
+    for (uint32_t v = 0; v < n_views; v++) {
+        uint32_t c = 0;
+        uint64_t l = 0;
+        for (int t = 0; t < n_threads; t++) {
+            jobs[t].count_base[v] = c;
+            jobs[t].len_base[v] = l;
+            c += jobs[t].count[v];
+            l += jobs[t].len[v];
+        }
+        if (counts) counts[v] = c;
+        if (index_totals) index_totals[v] = l;
+    }
+    if (cmds || visible) fused_run(jobs, n_threads, fused_phase_b);
+    free(jobs);
+    free(mask);
+    return 0;
+}
+
 /* ---- per-mesh instanced emission (BASELINE config 4) -------------------------- */
 int oracle_emit_per_mesh(const float *pos, const uint32_t *mesh_id, const uint8_t *flags, uint64_t n,
                          const oracle_mesh *meshes, uint32_t n_meshes, const float cam_pos[3],

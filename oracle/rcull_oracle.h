@@ -85,6 +85,17 @@ int oracle_frame(const float *pos, const float *quat, const float *scale, const 
                  oracle_cmd *cmds, uint32_t *visible, uint32_t *counts, uint64_t *index_totals,
                  int n_threads);
 
+/* The same frame with a fused schedule (CPU baseline (ii)): one pass per entity, per-thread
+ * counts, an exclusive prefix over the threads, a second pass that writes each thread's slice of the
+ * lists.  Same arguments, bit-identical outputs; n_views <= 8. */
+int oracle_frame_fused(const float *pos, const float *quat, const float *scale, const uint32_t *mesh_id,
+                       uint64_t n, const oracle_mesh *meshes, uint32_t n_meshes,
+                       const float *planes /* [n_views][6][4] */, uint32_t n_views,
+                       const float cam_pos[3], float lod_distance, uint32_t draw_index_base,
+                       float *model, float *aabb, uint8_t *flags,
+                       oracle_cmd *cmds, uint32_t *visible, uint32_t *counts, uint64_t *index_totals,
+                       int n_threads);
+
 /* Per-mesh instanced emission (BASELINE config 4): one command per (mesh, lod)
  * slot with instanceCount = survivors, firstInstance = bucket start in the
  * bucketed visible list (stable by draw_index), firstIndex = the lod's own

@@ -37,6 +37,8 @@ def lib():
         L.oracle_mat4_mul.argtypes = [_P, _P, _P]
         L.oracle_frame.argtypes = [_P, _P, _P, _P, _u64, _P, _u32, _P, _u32, _P, _f, _u32, _P, _P, _P, _P, _P, _P, _P, C.c_int]
         L.oracle_frame.restype = C.c_int
+        L.oracle_frame_fused.argtypes = L.oracle_frame.argtypes
+        L.oracle_frame_fused.restype = C.c_int
         L.oracle_emit_per_mesh.argtypes = [_P, _P, _P, _u64, _P, _u32, _P, _f, _u32, _P, _P, _P, _P]
         L.oracle_emit_per_mesh.restype = C.c_int
         L.oracle_tri_cull.argtypes = [_P, _P, _u32, _P, _u32, _P, _P, _u64, _P, _u64, _P, _u64, _P, _P, _P, C.c_int]
@@ -119,8 +121,9 @@ def synth_entities(seed, first, n, half_box, n_meshes):
 
 
 def frame(pos, quat, scale, mesh_id, meshes, planes, cam_pos, lod_distance=10.0, draw_index_base=0,
-          n_threads=1, want=("model", "aabb", "flags", "cmds", "visible")):
-    """Runs oracle_frame; returns a dict of the requested outputs (lists trimmed to counts)."""
+          n_threads=1, want=("model", "aabb", "flags", "cmds", "visible"), fused=False):
+    """Runs oracle_frame (or oracle_frame_fused: same results, one pass per entity + parallel emit);
+    returns a dict of the requested outputs (lists trimmed to counts)."""
     pos, quat, scale = f32(pos).reshape(-1, 3), f32(quat).reshape(-1, 4), f32(scale).reshape(-1)
     mesh_id = np.ascontiguousarray(mesh_id, np.uint32)
     meshes = np.ascontiguousarray(meshes, MESH_DTYPE)
@@ -135,7 +138,7 @@ def frame(pos, quat, scale, mesh_id, meshes, planes, cam_pos, lod_distance=10.0,
     }
     counts, totals = np.zeros(v, np.uint32), np.zeros(v, np.uint64)
     cam = f32(cam_pos)
-    rc = lib().oracle_frame(p(pos), p(quat), p(scale), p(mesh_id), n, p(meshes), len(meshes), p(planes), v,
+    rc = (lib().oracle_frame_fused if fused else lib().oracle_frame)(p(pos), p(quat), p(scale), p(mesh_id), n, p(meshes), len(meshes), p(planes), v,
                             p(cam), lod_distance, draw_index_base, p(out["model"]), p(out["aabb"]),
                             p(out["flags"]), p(out["cmds"]), p(out["visible"]), p(counts), p(totals), n_threads)
     if rc != 0:

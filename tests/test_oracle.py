@@ -182,6 +182,49 @@ def test_threads_do_not_change_results():
 
 
 # ---- stage 2: per-triangle cull (generate_work.comp) + compact_draw_stream ------------------
+@pytest.mark.parametrize("n,n_views,threads,want", [
+    (0, 2, 4, ("model", "aabb", "flags", "cmds", "visible")),
+    (1, 1, 1, ("model", "aabb", "flags", "cmds", "visible")),
+    (1023, 3, 8, ("model", "aabb", "flags", "cmds", "visible")),
+    (20_000, 5, 1, ("model", "aabb", "flags", "cmds", "visible")),
+    (20_000, 5, 7, ("model", "aabb", "flags", "cmds", "visible")),
+    (50_001, 8, 16, ("cmds", "visible")),
+    (50_001, 2, 3, ("flags",)),
+])
+def test_fused_schedule_is_bit_identical_to_the_reference_shaped_passes(n, n_views, threads, want):
+    """oracle_frame_fused (the stronger CPU baseline of bench.py) only reschedules the same per-entity functions:
+    every output equals oracle_frame's, for any thread count and any subset of outputs, draw_index_base included."""
+    ps, rot, mesh = scene.synth_entities(scene.SEED + 3, 0, n, 45.0)
+    meshes = scene.synth_mesh_table()
+    views = scene.scene_views(n_views)
+    pos, quat, scale = scene.to_components(ps, rot)
+    a = O.frame(pos, quat, scale, mesh, meshes, views, scene.CAMERA_POS, draw_index_base=11, want=want)
+    b = O.frame(pos, quat, scale, mesh, meshes, views, scene.CAMERA_POS, draw_index_base=11, want=want, n_threads=threads, fused=True)
+    assert np.array_equal(a["counts"], b["counts"]) and np.array_equal(a["totals"], b["totals"])
+    for key in ("model", "aabb", "flags"):
+        if key in want:
+            assert a[key].tobytes() == b[key].tobytes(), key
+    for key in ("cmds", "visible"):
+        if key in want:
+            for k in range(n_views):
+                assert np.array_equal(a[key][k], b[key][k]), (key, k)
+
+
+def test_fused_schedule_wraps_first_index_like_the_serial_emit():
+    """index_len sums beyond 2^32: firstIndex is a u32 that wraps, the index totals stay exact -- across thread ranges too."""
+    n = 6000
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, 6.0)
+    meshes = scene.synth_mesh_table().copy()
+    meshes["lod"][:, :, 1] = 3 * 11_200_000
+    views = scene.scene_views(2)
+    pos, quat, scale = scene.to_components(ps, rot)
+    a = O.frame(pos, quat, scale, mesh, meshes, views, scene.CAMERA_POS, want=("cmds",))
+    b = O.frame(pos, quat, scale, mesh, meshes, views, scene.CAMERA_POS, want=("cmds",), n_threads=5, fused=True)
+    assert int(a["totals"][1]) > 2**32 and np.array_equal(a["totals"], b["totals"])
+    for k in range(2):
+        assert np.array_equal(a["cmds"][k], b["cmds"][k])
+
+
 def _one_cmd(index_len, first_instance=0, first_index=0):
     c = np.zeros(1, O.CMD_DTYPE)
     c[0] = (index_len, 1, first_index, 0, first_instance)
