@@ -17,8 +17,10 @@ def pytest_configure(config):
 def _built():
     """The oracle is cheap to build anywhere (gcc); librcull.so needs nvcc and is
     built by __graft_entry__.build() -- here only if it is missing and nvcc exists."""
-    if not os.path.exists(os.path.join(ROOT, "oracle", "librcull_oracle.so")):
-        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")])
+    oracle_so = os.path.join(ROOT, "oracle", "librcull_oracle.so")
+    rc = subprocess.call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])  # no-op when up to date
+    if rc != 0 and not os.path.exists(oracle_so):
+        raise RuntimeError("the CPU oracle could not be built (make -C oracle)")
     lib = os.path.join(ROOT, "renderer_b200", "librcull.so")
     if not os.path.exists(lib) and os.path.exists("/usr/local/cuda/bin/nvcc"):
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "renderer_b200", "csrc")])
