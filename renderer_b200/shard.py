@@ -131,6 +131,115 @@ class ShardMerger:
         return plan
 
 
+# ---- per-mesh instanced mode (BASELINE configs[3]) over range shards: SURVEY 8e, last paragraph ----
+# Every rank buckets its own survivors by (mesh, lod) slot; the merged output is the single-GPU one: one
+# command per non-empty slot with instanceCount summed over ranks, and the visible list slot-major with the
+# ranks' buckets of a slot in rank order (ranges ascend with the rank, so that IS draw_index order).  No
+# reduction collective: an all_gather of the per-slot counts (S words per rank) gives every rank all it
+# needs to place every bucket.
+@dataclass
+class PerMeshMergePlan:
+    slot_counts: np.ndarray  # [S] merged survivors per slot
+    slot_start: np.ndarray  # [S] exclusive prefix over slots = firstInstance of the slot's command
+    dest: np.ndarray  # [world, S] start of rank r's bucket of slot s in the MERGED visible list
+    src: np.ndarray  # [world, S] start of that bucket in rank r's OWN bucketed visible list
+    rank_base: np.ndarray  # [world] start of rank r's list in the rank-ordered staging buffer
+    total: int  # merged survivors
+
+
+def _exclusive(a: np.ndarray, axis: int) -> np.ndarray:
+    out = np.zeros_like(a)
+    sl_dst = [slice(None)] * a.ndim
+    sl_src = [slice(None)] * a.ndim
+    sl_dst[axis], sl_src[axis] = slice(1, None), slice(None, -1)
+    out[tuple(sl_dst)] = np.cumsum(a, axis=axis)[tuple(sl_src)]
+    return out
+
+
+def plan_merge_per_mesh(slot_counts_all: np.ndarray) -> PerMeshMergePlan:
+    """slot_counts_all: [world, S] survivors of every rank in every (mesh, lod) slot, as gathered."""
+    c = np.asarray(slot_counts_all, np.uint64)
+    totals = c.sum(axis=0)
+    start = _exclusive(totals, 0)
+    per_rank = c.sum(axis=1)
+    return PerMeshMergePlan(totals, start, start[None, :] + _exclusive(c, 0), _exclusive(c, 1), _exclusive(per_rank, 0), int(per_rank.sum()))
+
+
+def per_mesh_commands(meshes: np.ndarray, plan: PerMeshMergePlan, max_lods: int = 6) -> np.ndarray:
+    """The merged command list: one command per non-empty slot, ascending slot = mesh * 6 + lod
+    (the keep rule of compact_draw_stream.comp:41 on instanceCount, as in the single-GPU mode)."""
+    from ._lib import CMD_DTYPE
+
+    keep = np.nonzero(plan.slot_counts)[0]
+    mesh, lod = keep // max_lods, keep % max_lods
+    out = np.zeros(len(keep), CMD_DTYPE)
+    out["indexCount"] = meshes["lod"][mesh, lod, 1]
+    out["instanceCount"] = plan.slot_counts[keep].astype(np.uint32)
+    out["firstIndex"] = meshes["lod"][mesh, lod, 0]
+    out["vertexOffset"] = meshes["vertex_offset"][mesh]
+    out["firstInstance"] = plan.slot_start[keep].astype(np.uint32)
+    return out
+
+
+def per_mesh_permutation(plan: PerMeshMergePlan) -> np.ndarray:
+    """perm with merged[j] = staged[perm[j]], staged = the ranks' own bucketed lists back to back in rank order."""
+    # [world, S] bucket lengths, recovered from the prefixes
+    src_end = np.concatenate([plan.src[:, 1:], np.diff(np.append(plan.rank_base, plan.total)).reshape(-1, 1).astype(plan.src.dtype)], axis=1)
+    c = (src_end - plan.src).astype(np.int64)
+    seg_len = c.reshape(-1)
+    seg_dst = plan.dest.astype(np.int64).reshape(-1)
+    seg_src = (plan.rank_base.astype(np.int64)[:, None] + plan.src.astype(np.int64)).reshape(-1)
+    within = np.arange(int(seg_len.sum()), dtype=np.int64) - np.repeat(np.cumsum(seg_len) - seg_len, seg_len)
+    perm = np.empty(plan.total, np.int64)
+    perm[np.repeat(seg_dst, seg_len) + within] = np.repeat(seg_src, seg_len) + within
+    return perm
+
+
+class PerMeshShardMerger:
+    """Host side of the per-mesh merge: all_gather of the slot counts, in-place allgatherv of the ranks' bucketed
+    visible lists into a rank-ordered staging buffer (one broadcast per rank, as ShardMerger does), then the
+    slot-major permutation.  The permutation runs as a torch index_select here; a segmented peer-store kernel
+    (one warp per (slot, rank) bucket, like rcull_merge_scatter) is the device-side follow-up."""
+
+    def __init__(self, n_slots: int, capacity: int, device, group=None):
+        import torch
+        import torch.distributed as dist
+
+        self.torch, self.dist, self.group = torch, dist, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.n_slots, self.capacity, self.device = n_slots, capacity, device
+        self._counts = torch.zeros(n_slots, dtype=torch.int64, device=device)
+        self._counts_flat = torch.zeros(self.world * n_slots, dtype=torch.int64, device=device)
+        self.staged = torch.empty(capacity, dtype=torch.int32, device=device)
+        self.plan: PerMeshMergePlan | None = None
+
+    def gather_counts(self, slot_counts) -> PerMeshMergePlan:
+        torch = self.torch
+        self._counts[:] = torch.as_tensor(slot_counts, device=self.device).to(torch.int64)
+        self.dist.all_gather_into_tensor(self._counts_flat, self._counts, group=self.group)
+        self.plan = plan_merge_per_mesh(self._counts_flat.view(self.world, self.n_slots).cpu().numpy())
+        if self.plan.total > self.capacity:
+            raise ValueError(f"merged visible list of {self.plan.total} entries exceeds capacity {self.capacity}")
+        return self.plan
+
+    def merge_visible(self, own_visible):
+        """own_visible: this rank's bucketed visible list (int32 tensor on `device`).  Returns the merged list."""
+        torch, dist, plan = self.torch, self.dist, self.plan
+        bounds = np.append(plan.rank_base, plan.total).astype(np.int64)
+        lo, hi = int(bounds[self.rank]), int(bounds[self.rank + 1])
+        self.staged[lo:hi] = own_visible[: hi - lo]
+        works = []
+        for r in range(self.world):
+            a, b = int(bounds[r]), int(bounds[r + 1])
+            if b > a:
+                src = dist.get_global_rank(self.group, r) if self.group is not None else r
+                works.append(dist.broadcast(self.staged[a:b], src=src, group=self.group, async_op=True))
+        for w in works:
+            w.wait()
+        perm = torch.as_tensor(per_mesh_permutation(plan), device=self.device)
+        return self.staged[: plan.total].index_select(0, perm)
+
+
 def _wrap_device(torch, ptr: int, n: int, dtype, device):
     """Zero-copy torch view of a librcull device buffer (for NCCL plumbing only)."""
     itemsize = torch.empty((), dtype=dtype).element_size()
