@@ -161,6 +161,15 @@ int rcull_download_flags(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t view, uint
 int rcull_download_cmds(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t view, uint64_t first, uint64_t n, rcull_draw_cmd *cmds);
 int rcull_download_visible(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t view, uint64_t first, uint64_t n, uint32_t *visible);
 
+/* RCULL_PER_MESH_INSTANCED only: the per-slot survivor counts of one view as the last rcull_frame
+ * left them -- slot = mesh * RCULL_MAX_LODS + lod, n_slots = meshes in the table * RCULL_MAX_LODS,
+ * every slot's instanceCount, empty slots included.  This is what a range-shard merge of the
+ * per-mesh lists all_gathers (renderer_b200/shard.py plan_merge_per_mesh).  The scratch
+ * is shared by the output sets: read it before the next rcull_frame. */
+int rcull_get_slot_counts(rcull_ctx *ctx, uint32_t view, uint32_t **counts, uint32_t *n_slots);
+/* Blocking copy of counts[0 .. n_slots) for tests and host-side merges. */
+int rcull_download_slot_counts(rcull_ctx *ctx, uint32_t view, uint32_t *counts, uint32_t n_slots);
+
 /* ---- Stage 2: per-triangle cull + command compaction -------------
  * Consolidated position / index buffers (ConsolidatedMeshBuffers.position_buffer / index_buffer,
  * consolidate_mesh_buffers.rs:26-35; vec3 and u32, scalar layout).  Host pointers, copied

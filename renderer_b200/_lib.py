@@ -111,6 +111,8 @@ SYMBOLS = {
     "rcull_download_flags": (C.c_int, [_P, _u32, _u32, _u64, _u64, _P]),
     "rcull_download_cmds": (C.c_int, [_P, _u32, _u32, _u64, _u64, _P]),
     "rcull_download_visible": (C.c_int, [_P, _u32, _u32, _u64, _u64, _P]),
+    "rcull_get_slot_counts": (C.c_int, [_P, _u32, C.POINTER(_P), C.POINTER(_u32)]),
+    "rcull_download_slot_counts": (C.c_int, [_P, _u32, _P, _u32]),
     "rcull_set_geometry": (C.c_int, [_P, _P, _u64, _P, _u64]),
     "rcull_tri_cull": (C.c_int, [_P, _P, _u32, _u32, _P]),
     "rcull_get_tri_outputs": (C.c_int, [_P, C.POINTER(TriOutputs)]),

@@ -221,6 +221,12 @@ class CullContext:
         check(self._lib.rcull_download_tri(self._h, ptr(count), None, None, 0, ptr(out), first, n))
         return out
 
+    def slot_counts(self, view: int, n_slots: int) -> np.ndarray:
+        """Per-mesh instanced mode: survivors per (mesh, lod) slot of one view after the last frame."""
+        out = np.zeros(n_slots, np.uint32)
+        check(self._lib.rcull_download_slot_counts(self._h, view, ptr(out), n_slots))
+        return out
+
     # -- acceleration-structure instance records (acceleration_strucures.rs:419-445) -------
     def set_blas_table(self, addresses: np.ndarray) -> None:
         a = np.ascontiguousarray(addresses, dtype=np.uint64)

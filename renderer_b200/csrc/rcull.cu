@@ -433,6 +433,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
         CU(cudaMemsetAsync(o.counts, 0, kMaxViews * 4, s));
         CU(cudaMemsetAsync(o.totals, 0, kMaxViews * 8, s));
         if (c->meta_out) CU(cudaMemsetAsync(c->meta_out + (size_t)buffer_ix * 2 * c->cfg.max_views, 0, 2 * c->cfg.max_views * 8, s));
+        if (per_mesh) CU(cudaMemsetAsync(c->slot_total, 0, (size_t)c->n_meshes * kMaxLods * c->cfg.max_views * 4, s));  // rcull_get_slot_counts
         return RCULL_OK;
     }
     const uint32_t n_tiles = (uint32_t)((n + kTile - 1) / kTile);
@@ -676,6 +677,28 @@ int rcull_frame_frozen(rcull_ctx* c, uint64_t n, uint32_t buffer_ix, void* strea
     model_only<<<c->sm_count * 8, 256, 0, (cudaStream_t)stream>>>(c->pos_scale, c->rot, (uint32_t)n, c->out[buffer_ix].model);
     CU(cudaGetLastError());
     c->launches += 1;
+    return RCULL_OK;
+}
+
+int rcull_get_slot_counts(rcull_ctx* c, uint32_t view, uint32_t** counts, uint32_t* n_slots) {
+    if (!c || !counts || !n_slots) return fail(RCULL_ERR_INVALID, "rcull_get_slot_counts: null argument");
+    if (c->cfg.output_mode != RCULL_PER_MESH_INSTANCED) return fail(RCULL_ERR_INVALID, "slot counts exist in per-mesh instanced mode only");
+    if (view >= c->cfg.max_views) return fail(RCULL_ERR_INVALID, "view %u of %u", view, c->cfg.max_views);
+    if (c->n_meshes == 0) return fail(RCULL_ERR_INVALID, "rcull_set_mesh_table has not been called");
+    *n_slots = c->n_meshes * kMaxLods;
+    *counts = c->slot_total + (size_t)view * *n_slots;  // rows are packed at the table's slot count (BucketArgs.n_slots)
+    return RCULL_OK;
+}
+
+int rcull_download_slot_counts(rcull_ctx* c, uint32_t view, uint32_t* counts, uint32_t n_slots) {
+    uint32_t* src = nullptr;
+    uint32_t have = 0;
+    int rc = rcull_get_slot_counts(c, view, &src, &have);
+    if (rc) return rc;
+    if (!counts || n_slots > have) return fail(RCULL_ERR_INVALID, "rcull_download_slot_counts: %u slots asked, %u exist", n_slots, have);
+    CU(cudaSetDevice(c->cfg.device));
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(counts, src, (size_t)n_slots * 4, cudaMemcpyDeviceToHost));
     return RCULL_OK;
 }
 

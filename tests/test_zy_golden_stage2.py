@@ -89,3 +89,29 @@ def test_gpu_per_mesh_mode_matches_the_fixture():
         for k in range(len(views)):
             assert counts[k] == len(g[f"pm_cmds_{k}"]) and totals[k] == len(g[f"pm_visible_{k}"])
             check_per_mesh(g, k, ctx.cmds(k, int(counts[k])), ctx.visible(k, int(totals[k])))
+
+
+@pytest.mark.gpu
+def test_gpu_slot_counts_are_the_instance_counts_of_every_slot():
+    """rcull_get_slot_counts / rcull_download_slot_counts: what a range-shard merge of the per-mesh lists
+    all_gathers (shard.plan_merge_per_mesh) -- every slot's survivors, empty slots included."""
+    from renderer_b200 import PER_MESH_INSTANCED, CullContext, RcullError
+
+    g = np.load(GOLDEN)
+    meshes, views = g["meshes"], g["pm_views"]
+    n, n_slots = int(g["pm_n"]), len(meshes) * 6
+    ps, rot, mesh = scene.synth_entities(int(g["seed"]), 0, n, float(g["pm_half_box"]), len(meshes))
+    with CullContext(n, max_views=len(views), max_meshes=len(meshes), output_mode=PER_MESH_INSTANCED) as ctx:
+        ctx.set_mesh_table(meshes)
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(views, g["cam_pos"], draw_index_base=int(g["pm_base"]))
+        for k in range(len(views)):
+            got = ctx.slot_counts(k, n_slots)
+            assert np.array_equal(got[got > 0], g[f"pm_cmds_{k}"]["instanceCount"])
+            assert int(got.sum()) == len(g[f"pm_visible_{k}"])
+        with pytest.raises(RcullError):
+            ctx.slot_counts(0, n_slots + 1)
+    with CullContext(n, max_views=1, max_meshes=len(meshes)) as ctx:  # per-entity mode has no slots
+        ctx.set_mesh_table(meshes)
+        with pytest.raises(RcullError):
+            ctx.slot_counts(0, n_slots)
