@@ -190,7 +190,7 @@ int make_model_map(CUtensorMap* map, float4* model, uint64_t cap) {
 extern "C" {
 
 const char* rcull_last_error(void) { return g_err; }
-uint32_t rcull_version(void) { return (0u << 16) | 2u; }  // 0.2: triangle stage, rcull_config.capacity_tri_indices
+uint32_t rcull_version(void) { return (0u << 16) | 3u; }  // 0.2: triangle stage, rcull_config.capacity_tri_indices; 0.3: slot counts
 
 void rcull_destroy(rcull_ctx* c) {
     if (!c) return;
