@@ -6,7 +6,7 @@
 // What mirrors what (paths relative to the reference tree):
 //   Position / Rotation / Scale / ModelMatrix / AABB / Light   src/ecs/components.rs:5-27
 //   GltfMesh (as the row of the mesh table)                    src/renderer.rs:117-126
-//   Camera + project_camera                                    src/ecs/resources/camera_controller.rs:6-24, src/ecs.rs:66-91
+//   Camera + project_camera                                    src/ecs/camera_controller.rs:10-24, src/ecs.rs:66-91
 //   shadow_mapping_mvp_calculation (per-light pv)              src/renderer/systems/shadow_mapping.rs:314-342
 //   ImageIndex / DoubleBuffered::current                       src/renderer/helpers/double_buffered.rs:17-19
 //   RuntimeConfiguration.freeze_culling                        src/renderer/systems/cull_pipeline.rs:331-421
@@ -52,7 +52,7 @@ static_assert(sizeof(Position) == 12 && sizeof(Rotation) == 16 && sizeof(Scale) 
 static_assert(sizeof(ModelMatrix) == 64 && sizeof(AABB) == 24 && sizeof(rcull_draw_cmd) == 20, "component layout");
 
 // ---- resources ------------------------------------------------------------------------------
-// Camera (camera_controller.rs:6-24): default position (0, 1, 2), identity rotation.
+// Camera (src/ecs/camera_controller.rs:10-24): default position (0, 1, 2), identity rotation.
 struct Camera {
     float position[3] = {0.f, 1.f, 2.f};
     float rotation[4] = {0.f, 0.f, 0.f, 1.f};  // i, j, k, w

@@ -114,3 +114,22 @@ def test_sass_of_the_frame_kernel():
         assert "UBLKCP" in text, f"no bulk TMA load in {name}"
         assert "UTMASTG" in text, f"no TMA tensor store in {name}"
         assert "FMUL2" in text and "SYNCS" in text
+
+
+def test_rust_ffi_file_is_generated_from_the_current_header():
+    """integration/rust/rcull_ffi.rs (source only: no rustc here) declares every entry point of rcull.h and is
+    what gen_ffi.py produces from the header as it stands."""
+    import importlib.util
+
+    rust = os.path.join(os.path.dirname(HEADER), "..", "integration", "rust")
+    spec = importlib.util.spec_from_file_location("gen_ffi", os.path.join(rust, "gen_ffi.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    text = open(os.path.join(rust, "rcull_ffi.rs")).read()
+    assert text == gen.generate(), "run python integration/rust/gen_ffi.py"
+    declared = re.findall(r"pub fn (rcull_\w+)\(", text)
+    assert sorted(declared) == declared_functions()
+    for name, (res, args) in _lib.SYMBOLS.items():  # same arity as the ctypes binding
+        params = re.search(r"pub fn %s\((.*?)\)( -> [^;]+)?;" % name, text)
+        assert len([p for p in params.group(1).split(",") if p.strip()]) == len(args), name
+        assert (params.group(2) is None) == (res is None), name
