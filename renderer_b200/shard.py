@@ -139,6 +139,7 @@ class ShardMerger:
 # needs to place every bucket.
 @dataclass
 class PerMeshMergePlan:
+    counts_all: np.ndarray  # [world, S] as gathered
     slot_counts: np.ndarray  # [S] merged survivors per slot
     slot_start: np.ndarray  # [S] exclusive prefix over slots = firstInstance of the slot's command
     dest: np.ndarray  # [world, S] start of rank r's bucket of slot s in the MERGED visible list
@@ -162,7 +163,7 @@ def plan_merge_per_mesh(slot_counts_all: np.ndarray) -> PerMeshMergePlan:
     totals = c.sum(axis=0)
     start = _exclusive(totals, 0)
     per_rank = c.sum(axis=1)
-    return PerMeshMergePlan(totals, start, start[None, :] + _exclusive(c, 0), _exclusive(c, 1), _exclusive(per_rank, 0), int(per_rank.sum()))
+    return PerMeshMergePlan(c, totals, start, start[None, :] + _exclusive(c, 0), _exclusive(c, 1), _exclusive(per_rank, 0), int(per_rank.sum()))
 
 
 def per_mesh_commands(meshes: np.ndarray, plan: PerMeshMergePlan, max_lods: int = 6) -> np.ndarray:
@@ -183,10 +184,7 @@ def per_mesh_commands(meshes: np.ndarray, plan: PerMeshMergePlan, max_lods: int 
 
 def per_mesh_permutation(plan: PerMeshMergePlan) -> np.ndarray:
     """perm with merged[j] = staged[perm[j]], staged = the ranks' own bucketed lists back to back in rank order."""
-    # [world, S] bucket lengths, recovered from the prefixes
-    src_end = np.concatenate([plan.src[:, 1:], np.diff(np.append(plan.rank_base, plan.total)).reshape(-1, 1).astype(plan.src.dtype)], axis=1)
-    c = (src_end - plan.src).astype(np.int64)
-    seg_len = c.reshape(-1)
+    seg_len = plan.counts_all.astype(np.int64).reshape(-1)  # one segment per (rank, slot) bucket
     seg_dst = plan.dest.astype(np.int64).reshape(-1)
     seg_src = (plan.rank_base.astype(np.int64)[:, None] + plan.src.astype(np.int64)).reshape(-1)
     within = np.arange(int(seg_len.sum()), dtype=np.int64) - np.repeat(np.cumsum(seg_len) - seg_len, seg_len)
