@@ -146,9 +146,17 @@ def cpu_baseline(wl, steps: int, warmup: int, threads: int):
         if i >= warmup:
             fused.append(time.perf_counter() - t0)
     tf = float(np.mean(fused))
+    # "1 thread and all online cores" -- one untimed + one timed reference-shaped step on a single thread
+    n1 = min(n, 1 << 19)
+    one = []
+    for i in range(2):
+        t0 = time.perf_counter()
+        O.frame(pos[:n1], quat[:n1], scale[:n1], mesh[:n1], meshes, views, scene.CAMERA_POS, n_threads=1, want=("cmds", "visible"))
+        one.append(time.perf_counter() - t0)
     return {"value": n / t, "unit": UNIT, "cores": threads, "kind": "port",
             "sample": f"first {n} entities of the workload, {wl['n_views']} views, {steps} steps, reference-shaped passes + serial emit",
             "ms_per_step": t * 1e3, "visible": [int(c) for c in r["counts"]],
+            "one_thread": {"value": n1 / one[1], "unit": UNIT, "sample": f"first {n1} entities, reference-shaped, 1 thread"},
             "fused": {"value": n / tf, "unit": UNIT, "ms_per_step": tf * 1e3,
                       "note": "oracle_frame_fused: one pass per entity, per-thread counts + prefix, parallel emit; same results"}}
 
@@ -463,7 +471,7 @@ def reference_arm(args, wl):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload, "entities_per_step": n_sample, "n_views": wl["n_views"], "half_box": wl["half_box"],
                    "note": "CPU oracle (C restatement of the reference's bevy systems; Rust toolchain absent), all host threads"},
-        "cpu_baseline": {k: b[k] for k in ("value", "unit", "cores", "kind", "sample", "fused")},
+        "cpu_baseline": {k: b[k] for k in ("value", "unit", "cores", "kind", "sample", "fused", "one_thread")},
         "e2e": {"value": b["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
 
