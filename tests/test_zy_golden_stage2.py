@@ -115,3 +115,43 @@ def test_gpu_slot_counts_are_the_instance_counts_of_every_slot():
         ctx.set_mesh_table(meshes)
         with pytest.raises(RcullError):
             ctx.slot_counts(0, n_slots)
+
+
+def merge_per_mesh_parts(parts, meshes):
+    """parts[r] = (bucketed visible list, slot counts) of rank r for one view -> (merged commands, merged visible list)."""
+    from renderer_b200.shard import per_mesh_commands, per_mesh_permutation, plan_merge_per_mesh
+
+    plan = plan_merge_per_mesh(np.stack([p[1] for p in parts]))
+    staged = np.concatenate([p[0] for p in parts])
+    return per_mesh_commands(meshes, plan), staged[per_mesh_permutation(plan)], plan.slot_counts.astype(np.uint32)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 3])
+def test_gpu_per_mesh_range_shards_merge_to_the_single_range_output(world):
+    """SURVEY 8e, per-mesh mode: `world` contiguous ranges run one after the other on this GPU (global draw
+    indices, rcull_get_slot_counts), merged on the host with shard.plan_merge_per_mesh -- commands and bucketed
+    visible lists equal what one context produces for the whole range."""
+    from renderer_b200 import PER_MESH_INSTANCED, CullContext
+    from renderer_b200.shard import shard_range
+
+    meshes, views, n = scene.synth_mesh_table(), scene.scene_views(2), 40_001
+    n_slots = len(meshes) * 6
+    ps, rot, mesh = scene.synth_entities(scene.SEED + 9, 0, n, 35.0, len(meshes))
+
+    def run(lo, hi):
+        with CullContext(hi - lo, max_views=2, max_meshes=len(meshes), output_mode=PER_MESH_INSTANCED) as ctx:
+            ctx.set_mesh_table(meshes)
+            ctx.upload_entities(ps[lo:hi], rot[lo:hi], mesh[lo:hi])
+            ctx.frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+            counts, totals = ctx.counts()
+            return [(ctx.cmds(k, int(counts[k])), ctx.visible(k, int(totals[k])), ctx.slot_counts(k, n_slots)) for k in range(2)]
+
+    whole = run(0, n)
+    parts = [run(*shard_range(n, world, r)) for r in range(world)]
+    for k in range(2):
+        cmds, visible, slot_counts = merge_per_mesh_parts([(parts[r][k][1], parts[r][k][2]) for r in range(world)], meshes)
+        assert len(whole[k][1]) > 0
+        assert np.array_equal(visible, whole[k][1]), f"view {k} merged visible list"
+        assert np.array_equal(cmds, whole[k][0]), f"view {k} merged commands"
+        assert np.array_equal(slot_counts, whole[k][2])
