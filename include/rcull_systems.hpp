@@ -146,9 +146,12 @@ inline rcull_view light_frustum(const Light& light) {
 // model_matrices_upload and cull_pass' emit loop.  Columns are the query's components in
 // iteration order; views = camera + one per light.  Outputs stay on the device
 // (rcull_get_outputs); counts / index totals land in `rc`.
+// With runtime_config.freeze_culling the reference runs cull_pass_bypass (cull_pipeline.rs:331-421):
+// the entities keep moving and their model matrices follow, the draw lists, counts and culled
+// indices stay those of the last unfrozen frame.
 inline void gpu_transform_cull(RcullRes& rc, ImageIndex image_index, const Camera& camera, const std::vector<Light>& lights,
-                               const Position* position, const Rotation* rotation, const Scale* scale,
-                               const GltfMesh* gltf_mesh, uint64_t n_entities, uint32_t draw_index_base = 0) {
+                               const RuntimeConfiguration& runtime_config, const Position* position, const Rotation* rotation,
+                               const Scale* scale, const GltfMesh* gltf_mesh, uint64_t n_entities, uint32_t draw_index_base = 0) {
     rc.pos_scale.resize(4 * n_entities);
     rc.rot.resize(4 * n_entities);
     rc.mesh.resize(n_entities);
@@ -156,6 +159,13 @@ inline void gpu_transform_cull(RcullRes& rc, ImageIndex image_index, const Camer
                                  reinterpret_cast<const float*>(scale), rc.pos_scale.data(), rc.rot.data()),
            "rcull_pack_components");
     for (uint64_t e = 0; e < n_entities; ++e) rc.mesh[e] = gltf_mesh[e].table_row;
+
+    if (runtime_config.freeze_culling) {
+        expect(rcull_upload_entities(rc.ctx(), 0, n_entities, rc.pos_scale.data(), rc.rot.data(), rc.mesh.data(), nullptr),
+               "rcull_upload_entities");
+        expect(rcull_frame_frozen(rc.ctx(), n_entities, image_index.ix, nullptr), "rcull_frame_frozen");
+        return;  // rc.counts / rc.index_totals / rc.n_views keep describing the lists that are drawn
+    }
 
     std::vector<rcull_view> views;
     views.reserve(1 + lights.size());
@@ -171,14 +181,12 @@ inline void gpu_transform_cull(RcullRes& rc, ImageIndex image_index, const Camer
     rc.n_views = static_cast<uint32_t>(views.size());
 }
 
-// The second half of cull_pass: per-triangle cull of the camera view's survivors + compact_draw_stream;
-// with freeze_culling on, cull_pass_bypass' behaviour (only the model matrices are refreshed).
+// The second half of cull_pass: per-triangle cull of the camera view's survivors + compact_draw_stream.
+// Frozen frames keep the triangle-stage outputs of the last unfrozen frame (cull_pass_bypass copies the
+// buffers onto themselves), so there is nothing to launch.
 inline void gpu_cull_triangles(RcullRes& rc, ImageIndex image_index, const Camera& camera, const RuntimeConfiguration& runtime_config,
                                uint32_t draw_index_base = 0) {
-    if (runtime_config.freeze_culling) {
-        expect(rcull_frame_frozen(rc.ctx(), rc.n_entities, image_index.ix, nullptr), "rcull_frame_frozen");
-        return;
-    }
+    if (runtime_config.freeze_culling) return;
     expect(rcull_tri_cull(rc.ctx(), camera.pv, draw_index_base, image_index.ix, nullptr), "rcull_tri_cull");
 }
 

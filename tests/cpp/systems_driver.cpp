@@ -128,8 +128,8 @@ int main(int argc, char** argv) {
         rc.set_geometry(s.positions_xyz, s.indices);
         rc.set_blas_table(s.blas);
         const ImageIndex image_index{0};
-        gpu_transform_cull(rc, image_index, s.camera, {}, s.position.data(), s.rotation.data(), s.scale.data(), s.gltf_mesh.data(),
-                           s.n, s.draw_index_base);
+        gpu_transform_cull(rc, image_index, s.camera, {}, RuntimeConfiguration{}, s.position.data(), s.rotation.data(),
+                           s.scale.data(), s.gltf_mesh.data(), s.n, s.draw_index_base);
         gpu_cull_triangles(rc, image_index, s.camera, RuntimeConfiguration{}, s.draw_index_base);
         const TriangleStage t = download_triangle_stage(rc);
         const std::vector<uint32_t> culled = download_culled_indices(rc, 0, rc.index_totals[0]);
@@ -178,8 +178,8 @@ int main(int argc, char** argv) {
     rc.set_mesh_table(s.meshes);
 
     const ImageIndex image_index{1};
-    gpu_transform_cull(rc, image_index, s.camera, s.lights, s.position.data(), s.rotation.data(), s.scale.data(),
-                       s.gltf_mesh.data(), s.n, s.draw_index_base);
+    gpu_transform_cull(rc, image_index, s.camera, s.lights, RuntimeConfiguration{}, s.position.data(), s.rotation.data(),
+                       s.scale.data(), s.gltf_mesh.data(), s.n, s.draw_index_base);
 
     put(out, &rc.n_views);
     put(out, rc.counts, RCULL_MAX_VIEWS);
@@ -205,15 +205,11 @@ int main(int argc, char** argv) {
     // freeze_culling: the entities keep moving (here: every Scale doubles) but only the model
     // matrices follow; counts and lists stay those of the frame above (cull_pipeline.rs:331-421).
     for (Scale& sc : s.scale) sc.s *= 2.f;
-    expect(rcull_pack_components(s.n, reinterpret_cast<const float*>(s.position.data()),
-                                 reinterpret_cast<const float*>(s.rotation.data()),
-                                 reinterpret_cast<const float*>(s.scale.data()), rc.pos_scale.data(), rc.rot.data()),
-           "rcull_pack_components");
-    expect(rcull_upload_entities(rc.ctx(), 0, s.n, rc.pos_scale.data(), rc.rot.data(), rc.mesh.data(), nullptr),
-           "rcull_upload_entities");
-    RuntimeConfiguration runtime_config;
-    runtime_config.freeze_culling = true;
-    gpu_cull_triangles(rc, image_index, s.camera, runtime_config, s.draw_index_base);
+    RuntimeConfiguration frozen_config;
+    frozen_config.freeze_culling = true;
+    gpu_transform_cull(rc, image_index, s.camera, s.lights, frozen_config, s.position.data(), s.rotation.data(), s.scale.data(),
+                       s.gltf_mesh.data(), s.n, s.draw_index_base);
+    gpu_cull_triangles(rc, image_index, s.camera, frozen_config, s.draw_index_base);  // nothing to launch
     const std::vector<ModelMatrix> frozen = download_model(rc, image_index);
     put(out, frozen.data(), frozen.size());
     uint32_t counts_after[RCULL_MAX_VIEWS] = {};
