@@ -217,7 +217,9 @@ inline std::vector<rcull_draw_cmd> download_commands(RcullRes& rc, ImageIndex ix
     return out;
 }
 inline std::vector<DrawIndex> download_visible(RcullRes& rc, ImageIndex ix, uint32_t view) {
-    std::vector<DrawIndex> out(rc.counts[view]);
+    // per-entity mode: one entry per command; per-mesh instanced mode: one per instance (index_totals counts instances there)
+    const uint64_t n = rc.config().output_mode == RCULL_PER_MESH_INSTANCED ? rc.index_totals[view] : rc.counts[view];
+    std::vector<DrawIndex> out(n);
     if (!out.empty()) expect(rcull_download_visible(rc.ctx(), ix.ix, view, 0, out.size(), &out[0].ix), "rcull_download_visible");
     return out;
 }
