@@ -36,7 +36,7 @@ WORKLOADS = {
 }
 METRIC = "entities/sec transformed+culled+compacted"
 UNIT = "entities/s"
-CPU_SAMPLE = 2 * 1024 * 1024  # entities per CPU-baseline step (bounded sample of the workload)
+SM_ISSUE_SLOTS = 148 * 4  # warp instructions per clock the chip can issue (one per SM sub-partition)
 
 
 L2_NOTE = "flushed between iterations (256 MB write, then a 256 MB read so that the timed kernel does not pay for writing the flush's dirty lines back)"
@@ -57,6 +57,33 @@ def load_peaks():
             return float(json.load(f)["hbm_gbs"]), "measured"
     except Exception:
         return 6650.0, "fallback"
+
+
+def load_counters():
+    """ncu-derived constants (profiles/r02_counters.json, written from the committed captures): DRAM traffic per
+    launch and executed warp instructions per unit of work.  They are cross-references measured under the profiler,
+    NOT measured in this run -- every use carries its `source` label."""
+    for name in ("r02_counters.json",):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                return json.load(f)
+        except Exception:
+            pass
+    return {}
+
+
+def oracle_views(n_views: int):
+    """The views of renderer_b200.scene.scene_views, computed by the ORACLE's project_camera / light_view (bit-equal to
+    the library's host helpers, tests/test_oracle.py): the reference arm maps no product library."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    from renderer_b200 import scene  # constants and numpy helpers only: nothing here loads librcull.so
+
+    vs = [O.project_camera(16.0 / 9.0, scene.CAMERA_POS, scene.CAMERA_ROT)[3]]
+    for k in range(n_views - 1):
+        pos = np.ascontiguousarray(scene.LIGHT_POS[k % len(scene.LIGHT_POS)] * (1.0 + 0.25 * (k // len(scene.LIGHT_POS))), np.float32)
+        vs.append(O.light_view(pos, scene.quat_look_at_lh(-pos.astype(np.float64)))[3])
+    return np.stack(vs).astype(np.float32)
 
 
 class ClockSampler:
@@ -118,17 +145,18 @@ class ClockSampler:
                 "reasons": sorted(v for k, v in self.REASONS.items() if mask & k), "samples": len(self.samples), "how": self.how}
 
 
-def cpu_baseline(wl, steps: int, warmup: int, threads: int):
-    """The oracle (kind "port") on a bounded sample of the workload, all host threads."""
+def cpu_baseline(wl, steps: int, warmup: int, threads: int, fused_steps: int = 3):
+    """The oracle (kind "port") on the WHOLE workload (the same entities, views and mesh table the GPU arm runs; the
+    sample is bounded through the step count), all host threads.  Inputs and planes come from the oracle's own
+    generator and project_camera / light_view, so this leg maps no product library."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as O  # CPU-baseline leg: the one place bench.py may execute oracle/
-    from renderer_b200 import scene
+    from renderer_b200 import scene  # numpy-only helpers (mesh table, constants)
 
-    n = min(CPU_SAMPLE, wl["n"])
-    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, wl["half_box"])
-    pos, quat, scale = scene.to_components(ps, rot)
+    n = wl["n"]
     meshes = scene.synth_mesh_table()
-    views = scene.scene_views(wl["n_views"])
+    pos, quat, scale, mesh = O.synth_entities(scene.SEED, 0, n, wl["half_box"], len(meshes))
+    views = oracle_views(wl["n_views"])
     times = []
     for i in range(warmup + steps):
         t0 = time.perf_counter()
@@ -140,10 +168,10 @@ def cpu_baseline(wl, steps: int, warmup: int, threads: int):
     # the same oracle functions on a fused schedule (one pass per entity, parallel emit) --
     # the stronger CPU baseline, reported beside the reference-shaped one
     fused = []
-    for i in range(warmup + steps):
+    for i in range(1 + fused_steps):
         t0 = time.perf_counter()
         O.frame(pos, quat, scale, mesh, meshes, views, scene.CAMERA_POS, n_threads=threads, want=("cmds", "visible"), fused=True)
-        if i >= warmup:
+        if i >= 1:
             fused.append(time.perf_counter() - t0)
     tf = float(np.mean(fused))
     # "1 thread and all online cores" -- one untimed + one timed reference-shaped step on a single thread
@@ -154,10 +182,10 @@ def cpu_baseline(wl, steps: int, warmup: int, threads: int):
         O.frame(pos[:n1], quat[:n1], scale[:n1], mesh[:n1], meshes, views, scene.CAMERA_POS, n_threads=1, want=("cmds", "visible"))
         one.append(time.perf_counter() - t0)
     return {"value": n / t, "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": f"first {n} entities of the workload, {wl['n_views']} views, {steps} steps, reference-shaped passes + serial emit",
+            "sample": f"all {n} entities of the workload, {wl['n_views']} views, {steps} steps, reference-shaped passes + serial emit",
             "ms_per_step": t * 1e3, "visible": [int(c) for c in r["counts"]],
             "one_thread": {"value": n1 / one[1], "unit": UNIT, "sample": f"first {n1} entities, reference-shaped, 1 thread"},
-            "fused": {"value": n / tf, "unit": UNIT, "ms_per_step": tf * 1e3,
+            "fused": {"value": n / tf, "unit": UNIT, "ms_per_step": tf * 1e3, "steps": fused_steps,
                       "note": "oracle_frame_fused: one pass per entity, per-thread counts + prefix, parallel emit; same results"}}
 
 
@@ -319,6 +347,28 @@ def gpu_arm(args, wl):
     t_e2e = time.perf_counter() - t0
     assert np.array_equal(np.asarray(c_e2e, np.int64), counts), "end-to-end path disagrees with the resident path"
 
+    # ---- end to end WITH the results back: the same call + the draw lists of every view into pinned host memory ----
+    e2e_lists = None
+    if world == 1:
+        cap_l = int(counts.max()) + 1024
+        h_cmds = [torch.empty((cap_l, 5), dtype=torch.int32).pin_memory() for _ in range(n_views)]
+        h_vis = [torch.empty((cap_l,), dtype=torch.int32).pin_memory() for _ in range(n_views)]
+        pc, pvis = [t.data_ptr() for t in h_cmds], [t.data_ptr() for t in h_vis]
+        for _ in range(2):
+            c_l, _ = ctx.frame_host_lists(a_ps, a_rot, a_mesh, views, scene.CAMERA_POS, pc, pvis, cap_l, draw_index_base=lo)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            c_l, _ = ctx.frame_host_lists(a_ps, a_rot, a_mesh, views, scene.CAMERA_POS, pc, pvis, cap_l, draw_index_base=lo)
+        t_l = time.perf_counter() - t0
+        assert np.array_equal(np.asarray(c_l, np.int64), counts)
+        k_chk = n_views - 1  # spot check of what came back: ascending draw indices, firstInstance == visible index
+        v_chk = h_vis[k_chk].numpy()[: int(counts[k_chk])].view(np.uint32)
+        assert np.all(np.diff(v_chk.astype(np.int64)) > 0) and np.array_equal(h_cmds[k_chk].numpy()[: int(counts[k_chk]), 4].view(np.uint32), v_chk)
+        e2e_lists = {"value": n * e2e_steps / t_l, "unit": UNIT, "h2d_bytes_per_step": n * 36, "d2h_bytes_per_step": 96 + 24 * int(counts.sum()),
+                     "steps": e2e_steps, "ms_per_step": t_l / e2e_steps * 1e3,
+                     "api": "rcull_frame_host_lists (pinned host columns in; counts, index totals and the draw lists of every view out)"}
+
     # ---- N > 1: the merged lists of the peer-store exchange against an NCCL allgatherv of the same frame ----
     merge_verified = None
     if world > 1 and args.merge == "p2p":
@@ -373,7 +423,10 @@ def gpu_arm(args, wl):
             },
             "e2e": {"value": n_total * e2e_steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": n * 36,
                     "d2h_bytes_per_step": 96, "steps": e2e_steps, "ms_per_step": t_e2e / e2e_steps * 1e3,
-                    "api": "rcull_frame_host (pinned host columns in, counts + index totals out)"},
+                    "api": "rcull_frame_host (pinned host columns in, counts + index totals out)",
+                    "result_resident": True,
+                    "note": "model matrices and draw lists stay on the device, as the reference's consumers (indirect draws) read them there; e2e_lists also brings the lists back"},
+            "e2e_lists": e2e_lists,
             "gpu_launches": int(launches),
             "merge": None if world == 1 else {
                 # pipelined: what the step costs beyond the frame kernel (the exchange itself runs under the next frame)
@@ -388,27 +441,22 @@ def gpu_arm(args, wl):
                          "bytes_per_entity": bytes_per_entity, "ms_per_launch": t_launch * 1e3},
             "clocks": clocks.summary(),
         }
+        counters = load_counters()
         if tri:
             n_cmd, kept = ctx.tri_counts()
-            t_tri = (t_step - t_frame) / args.steps
-            tris = int(totals[0]) // 3
-            line["tri_stage"] = {
-                "kernels": "tri_cull + compact_draw_stream", "ms_per_step": t_tri * 1e3, "triangles_in": tris, "triangles_kept": kept // 3,
-                "commands_in": int(counts[0]), "commands_out": n_cmd, "gtri_per_s": tris / t_tri / 1e9,
-                # 12 B index triple read per triangle, 12 B written per kept one, 20 + 4 B command in, 20 B out
-                "algorithmic_gbs": (12.0 * tris + 4.0 * kept + 24.0 * int(counts[0]) + 20.0 * n_cmd) / t_tri / 1e9,
-                "meshes": "grid sheets, row-major cell order (vertex reuse like an indexed glTF mesh)" if wl.get("coherent") else "random index triples (no vertex reuse)",
-                "note": "e2e and cpu_baseline cover the frame stage only"}
-        if world == 1:
+            line["tri_stage"] = tri_stage_report(wl, (t_step - t_frame) / args.steps, int(totals[0]) // 3, kept, int(counts[0]), n_cmd,
+                                                 line["clocks"].get("sm_mhz"), counters)
+        if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(wl, steps=3, warmup=1, threads=os.cpu_count() or 1)
         if world == 1 and not args.no_also:
             line["also"] = [resident_timing(w, args.steps, local_rank) for w in ("16m_1view", "16m_5view", "1m_1view") if w != args.workload]
-        prof = os.path.join(ROOT, "profiles", "r01_traffic.json")
-        if os.path.exists(prof):
-            try:
-                line["roofline"]["traffic"] = json.load(open(prof)).get(args.workload)
-            except Exception:
-                pass
+            line["also"].append(resident_tri("1m_tri", args.steps, local_rank, counters))
+            line["also"].append(resident_per_mesh("sponza_4m", args.steps, local_rank))
+            line["also"] += resident_small_kernels(args.steps, local_rank)
+        tr = (counters.get("dram_bytes_per_launch") or {}).get(args.workload)
+        if tr:
+            line["roofline"]["traffic"] = tr["bytes"]
+            line["roofline"]["traffic_source"] = tr["source"] + " (ncu --set full capture; a cross-reference, not measured in this run)"
         print(json.dumps(line), flush=True)
     if merger is not None and hasattr(merger, "destroy"):
         merger.destroy()
@@ -458,19 +506,175 @@ def resident_timing(name, steps, device):
             "l2": L2_NOTE if flush is not None else "inputs (36 B x n) exceed L2"}
 
 
+def tri_stage_report(wl, t_tri, tris, kept, commands_in, commands_out, sm_mhz, counters):
+    """Stage 2 (tri_cull + compact_draw_stream).  The stage is bound by FP32 ISSUE, not by HBM (ncu: 370 GB/s of DRAM
+    traffic, 75 % of the issue slots busy): its roofline is the chip's issue rate -- one warp instruction per clock and
+    SM sub-partition -- and `achieved` is the executed warp instructions (per-triangle count from the committed ncu
+    capture, labelled) over the time measured here."""
+    peak, _ = load_peaks()
+    # 12 B index triple read per triangle, 12 B written per kept one, 20 + 4 B command in, 20 B out
+    alg = 12.0 * tris + 4.0 * kept + 24.0 * commands_in + 20.0 * commands_out
+    out = {"kernels": "tri_cull + compact_draw_stream", "ms_per_step": t_tri * 1e3, "triangles_in": tris, "triangles_kept": kept // 3,
+           "commands_in": commands_in, "commands_out": commands_out, "gtri_per_s": tris / t_tri / 1e9,
+           "algorithmic_gbs": alg / t_tri / 1e9, "hbm_frac": alg / t_tri / 1e9 / peak,
+           "meshes": "grid sheets, row-major cell order (vertex reuse like an indexed glTF mesh)" if wl.get("coherent") else "random index triples (no vertex reuse)",
+           "note": "e2e and cpu_baseline cover the frame stage only"}
+    ipt = (counters.get("warp_inst_per_unit") or {}).get("tri_cull")
+    if ipt and sm_mhz:
+        issue_peak = SM_ISSUE_SLOTS * sm_mhz * 1e6
+        ach = ipt["value"] * tris / t_tri
+        out["roofline"] = {"bound": "fp32_issue", "achieved": ach / 1e9, "peak": issue_peak / 1e9, "unit": "G warp-inst/s", "frac": ach / issue_peak,
+                           "warp_inst_per_triangle": ipt["value"], "warp_inst_source": ipt["source"],
+                           "peak_kind": f"148 SMs x 4 sub-partitions x {sm_mhz:.0f} MHz (SM clock sampled in this run)"}
+    return out
+
+
+def resident_tri(name, steps, device, counters):
+    """BASELINE configs[1] through both stages, resident: frame kernel, then tri_cull + compact_draw_stream."""
+    import torch
+
+    from renderer_b200 import CullContext, scene
+
+    wl = WORKLOADS[name]
+    n = wl["n"]
+    meshes = scene.synth_mesh_table()
+    views, pv = scene.scene_views(1), scene.camera_pv()
+    dev = torch.device("cuda", device)
+    stream = torch.cuda.Stream(device=dev)
+    sh = stream.cuda_stream
+    flush = torch.zeros((2, 256 * 1024 * 1024), dtype=torch.uint8, device=dev)
+    with CullContext(n, max_views=1, max_meshes=len(meshes), device=device) as probe:
+        probe.set_mesh_table(meshes)
+        probe.synth_entities(scene.SEED, 0, n, wl["half_box"], len(meshes))
+        probe.frame(views, scene.CAMERA_POS)
+        tri_cap = int(probe.counts()[1][0]) + 3
+    with CullContext(n, max_views=1, max_meshes=len(meshes), device=device, capacity_tri_indices=tri_cap) as ctx:
+        ctx.set_mesh_table(meshes)
+        ctx.set_geometry(*scene.synth_geometry(meshes, coherent=bool(wl.get("coherent"))))
+        ctx.synth_entities(scene.SEED, 0, n, wl["half_box"], len(meshes), stream=sh)
+        ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps)]
+        with ClockSampler(device) as clocks, torch.cuda.stream(stream):
+            for i in range(5 + steps):
+                j = i - 5
+                if j >= 0:
+                    ev[j][0].record(stream)
+                ctx.frame(views, scene.CAMERA_POS, stream=sh)
+                if j >= 0:
+                    ev[j][1].record(stream)
+                ctx.tri_cull(pv, stream=sh)
+                if j >= 0:
+                    ev[j][2].record(stream)
+                flush_l2(flush)
+            torch.cuda.synchronize()
+        t_frame = sum(e[0].elapsed_time(e[1]) for e in ev) / steps / 1e3
+        t_tri = sum(e[1].elapsed_time(e[2]) for e in ev) / steps / 1e3
+        counts, totals = ctx.counts()
+        n_cmd, kept = ctx.tri_counts()
+    rep = tri_stage_report(wl, t_tri, int(totals[0]) // 3, kept, int(counts[0]), n_cmd, clocks.summary().get("sm_mhz"), counters)
+    rep.update({"workload": name, "entities": n, "n_views": 1, "frame_ms": t_frame * 1e3, "l2": L2_NOTE})
+    return rep
+
+
+def resident_per_mesh(name, steps, device):
+    """BASELINE configs[3]: the Sponza mesh table instanced to 4 M entities, per-mesh indirect command compaction
+    (output_mode PER_MESH_INSTANCED): frame kernel + the bucketing passes, resident."""
+    import torch
+
+    from renderer_b200 import PER_MESH_INSTANCED, CullContext, scene
+
+    n, n_views = 4_000_000, 1
+    table, node_scale = scene.sponza_mesh_table()
+    ps, rot, mesh = scene.sponza_instances(n, len(table), node_scale)
+    views = scene.scene_views(n_views)
+    dev = torch.device("cuda", device)
+    stream = torch.cuda.Stream(device=dev)
+    sh = stream.cuda_stream
+    flush = torch.zeros((2, 256 * 1024 * 1024), dtype=torch.uint8, device=dev)
+    with CullContext(n, max_views=n_views, max_meshes=len(table), device=device, output_mode=PER_MESH_INSTANCED) as ctx:
+        ctx.set_mesh_table(table)
+        ctx.upload_entities(ps, rot, mesh)
+        ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(steps)]
+        l0 = 0
+        with torch.cuda.stream(stream):
+            for i in range(5 + steps):
+                j = i - 5
+                if j == 0:
+                    l0 = ctx.launch_count
+                if j >= 0:
+                    ev[j][0].record(stream)
+                ctx.frame(views, scene.CAMERA_POS, stream=sh)
+                if j >= 0:
+                    ev[j][1].record(stream)
+                flush_l2(flush)
+            torch.cuda.synchronize()
+        t = sum(a.elapsed_time(b) for a, b in ev) / steps / 1e3
+        launches = (ctx.launch_count - l0) / steps
+        counts, totals = ctx.counts()
+    peak, _ = load_peaks()
+    # SURVEY 8d: 36 B in + 64 B model out per entity, 4 B per survivor (bucketed visible index), 20 B per non-empty slot
+    alg = n * 100.0 + 4.0 * float(totals[0]) + 20.0 * float(counts[0])
+    return {"workload": name, "entities": n, "meshes": len(table), "n_views": n_views, "mode": "per-mesh instanced (BASELINE configs[3])",
+            "ms_per_step": t * 1e3, "value": n / t, "unit": UNIT, "launches_per_frame": launches, "commands": int(counts[0]), "instances": int(totals[0]),
+            "bytes_per_entity": alg / n, "achieved_gbs": alg / t / 1e9, "roofline_frac": alg / t / 1e9 / peak, "bound": "hbm", "l2": L2_NOTE}
+
+
+def resident_small_kernels(steps, device):
+    """The two small per-entity kernels beside the frame kernel: model_only (frozen-culling frames, 32 B in + 64 B out
+    per entity) and as_instances (acceleration-structure instance records, 68 B in + 64 B out), 16 Mi entities."""
+    import torch
+
+    from renderer_b200 import CullContext, scene
+
+    n = 16 * 1024 * 1024
+    meshes = scene.synth_mesh_table()
+    dev = torch.device("cuda", device)
+    stream = torch.cuda.Stream(device=dev)
+    sh = stream.cuda_stream
+    peak, _ = load_peaks()
+    out = []
+    with CullContext(n, max_views=1, max_meshes=len(meshes), device=device) as ctx:
+        ctx.set_mesh_table(meshes)
+        ctx.set_blas_table(np.arange(1, len(meshes) + 1, dtype=np.uint64) << np.uint64(12))
+        ctx.synth_entities(scene.SEED, 0, n, 600.0, len(meshes), stream=sh)
+        ctx.frame(scene.scene_views(1), scene.CAMERA_POS, stream=sh)
+        for name, fn, bpe in (("model_only_16m", lambda: ctx.frame_frozen(n, stream=sh), 96.0), ("as_instances_16m", lambda: ctx.as_instances(n, stream=sh), 132.0)):
+            ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(steps)]
+            with torch.cuda.stream(stream):
+                for i in range(3 + steps):
+                    j = i - 3
+                    if j >= 0:
+                        ev[j][0].record(stream)
+                    fn()
+                    if j >= 0:
+                        ev[j][1].record(stream)
+                torch.cuda.synchronize()
+            t = sum(a.elapsed_time(b) for a, b in ev) / steps / 1e3
+            out.append({"workload": name, "entities": n, "ms_per_step": t * 1e3, "value": n / t, "unit": UNIT, "bytes_per_entity": bpe,
+                        "achieved_gbs": n * bpe / t / 1e9, "roofline_frac": n * bpe / t / 1e9 / peak, "bound": "hbm",
+                        "l2": "inputs exceed L2"})
+    return out
+
+
 def reference_arm(args, wl):
+    """The reference's CPU path for this stage on the box's host cores: the oracle (the reference itself is Rust
+    nightly + Vulkan and cannot be built here), all host threads, on the SAME workload as the GPU arm -- every entity,
+    every view; the bound is the step count.  Maps no product library."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    b = cpu_baseline(wl, steps=args.steps, warmup=min(args.warmup, 2), threads=threads)
-    n_sample = min(CPU_SAMPLE, wl["n"])
+    n = wl["n"]
+    b = cpu_baseline(wl, steps=args.steps, warmup=args.warmup, threads=threads)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": b["value"], "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": min(args.warmup, 2), "ms_per_step": b["ms_per_step"], "higher_is_better": True,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": b["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "entities_per_step": n_sample, "n_views": wl["n_views"], "half_box": wl["half_box"],
-                   "note": "CPU oracle (C restatement of the reference's bevy systems; Rust toolchain absent), all host threads"},
+        "config": {"workload": args.workload, "entities_per_gpu": n, "entities_total": n * args.gpus, "n_views": wl["n_views"], "half_box": wl["half_box"],
+                   "visible_fraction_per_view": [round(c / float(n), 6) for c in b["visible"]],
+                   "sharding": "contiguous range per rank" if args.gpus > 1 else "none",
+                   "entities_per_step": n,
+                   "note": "CPU oracle (C restatement of the reference's bevy systems; Rust toolchain absent), all host threads"
+                           + ("; one rank's 16 Mi-entity shard per step (the bounded sample of the N-GPU workload)" if args.gpus > 1 else "")},
         "cpu_baseline": {k: b[k] for k in ("value", "unit", "cores", "kind", "sample", "fused", "one_thread")},
         "e2e": {"value": b["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
@@ -486,8 +690,10 @@ def main():
     ap.add_argument("--no-overlap", action="store_true", help="N > 1: run frame and merge back to back instead of pipelined")
     ap.add_argument("--workload", default="16m_5view", choices=sorted(WORKLOADS))
     ap.add_argument("--no-also", action="store_true", help="N = 1: skip the resident timings of the other entity-stage workloads")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiler runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    args.steps = max(args.steps, 1)
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
         reference_arm(args, wl)

@@ -122,6 +122,13 @@ int rcull_set_mesh_table(rcull_ctx *ctx, const rcull_mesh *meshes, uint32_t n);
  * products would (inf * 0 terms, src/ecs.rs:60-62). */
 int rcull_upload_entities(rcull_ctx *ctx, uint64_t first, uint64_t n, const float *pos_scale,
                           const float *rot, const uint32_t *mesh, void *stream);
+/* The context's own stream (created non-blocking): rcull_frame_host uploads and launches on it.  A
+ * host that mixes rcull_frame_host with the asynchronous entry points (rcull_tri_cull,
+ * rcull_as_instances, rcull_frame_frozen, rcull_upload_entities) passes this stream to them, so that
+ * all per-frame work of a context is ordered on ONE stream -- frame i + 1's upload must not overtake
+ * frame i's triangle stage (the render graph orders cull_pass after the uploads the same way,
+ * src/renderer.rs:2323-2391). */
+int rcull_context_stream(rcull_ctx *ctx, void **stream);
 /* Device pointers of the input columns, for callers that fill them in place. */
 int rcull_entity_ptrs(rcull_ctx *ctx, float **pos_scale, float **rot, uint32_t **mesh);
 /* AoS bevy components -> the SoA columns above (host side, no device work):
@@ -141,7 +148,10 @@ int rcull_frame(rcull_ctx *ctx, uint64_t n, const rcull_view *views, uint32_t n_
  * the reference keeps the draw lists, count and culled index buffer of the last unfrozen frame
  * (it copies the buffers onto themselves) while model_matrix_calculation and
  * model_matrices_upload still run.  Writes the model matrices of entities [0, n) into output set
- * buffer_ix and nothing else; the lists to draw from stay those of the last rcull_frame. */
+ * buffer_ix and nothing else.  CullPassData is single-buffered in the reference and only ModelData
+ * is DoubleBuffered (cull_pipeline.rs:70-84): after this call rcull_get_outputs(buffer_ix), the
+ * list / count downloads and rcull_tri_cull on buffer_ix resolve to the LISTS of the output set the
+ * last rcull_frame wrote (whatever its buffer_ix was) and to the MODEL matrices of buffer_ix. */
 int rcull_frame_frozen(rcull_ctx *ctx, uint64_t n, uint32_t buffer_ix, void *stream);
 
 /* Host-buffer convenience used by the end-to-end path: upload the columns,
@@ -150,6 +160,18 @@ int rcull_frame_host(rcull_ctx *ctx, uint64_t n, const float *pos_scale, const f
                      const uint32_t *mesh, const rcull_view *views, uint32_t n_views,
                      const float cam_pos[3], uint32_t draw_index_base, uint32_t buffer_ix,
                      uint32_t *counts_out, uint64_t *index_totals_out);
+
+/* rcull_frame_host + the draw lists back on the host: after the frame, cmds_out[k][0 .. counts[k]) and
+ * visible_out[k][0 .. counts[k]) of every view k < n_views (per-mesh mode: index_totals[k] visible
+ * entries).  Each destination holds `capacity` entries (host pointers, pinned for full PCIe speed; a
+ * NULL array or NULL entry skips that list).  The reference's consumers are GPU draws
+ * (cmd_draw_indexed_indirect_count, depth_pass.rs:183-192), so lists normally stay resident: this is the
+ * "results back" variant of the end-to-end call.  Blocks until the copies are done. */
+int rcull_frame_host_lists(rcull_ctx *ctx, uint64_t n, const float *pos_scale, const float *rot,
+                           const uint32_t *mesh, const rcull_view *views, uint32_t n_views,
+                           const float cam_pos[3], uint32_t draw_index_base, uint32_t buffer_ix,
+                           uint32_t *counts_out, uint64_t *index_totals_out,
+                           rcull_draw_cmd *const *cmds_out, uint32_t *const *visible_out, uint64_t capacity);
 
 int rcull_get_outputs(rcull_ctx *ctx, uint32_t buffer_ix, rcull_outputs *out);
 

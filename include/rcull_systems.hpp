@@ -85,7 +85,10 @@ inline void expect(int status, const char* what) {
 // ---- the context resource (ResMut<RcullRes>: exclusive access, one GPU) -----------------------
 class RcullRes {
   public:
-    explicit RcullRes(const rcull_config& cfg) : cfg_(cfg) { expect(rcull_create(&cfg_, &ctx_), "rcull_create"); }
+    explicit RcullRes(const rcull_config& cfg) : cfg_(cfg) {
+        expect(rcull_create(&cfg_, &ctx_), "rcull_create");
+        expect(rcull_context_stream(ctx_, &stream_), "rcull_context_stream");
+    }
     ~RcullRes() { destroy(); }
     RcullRes(const RcullRes&) = delete;
     RcullRes& operator=(const RcullRes&) = delete;
@@ -95,6 +98,9 @@ class RcullRes {
         ctx_ = nullptr;
     }
     rcull_ctx* ctx() const { return ctx_; }
+    // Every system enqueues on this one stream (the one rcull_frame_host uses): frame i + 1's upload and
+    // frame kernel are ordered after frame i's triangle stage / instance packing without a host sync.
+    void* stream() const { return stream_; }
     const rcull_config& config() const { return cfg_; }
 
     // consolidate_mesh_buffers changed its offset maps (consolidate_mesh_buffers.rs:99-162)
@@ -122,6 +128,7 @@ class RcullRes {
   private:
     rcull_config cfg_;
     rcull_ctx* ctx_ = nullptr;
+    void* stream_ = nullptr;
 };
 
 // ---- systems ----------------------------------------------------------------------------------
@@ -161,9 +168,10 @@ inline void gpu_transform_cull(RcullRes& rc, ImageIndex image_index, const Camer
     for (uint64_t e = 0; e < n_entities; ++e) rc.mesh[e] = gltf_mesh[e].table_row;
 
     if (runtime_config.freeze_culling) {
-        expect(rcull_upload_entities(rc.ctx(), 0, n_entities, rc.pos_scale.data(), rc.rot.data(), rc.mesh.data(), nullptr),
+        expect(rcull_upload_entities(rc.ctx(), 0, n_entities, rc.pos_scale.data(), rc.rot.data(), rc.mesh.data(), rc.stream()),
                "rcull_upload_entities");
-        expect(rcull_frame_frozen(rc.ctx(), n_entities, image_index.ix, nullptr), "rcull_frame_frozen");
+        expect(rcull_frame_frozen(rc.ctx(), n_entities, image_index.ix, rc.stream()), "rcull_frame_frozen");
+        rc.n_entities = n_entities;
         return;  // rc.counts / rc.index_totals / rc.n_views keep describing the lists that are drawn
     }
 
@@ -187,12 +195,12 @@ inline void gpu_transform_cull(RcullRes& rc, ImageIndex image_index, const Camer
 inline void gpu_cull_triangles(RcullRes& rc, ImageIndex image_index, const Camera& camera, const RuntimeConfiguration& runtime_config,
                                uint32_t draw_index_base = 0) {
     if (runtime_config.freeze_culling) return;
-    expect(rcull_tri_cull(rc.ctx(), camera.pv, draw_index_base, image_index.ix, nullptr), "rcull_tri_cull");
+    expect(rcull_tri_cull(rc.ctx(), camera.pv, draw_index_base, image_index.ix, rc.stream()), "rcull_tri_cull");
 }
 
 // build_acceleration_structures' per-entity instance loop (acceleration_strucures.rs:419-445).
 inline void gpu_as_instances(RcullRes& rc, ImageIndex image_index, uint32_t draw_index_base = 0) {
-    expect(rcull_as_instances(rc.ctx(), rc.n_entities, draw_index_base, image_index.ix, nullptr), "rcull_as_instances");
+    expect(rcull_as_instances(rc.ctx(), rc.n_entities, draw_index_base, image_index.ix, rc.stream()), "rcull_as_instances");
 }
 
 // ---- read-back (tests, debug_aabb-style consumers; blocking) -----------------------------------

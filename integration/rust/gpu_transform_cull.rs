@@ -20,6 +20,8 @@ use crate::{
 /// ResMut => exclusive access: one context = one GPU = externally serialised calls.
 pub(crate) struct RcullRes {
     pub(crate) ctx: *mut RcullCtx,
+    /// the context's own stream: every call of a frame is enqueued on it (rcull_context_stream)
+    stream: *mut std::ffi::c_void,
     ps: Vec<f32>,
     rot: Vec<f32>,
     mesh: Vec<u32>,
@@ -33,7 +35,9 @@ impl RcullRes {
     pub(crate) fn new(cfg: &RcullConfig) -> RcullRes {
         let mut ctx = std::ptr::null_mut();
         check(unsafe { rcull_create(cfg, &mut ctx) }); // aborts without a CUDA device: there is no CPU path
-        RcullRes { ctx, ps: vec![], rot: vec![], mesh: vec![], counts: [0; 8], index_totals: [0; 8] }
+        let mut stream = std::ptr::null_mut();
+        check(unsafe { rcull_context_stream(ctx, &mut stream) });
+        RcullRes { ctx, stream, ps: vec![], rot: vec![], mesh: vec![], counts: [0; 8], index_totals: [0; 8] }
     }
     /// consolidate_mesh_buffers changed its offset maps (consolidate_mesh_buffers.rs:99-162)
     pub(crate) fn set_mesh_table(&mut self, rows: &[RcullMesh]) {
@@ -73,8 +77,8 @@ pub(crate) fn gpu_transform_cull(
 
     if runtime_config.freeze_culling {
         // cull_pass_bypass (cull_pipeline.rs:331-421): lists, count and culled indices of the last unfrozen frame stay
-        check(unsafe { rcull_upload_entities(rc.ctx, 0, n, rc.ps.as_ptr(), rc.rot.as_ptr(), rc.mesh.as_ptr(), std::ptr::null_mut()) });
-        check(unsafe { rcull_frame_frozen(rc.ctx, n, image_index.0, std::ptr::null_mut()) });
+        check(unsafe { rcull_upload_entities(rc.ctx, 0, n, rc.ps.as_ptr(), rc.rot.as_ptr(), rc.mesh.as_ptr(), rc.stream) });
+        check(unsafe { rcull_frame_frozen(rc.ctx, n, image_index.0, rc.stream) });
         return;
     }
 
@@ -96,7 +100,7 @@ pub(crate) fn gpu_transform_cull(
     // second half of cull_pass: per-triangle cull of the camera view's survivors + compact_draw_stream
     let pv = camera.projection * camera.view; // what camera_matrices_upload writes as `pv` (generate_work.comp:33); column-major
     let pv: [f32; 16] = pv.as_slice().try_into().unwrap();
-    check(unsafe { rcull_tri_cull(rc.ctx, pv.as_ptr(), 0, image_index.0, std::ptr::null_mut()) });
+    check(unsafe { rcull_tri_cull(rc.ctx, pv.as_ptr(), 0, image_index.0, rc.stream) });
 
     // Outputs stay on the device: rcull_get_outputs(..).model / cmds[k] / counts and rcull_get_tri_outputs(..)
     // .{cmds, count, indices} are what depth_only_pass / render_frame bind in place of ModelData.model_buffer and

@@ -168,24 +168,33 @@ static void cross3(const float a[3], const float b[3], float o[3]) {
     o[1] = a[2] * b[0] - a[0] * b[2];
     o[2] = a[0] * b[1] - a[1] * b[0];
 }
-/* rotate v by unit quaternion q (i,j,k,w) through its rotation matrix. */
+/* UnitQuaternion * Vector3 (nalgebra 0.29 geometry/quaternion_ops.rs, what
+ * transform_vector and `rot * v` evaluate): t = (q.ijk x v) * 2;
+ * result = ((t * w) + (q.ijk x t)) + v -- the cross-product form, not the matrix. */
 static void quat_rotate(const float q[4], const float v[3], float o[3]) {
-    float r[16];
-    quat_to_homogeneous(q, r);
-    for (int a = 0; a < 3; a++) o[a] = (r[0 * 4 + a] * v[0] + r[1 * 4 + a] * v[1]) + r[2 * 4 + a] * v[2];
+    float t[3], c[3];
+    cross3(q, v, t);
+    for (int a = 0; a < 3; a++) t[a] = t[a] * 2.0f;
+    cross3(q, t, c);
+    for (int a = 0; a < 3; a++) o[a] = (t[a] * q[3] + c[a]) + v[a];
 }
 
 /* project_camera (src/ecs.rs:66-91): near 0.1, far 100, fov 70 deg, view =
- * look_at_lh(position, position + rot*z, rot*y).  tanf and the look-at chain are
- * not bit-pinned; planes are INPUTS to both the oracle frame and the GPU. */
+ * look_at_lh(position, position + rot*z, rot*y): the direction the look-at normalises is
+ * (position + dir) - position, as the reference builds it (ecs.rs:76-80), and
+ * Matrix4::look_at_lh goes through Rotation3::face_towards(dir, up).inverse() with the
+ * translation rot * (-eye) (nalgebra geometry/isometry_construction.rs).  tanf is not
+ * bit-pinned; planes are INPUTS to both the oracle frame and the GPU. */
 void oracle_project_camera(float aspect, const float pos[3], const float rot[4],
                            float proj[16], float view[16], float pv[16], float planes[6][4]) {
     const float fwd[3] = {0, 0, 1}, upv[3] = {0, 1, 0};
     float fovy = 70.0f * 0.017453292519943295f;
     perspective_lh_zo(aspect, fovy, 0.1f, 100.0f, proj);
     float f[3], up[3], s[3], u[3];
-    quat_rotate(rot, fwd, f);
+    float dir[3];
+    quat_rotate(rot, fwd, dir);
     quat_rotate(rot, upv, up);
+    for (int a = 0; a < 3; a++) f[a] = (pos[a] + dir[a]) - pos[a]; /* target - eye */
     normalize3(f);
     cross3(up, f, s);
     normalize3(s);

@@ -99,11 +99,13 @@ SYMBOLS = {
     "rcull_destroy": (None, [_P]),
     "rcull_set_mesh_table": (C.c_int, [_P, _P, _u32]),
     "rcull_upload_entities": (C.c_int, [_P, _u64, _u64, _P, _P, _P, _P]),
+    "rcull_context_stream": (C.c_int, [_P, C.POINTER(_P)]),
     "rcull_entity_ptrs": (C.c_int, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)]),
     "rcull_pack_components": (C.c_int, [_u64, _P, _P, _P, _P, _P]),
     "rcull_frame": (C.c_int, [_P, _u64, _P, _u32, _P, _u32, _u32, _P]),
     "rcull_frame_frozen": (C.c_int, [_P, _u64, _u32, _P]),
     "rcull_frame_host": (C.c_int, [_P, _u64, _P, _P, _P, _P, _u32, _P, _u32, _u32, _P, _P]),
+    "rcull_frame_host_lists": (C.c_int, [_P, _u64, _P, _P, _P, _P, _u32, _P, _u32, _u32, _P, _P, _P, _P, _u64]),
     "rcull_get_outputs": (C.c_int, [_P, _u32, C.POINTER(Outputs)]),
     "rcull_download_counts": (C.c_int, [_P, _u32, _P, _P]),
     "rcull_download_model": (C.c_int, [_P, _u32, _u64, _u64, _P]),

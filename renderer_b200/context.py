@@ -146,6 +146,35 @@ class CullContext:
         self._last = (n, len(v))
         return counts[: len(v)], totals[: len(v)]
 
+    def frame_host_lists(self, pos_scale, rot, mesh, views, cam_pos, cmds_out, visible_out, capacity: int,
+                         draw_index_base: int = 0, buffer_ix: int = 0):
+        """frame_host + the draw lists back: cmds_out / visible_out are sequences (one per view) of host
+        addresses (int; pinned memory for full PCIe speed) each holding `capacity` entries."""
+        v = views_array(views)
+        cam = np.ascontiguousarray(cam_pos, dtype=np.float32).reshape(3)
+        n = len(mesh)
+        counts = np.zeros(_lib.MAX_VIEWS, np.uint32)
+        totals = np.zeros(_lib.MAX_VIEWS, np.uint64)
+        ca = (C.c_void_p * len(v))(*[C.c_void_p(int(a)) for a in cmds_out])
+        va = (C.c_void_p * len(v))(*[C.c_void_p(int(a)) for a in visible_out])
+        check(
+            self._lib.rcull_frame_host_lists(
+                self._h, n, ptr(pos_scale), ptr(rot), ptr(mesh), ptr(v), len(v), ptr(cam), draw_index_base, buffer_ix,
+                ptr(counts), ptr(totals), C.cast(ca, C.c_void_p), C.cast(va, C.c_void_p), capacity,
+            )
+        )
+        self.n = n
+        self._last = (n, len(v))
+        return counts[: len(v)], totals[: len(v)]
+
+    @property
+    def stream(self) -> int:
+        """The context's own stream (rcull_context_stream): pass it to the asynchronous calls that follow a
+        frame_host so that all per-frame work is ordered on one stream."""
+        s = C.c_void_p()
+        check(self._lib.rcull_context_stream(self._h, C.byref(s)))
+        return int(s.value or 0)
+
     # -- outputs ----------------------------------------------------------------
     def outputs(self, buffer_ix: int = 0) -> Outputs:
         o = Outputs()

@@ -4,6 +4,7 @@
 #include "rcull.h"
 
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>  // header-only NVTX 3: ranges cost nothing unless a tool (nsys / ncu --nvtx) is attached
 
 #include <cmath>
 #include <cstdarg>
@@ -44,6 +45,26 @@ int fail(int code, const char* fmt, ...) {
             return fail(RCULL_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, \
                         __LINE__);                                                                 \
     } while (0)
+
+// One NVTX range per entry point that enqueues device work, named like the scope!() of the system it
+// replaces (src/ecs.rs:56,59,142,145; cull_pipeline.rs:104,107,439) -- domain "rcull".
+struct Scope {
+    static nvtxDomainHandle_t domain() {
+        static nvtxDomainHandle_t d = nvtxDomainCreateA("rcull");
+        return d;
+    }
+    explicit Scope(const char* name) {
+        nvtxEventAttributes_t a = {};
+        a.version = NVTX_VERSION;
+        a.size = NVTX_EVENT_ATTRIB_STRUCT_SIZE;
+        a.messageType = NVTX_MESSAGE_TYPE_ASCII;
+        a.message.ascii = name;
+        nvtxDomainRangePushEx(domain(), &a);
+    }
+    ~Scope() { nvtxDomainRangePop(domain()); }
+    Scope(const Scope&) = delete;
+    Scope& operator=(const Scope&) = delete;
+};
 
 struct OutputSet {
     float4* model = nullptr;
@@ -105,6 +126,12 @@ struct rcull_ctx {
     uint64_t* tri_status = nullptr;  // [4 * tiles] + 2 ticket words at the end
     size_t tri_status_bytes = 0;
     unsigned long long* blas = nullptr;  // F4: BLAS address per mesh
+    uint32_t n_blas = 0;                 // entries rcull_set_blas_table filled
+    // CullPassData is single-buffered in the reference (cull_pipeline.rs:70-84), only ModelData is
+    // DoubleBuffered: a frozen frame on set j keeps the LISTS of the last unfrozen frame, whichever set holds them
+    uint32_t lists_ix = 0;               // output set written by the last rcull_frame
+    bool set_frozen[3] = {false, false, false};  // the last call on set j was rcull_frame_frozen
+    uint32_t* h_error = nullptr;         // pinned: device error word read back by rcull_frame_host
     uint4* instances = nullptr;          // F4: VkAccelerationStructureInstanceKHR [cap]
     std::vector<void*> allocs;
 };
@@ -119,6 +146,10 @@ int dev_alloc(rcull_ctx* c, T** p, size_t count) {
     *p = static_cast<T*>(q);
     return 0;
 }
+
+// Output set whose draw lists belong to set j: its own, or -- after a frozen frame on j -- the set the
+// last unfrozen frame wrote (cull_pass_bypass keeps CullPassData as it is, cull_pipeline.rs:331-421).
+uint32_t lists_of(const rcull_ctx* c, uint32_t j) { return c->set_frozen[j] ? c->lists_ix : j; }
 
 // Largest x with sqrtf(x) <= d, so that (sqrtf(d2) > d) == (d2 > x) exactly
 // (helpers.rs:4-6; sqrtf is correctly rounded and monotone on host and device).
@@ -190,7 +221,7 @@ int make_model_map(CUtensorMap* map, float4* model, uint64_t cap) {
 extern "C" {
 
 const char* rcull_last_error(void) { return g_err; }
-uint32_t rcull_version(void) { return (0u << 16) | 3u; }  // 0.2: triangle stage, rcull_config.capacity_tri_indices; 0.3: slot counts
+uint32_t rcull_version(void) { return (0u << 16) | 4u; }  // 0.2: triangle stage, rcull_config.capacity_tri_indices; 0.3: slot counts; 0.4: rcull_context_stream
 
 void rcull_destroy(rcull_ctx* c) {
     if (!c) return;
@@ -201,6 +232,7 @@ void rcull_destroy(rcull_ctx* c) {
     if (c->indices) cudaFree(c->indices);
     if (c->h_counts) cudaFreeHost(c->h_counts);
     if (c->h_totals) cudaFreeHost(c->h_totals);
+    if (c->h_error) cudaFreeHost(c->h_error);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -315,6 +347,7 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
     }
     if (cudaMallocHost((void**)&c->h_counts, kMaxViews * 4) != cudaSuccess ||
         cudaMallocHost((void**)&c->h_totals, kMaxViews * 8) != cudaSuccess ||
+        cudaMallocHost((void**)&c->h_error, 4) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
         rcull_destroy(c);
         return fail(RCULL_ERR_CUDA, "host staging / stream creation failed");
@@ -378,6 +411,7 @@ int rcull_set_mesh_table(rcull_ctx* c, const rcull_mesh* meshes, uint32_t n) {
 
 int rcull_upload_entities(rcull_ctx* c, uint64_t first, uint64_t n, const float* pos_scale, const float* rot,
                           const uint32_t* mesh, void* stream) {
+    Scope scope("rcull::upload_entities");
     if (!c || (n && (!pos_scale || !rot || !mesh))) return fail(RCULL_ERR_INVALID, "rcull_upload_entities: null argument");
     if (first + n > c->cfg.capacity_entities) return fail(RCULL_ERR_INVALID, "entities [%llu, %llu) exceed capacity %llu", (unsigned long long)first, (unsigned long long)(first + n), (unsigned long long)c->cfg.capacity_entities);
     if (n == 0) return RCULL_OK;
@@ -386,6 +420,12 @@ int rcull_upload_entities(rcull_ctx* c, uint64_t first, uint64_t n, const float*
     CU(cudaMemcpyAsync(c->pos_scale + first, pos_scale, n * 16, cudaMemcpyHostToDevice, s));
     CU(cudaMemcpyAsync(c->rot + first, rot, n * 16, cudaMemcpyHostToDevice, s));
     CU(cudaMemcpyAsync(c->mesh + first, mesh, n * 4, cudaMemcpyHostToDevice, s));
+    return RCULL_OK;
+}
+
+int rcull_context_stream(rcull_ctx* c, void** stream) {
+    if (!c || !stream) return fail(RCULL_ERR_INVALID, "rcull_context_stream: null argument");
+    *stream = c->own_stream;
     return RCULL_OK;
 }
 
@@ -420,6 +460,7 @@ extern "C" {
 
 int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_views, const float cam_pos[3],
                 uint32_t draw_index_base, uint32_t buffer_ix, void* stream) {
+    Scope scope("rcull::frame (model_matrix_calculation + aabb_calculation + coarse_culling + cull_pass)");
     if (!c || !views || !cam_pos) return fail(RCULL_ERR_INVALID, "rcull_frame: null argument");
     if (n > c->cfg.capacity_entities) return fail(RCULL_ERR_INVALID, "n %llu exceeds capacity_entities %llu", (unsigned long long)n, (unsigned long long)c->cfg.capacity_entities);
     if (n_views < 1 || n_views > c->cfg.max_views) return fail(RCULL_ERR_INVALID, "n_views %u not in 1..%u", n_views, c->cfg.max_views);
@@ -429,6 +470,8 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     CU(cudaSetDevice(c->cfg.device));
     cudaStream_t s = (cudaStream_t)stream;
     OutputSet& o = c->out[buffer_ix];
+    c->lists_ix = buffer_ix;
+    c->set_frozen[buffer_ix] = false;
     if (n == 0) {  // empty query: cull_pass still clears the buffers (cull_pipeline.rs:498-511)
         CU(cudaMemsetAsync(o.counts, 0, kMaxViews * 4, s));
         CU(cudaMemsetAsync(o.totals, 0, kMaxViews * 8, s));
@@ -463,9 +506,18 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
             pc.px = make_float2(pl[0], pl[0]);
             pc.py = make_float2(pl[1], pl[1]);
             pc.pz = make_float2(pl[2], pl[2]);
-            pc.pw = pl[3];
+            pc.pw = make_float2(pl[3], pl[3]);
         }
     }
+    // packed-sum plane tests multiply with .ftz (rcull_frame.cuh): allowed while no plane factor is a tiny nonzero number
+    a.planes_ftz_safe = 1u;
+    for (uint32_t v = 0; v < n_views; ++v)
+        for (int p = 0; p < 6; ++p)
+            for (int x = 0; x < 3; ++x) {
+                const float f = fabsf(views[v].planes[p][x]);
+                if (!(f == 0.f || f >= kFtzSafe)) a.planes_ftz_safe = 0u;  // tiny, or NaN
+            }
+    if (getenv("RCULL_NO_PACKED_SUMS")) a.planes_ftz_safe = 0u;  // A/B switch: the scalar-sum body for every tile
     a.src_first = o.src_first;
     a.counts = o.counts;
     a.totals = o.totals;
@@ -502,7 +554,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
         case 8: e = launch<8>(mat, a, o.model_map, grid, s); break;
     }
     if (e != cudaSuccess) return fail(RCULL_ERR_CUDA, "transform_cull_compact launch failed: %s", cudaGetErrorString(e));
-    c->ticket_base += n_tiles;  // n_tiles - grid real tickets (the first tile of a CTA is its block index) + one past the end per CTA
+    c->ticket_base += n_tiles + (uint32_t)grid;  // every tile is a ticket, and every CTA draws one ticket past the end
     c->launches += 1;
     if (per_mesh) {
         // Stable bucketing by (mesh, lod) slot: counting sort over tiles of the survivor pairs
@@ -554,9 +606,10 @@ static int check_device_error(rcull_ctx* c) {
     return RCULL_OK;
 }
 
-int rcull_frame_host(rcull_ctx* c, uint64_t n, const float* pos_scale, const float* rot, const uint32_t* mesh,
-                     const rcull_view* views, uint32_t n_views, const float cam_pos[3], uint32_t draw_index_base,
-                     uint32_t buffer_ix, uint32_t* counts_out, uint64_t* index_totals_out) {
+static int frame_host_impl(rcull_ctx* c, uint64_t n, const float* pos_scale, const float* rot, const uint32_t* mesh,
+                           const rcull_view* views, uint32_t n_views, const float cam_pos[3], uint32_t draw_index_base,
+                           uint32_t buffer_ix, uint32_t* counts_out, uint64_t* index_totals_out,
+                           rcull_draw_cmd* const* cmds_out, uint32_t* const* visible_out, uint64_t capacity) {
     if (!c) return fail(RCULL_ERR_INVALID, "rcull_frame_host: null context");
     int rc = rcull_upload_entities(c, 0, n, pos_scale, rot, mesh, c->own_stream);
     if (rc) return rc;
@@ -565,28 +618,68 @@ int rcull_frame_host(rcull_ctx* c, uint64_t n, const float* pos_scale, const flo
     OutputSet& o = c->out[buffer_ix];
     CU(cudaMemcpyAsync(c->h_counts, o.counts, kMaxViews * 4, cudaMemcpyDeviceToHost, c->own_stream));
     CU(cudaMemcpyAsync(c->h_totals, o.totals, kMaxViews * 8, cudaMemcpyDeviceToHost, c->own_stream));
+    CU(cudaMemcpyAsync(c->h_error, c->ticket + 1, 4, cudaMemcpyDeviceToHost, c->own_stream));
     CU(cudaStreamSynchronize(c->own_stream));
+    if (*c->h_error) {  // the reference panics here ("Vertex buffer not consolidated", cull_pipeline.rs:543)
+        CU(cudaMemsetAsync(c->ticket + 1, 0, 4, c->own_stream));
+        CU(cudaStreamSynchronize(c->own_stream));
+        return fail(RCULL_ERR_INVALID, "mesh id out of range of the mesh table (Vertex/Index buffer not consolidated, cull_pipeline.rs:543)");
+    }
     for (uint32_t v = 0; v < n_views; ++v) {
         if (counts_out) counts_out[v] = c->h_counts[v];
         if (index_totals_out) index_totals_out[v] = c->h_totals[v];
     }
+    if (cmds_out || visible_out) {  // the lists themselves: sizes are known now
+        const bool per_mesh = c->cfg.output_mode == RCULL_PER_MESH_INSTANCED;
+        for (uint32_t v = 0; v < n_views; ++v) {
+            // per-mesh mode: counts = commands, index totals = instances in the bucketed visible list
+            uint64_t n_cmd = c->h_counts[v], n_vis = per_mesh ? c->h_totals[v] : c->h_counts[v];
+            if (n_cmd > c->cap_cmds) n_cmd = c->cap_cmds;
+            if (n_vis > c->cap_vis) n_vis = c->cap_vis;
+            if (n_cmd > capacity || n_vis > capacity)
+                return fail(RCULL_ERR_INVALID, "view %u: %llu commands / %llu visible entries exceed the host capacity %llu", v,
+                            (unsigned long long)n_cmd, (unsigned long long)n_vis, (unsigned long long)capacity);
+            if (cmds_out && cmds_out[v] && n_cmd) CU(cudaMemcpyAsync(cmds_out[v], o.cmds[v], n_cmd * 20, cudaMemcpyDeviceToHost, c->own_stream));
+            if (visible_out && visible_out[v] && n_vis) CU(cudaMemcpyAsync(visible_out[v], o.visible[v], n_vis * 4, cudaMemcpyDeviceToHost, c->own_stream));
+        }
+        CU(cudaStreamSynchronize(c->own_stream));
+    }
     return RCULL_OK;
+}
+
+int rcull_frame_host(rcull_ctx* c, uint64_t n, const float* pos_scale, const float* rot, const uint32_t* mesh,
+                     const rcull_view* views, uint32_t n_views, const float cam_pos[3], uint32_t draw_index_base,
+                     uint32_t buffer_ix, uint32_t* counts_out, uint64_t* index_totals_out) {
+    Scope scope("rcull::frame_host (upload + frame + counts)");
+    return frame_host_impl(c, n, pos_scale, rot, mesh, views, n_views, cam_pos, draw_index_base, buffer_ix, counts_out,
+                           index_totals_out, nullptr, nullptr, 0);
+}
+
+int rcull_frame_host_lists(rcull_ctx* c, uint64_t n, const float* pos_scale, const float* rot, const uint32_t* mesh,
+                           const rcull_view* views, uint32_t n_views, const float cam_pos[3], uint32_t draw_index_base,
+                           uint32_t buffer_ix, uint32_t* counts_out, uint64_t* index_totals_out,
+                           rcull_draw_cmd* const* cmds_out, uint32_t* const* visible_out, uint64_t capacity) {
+    Scope scope("rcull::frame_host_lists (upload + frame + counts + draw lists back)");
+    if (!cmds_out && !visible_out) return fail(RCULL_ERR_INVALID, "rcull_frame_host_lists: no list destination");
+    return frame_host_impl(c, n, pos_scale, rot, mesh, views, n_views, cam_pos, draw_index_base, buffer_ix, counts_out,
+                           index_totals_out, cmds_out, visible_out, capacity);
 }
 
 int rcull_get_outputs(rcull_ctx* c, uint32_t buffer_ix, rcull_outputs* out) {
     if (!c || !out) return fail(RCULL_ERR_INVALID, "rcull_get_outputs: null argument");
     if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
     const OutputSet& o = c->out[buffer_ix];
+    const OutputSet& l = c->out[lists_of(c, buffer_ix)];  // frozen set: the lists of the last unfrozen frame
     memset(out, 0, sizeof *out);
     out->model = reinterpret_cast<float*>(o.model);
     out->aabb = o.aabb;
     for (int v = 0; v < kMaxViews; ++v) {
         out->flags[v] = o.flags[v];
-        out->cmds[v] = reinterpret_cast<rcull_draw_cmd*>(o.cmds[v]);
-        out->visible[v] = o.visible[v];
+        out->cmds[v] = reinterpret_cast<rcull_draw_cmd*>(l.cmds[v]);
+        out->visible[v] = l.visible[v];
     }
-    out->counts = o.counts;
-    out->index_totals = reinterpret_cast<uint64_t*>(o.totals);
+    out->counts = l.counts;
+    out->index_totals = reinterpret_cast<uint64_t*>(l.totals);
     return RCULL_OK;
 }
 
@@ -600,8 +693,9 @@ int rcull_download_counts(rcull_ctx* c, uint32_t buffer_ix, uint32_t* dst, uint6
     DL_PROLOGUE("rcull_download_counts");
     int rc = check_device_error(c);
     if (rc) return rc;
-    CU(cudaMemcpy(dst, c->out[buffer_ix].counts, c->cfg.max_views * 4, cudaMemcpyDeviceToHost));
-    if (index_totals) CU(cudaMemcpy(index_totals, c->out[buffer_ix].totals, c->cfg.max_views * 8, cudaMemcpyDeviceToHost));
+    const OutputSet& l = c->out[lists_of(c, buffer_ix)];
+    CU(cudaMemcpy(dst, l.counts, c->cfg.max_views * 4, cudaMemcpyDeviceToHost));
+    if (index_totals) CU(cudaMemcpy(index_totals, l.totals, c->cfg.max_views * 8, cudaMemcpyDeviceToHost));
     return RCULL_OK;
 }
 int rcull_download_model(rcull_ctx* c, uint32_t buffer_ix, uint64_t first, uint64_t n, float* dst) {
@@ -628,23 +722,24 @@ int rcull_download_cmds(rcull_ctx* c, uint32_t buffer_ix, uint32_t view, uint64_
     DL_PROLOGUE("rcull_download_cmds");
     if (view >= c->cfg.max_views) return fail(RCULL_ERR_INVALID, "view %u of %u", view, c->cfg.max_views);
     if (first + n > c->cap_cmds) return fail(RCULL_ERR_INVALID, "command range out of bounds");
-    CU(cudaMemcpy(dst, c->out[buffer_ix].cmds[view] + first * 5, n * 20, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(dst, c->out[lists_of(c, buffer_ix)].cmds[view] + first * 5, n * 20, cudaMemcpyDeviceToHost));
     return RCULL_OK;
 }
 int rcull_download_visible(rcull_ctx* c, uint32_t buffer_ix, uint32_t view, uint64_t first, uint64_t n, uint32_t* dst) {
     DL_PROLOGUE("rcull_download_visible");
     if (view >= c->cfg.max_views) return fail(RCULL_ERR_INVALID, "view %u of %u", view, c->cfg.max_views);
     if (first + n > c->cap_vis) return fail(RCULL_ERR_INVALID, "visible range out of bounds");
-    CU(cudaMemcpy(dst, c->out[buffer_ix].visible[view] + first, n * 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(dst, c->out[lists_of(c, buffer_ix)].visible[view] + first, n * 4, cudaMemcpyDeviceToHost));
     return RCULL_OK;
 }
 
 int rcull_rebase_into(rcull_ctx* c, uint32_t buffer_ix, uint32_t view, uint64_t index_prefix, rcull_draw_cmd* dst_cmds,
                       uint32_t* dst_visible, void* stream) {
+    Scope scope("rcull::rebase_into");
     if (!c || !dst_cmds || !dst_visible) return fail(RCULL_ERR_INVALID, "rcull_rebase_into: null argument");
     if (buffer_ix >= c->cfg.n_buffers || view >= c->cfg.max_views) return fail(RCULL_ERR_INVALID, "rcull_rebase_into: bad buffer/view");
     CU(cudaSetDevice(c->cfg.device));
-    const OutputSet& o = c->out[buffer_ix];
+    const OutputSet& o = c->out[lists_of(c, buffer_ix)];
     rebase_into<<<c->sm_count * 4, 256, 0, (cudaStream_t)stream>>>(
         o.cmds[view], o.visible[view], o.counts + view, (uint32_t)(c->cap_vis > 0xffffffffull ? 0xffffffffull : c->cap_vis),
         (uint32_t)index_prefix, reinterpret_cast<uint32_t*>(dst_cmds), dst_visible);
@@ -655,6 +750,7 @@ int rcull_rebase_into(rcull_ctx* c, uint32_t buffer_ix, uint32_t view, uint64_t 
 
 int rcull_synth_entities(rcull_ctx* c, uint64_t seed, uint64_t first_global, uint64_t n, float half_box,
                          uint32_t n_meshes, void* stream) {
+    Scope scope("rcull::synth_entities");
     if (!c) return fail(RCULL_ERR_INVALID, "rcull_synth_entities: null context");
     if (n > c->cfg.capacity_entities) return fail(RCULL_ERR_INVALID, "n exceeds capacity_entities");
     if (n == 0) return RCULL_OK;
@@ -669,9 +765,11 @@ int rcull_synth_entities(rcull_ctx* c, uint64_t seed, uint64_t first_global, uin
 uint64_t rcull_launch_count(rcull_ctx* c) { return c ? c->launches : 0; }
 
 int rcull_frame_frozen(rcull_ctx* c, uint64_t n, uint32_t buffer_ix, void* stream) {
+    Scope scope("rcull::frame_frozen (cull_pass_bypass)");
     if (!c) return fail(RCULL_ERR_INVALID, "rcull_frame_frozen: null context");
     if (n > c->cfg.capacity_entities) return fail(RCULL_ERR_INVALID, "n = %llu exceeds capacity_entities", (unsigned long long)n);
     if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
+    c->set_frozen[buffer_ix] = buffer_ix != c->lists_ix;  // the lists of this set are now those of set lists_ix
     if (n == 0) return RCULL_OK;
     CU(cudaSetDevice(c->cfg.device));
     model_only<<<c->sm_count * 8, 256, 0, (cudaStream_t)stream>>>(c->pos_scale, c->rot, (uint32_t)n, c->out[buffer_ix].model);
@@ -714,12 +812,16 @@ int rcull_set_blas_table(rcull_ctx* c, const uint64_t* blas, uint32_t n) {
     }
     CU(cudaDeviceSynchronize());
     CU(cudaMemcpy(c->blas, blas, (size_t)n * 8, cudaMemcpyHostToDevice));
+    c->n_blas = n;
     return RCULL_OK;
 }
 
 int rcull_as_instances(rcull_ctx* c, uint64_t n, uint32_t draw_index_base, uint32_t buffer_ix, void* stream) {
+    Scope scope("rcull::as_instances (build_acceleration_structures instance loop)");
     if (!c) return fail(RCULL_ERR_INVALID, "rcull_as_instances: null context");
     if (!c->blas) return fail(RCULL_ERR_INVALID, "rcull_set_blas_table has not been called");
+    // a mesh id past the BLAS table would pack an address nobody set (the reference indexes a Vec: it would panic)
+    if (c->n_blas < c->n_meshes) return fail(RCULL_ERR_INVALID, "BLAS table has %u entries, the mesh table %u", c->n_blas, c->n_meshes);
     if (n > c->cfg.capacity_entities) return fail(RCULL_ERR_INVALID, "n exceeds capacity_entities");
     if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
     if (n == 0) return RCULL_OK;
@@ -768,13 +870,14 @@ int rcull_set_geometry(rcull_ctx* c, const float* positions, uint64_t n_vertices
 }
 
 int rcull_tri_cull(rcull_ctx* c, const float pv[16], uint32_t draw_index_base, uint32_t buffer_ix, void* stream) {
+    Scope scope("rcull::tri_cull (generate_work + compact_draw_stream)");
     if (!c || !pv) return fail(RCULL_ERR_INVALID, "rcull_tri_cull: null argument");
     if (!c->cfg.capacity_tri_indices) return fail(RCULL_ERR_INVALID, "context created without capacity_tri_indices");
     if (!c->positions) return fail(RCULL_ERR_INVALID, "rcull_set_geometry has not been called");
     if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
     CU(cudaSetDevice(c->cfg.device));
     cudaStream_t s = (cudaStream_t)stream;
-    OutputSet& o = c->out[buffer_ix];
+    OutputSet& o = c->out[lists_of(c, buffer_ix)];  // a frozen set draws from the lists of the last unfrozen frame
     CU(cudaMemsetAsync(c->tri_status, 0, c->tri_status_bytes, s));  // descriptors + the two tickets behind them
     const size_t tiles = (c->cap_cmds + kCompactTile - 1) / kCompactTile;
     uint32_t* tickets = reinterpret_cast<uint32_t*>(c->tri_status + 4 * tiles);
@@ -783,7 +886,7 @@ int rcull_tri_cull(rcull_ctx* c, const float pv[16], uint32_t draw_index_base, u
     t.cmds = o.cmds[0];
     t.src_first = o.src_first;
     t.count = o.counts;
-    t.model = reinterpret_cast<const float*>(o.model);
+    t.model = reinterpret_cast<const float*>(c->out[buffer_ix].model);
     t.positions = c->positions;
     t.indices = c->indices;
     t.out_indices = c->tri_indices;
@@ -1058,6 +1161,7 @@ static int merge_args(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, Merg
 }
 
 int rcull_merge_scatter(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, void* stream) {
+    Scope scope("rcull::merge_scatter");
     if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_scatter: null argument");
     MergeArgs a;
     int rc = merge_args(m, buffer_ix, n_views, &a);
@@ -1069,6 +1173,7 @@ int rcull_merge_scatter(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, vo
 }
 
 int rcull_merge_exchange(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, void* stream) {
+    Scope scope("rcull::merge_exchange");
     if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_exchange: null argument");
     MergeArgs a;
     int rc = merge_args(m, buffer_ix, n_views, &a);
@@ -1092,6 +1197,7 @@ int rcull_merge_exchange(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, v
 }
 
 int rcull_merge_wait(rcull_merge* m, void* stream) {
+    Scope scope("rcull::merge_wait");
     if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_wait: null argument");
     CU(cudaSetDevice(m->ctx->cfg.device));
     merge_wait<<<1, 32, 0, (cudaStream_t)stream>>>(reinterpret_cast<const MergeSync*>(m->base + m->sync_off), m->world, m->epoch);

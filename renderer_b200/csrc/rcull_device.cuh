@@ -173,6 +173,19 @@ __device__ __forceinline__ float2 mul2_rn(float2 a, float2 b) {
         : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)));
     return *reinterpret_cast<float2*>(&r);
 }
+// The same product with .ftz.  ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even with an explicit
+// .rn and --fmad=false (the scalar forms are left alone), which would round once where the reference rounds
+// twice; it does NOT contract when the two instructions disagree on .ftz.  A flushing product followed by a
+// non-flushing sum therefore stays FMUL2.FTZ + FADD2, and equals the IEEE product whenever both factors are
+// zero or at least 2^-63 in magnitude (no subnormal goes in, none can come out) -- callers check that.
+__device__ __forceinline__ float2 mul2_ftz(float2 a, float2 b) {
+    unsigned long long r;
+    asm("mul.rn.ftz.f32x2 %0, %1, %2;"
+        : "=l"(r)
+        : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)));
+    return *reinterpret_cast<float2*>(&r);
+}
+constexpr float kFtzSafe = 1.0842021724855044e-19f;  // 2^-63: |a|, |b| >= this (or zero) => a * b is zero or a normal number
 __device__ __forceinline__ float2 add2_rn(float2 a, float2 b) {
     unsigned long long r;
     asm("add.rn.f32x2 %0, %1, %2;"

@@ -18,6 +18,7 @@
 // tile loop.
 #pragma once
 #include <cuda.h>  // CUtensorMap (type only; the encoder is resolved at run time)
+#include <cuda/std/type_traits>
 
 #include "rcull_device.cuh"
 
@@ -71,7 +72,8 @@ constexpr uint64_t kFlagAgg = 1, kFlagIncl = 2;
 struct PlaneC {
     float2 ax, ay, az;  // |p.x|, |p.y|, |p.z|
     float2 px, py, pz;
-    float pw, pad0, pad1, pad2;
+    float2 pw;  // (pw, pw): the addend of the packed sums
+    float pad1, pad2;
 };
 
 struct FrameArgs {
@@ -102,6 +104,7 @@ struct FrameArgs {
     uint32_t cap_visible;
     uint32_t per_mesh;   // RCULL_PER_MESH_INSTANCED: emit (slot key, draw_index) pairs for the bucketing passes
     uint32_t len_small;  // every index_len in the mesh table is < 2^25: 128 of them add up in 32 bits
+    uint32_t planes_ftz_safe;  // every plane normal component is zero or >= 2^-63 in magnitude (packed-sum plane tests allowed)
     float cam[3];
     float lod_d2_max;  // lod 1 iff |cam-pos|^2 > lod_d2_max  (== sqrt(d2) > lod_distance)
     PlaneC planes[kMaxViews][6];
@@ -402,6 +405,9 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
     const uint32_t lane = tid & 31u;
     const uint32_t warp = tid >> 5;
 
+    // the CTA's first tile ticket: requested before the barrier set-up so that its round trip overlaps it
+    uint32_t first_t = 0;
+    if (tid == 0) first_t = atomicAdd(args.ticket, 1u) - args.ticket_base;
     if (tid == 0) {
 #pragma unroll
         for (int s = 0; s < kStages; ++s) {
@@ -419,12 +425,13 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
     // loads one tile ahead, as soon as the other stage has been read by every compute warp.
     // Tickets are drawn one tile EARLIER than they are needed (the atomic's round trip through L2
     // would otherwise sit in warp 0's timeline every tile, and every other warp ends up paced by
-    // the warp that feeds them).  The first tile of a CTA is its block index (every CTA of the
-    // persistent grid is resident, so tiles 0 .. grid-1 are all in flight).
+    // the warp that feeds them).  EVERY tile is a ticket, the first one of a CTA included: a tile is
+    // only ever owned by a CTA that is running, so the look-back never waits on a CTA the hardware has
+    // not scheduled yet (fewer SMs than the grid was sized for: MPS limits, green contexts).
     const bool producer = tid == 0;
     bool more = true;      // producer only: the last ticket used was a real tile
     uint32_t next_t = 0;   // producer only: the ticket drawn for the tile after the one being loaded
-    auto draw_ticket = [&]() { return atomicAdd(args.ticket, 1u) - args.ticket_base + gridDim.x; };
+    auto draw_ticket = [&]() { return atomicAdd(args.ticket, 1u) - args.ticket_base; };
     auto load_tile = [&](uint32_t for_it, uint32_t t) {
         const uint32_t stage = for_it & 1u;
         sm.tile_ring[for_it % kRing] = t;
@@ -441,8 +448,8 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
         }
     };
     if (producer) {  // in flight while the CTA copies its tables below
-        load_tile(0, blockIdx.x);
-        next_t = draw_ticket();
+        load_tile(0, first_t);
+        if (more) next_t = draw_ticket();
     }
     float4* const sm_planes = reinterpret_cast<float4*>(reinterpret_cast<unsigned char*>(&sm) + sizeof(FrameSmem));
     for (uint32_t i = tid; i < V * 6 * 4; i += kThreads) sm_planes[i] = reinterpret_cast<const float4*>(&args.planes[0][0])[i];
@@ -622,68 +629,112 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
         const uint32_t wlist_s = smem_u32(wlist);
 
         // A3 per view: planes outer, the thread's 4 entities inner
-        // (the view loop stays rolled: unrolled, the kernel outgrows the instruction cache)
-        uint32_t woff = 0;  // start of view k in the warp's combined list
-#pragma unroll kViewUnroll
-        for (int k = 0; k < V; ++k) {
-            bool outside[kItems];
+        // (the view loop stays rolled: unrolled, the kernel outgrows the instruction cache).
+        // Two bodies, chosen per warp and tile:
+        //   packed  -- products FMUL2.FTZ, every sum FADD2 (13 instructions per plane and entity pair).  Exact as
+        //              long as no factor is a nonzero number below 2^-63 (mul2_ftz, rcull_device.cuh);
+        //   scalar  -- products FMUL2, sums scalar FADD (17 instructions): any input.
+        // The packed body needs a second use of nothing and no FFMA2: the .ftz mismatch is what keeps ptxas from
+        // contracting the pairs (tests/test_abi.py checks the SASS for FFMA / FFMA2).
+        bool packed = V >= 2 && args.planes_ftz_safe != 0u;  // one view is HBM-bound either way: it keeps the plain body
+        if (V >= 2) {
+            float tiny = fminf(fminf(fabsf(cx[0]), fabsf(cy[0])), fabsf(cz[0]));
+            tiny = fminf(tiny, fminf(fminf(fabsf(hx[0]), fabsf(hy[0])), fabsf(hz[0])));
 #pragma unroll
-            for (int j = 0; j < kItems; ++j) outside[j] = !valid[j];  // padding slots are never visible
+            for (int j = 1; j < kItems; ++j) {
+                tiny = fminf(tiny, fminf(fminf(fabsf(cx[j]), fabsf(cy[j])), fabsf(cz[j])));
+                tiny = fminf(tiny, fminf(fminf(fabsf(hx[j]), fabsf(hy[j])), fabsf(hz[j])));
+            }
+            if (__any_sync(kFullMask, tiny < kFtzSafe)) {  // rare: an exact zero (fine) or a tiny nonzero factor (not fine)
+                bool bad = false;
 #pragma unroll
-            for (int p = 0; p < 6; ++p) {
-                const float4* pp = sm_planes + (k * 6 + p) * 4;
-                const float4 q0 = pp[0], q1 = pp[1], q2 = pp[2];  // (ax ax ay ay) (az az px px) (py py pz pz)
-                const float pw = pp[3].x;
-                const float2 ax = make_float2(q0.x, q0.y), ay = make_float2(q0.z, q0.w), az = make_float2(q1.x, q1.y);
-                const float2 px = make_float2(q1.z, q1.w), py = make_float2(q2.x, q2.y), pz = make_float2(q2.z, q2.w);
+                for (int j = 0; j < kItems; ++j) {
+                    const float v6[6] = {cx[j], cy[j], cz[j], hx[j], hy[j], hz[j]};
 #pragma unroll
-                for (int i = 0; i < kItems / 2; ++i) {
-                    // Products of two entities per FMUL2; every sum that consumes a packed product
-                    // is a scalar FADD, so ptxas has no packed mul+add pair to contract into FFMA2
-                    // (it does that even under --fmad=false; tests/test_abi.py checks the SASS).
-                    const float2 m1 = mul2_rn(h2x[i], ax), m2 = mul2_rn(h2y[i], ay), m3 = mul2_rn(h2z[i], az);
-                    const float e0 = __fadd_rn(__fadd_rn(m1.x, m2.x), m3.x);
-                    const float e1 = __fadd_rn(__fadd_rn(m1.y, m2.y), m3.y);
-                    const float2 p1 = mul2_rn(c2x[i], px), p3 = mul2_rn(c2z[i], pz), p2 = mul2_rn(c2y[i], py);
-                    const float2 a = make_float2(__fadd_rn(p1.x, p3.x), __fadd_rn(p1.y, p3.y));
-                    const float2 b = make_float2(__fadd_rn(p2.x, pw), __fadd_rn(p2.y, pw));
-                    const float2 s = add2_rn(a, b);
-                    // (s - e > 0.0) == (s > e): the rounded difference of two floats keeps its sign,
-                    // and both forms are false for NaN and for inf - inf
-                    outside[2 * i] = outside[2 * i] || (s.x > e0);
-                    outside[2 * i + 1] = outside[2 * i + 1] || (s.y > e1);
+                    for (int a = 0; a < 6; ++a) bad = bad || (v6[a] != 0.f && fabsf(v6[a]) < kFtzSafe);
                 }
+                if (__any_sync(kFullMask, bad)) packed = false;
             }
-            // ballot compaction, branch-free
-            uint32_t wc = 0, lo = 0, hi = 0;
-#pragma unroll
-            for (int j = 0; j < kItems; ++j) {
-                const bool vis = !outside[j];
-                if (kMat && args.flags[k] != nullptr && valid[j]) args.flags[k][tile_base + e0 + 32 * j] = outside[j] ? 1 : 0;
-                const uint32_t b = __ballot_sync(kFullMask, vis);
-                if (vis) sts_u8(wlist_s + woff + wc + __popc(b & lt), entry[j]);  // compiles to a predicated STS
-                if (!kMat || args.len_small) {  // compile-time in the hot variant
-                    lo += vis ? len[j] : 0u;
-                } else {
-                    lo += vis ? (len[j] & 0xffffu) : 0u;
-                    hi += vis ? (len[j] >> 16) : 0u;
-                }
-                wc += __popc(b);
-            }
-            uint64_t wl;
-            if (!kMat || args.len_small) {  // compile-time in the hot variant
-                wl = __reduce_add_sync(kFullMask, lo);  // 128 values below 2^25
-            } else {
-                lo = __reduce_add_sync(kFullMask, lo);  // 128 x 16-bit pieces: no overflow
-                hi = __reduce_add_sync(kFullMask, hi);
-                wl = (uint64_t)lo + ((uint64_t)hi << 16);
-            }
-            if (lane == 0) {
-                sm.wcnt[buf][k][warp] = wc;
-                sm.wlen[buf][k][warp] = wl;
-            }
-            woff += wc;
         }
+        uint32_t woff = 0;  // start of view k in the warp's combined list
+        const float4* vp = sm_planes;  // planes of view k: 6 x 4 float4
+        auto view_loop = [&](auto packed_c) {
+            constexpr bool kPacked = decltype(packed_c)::value;
+#pragma unroll kViewUnroll
+            for (int k = 0; k < V; ++k, vp += 24) {
+                bool outside[kItems];
+#pragma unroll
+                for (int j = 0; j < kItems; ++j) outside[j] = !valid[j];  // padding slots are never visible
+#pragma unroll
+                for (int p = 0; p < 6; ++p) {
+                    const float4* pp = vp + p * 4;
+                    const float4 q0 = pp[0], q1 = pp[1], q2 = pp[2];  // (ax ax ay ay) (az az px px) (py py pz pz)
+                    const float pw = pp[3].x;
+                    const float2 ax = make_float2(q0.x, q0.y), ay = make_float2(q0.z, q0.w), az = make_float2(q1.x, q1.y);
+                    const float2 px = make_float2(q1.z, q1.w), py = make_float2(q2.x, q2.y), pz = make_float2(q2.z, q2.w);
+#pragma unroll
+                    for (int i = 0; i < kItems / 2; ++i) {
+                        if constexpr (kPacked) {
+                            const float2 pw2 = make_float2(pp[3].x, pp[3].y);  // (pw, pw)
+                            const float2 e = add2_rn(add2_rn(mul2_ftz(h2x[i], ax), mul2_ftz(h2y[i], ay)), mul2_ftz(h2z[i], az));
+                            const float2 a = add2_rn(mul2_ftz(c2x[i], px), mul2_ftz(c2z[i], pz));
+                            const float2 b = add2_rn(mul2_ftz(c2y[i], py), pw2);
+                            const float2 s = add2_rn(a, b);
+                            outside[2 * i] = outside[2 * i] || (s.x > e.x);
+                            outside[2 * i + 1] = outside[2 * i + 1] || (s.y > e.y);
+                        } else {
+                            // Products of two entities per FMUL2; every sum that consumes a packed product
+                            // is a scalar FADD, so ptxas has no packed mul+add pair to contract into FFMA2
+                            // (it does that even under --fmad=false; tests/test_abi.py checks the SASS).
+                            const float2 m1 = mul2_rn(h2x[i], ax), m2 = mul2_rn(h2y[i], ay), m3 = mul2_rn(h2z[i], az);
+                            const float e0 = __fadd_rn(__fadd_rn(m1.x, m2.x), m3.x);
+                            const float e1 = __fadd_rn(__fadd_rn(m1.y, m2.y), m3.y);
+                            const float2 p1 = mul2_rn(c2x[i], px), p3 = mul2_rn(c2z[i], pz), p2 = mul2_rn(c2y[i], py);
+                            const float2 a = make_float2(__fadd_rn(p1.x, p3.x), __fadd_rn(p1.y, p3.y));
+                            const float2 b = make_float2(__fadd_rn(p2.x, pw), __fadd_rn(p2.y, pw));
+                            const float2 s = add2_rn(a, b);
+                            // (s - e > 0.0) == (s > e): the rounded difference of two floats keeps its sign,
+                            // and both forms are false for NaN and for inf - inf
+                            outside[2 * i] = outside[2 * i] || (s.x > e0);
+                            outside[2 * i + 1] = outside[2 * i + 1] || (s.y > e1);
+                        }
+                    }
+                }
+                // ballot compaction, branch-free
+                uint32_t wc = 0, lo = 0, hi = 0;
+#pragma unroll
+                for (int j = 0; j < kItems; ++j) {
+                    const bool vis = !outside[j];
+                    if (kMat && args.flags[k] != nullptr && valid[j]) args.flags[k][tile_base + e0 + 32 * j] = outside[j] ? 1 : 0;
+                    const uint32_t b = __ballot_sync(kFullMask, vis);
+                    if (vis) sts_u8(wlist_s + woff + wc + __popc(b & lt), entry[j]);  // compiles to a predicated STS
+                    if (!kMat || args.len_small) {  // compile-time in the hot variant
+                        lo += vis ? len[j] : 0u;
+                    } else {
+                        lo += vis ? (len[j] & 0xffffu) : 0u;
+                        hi += vis ? (len[j] >> 16) : 0u;
+                    }
+                    wc += __popc(b);
+                }
+                uint64_t wl;
+                if (!kMat || args.len_small) {  // compile-time in the hot variant
+                    wl = __reduce_add_sync(kFullMask, lo);  // 128 values below 2^25
+                } else {
+                    lo = __reduce_add_sync(kFullMask, lo);  // 128 x 16-bit pieces: no overflow
+                    hi = __reduce_add_sync(kFullMask, hi);
+                    wl = (uint64_t)lo + ((uint64_t)hi << 16);
+                }
+                if (lane == 0) {
+                    sm.wcnt[buf][k][warp] = wc;
+                    sm.wlen[buf][k][warp] = wl;
+                }
+                woff += wc;
+            }
+        };
+        if (V >= 2 && packed)
+            view_loop(cuda::std::true_type{});
+        else
+            view_loop(cuda::std::false_type{});
         __syncwarp();
         if (lane == 0) mbar_arrive(&sm.done[buf]);
     }

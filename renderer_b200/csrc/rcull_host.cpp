@@ -61,9 +61,6 @@ M4 rotation(const float q[4]) {
     m.at(2, 0) = ik - wj;           m.at(2, 1) = wi + jk;           m.at(2, 2) = ww - ii - jj + kk;
     return m;
 }
-void rotate(const M4& r, const float v[3], float o[3]) {
-    for (int a = 0; a < 3; ++a) o[a] = (r.at(a, 0) * v[0] + r.at(a, 1) * v[1]) + r.at(a, 2) * v[2];
-}
 float dot(const float a[3], const float b[3]) { return (a[0] * b[0] + a[1] * b[1]) + a[2] * b[2]; }
 void normalize(float v[3]) {
     const float n = std::sqrt(dot(v, v));
@@ -73,6 +70,15 @@ void cross(const float a[3], const float b[3], float o[3]) {
     o[0] = a[1] * b[2] - a[2] * b[1];
     o[1] = a[2] * b[0] - a[0] * b[2];
     o[2] = a[0] * b[1] - a[1] * b[0];
+}
+// UnitQuaternion * Vector3 as nalgebra 0.29 evaluates it (transform_vector, `rot * v`):
+// t = (q.ijk x v) * 2; ((t * w) + (q.ijk x t)) + v
+void rotate(const float q[4], const float v[3], float o[3]) {
+    float t[3], c[3];
+    cross(q, v, t);
+    for (int a = 0; a < 3; ++a) t[a] = t[a] * 2.f;
+    cross(q, t, c);
+    for (int a = 0; a < 3; ++a) o[a] = (t[a] * q[3] + c[a]) + v[a];
 }
 constexpr float kFov70 = 70.0f * 0.017453292519943295f;  // glm::radians(70)
 
@@ -95,11 +101,11 @@ void rcull_frustum_planes(const float pv[16], rcull_view* out) {
 void rcull_project_camera(float aspect, const float pos[3], const float rot[4], float proj[16], float view[16],
                           float pv[16], rcull_view* out) {
     const M4 p = perspective_lh_zo(aspect, kFov70, 0.1f, 100.0f);
-    const M4 r = rotation(rot);
     const float z[3] = {0, 0, 1}, y[3] = {0, 1, 0};
-    float f[3], up[3], s[3], u[3];
-    rotate(r, z, f);
-    rotate(r, y, up);
+    float dir[3], f[3], up[3], s[3], u[3];
+    rotate(rot, z, dir);
+    rotate(rot, y, up);
+    for (int a = 0; a < 3; ++a) f[a] = (pos[a] + dir[a]) - pos[a];  // look_at_lh(eye, eye + dir, up): target - eye
     normalize(f);
     cross(up, f, s);
     normalize(s);
@@ -129,7 +135,7 @@ void rcull_light_view(const float pos[3], const float rot[4], float proj[16], fl
     const M4 r = rotation(rot);
     const float neg[3] = {-pos[0], -pos[1], -pos[2]};
     float t[3];
-    rotate(r, neg, t);
+    rotate(rot, neg, t);
     M4 tm = identity();
     tm.at(0, 3) = t[0];
     tm.at(1, 3) = t[1];

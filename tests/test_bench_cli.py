@@ -43,3 +43,15 @@ def test_gpu_arm_has_no_cpu_fallback():
     r = _run("--steps", "1", "--warmup", "3")
     assert r.returncode != 0
     assert "no CPU path" in (r.stderr + r.stdout)
+
+
+def test_reference_arm_views_are_the_library_views():
+    """bench.py's reference arm takes its planes from the oracle (no product library mapped): same bits as scene.scene_views."""
+    import numpy as np
+
+    sys.path.insert(0, ROOT)
+    import bench
+    from renderer_b200 import scene
+
+    for v in (1, 5, 8):
+        assert np.array_equal(bench.oracle_views(v), scene.scene_views(v))

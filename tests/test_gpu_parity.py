@@ -263,31 +263,42 @@ def _list_properties(ctx, k, count, total, meshes, base=0):
     return vis
 
 
-def test_config3_16m_five_views_properties_and_sampled_oracle():
-    """BASELINE configs[2] at full size: list properties + exact oracle comparison on slices."""
+@pytest.mark.parametrize("rank", [0, 1, 7])
+def test_config3_16m_five_views_full_compare(rank):
+    """BASELINE configs[2] at full size (rank 0), and ranks 1 and 7 of configs[4] (128 Mi entities in 8 range
+    shards of 16 Mi: entity i of the shard is entity rank * 16 Mi + i of the scene, draw_index_base = rank * 16 Mi;
+    firstInstance = gltfIndex, generate_work.comp:63-66; prefix sum cull_pipeline.rs:558): ALL five visible lists
+    and command lists bit-equal to the oracle's, counts, index totals, list properties, idempotence; the model
+    matrices (1 GiB) are compared on three slices."""
+    import os
+
     n, n_views = 16 * 1024 * 1024, 5
+    first = rank * n
     views = scene.scene_views(n_views)
+    pos, quat, scale, mesh = O.synth_entities(scene.SEED, first, n, 600.0, len(MESHES))
+    ref = O.frame(pos, quat, scale, mesh, MESHES, views, scene.CAMERA_POS, draw_index_base=first,
+                  n_threads=os.cpu_count() or 8, want=("cmds", "visible"))
     with CullContext(n, max_views=n_views, max_meshes=len(MESHES)) as ctx:
         ctx.set_mesh_table(MESHES)
-        ctx.synth_entities(scene.SEED, 0, n, 600.0, len(MESHES))
-        ctx.frame(views, scene.CAMERA_POS)
+        ctx.synth_entities(scene.SEED, first, n, 600.0, len(MESHES))
+        ctx.frame(views, scene.CAMERA_POS, draw_index_base=first)
         counts, totals = ctx.counts()
-        vis = [_list_properties(ctx, k, int(counts[k]), totals[k], MESHES) for k in range(n_views)]
+        assert np.array_equal(counts[:n_views], ref["counts"]) and np.array_equal(totals[:n_views], ref["totals"])
+        for k in range(n_views):
+            c = int(counts[k])
+            assert np.array_equal(ctx.visible(k, c), ref["visible"][k]), f"rank {rank} view {k} visible"
+            assert np.array_equal(ctx.cmds(k, c), ref["cmds"][k]), f"rank {rank} view {k} cmds"
+            vis = _list_properties(ctx, k, c, totals[k], MESHES)
+            assert c == 0 or (vis[0] >= first and int(vis[-1]) < first + n)
         # second frame on the same context: identical (idempotence, epoch/ticket reuse)
-        ctx.frame(views, scene.CAMERA_POS)
+        ctx.frame(views, scene.CAMERA_POS, draw_index_base=first)
         c2, t2 = ctx.counts()
         assert np.array_equal(c2, counts) and np.array_equal(t2, totals)
-        # exact visible sets on three slices, against the oracle
         for lo in (0, 7_654_321, n - 300_000):
             m = 300_000
-            ps, rot, mesh = scene.synth_entities(scene.SEED, lo, m, 600.0)
-            pos, quat, scale = scene.to_components(ps, rot)
-            ref = O.frame(pos, quat, scale, mesh, MESHES, views, scene.CAMERA_POS, draw_index_base=lo, n_threads=8,
-                          want=("model", "visible"))
-            assert np.array_equal(ctx.model(m, first=lo), ref["model"])
-            for k in range(n_views):
-                got = vis[k][(vis[k] >= lo) & (vis[k] < lo + m)]
-                assert np.array_equal(got, ref["visible"][k]), (lo, k)
+            want = O.frame(pos[lo:lo + m], quat[lo:lo + m], scale[lo:lo + m], mesh[lo:lo + m], MESHES, views, scene.CAMERA_POS,
+                           n_threads=8, want=("model",))
+            assert np.array_equal(ctx.model(m, first=lo), want["model"])
 
 
 def test_range_shards_merge_to_the_single_gpu_lists():
@@ -434,11 +445,13 @@ def test_per_mesh_instanced_mode_synthetic(n):
     _per_mesh_compare(ps, rot, mesh, MESHES, scene.scene_views(3), 3, base=17)
 
 
-def test_config4_sponza_instanced_per_mesh():
-    """BASELINE configs[3] (reduced to 300 k entities so the oracle stays fast; a parity case, not a bench line)."""
+@pytest.mark.parametrize("n", [300_000, 4_000_000])
+def test_config4_sponza_instanced_per_mesh(n):
+    """BASELINE configs[3]: the Sponza mesh table instanced to 4 M entities (and a 300 k cut), per-mesh indirect
+    command compaction, camera + one shadow view; commands and bucketed visible lists bit-equal to the oracle's."""
     table, node_scale = scene.sponza_mesh_table()
     assert len(table) == 87
-    ps, rot, mesh = scene.sponza_instances(300_000, len(table), node_scale)
+    ps, rot, mesh = scene.sponza_instances(n, len(table), node_scale)
     counts = _per_mesh_compare(ps, rot, mesh, table, scene.scene_views(2), 2)
     assert 0 < counts[0] <= len(table) * 2
 
@@ -571,3 +584,165 @@ def test_fused_exchange_two_ranks_in_one_process():
             lib.rcull_merge_destroy(h)
         for c in ctxs:
             c.destroy()
+
+
+# ---- round 2: host-path ordering, frozen frames across output sets, loud errors ---------------------
+def test_frame_host_tri_cull_frame_host_back_to_back_on_the_context_stream():
+    """Per-frame work of a context lives on ONE stream (rcull_context_stream): frame_host(A), the triangle stage of A,
+    frame_host(B) with no download in between -- B's upload and frame kernel must not overtake A's triangle stage."""
+    n = 60_000
+    A = scene.synth_entities(scene.SEED, 0, n, 30.0, len(MESHES))
+    B = scene.synth_entities(scene.SEED + 9, 0, n, 30.0, len(MESHES))
+    positions, indices = scene.synth_geometry(MESHES)
+    views, pv = scene.scene_views(1), scene.camera_pv()
+    pos, quat, scale = scene.to_components(A[0], A[1])
+    ref = O.frame(pos, quat, scale, A[2], MESHES, views, scene.CAMERA_POS, n_threads=8)
+    src = O.src_first_index(pos, A[2], ref["cmds"][0], MESHES, scene.CAMERA_POS)
+    want = O.tri_cull(ref["cmds"][0], src, ref["model"], pv, positions, indices, int(ref["totals"][0]) + 3, n_threads=8)
+    with CullContext(n, max_views=1, max_meshes=len(MESHES), capacity_tri_indices=int(ref["totals"][0]) + 3) as ctx:
+        ctx.set_mesh_table(MESHES)
+        ctx.set_geometry(positions, indices)
+        s = ctx.stream
+        assert s != 0
+        for _ in range(3):  # a few rounds: a race would not lose every time
+            ctx.frame_host(A[0], A[1], A[2], views, scene.CAMERA_POS)
+            ctx.tri_cull(pv, stream=s)
+            cB, _ = ctx.frame_host(B[0], B[1], B[2], views, scene.CAMERA_POS)  # overwrites cmds / counts / model of set 0
+            n_cmd, kept = ctx.tri_counts()
+            assert (n_cmd, kept) == (want["count"], want["kept_indices"])
+            assert np.array_equal(ctx.tri_cmds(n_cmd), want["cmds"])
+            got = ctx.tri_indices(0, int(ref["totals"][0]))
+            for c in want["cmds"][:: max(1, len(want["cmds"]) // 200)]:
+                a, b = int(c["firstIndex"]), int(c["firstIndex"]) + int(c["indexCount"])
+                assert np.array_equal(got[a:b], want["indices"][a:b])
+        assert int(cB[0]) != int(ref["counts"][0]) or True
+
+
+def test_frozen_frame_on_the_other_output_set_keeps_the_last_unfrozen_lists():
+    """CullPassData is single-buffered in the reference, only ModelData is DoubleBuffered (cull_pipeline.rs:70-84):
+    frame on image 0, frozen frame on image 1 -> the lists / counts read through set 1 are those of the frame on
+    set 0, the model matrices of set 1 are the moved entities'; an unfrozen frame on set 1 ends the redirection."""
+    n = 20_000
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, 60.0, len(MESHES))
+    ps2, rot2, _ = scene.synth_entities(scene.SEED + 1, 0, n, 60.0, len(MESHES))
+    views = scene.scene_views(2)
+    with CullContext(n, max_views=2, max_meshes=len(MESHES), n_buffers=2) as ctx:
+        ctx.set_mesh_table(MESHES)
+        ctx.upload_entities(ps2, rot2, mesh)
+        ctx.frame(views, scene.CAMERA_POS, buffer_ix=1)  # set 1 holds the lists of ANOTHER scene first
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(views, scene.CAMERA_POS, buffer_ix=0)
+        counts0, totals0 = ctx.counts(0)
+        cmds0 = [ctx.cmds(k, int(counts0[k]), buffer_ix=0) for k in range(2)]
+        vis0 = [ctx.visible(k, int(counts0[k]), buffer_ix=0) for k in range(2)]
+        ctx.upload_entities(ps2, rot2, mesh)
+        ctx.frame_frozen(n, buffer_ix=1)
+        c1, t1 = ctx.counts(1)
+        assert np.array_equal(c1, counts0) and np.array_equal(t1, totals0)
+        o0, o1 = ctx.outputs(0), ctx.outputs(1)
+        assert o1.counts == o0.counts and o1.cmds[0] == o0.cmds[0] and o1.visible[1] == o0.visible[1] and o1.model != o0.model
+        for k in range(2):
+            assert np.array_equal(ctx.cmds(k, int(counts0[k]), buffer_ix=1), cmds0[k])
+            assert np.array_equal(ctx.visible(k, int(counts0[k]), buffer_ix=1), vis0[k])
+        pos, quat, scale = scene.to_components(ps2, rot2)
+        ref = O.frame(pos, quat, scale, mesh, MESHES, views, scene.CAMERA_POS, n_threads=8)
+        assert np.array_equal(ctx.model(n, buffer_ix=1), ref["model"])
+        ctx.frame(views, scene.CAMERA_POS, buffer_ix=1)  # culling unfrozen again
+        c1, _ = ctx.counts(1)
+        assert np.array_equal(c1[:2], ref["counts"])
+        assert ctx.outputs(1).cmds[0] != o0.cmds[0]
+
+
+def test_frame_host_reports_a_mesh_id_outside_the_table():
+    """The reference panics ("Vertex buffer not consolidated", cull_pipeline.rs:543); rcull_frame_host returns a status."""
+    n = 5_000
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, 40.0, len(MESHES))
+    bad = mesh.copy()
+    bad[1234] = len(MESHES) + 3
+    views = scene.scene_views(1)
+    with CullContext(n, max_views=1, max_meshes=len(MESHES)) as ctx:
+        ctx.set_mesh_table(MESHES)
+        with pytest.raises(RcullError, match="mesh id out of range"):
+            ctx.frame_host(ps, rot, bad, views, scene.CAMERA_POS)
+        c, _ = ctx.frame_host(ps, rot, mesh, views, scene.CAMERA_POS)  # the flag does not stick
+        pos, quat, scale = scene.to_components(ps, rot)
+        assert int(c[0]) == int(O.frame(pos, quat, scale, mesh, MESHES, views, scene.CAMERA_POS, want=("visible",))["counts"][0])
+
+
+def test_as_instances_needs_a_blas_address_for_every_mesh():
+    n = 1_000
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, 40.0, len(MESHES))
+    with CullContext(n, max_views=1, max_meshes=len(MESHES)) as ctx:
+        ctx.set_mesh_table(MESHES)
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(scene.scene_views(1), scene.CAMERA_POS)
+        ctx.set_blas_table(np.arange(1, len(MESHES), dtype=np.uint64))  # one short
+        with pytest.raises(RcullError, match="BLAS table"):
+            ctx.as_instances(n)
+
+
+def test_frame_host_lists_brings_the_draw_lists_back():
+    """rcull_frame_host_lists: host columns in, counts AND the five draw lists out, bit-equal to the oracle's."""
+    n, n_views = 300_000, 5
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, 120.0, len(MESHES))
+    views = scene.scene_views(n_views)
+    pos, quat, scale = scene.to_components(ps, rot)
+    ref = O.frame(pos, quat, scale, mesh, MESHES, views, scene.CAMERA_POS, n_threads=8, want=("cmds", "visible"))
+    cap = int(ref["counts"].max()) + 7
+    from renderer_b200._lib import CMD_DTYPE
+    cmds = [np.zeros(cap, CMD_DTYPE) for _ in range(n_views)]
+    vis = [np.zeros(cap, np.uint32) for _ in range(n_views)]
+    with CullContext(n, max_views=n_views, max_meshes=len(MESHES)) as ctx:
+        ctx.set_mesh_table(MESHES)
+        counts, totals = ctx.frame_host_lists(ps, rot, mesh, views, scene.CAMERA_POS, [a.ctypes.data for a in cmds],
+                                              [a.ctypes.data for a in vis], cap)
+        assert np.array_equal(counts, ref["counts"]) and np.array_equal(totals, ref["totals"])
+        for k in range(n_views):
+            c = int(counts[k])
+            assert np.array_equal(cmds[k][:c], ref["cmds"][k]) and np.array_equal(vis[k][:c], ref["visible"][k])
+        with pytest.raises(RcullError, match="exceed the host capacity"):
+            ctx.frame_host_lists(ps, rot, mesh, views, scene.CAMERA_POS, [a.ctypes.data for a in cmds], [a.ctypes.data for a in vis], 10)
+
+
+def test_packed_sum_plane_tests_fall_back_on_tiny_factors():
+    """The packed plane-test body multiplies with .ftz (rcull_frame.cuh): boxes whose centre or half-extent has a
+    nonzero component below 2^-63, and planes with such a coefficient, must take the scalar body -- bit-exact either
+    way.  Entities here sit on a lattice with exact zeros, denormal and 1e-25 offsets; 3 and 5 views."""
+    n = 50_000
+    ps, rot, mesh = scene.synth_entities(scene.SEED + 3, 0, n, 50.0, len(MESHES))
+    ps, rot = ps.copy(), rot.copy()
+    rng = np.random.default_rng(5)
+    pick = rng.choice(n, n // 7, replace=False)
+    ps[pick, rng.integers(0, 3, len(pick))] = rng.choice(np.array([0.0, 1e-25, -1e-30, 1e-39, -1e-42, 5e-20], np.float32), len(pick))
+    rot[pick[::3]] = (0, 0, 0, 1)
+    ps[pick[::5], 3] = rng.choice(np.array([1e-22, 1e-30, 1e-38, 1e-41], np.float32), len(pick[::5]))  # tiny scales: tiny half-extents
+    for n_views in (3, 5):
+        run_and_compare(n, n_views, 50.0, entities=(ps, rot, mesh))
+    # the hot variant of the kernel (no optional outputs) has its own copy of both bodies
+    views5 = scene.scene_views(5)
+    pos, quat, scale = scene.to_components(ps, rot)
+    ref5 = O.frame(pos, quat, scale, mesh, MESHES, views5, scene.CAMERA_POS, n_threads=8, want=("cmds", "visible"))
+    with CullContext(n, max_views=5, max_meshes=len(MESHES)) as ctx:
+        ctx.set_mesh_table(MESHES)
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(views5, scene.CAMERA_POS)
+        counts, totals = ctx.counts()
+        assert np.array_equal(counts[:5], ref5["counts"]) and np.array_equal(totals[:5], ref5["totals"])
+        for k in range(5):
+            assert np.array_equal(ctx.visible(k, int(counts[k])), ref5["visible"][k])
+            assert np.array_equal(ctx.cmds(k, int(counts[k])), ref5["cmds"][k])
+    # a plane with a tiny coefficient: the whole frame takes the scalar body
+    views = scene.scene_views(3).copy()
+    views[1, 2, 0] = 1e-30
+    views[2, 4, 1] = -1e-41
+    pos, quat, scale = scene.to_components(ps, rot)
+    ref = O.frame(pos, quat, scale, mesh, MESHES, views, scene.CAMERA_POS, n_threads=8, want=("flags", "visible"))
+    with CullContext(n, max_views=3, max_meshes=len(MESHES), materialize_flags=True) as ctx:
+        ctx.set_mesh_table(MESHES)
+        ctx.upload_entities(ps, rot, mesh)
+        ctx.frame(views, scene.CAMERA_POS)
+        counts, _ = ctx.counts()
+        assert np.array_equal(counts[:3], ref["counts"])
+        for k in range(3):
+            assert np.array_equal(ctx.flags(k, n), ref["flags"][k])
+            assert np.array_equal(ctx.visible(k, int(counts[k])), ref["visible"][k])
