@@ -500,13 +500,13 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
         for (int p = 0; p < 6; ++p) {
             const float* pl = views[v].planes[p];
             PlaneC& pc = a.planes[v][p];
-            pc.ax = make_float2(fabsf(pl[0]), fabsf(pl[0]));
-            pc.ay = make_float2(fabsf(pl[1]), fabsf(pl[1]));
-            pc.az = make_float2(fabsf(pl[2]), fabsf(pl[2]));
-            pc.px = make_float2(pl[0], pl[0]);
-            pc.py = make_float2(pl[1], pl[1]);
-            pc.pz = make_float2(pl[2], pl[2]);
-            pc.pw = make_float2(pl[3], pl[3]);
+            pc.ax = fabsf(pl[0]);
+            pc.ay = fabsf(pl[1]);
+            pc.az = fabsf(pl[2]);
+            pc.px = pl[0];
+            pc.py = pl[1];
+            pc.pz = pl[2];
+            pc.pw = pl[3];
         }
     }
     // packed-sum plane tests multiply with .ftz (rcull_frame.cuh): allowed while no plane factor is a tiny nonzero number

@@ -44,11 +44,19 @@ constexpr int kCtasPerSm = kComputeWarps <= 7 ? 2 : 1;
 // can be resident beside it and overlap with the frame
 constexpr size_t kSmemPerCta = (228 * 1024 - (kCtasPerSm == 1 ? 2 : kCtasPerSm) * 1024) / kCtasPerSm;
 constexpr int kThreads = (kComputeWarps + 1) * 32;  // + scan warp
-constexpr int kItems = 4;                           // entities per thread per tile
+#ifndef RCULL_ITEMS
+#define RCULL_ITEMS 4
+#endif
+constexpr int kItems = RCULL_ITEMS;                 // entities per thread per tile
+constexpr int kPairs = kItems / 2;                  // entity pairs whose plane tests share packed (f32x2) instructions
+constexpr bool kOddItem = (kItems % 2) != 0;        // the last entity of an odd count runs the same arithmetic unpacked
 constexpr int kTile = kComputeWarps * 32 * kItems;  // 1920 entities with 15 compute warps
 constexpr int kWarpSpan = 32 * kItems;              // entities owned by one compute warp
 constexpr int kStages = 2;
-constexpr int kMaxBufs = 4;   // survivor bookkeeping ring (tiles whose commands are not emitted yet)
+#ifndef RCULL_MAX_BUFS
+#define RCULL_MAX_BUFS 4
+#endif
+constexpr int kMaxBufs = RCULL_MAX_BUFS;   // survivor bookkeeping ring (tiles whose commands are not emitted yet)
 constexpr int kRing = 8;      // tile-id ring: bookkeeping ring + the tile being loaded + slack
 constexpr int kMaxViews = 8;
 constexpr int kMaxLods = 6;
@@ -67,13 +75,11 @@ __device__ unsigned long long g_scan_stats[16];
 // Tile descriptor: x = epoch:30 | flag:2 | count:32, y = index sum.
 constexpr uint64_t kFlagAgg = 1, kFlagIncl = 2;
 
-// One frustum plane, laid out for the packed (two entities per instruction) products:
-// every multiplicand is stored twice so that a 64-bit uniform load yields the pair.
+// One frustum plane as the kernel reads it: two 16-byte words.  A packed (f32x2) product takes the plane value as a
+// SCALAR operand broadcast to both halves (SASS `FMUL2 R, Ra.F32x2, Rb.F32`), so nothing is stored twice.
 struct PlaneC {
-    float2 ax, ay, az;  // |p.x|, |p.y|, |p.z|
-    float2 px, py, pz;
-    float2 pw;  // (pw, pw): the addend of the packed sums
-    float pad1, pad2;
+    float ax, ay, az, px;  // |p.x|, |p.y|, |p.z|, p.x
+    float py, pz, pw, pad;
 };
 
 struct FrameArgs {
@@ -132,28 +138,42 @@ struct FrameSmem {
     // followed by: PlaneC planes[V][6] (a shared-memory copy: LDS.128 instead of indexed LDC), then
     // uint8_t wlist[bufs][kComputeWarps][V * kWarpSpan] -- per-warp combined survivor list,
     // view-major, entry = lod << 7 | slot in the warp's span (the view follows from the entry's
-    // position and the per-view counts) -- and, when it fits, a copy of the mesh table
-    // (float4 aabb[M][2], uint32_t len1[M]: 36 bytes per mesh)
+    // position and the per-view counts) --, uint8_t mid8[bufs][kTile] (mesh id of every entity of the tile, kept
+    // until its commands are emitted) and, when it fits, a copy of the mesh table (float4 aabb[M][2],
+    // uint4 lod01[M][2]: 64 bytes per mesh)
 };
 
+// Per bookkeeping buffer: the survivor lists (V bytes per entity) and one byte per entity with its mesh id (kept until
+// the tile's commands are emitted, so that emission needs no global load when the mesh table is small).
 template <int V>
 __host__ __device__ constexpr int frame_bufs() {  // what still lets kCtasPerSm CTAs share an SM's shared memory
-    constexpr size_t fixed = sizeof(FrameSmem) + V * 6 * sizeof(PlaneC) + 1024, per_buf = V * kTile;
+    // 4 buffers when they leave room for a useful mesh table behind them, else 3, never fewer than 2
+    constexpr size_t fixed = sizeof(FrameSmem) + V * 6 * sizeof(PlaneC) + 1024, per_buf = (V + 1) * kTile;
     constexpr size_t b = (kSmemPerCta - fixed) / per_buf;
-    return b > (size_t)kMaxBufs ? kMaxBufs : (int)b;
+    constexpr size_t want0 = (kSmemPerCta - fixed) >= 4 * per_buf + 12 * 1024 ? 4 : 3;
+    constexpr size_t want = want0 > (size_t)kMaxBufs ? (size_t)kMaxBufs : want0;
+    return b > want ? (int)want : (int)b;
 }
 template <int V>
-__host__ __device__ constexpr size_t frame_lists_end() {  // offset of the first byte behind the survivor lists
-    return (sizeof(FrameSmem) + V * 6 * sizeof(PlaneC) + frame_bufs<V>() * V * kTile + 15) / 16 * 16;
+__host__ __device__ constexpr size_t frame_mid8_off() {  // mesh-id bytes, behind the survivor lists
+    return sizeof(FrameSmem) + V * 6 * sizeof(PlaneC) + frame_bufs<V>() * V * kTile;
 }
 template <int V>
-__host__ __device__ constexpr uint32_t frame_mesh_cap() {  // meshes whose table fits behind the lists (36 bytes each)
+__host__ __device__ constexpr size_t frame_lists_end() {  // offset of the first byte behind the per-buffer bookkeeping
+    return (frame_mid8_off<V>() + frame_bufs<V>() * kTile + 15) / 16 * 16;
+}
+// Shared-memory copy of the mesh table, per mesh: float4 aabb[2] (+ n_lods, index_len of lod 0), and for lods 0 and 1
+// (the only ones pick_lod returns, helpers.rs:3-11) the uint4 (index_len, first_index, vertex_offset, 0) rows that
+// emission needs: 64 bytes.  Mesh ids must fit the byte kept per entity.
+constexpr uint32_t kMeshSmemBytes = 64;
+template <int V>
+__host__ __device__ constexpr uint32_t frame_mesh_cap() {
     constexpr size_t left = kSmemPerCta - 1024 - frame_lists_end<V>();
-    return left / 36 > 1024 ? 1024u : (uint32_t)(left / 36) / 4 * 4;
+    return left / kMeshSmemBytes > 256 ? 256u : (uint32_t)(left / kMeshSmemBytes);
 }
 template <int V>
 constexpr size_t frame_smem_bytes() {
-    return frame_lists_end<V>() + frame_mesh_cap<V>() * 36 + 1024;  // + slack to align the base
+    return frame_lists_end<V>() + frame_mesh_cap<V>() * kMeshSmemBytes + 1024;  // + slack to align the base
 }
 static_assert(frame_bufs<1>() >= 2 && frame_bufs<kMaxViews>() >= 2, "at least two tiles of survivor bookkeeping");
 
@@ -196,7 +216,7 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
     uint64_t acc_l[V];
     bool open[V];
     int base = 0;
-    long long t_pub[kMaxBufs] = {0, 0, 0, 0}, t_act = 0;
+    long long t_pub[kMaxBufs] = {}, t_act = 0;
     while (true) {
         bool progress = false;
         // ---- publish ----
@@ -339,9 +359,12 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
 
 // Compute-warp emission of its own survivors of a pending tile: one pass over the
 // warp's combined (all views) list, stable within every view.
+// sm_lod01 != nullptr: the mesh table is in shared memory (mesh ids fit a byte): the survivor's mesh id comes from
+// the tile's mid8 bytes and its LOD row from the shared copy -- no global load between a resolved tile and its
+// commands (the two dependent L2 round trips of the general path were 13 % of the compute warps' time).
 template <int V>
-__device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameSmem& sm, const uint8_t* wlist,
-                                             uint32_t buf, uint32_t tile_base, uint32_t warp, uint32_t lane) {
+__device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameSmem& sm, const uint8_t* wlist, const uint8_t* mid8,
+                                             const uint4* sm_lod01, uint32_t buf, uint32_t tile_base, uint32_t warp, uint32_t lane) {
     uint32_t vend[V];  // end of view k in the combined list
     uint32_t total = 0;
 #pragma unroll
@@ -360,10 +383,16 @@ __device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameS
             for (int kk = 0; kk < V - 1; ++kk) k += i >= vend[kk] ? 1u : 0u;
             const uint32_t entry = wlist[i];  // lod << 7 | slot in the warp's span
             e = warp * kWarpSpan + (entry & 127u);
-            uint32_t mid = __ldg(args.mesh + tile_base + e);  // survivors only: the column is still in L2
-            if (mid >= args.n_meshes) mid = 0;                // same clamp as the compute pass (error already flagged)
-            slot = mid * kMaxLods + (entry >> 7);
-            L = __ldg(args.lod_tab + slot);
+            if (sm_lod01 != nullptr) {
+                const uint32_t mid = mid8[e];  // already clamped by the compute pass
+                slot = mid * kMaxLods + (entry >> 7);
+                L = sm_lod01[2 * mid + (entry >> 7)];
+            } else {
+                uint32_t mid = __ldg(args.mesh + tile_base + e);  // survivors only: the column is still in L2
+                if (mid >= args.n_meshes) mid = 0;                // same clamp as the compute pass (error already flagged)
+                slot = mid * kMaxLods + (entry >> 7);
+                L = __ldg(args.lod_tab + slot);
+            }
         }
         const uint32_t incl = warp_incl_scan_u32(L.x, lane);
         const uint32_t excl = carry + incl - L.x;
@@ -452,18 +481,21 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
         if (more) next_t = draw_ticket();
     }
     float4* const sm_planes = reinterpret_cast<float4*>(reinterpret_cast<unsigned char*>(&sm) + sizeof(FrameSmem));
-    for (uint32_t i = tid; i < V * 6 * 4; i += kThreads) sm_planes[i] = reinterpret_cast<const float4*>(&args.planes[0][0])[i];
+    for (uint32_t i = tid; i < V * 6 * 2; i += kThreads) sm_planes[i] = reinterpret_cast<const float4*>(&args.planes[0][0])[i];
     // Mesh table: a shared-memory copy when it fits (the L1 left beside ~220 KB of shared memory
     // is a few KB: table lines kept falling out of it), else the global one through generic loads.
     const float4* mesh_tab = args.mesh_aabb;
     const uint32_t* len1_tab = args.mesh_len1;
+    const uint4* sm_lod01 = nullptr;  // set: emission reads mesh ids and LOD rows from shared memory
     if (args.n_meshes <= frame_mesh_cap<V>()) {
         float4* sm_mesh = reinterpret_cast<float4*>(reinterpret_cast<unsigned char*>(&sm) + frame_lists_end<V>());
-        uint32_t* sm_len1 = reinterpret_cast<uint32_t*>(sm_mesh + 2 * frame_mesh_cap<V>());
-        for (uint32_t i = tid; i < 2 * args.n_meshes; i += kThreads) sm_mesh[i] = args.mesh_aabb[i];
-        for (uint32_t i = tid; i < args.n_meshes; i += kThreads) sm_len1[i] = args.mesh_len1[i];
+        uint4* sm_lod = reinterpret_cast<uint4*>(sm_mesh + 2 * frame_mesh_cap<V>());
+        for (uint32_t i = tid; i < 2 * args.n_meshes; i += kThreads) {
+            sm_mesh[i] = args.mesh_aabb[i];
+            sm_lod[i] = args.lod_tab[(i >> 1) * kMaxLods + (i & 1u)];  // lods 0 and 1 of mesh i / 2
+        }
         mesh_tab = sm_mesh;
-        len1_tab = sm_len1;
+        sm_lod01 = sm_lod;
     }
     __syncthreads();
 
@@ -474,6 +506,7 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
 
     // ================================= compute warps =================================
     uint8_t* const wlist_base = reinterpret_cast<unsigned char*>(&sm) + sizeof(FrameSmem) + V * 6 * sizeof(PlaneC) + warp * (V * kWarpSpan);
+    uint8_t* const mid8_base = reinterpret_cast<unsigned char*>(&sm) + frame_mid8_off<V>();  // [bufs][kTile]
     const uint32_t lt = (1u << lane) - 1u;
     // swizzled (128-B pattern) byte offsets of this lane's four matrix columns in the warp's store box
     unsigned char* const box = reinterpret_cast<unsigned char*>(sm.mat[warp]);
@@ -491,7 +524,7 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
     uint32_t emitted = 0;  // iterations [emitted, it) of this CTA still have their commands pending
     auto emit_next = [&]() {
         const uint32_t b = emitted % B;
-        emit_pending<V>(args, sm, wlist_base + b * (V * kTile), b, sm.tile_ring[emitted % kRing] * kTile, warp, lane);
+        emit_pending<V>(args, sm, wlist_base + b * (V * kTile), mid8_base + b * kTile, sm_lod01, b, sm.tile_ring[emitted % kRing] * kTile, warp, lane);
         ++emitted;
     };
     for (;; ++it) {
@@ -554,20 +587,6 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
             valid[j] = g < args.n;
             const Mat34 m = model_matrix(ps[j], q[j]);
 
-            // model matrix out: swizzled box in smem -> one 2 KB TMA tensor store per warp and item
-            if (lane == 0) bulk_wait_read0();  // the previous store has finished reading the box
-            __syncwarp();
-            *reinterpret_cast<float4*>(box + moff0) = make_float4(m.m00, m.m10, m.m20, 0.f);
-            *reinterpret_cast<float4*>(box + moff1) = make_float4(m.m01, m.m11, m.m21, 0.f);
-            *reinterpret_cast<float4*>(box + moff2) = make_float4(m.m02, m.m12, m.m22, 0.f);
-            *reinterpret_cast<float4*>(box + moff3) = make_float4(m.tx, m.ty, m.tz, 1.f);
-            fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) {
-                tma_store_2d(&model_map, box, 0, (int)((tile_base + warp * kWarpSpan + 32 * j) >> 1));
-                bulk_commit();
-            }
-
             // A2: world AABB
             const float4 mn = mesh_tab[2 * mid[j]];
             const float4 mx = mesh_tab[2 * mid[j] + 1];
@@ -595,13 +614,29 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
             const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
             const uint32_t n_lods = __float_as_uint(mn.w);
             const bool lod1 = d2 > args.lod_d2_max && n_lods > 1u;
-            len[j] = lod1 ? len1_tab[mid[j]] : __float_as_uint(mx.w);  // index_len of the chosen lod
+            len[j] = lod1 ? (sm_lod01 != nullptr ? sm_lod01[2 * mid[j] + 1].x : len1_tab[mid[j]]) : __float_as_uint(mx.w);  // index_len of the chosen lod
             entry[j] = (lod1 ? 128u : 0u) + lane + 32u * j;            // survivor-list entry: lod << 7 | slot in span
+
+            // model matrix out: swizzled box in smem -> one 2 KB TMA tensor store per warp and item.  LAST in the
+            // item: the wait for the previous item's store to have read the box then has the whole A2 / A4 arithmetic of
+            // this item in front of it.
+            if (lane == 0) bulk_wait_read0();
+            __syncwarp();
+            *reinterpret_cast<float4*>(box + moff0) = make_float4(m.m00, m.m10, m.m20, 0.f);
+            *reinterpret_cast<float4*>(box + moff1) = make_float4(m.m01, m.m11, m.m21, 0.f);
+            *reinterpret_cast<float4*>(box + moff2) = make_float4(m.m02, m.m12, m.m22, 0.f);
+            *reinterpret_cast<float4*>(box + moff3) = make_float4(m.tx, m.ty, m.tz, 1.f);
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_2d(&model_map, box, 0, (int)((tile_base + warp * kWarpSpan + 32 * j) >> 1));
+                bulk_commit();
+            }
         }
 
-        float2 c2x[kItems / 2], c2y[kItems / 2], c2z[kItems / 2], h2x[kItems / 2], h2y[kItems / 2], h2z[kItems / 2];
+        float2 c2x[kPairs], c2y[kPairs], c2z[kPairs], h2x[kPairs], h2y[kPairs], h2z[kPairs];
 #pragma unroll
-        for (int i = 0; i < kItems / 2; ++i) {
+        for (int i = 0; i < kPairs; ++i) {
             c2x[i] = make_float2(cx[2 * i], cx[2 * i + 1]); h2x[i] = make_float2(hx[2 * i], hx[2 * i + 1]);
             c2y[i] = make_float2(cy[2 * i], cy[2 * i + 1]); h2y[i] = make_float2(hy[2 * i], hy[2 * i + 1]);
             c2z[i] = make_float2(cz[2 * i], cz[2 * i + 1]); h2z[i] = make_float2(hz[2 * i], hz[2 * i + 1]);
@@ -627,6 +662,11 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
         }
         __syncwarp();
         const uint32_t wlist_s = smem_u32(wlist);
+        if (sm_lod01 != nullptr) {  // this tile's mesh ids, for its emission a few tiles from now (the buffer's previous tile is emitted)
+            const uint32_t m8 = smem_u32(mid8_base + buf * kTile + e0);
+#pragma unroll
+            for (int j = 0; j < kItems; ++j) sts_u8(m8 + 32 * j, mid[j]);
+        }
 
         // A3 per view: planes outer, the thread's 4 entities inner
         // (the view loop stays rolled: unrolled, the kernel outgrows the instruction cache).
@@ -657,25 +697,32 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
             }
         }
         uint32_t woff = 0;  // start of view k in the warp's combined list
-        const float4* vp = sm_planes;  // planes of view k: 6 x 4 float4
+        const float4* vp = sm_planes;  // planes of view k: 6 x 2 float4
         auto view_loop = [&](auto packed_c) {
             constexpr bool kPacked = decltype(packed_c)::value;
 #pragma unroll kViewUnroll
-            for (int k = 0; k < V; ++k, vp += 24) {
+            for (int k = 0; k < V; ++k, vp += 12) {
                 bool outside[kItems];
 #pragma unroll
                 for (int j = 0; j < kItems; ++j) outside[j] = !valid[j];  // padding slots are never visible
 #pragma unroll
                 for (int p = 0; p < 6; ++p) {
-                    const float4* pp = vp + p * 4;
-                    const float4 q0 = pp[0], q1 = pp[1], q2 = pp[2];  // (ax ax ay ay) (az az px px) (py py pz pz)
-                    const float pw = pp[3].x;
-                    const float2 ax = make_float2(q0.x, q0.y), ay = make_float2(q0.z, q0.w), az = make_float2(q1.x, q1.y);
-                    const float2 px = make_float2(q1.z, q1.w), py = make_float2(q2.x, q2.y), pz = make_float2(q2.z, q2.w);
+                    const float4* pp = vp + p * 2;
+                    const float4 q0 = pp[0], q1 = pp[1];  // (ax ay az px) (py pz pw -)
+                    const float pw = q1.z;
+                    const float2 ax = make_float2(q0.x, q0.x), ay = make_float2(q0.y, q0.y), az = make_float2(q0.z, q0.z);
+                    const float2 px = make_float2(q0.w, q0.w), py = make_float2(q1.x, q1.x), pz = make_float2(q1.y, q1.y);
+                    if constexpr (kOddItem) {  // the unpaired entity: the same operations, one at a time (scalar IEEE products and sums)
+                        constexpr int o = kItems - 1;
+                        const float e = __fadd_rn(__fadd_rn(__fmul_rn(hx[o], ax.x), __fmul_rn(hy[o], ay.x)), __fmul_rn(hz[o], az.x));
+                        const float sa = __fadd_rn(__fmul_rn(cx[o], px.x), __fmul_rn(cz[o], pz.x));
+                        const float sb = __fadd_rn(__fmul_rn(cy[o], py.x), pw);
+                        outside[o] = outside[o] || (__fadd_rn(sa, sb) > e);
+                    }
 #pragma unroll
-                    for (int i = 0; i < kItems / 2; ++i) {
+                    for (int i = 0; i < kPairs; ++i) {
                         if constexpr (kPacked) {
-                            const float2 pw2 = make_float2(pp[3].x, pp[3].y);  // (pw, pw)
+                            const float2 pw2 = make_float2(pw, pw);
                             const float2 e = add2_rn(add2_rn(mul2_ftz(h2x[i], ax), mul2_ftz(h2y[i], ay)), mul2_ftz(h2z[i], az));
                             const float2 a = add2_rn(mul2_ftz(c2x[i], px), mul2_ftz(c2z[i], pz));
                             const float2 b = add2_rn(mul2_ftz(c2y[i], py), pw2);
