@@ -194,7 +194,7 @@ def gpu_arm(args, wl):
     import torch.distributed as dist
 
     from renderer_b200 import CullContext, scene
-    from renderer_b200.shard import PeerMerger, ShardMerger, _wrap_device
+    from renderer_b200.shard import RecordMerger, ShardMerger, _wrap_device
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -220,10 +220,11 @@ def gpu_arm(args, wl):
             probe.synth_entities(scene.SEED, lo, n, wl["half_box"], len(meshes))
             probe.frame(views, scene.CAMERA_POS, draw_index_base=lo)
             tri_cap = int(probe.counts()[1][0]) + 3
-    # N > 1 with the peer-store merge: two output sets, so the merge of frame i (its own stream) overlaps frame i + 1
-    pipelined = world > 1 and args.merge == "p2p" and not args.no_overlap
-    ctx = CullContext(n, max_views=n_views, max_meshes=len(meshes), device=local_rank, capacity_tri_indices=tri_cap,
-                      n_buffers=2 if pipelined else 1)
+    # N > 1, record merge: the frame kernel sends its survivors itself; then frame, expand, frame, expand on one stream
+    # (--pipeline queues the expand of frame i behind frame i + 1; --expand-sms splits the chip between the two kernels)
+    beside = world > 1 and args.merge == "p2p" and args.expand_sms > 0
+    pipelined = world > 1 and args.merge == "p2p" and args.pipeline and not beside
+    ctx = CullContext(n, max_views=n_views, max_meshes=len(meshes), device=local_rank, capacity_tri_indices=tri_cap)
     ctx.set_mesh_table(meshes)
     pv = None
     if tri:
@@ -235,45 +236,52 @@ def gpu_arm(args, wl):
     stream.synchronize()
 
     merger = None
+    cap = cap_r = 0
+    own_counts = own_totals = None
     if world > 1:
-        ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, stream=sh)
+        ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, stream=sh)  # sizes the merged lists; also this rank's own lists
         stream.synchronize()
-        c0, _ = ctx.counts()
-        tot = torch.tensor([int(c0[:n_views].max())], dtype=torch.int64, device=dev)
-        dist.all_reduce(tot)
-        cap = int(tot.item() * 1.05) + 1024
-        merger = PeerMerger(ctx, n_views, cap, dev, symmetric=world >= 8) if args.merge == "p2p" else ShardMerger(n_views, cap, dev)
+        own_counts, own_totals = ctx.counts()
+        c0 = torch.tensor(own_counts[:n_views].astype(np.int64), device=dev)
+        c_sum, c_max = c0.clone(), c0.clone()
+        dist.all_reduce(c_sum)
+        dist.all_reduce(c_max, op=dist.ReduceOp.MAX)
+        cap = int(c_sum.max().item() * 1.05) + 1024
+        cap_r = int(c_max.max().item() * 1.05) + 1024
+        merger = RecordMerger(ctx, cap, cap_r, dev, symmetric=args.multicast) if args.merge == "p2p" else ShardMerger(n_views, cap, dev)
+        if beside:
+            merger.set_overlap(args.expand_sms)
+    # expand beside the next frame: the chip is split -- the frame kernel's grid leaves expand_sms SMs, the expand's CTAs
+    # (one whole SM each) run there, on a second stream
+    expand_stream = torch.cuda.Stream(device=dev, priority=0) if beside else None
+    frame_ev = [torch.cuda.Event() for _ in range(2)]
 
     flush = torch.zeros((2, 256 * 1024 * 1024), dtype=torch.uint8, device=dev) if n * 36 < 256e6 else None
-
-    merge_stream = torch.cuda.Stream(device=dev, priority=0) if pipelined else None  # below the frame stream: frame CTAs are placed first
-    frame_done = [torch.cuda.Event() for _ in range(2)]
-    step_no = [0]
+    record = world > 1 and args.merge == "p2p"
+    pending = [0]  # merged frames issued and not expanded yet
 
     def step(ev0=None):
-        if not pipelined:
-            if ev0 is not None:
-                ev0.record(stream)
-            ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, stream=sh)
-            return
-        b = step_no[0] & 1
-        if step_no[0] >= 2:
-            stream.wait_event(merger.ev_scatter_done[b])  # merge i-2 has read output set b
         if ev0 is not None:
             ev0.record(stream)
-        ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, buffer_ix=b, stream=sh)
-        frame_done[b].record(stream)
+        ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, stream=sh)
+        pending[0] += 1
 
-    def do_merge():
-        if pipelined:
-            b = step_no[0] & 1
-            step_no[0] += 1
-            merge_stream.wait_event(frame_done[b])
-            with torch.cuda.stream(merge_stream):
-                merger.exchange(b)
-        elif args.merge == "p2p":
-            merger.merge()
+    def do_merge(final=False):
+        if beside:
+            e = frame_ev[pending[0] & 1]
+            e.record(stream)
+            expand_stream.wait_event(e)
+            merger.expand(expand_stream.cuda_stream)
+            pending[0] = 0
+            if final:
+                stream.wait_stream(expand_stream)  # the timed region ends when the last expand has
+        elif record:
+            # pipelined: frame i + 1 is already queued when frame i is expanded; the last step expands both
+            while pending[0] > (0 if (final or not pipelined) else 1):
+                merger.expand(sh)
+                pending[0] -= 1
         else:
+            pending[0] = 0
             merger.merge_from_context(ctx, stream=sh)
 
     def sync_all():
@@ -282,10 +290,10 @@ def gpu_arm(args, wl):
         torch.cuda.synchronize()
 
     with torch.cuda.stream(stream):
-        for _ in range(args.warmup):
+        for i in range(args.warmup):
             step()
             if merger:
-                do_merge()
+                do_merge(final=i == args.warmup - 1)
             if tri:
                 ctx.tri_cull(pv, draw_index_base=lo, stream=sh)
             if flush is not None:
@@ -298,19 +306,17 @@ def gpu_arm(args, wl):
                 step(ev[i][0])
                 ev[i][1].record(stream)
                 if merger:
-                    do_merge()
+                    do_merge(final=i == args.steps - 1)  # the timed region holds K frames AND K expands
                 if tri:
                     ctx.tri_cull(pv, draw_index_base=lo, stream=sh)
-                if pipelined and i == args.steps - 1:
-                    stream.wait_stream(merge_stream)  # the timed region ends when the last merge has
                 ev[i][2].record(stream)
                 if flush is not None:
                     flush_l2(flush)
             sync_all()
         launches = ctx.launch_count - launches0
     t_frame = sum(e[0].elapsed_time(e[1]) for e in ev) / 1e3  # seconds, all steps
-    t_step = (ev[0][0].elapsed_time(ev[-1][2]) if pipelined else sum(e[0].elapsed_time(e[2]) for e in ev)) / 1e3
-    counts, totals = ctx.counts()
+    t_step = (ev[0][0].elapsed_time(ev[-1][2]) if (pipelined or beside) else sum(e[0].elapsed_time(e[2]) for e in ev)) / 1e3
+    counts, totals = ctx.counts()  # this rank's own counts (the frame kernel writes them in every mode)
     counts = counts[:n_views].astype(np.int64)
 
     # ---- end to end: host (pinned) buffers in, counts out, through rcull_frame_host ----
@@ -328,12 +334,10 @@ def gpu_arm(args, wl):
     def e2e_step():
         c, _ = ctx.frame_host(a_ps, a_rot, a_mesh, views, scene.CAMERA_POS, draw_index_base=lo)
         if merger:
-            if pipelined:
-                merger.exchange(0)  # frame_host wrote output set 0 and has already completed
-            elif args.merge == "p2p":
-                merger.merge(0)
+            if record:
+                merger.expand(ctx.stream)  # frame_host has completed on the context's stream: the records are out
             else:
-                do_merge()
+                merger.merge_from_context(ctx, stream=sh)
             torch.cuda.synchronize()
         return c
 
@@ -369,30 +373,64 @@ def gpu_arm(args, wl):
                      "steps": e2e_steps, "ms_per_step": t_l / e2e_steps * 1e3,
                      "api": "rcull_frame_host_lists (pinned host columns in; counts, index totals and the draw lists of every view out)"}
 
-    # ---- N > 1: the merged lists of the peer-store exchange against an NCCL allgatherv of the same frame ----
-    merge_verified = None
-    if world > 1 and args.merge == "p2p":
-        with torch.cuda.stream(stream):
-            ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, buffer_ix=0, stream=sh)
-            if pipelined:
-                merger.exchange(0)
-            else:
-                merger.merge(0)
-        sync_all()
-        ref = ShardMerger(n_views, cap, dev)
-        with torch.cuda.stream(stream):
-            ref.merge_from_context(ctx, stream=sh)
-        sync_all()
-        ok = True
+    # ---- N > 1: what the merge delivered.  (a) every rank's OWN slice of every merged list, bit for bit, against the
+    # oracle run on that rank's shard (the shards with draw_index_base >= 16 Mi included), plus the
+    # merged counts / totals against the sum of the ranks' oracle counts; (b) the merged lists against an NCCL
+    # allgatherv of per-rank lists produced by a second, merge-free context. ----
+    merge_verified = oracle_verified = None
+    if record and not args.no_verify:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_lib as O  # checker
+
+        pos, quat, scale, mesh_h = O.synth_entities(scene.SEED, lo, n, wl["half_box"], len(meshes))
+        ref = O.frame(pos, quat, scale, mesh_h, meshes, views, scene.CAMERA_POS, draw_index_base=lo, n_threads=max(1, (os.cpu_count() or 8) // world * 2),
+                      want=("cmds", "visible"), fused=True)
+        del pos, quat, scale, mesh_h
+        ok = bool(np.array_equal(ref["counts"].astype(np.int64), counts))
+        meta = torch.tensor(np.concatenate([ref["counts"].astype(np.int64), ref["totals"].astype(np.int64)]), dtype=torch.int64, device=dev)
+        meta_all = torch.zeros(world * 2 * n_views, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(meta_all, meta)
+        meta_all = meta_all.view(world, 2, n_views).cpu().numpy()
+        torch.cuda.synchronize()
         for k in range(n_views):
-            cp, vp, _, _ = merger.lists(k)
-            cnt = int(ref.plan.counts[k])
-            ok = ok and torch.equal(_wrap_device(torch, cp, max(cnt, 1) * 5, torch.int32, dev)[: cnt * 5], ref.merged_cmds[k][: cnt * 5])
-            ok = ok and torch.equal(_wrap_device(torch, vp, max(cnt, 1), torch.int32, dev)[:cnt], ref.merged_visible[k][:cnt])
+            cp, vp, cntp, totp = merger.lists(k)
+            cnt_all = _wrap_device(torch, cntp, n_views, torch.int32, dev).cpu().numpy().view(np.uint32)
+            tot_all = _wrap_device(torch, totp, n_views, torch.int64, dev).cpu().numpy().view(np.uint64)
+            ok = ok and int(cnt_all[k]) == int(meta_all[:, 0, k].sum()) and int(tot_all[k]) == int(meta_all[:, 1, k].sum())
+            first = int(meta_all[:rank, 0, k].sum())
+            idx_prefix = int(meta_all[:rank, 1, k].sum()) & 0xFFFFFFFF
+            c = int(ref["counts"][k])
+            got_v = _wrap_device(torch, vp + 4 * first, max(c, 1), torch.int32, dev)[:c].cpu().numpy().view(np.uint32)
+            got_c = _wrap_device(torch, cp + 20 * first, max(c, 1) * 5, torch.int32, dev)[: c * 5].cpu().numpy().view(np.uint32).reshape(c, 5)
+            want_c = ref["cmds"][k].view(np.uint32).reshape(c, 5).copy()
+            want_c[:, 2] += np.uint32(idx_prefix)  # the rank prefix of the merged running sum (u32 wrap like the reference's)
+            ok = ok and bool(np.array_equal(got_v, ref["visible"][k])) and bool(np.array_equal(got_c, want_c))
         flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-        merge_verified = bool(flag.item())
-        assert merge_verified, "merged draw lists of the peer-store exchange differ from the NCCL allgatherv of the same frame"
+        oracle_verified = bool(flag.item())
+        assert oracle_verified, "merged draw lists differ from the oracle run on the ranks' shards"
+        del ref
+        # (b) transport cross-check: NCCL allgatherv of a merge-free context's lists of the same shard
+        with CullContext(n, max_views=n_views, max_meshes=len(meshes), device=local_rank) as plain:
+            plain.set_mesh_table(meshes)
+            plain.synth_entities(scene.SEED, lo, n, wl["half_box"], len(meshes), stream=sh)
+            plain.frame(views, scene.CAMERA_POS, draw_index_base=lo, stream=sh)
+            sync_all()
+            ref_m = ShardMerger(n_views, cap, dev)
+            with torch.cuda.stream(stream):
+                ref_m.merge_from_context(plain, stream=sh)
+            sync_all()
+            ok = True
+            for k in range(n_views):
+                cp, vp, _, _ = merger.lists(k)
+                cnt = int(ref_m.plan.counts[k])
+                ok = ok and torch.equal(_wrap_device(torch, cp, max(cnt, 1) * 5, torch.int32, dev)[: cnt * 5], ref_m.merged_cmds[k][: cnt * 5])
+                ok = ok and torch.equal(_wrap_device(torch, vp, max(cnt, 1), torch.int32, dev)[:cnt], ref_m.merged_visible[k][:cnt])
+            flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            merge_verified = bool(flag.item())
+            assert merge_verified, "merged draw lists of the record merge differ from the NCCL allgatherv of the ranks' lists"
+            del ref_m
 
     # ---- reduce over ranks: time = max, work = sum ----
     times = torch.tensor([t_step, t_frame, t_e2e], dtype=torch.float64, device=dev)
@@ -407,7 +445,29 @@ def gpu_arm(args, wl):
     if rank == 0:
         peak, peak_kind = load_peaks()
         v_frac = counts / float(n)  # this rank's visible fractions (rank 0's launch is the one timed)
-        bytes_per_entity = 36.0 + 64.0 + 24.0 * float(v_frac.sum())
+        if record:  # 8-byte records instead of 24-byte list entries, and every rank's records land in this GPU's window during the frame
+            bytes_per_entity = 36.0 + 64.0 + 8.0 * float(vis.sum()) / n
+        else:
+            bytes_per_entity = 36.0 + 64.0 + 24.0 * float(v_frac.sum())
+        merge_report = None
+        if world > 1:
+            t_expand = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps / 1e3
+            inbound = 8.0 * (float(vis.sum()) - float(counts.sum())) if record else 24.0 * (float(vis.sum()) - float(counts.sum()))
+            merge_report = {
+                "expand_ms_per_step" if record else "ms_per_step": t_expand * 1e3,
+                "step_minus_frame_ms": (t_step - t_frame) / args.steps * 1e3,
+                "expand_queued_behind_next_frame": pipelined, "expand_beside_next_frame": beside,
+                "record_bytes_per_survivor": 8 if record else 24,
+                "nvlink_inbound_bytes_per_gpu_per_frame": int(inbound),
+                "nvlink_outbound_bytes_per_gpu_per_frame": int((8.0 if record else 24.0) * float(counts.sum()) * (1 if "multicast" in getattr(merger, "transport", "") else world - 1)),
+                # records travel while the frame kernel runs: the link is busy for the frame's duration
+                "nvlink_inbound_gbs_per_gpu": inbound / (t_frame / args.steps) / 1e9 if record else inbound / max(t_expand, 1e-9) / 1e9,
+                "nvlink_peak_gbs": 770.0,
+                "nvlink_frac": (inbound / (t_frame / args.steps) / 1e9 if record else inbound / max(t_expand, 1e-9) / 1e9) / 770.0,
+                "expand_hbm_gbs": (32.0 * float(vis.sum()) / max(t_expand, 1e-9) / 1e9) if record else None,
+                "transport": getattr(merger, "transport", "nccl"),
+                "verified_against_oracle_per_rank": oracle_verified, "verified_against_nccl_allgatherv": merge_verified,
+                "note": "peak = measured peer copy per direction; inbound = the other ranks' records landing in this GPU's window during the frame; expand = 8 B read + 24 B written per merged survivor, local"}
         t_launch = t_frame / args.steps
         achieved = n * bytes_per_entity / t_launch / 1e9
         line = {
@@ -418,7 +478,10 @@ def gpu_arm(args, wl):
                 "workload": args.workload, "entities_per_gpu": n, "entities_total": n_total, "n_views": n_views,
                 "half_box": wl["half_box"], "visible_fraction_per_view": [round(float(x), 6) for x in vis / float(n_total)],
                 "sharding": "contiguous range per rank" if world > 1 else "none",
-                "merge": ((("one fused exchange kernel per rank: counts to every peer's mailbox, rebased lists stored into every rank's allocation over NVLink, done tags; on its own stream, the exchange of frame i overlaps frame i+1 (two output sets)" if pipelined else "NCCL all_gather(meta) + one peer-store kernel per rank (NVLink P2P) + 1-word all_reduce")) if args.merge == "p2p" else "NCCL all_gather(counts) + in-place broadcast allgatherv") if world > 1 else "none",
+                "merge": (("records: the frame kernel stores an 8-byte {draw_index, slot} record per survivor into every rank's window over NVLink as it emits (no exchange kernel, no collective); merge_expand rebuilds the merged commands on every GPU"
+                           + (f"; the expand of frame i runs beside frame i+1 on {args.expand_sms} SMs of its own (second stream)" if beside else
+                              "; the expand of frame i is queued behind frame i+1" if pipelined else "; frame, expand, frame, expand"))
+                          if args.merge == "p2p" else "NCCL all_gather(counts) + in-place broadcast allgatherv") if world > 1 else "none",
                 "l2": L2_NOTE if flush is not None else "inputs (36 B x n) exceed L2",
             },
             "e2e": {"value": n_total * e2e_steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": n * 36,
@@ -428,14 +491,7 @@ def gpu_arm(args, wl):
                     "note": "model matrices and draw lists stay on the device, as the reference's consumers (indirect draws) read them there; e2e_lists also brings the lists back"},
             "e2e_lists": e2e_lists,
             "gpu_launches": int(launches),
-            "merge": None if world == 1 else {
-                # pipelined: what the step costs beyond the frame kernel (the exchange itself runs under the next frame)
-                ("exposed_ms_per_step" if pipelined else "ms_per_step"): (t_step - t_frame) / args.steps * 1e3,
-                "overlapped_with_next_frame": pipelined,
-                "bytes_delivered_to_peers_per_gpu": int(24 * int(counts.sum()) * (world - 1)),
-                "bytes_leaving_each_gpu": int(24 * int(counts.sum()) * (1 if "multicast" in getattr(merger, "transport", "") else world - 1)),
-                "nvlink_gbs_per_gpu": None if pipelined else 24.0 * float(counts.sum()) * (world - 1) / max((t_step - t_frame) / args.steps, 1e-9) / 1e9,
-                "nvlink_peak_gbs": 770.0, "transport": getattr(merger, "transport", "nccl"), "verified_against_nccl_allgatherv": merge_verified, "note": "rank 0's own lists delivered to every peer (one multicast store each when the transport says so); peak = measured peer copy per direction"},
+            "merge": None if world == 1 else merge_report,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "frac_of_nominal_8000": achieved / 8000.0, "traffic": None, "peak_kind": peak_kind, "kernel": f"transform_cull_compact<{n_views}>",
                          "bytes_per_entity": bytes_per_entity, "ms_per_launch": t_launch * 1e3},
@@ -687,7 +743,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--merge", default="p2p", choices=["p2p", "nccl"], help="N > 1: peer-store merge kernel or NCCL broadcasts")
-    ap.add_argument("--no-overlap", action="store_true", help="N > 1: run frame and merge back to back instead of pipelined")
+    ap.add_argument("--pipeline", action="store_true", help="N > 1: queue the expand of frame i behind frame i + 1 instead of frame, expand, frame, expand (measured slower: with two record regions the next frame then waits for the peers' expand of the frame before)")
+    ap.add_argument("--expand-sms", type=int, default=0, help="N > 1: > 0 splits the chip -- the frame kernel leaves that many SMs to the expand of the previous frame, which runs beside it on a second stream; 0: the expand runs between frames")
+    ap.add_argument("--multicast", action="store_true", help="N > 1: windows in torch symmetric memory, records leave through the NVLS multicast mapping (default: CUDA IPC peer stores)")
+    ap.add_argument("--no-verify", action="store_true", help="N > 1: skip the oracle / NCCL verification of the merged lists")
     ap.add_argument("--workload", default="16m_5view", choices=sorted(WORKLOADS))
     ap.add_argument("--no-also", action="store_true", help="N = 1: skip the resident timings of the other entity-stage workloads")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiler runs)")

@@ -243,53 +243,64 @@ int rcull_download_as_instances(rcull_ctx *ctx, uint64_t first, uint64_t n, void
 int rcull_rebase_into(rcull_ctx *ctx, uint32_t buffer_ix, uint32_t view, uint64_t index_prefix,
                       rcull_draw_cmd *dst_cmds, uint32_t *dst_visible, void *stream);
 
-/* ---- Range-shard merge over peer memory (NVLink P2P stores) ---------------
- * Every rank owns one MERGED allocation of identical layout (max_views draw lists of
- * `capacity` commands + their visible-index lists).  Per frame: rcull_merge_pack_meta,
- * an all_gather of the meta words (the caller's collective: 2*max_views u64 per rank),
- * then rcull_merge_scatter -- ONE kernel that computes this rank's slot from the gathered
- * words and stores its rebased lists into that slot of EVERY rank's allocation, its own
- * and the peers' (peer-mapped pointers).  A barrier on the caller's side tells when all
- * peers have written.  The merged list equals the single-GPU list byte for byte. */
+/* ---- Range-shard merge over peer memory (NVLink peer / NVLS multicast stores) ------
+ * The entity set is sharded by contiguous range, one rank per GPU; the merged draw lists (every
+ * rank's survivors, ascending global draw_index, byte-identical to the single-GPU lists) land on
+ * EVERY rank.  What crosses NVLink is an 8-byte record per survivor {draw_index, slot = mesh * 6 +
+ * lod}, a third of the 24 bytes of a command + visible index; the frame kernel sends it itself, at
+ * emission time, with one store per peer (or one multimem.st through an NVLS multicast mapping)
+ * into the part of every rank's WINDOW that belongs to the sender -- the transfer is spread over
+ * the whole frame and there is no exchange kernel and no collective call.  rcull_merge_expand then
+ * rebuilds the commands on the receiving GPU: indexCount / vertexOffset from the mesh table,
+ * firstIndex as the running sum over the merged order (cull_pipeline.rs:558 over all ranks),
+ * firstInstance = draw_index (generate_work.comp:63-66).  In RCULL_PER_MESH_INSTANCED mode the
+ * expand merges the ranks' (slot, draw_index) pairs in draw order and runs the bucketing passes on
+ * them: one command per non-empty slot with instanceCount summed over ranks.
+ *
+ * Protocol: after rcull_merge_create every rcull_frame on the context is a MERGED frame (the rank's
+ * own per-rank lists are not written; every rank must issue the same frames in the same order).
+ * Each merged frame is followed -- at once, or one frame later to hide the skew between ranks --
+ * by one rcull_merge_expand; at most two merged frames may be in flight.  The expand kernel waits
+ * for every rank's records of that frame; a frame kernel waits until every rank has expanded the
+ * frame before the previous one (the record regions are double-buffered).  A single process that
+ * drives several ranks on ONE GPU must therefore complete all ranks' frames before any expand. */
 typedef struct rcull_merge rcull_merge;
 #define RCULL_MAX_RANKS 8
 #define RCULL_IPC_HANDLE_BYTES 64
-int rcull_merge_create(rcull_ctx *ctx, uint32_t world, uint32_t rank, uint64_t capacity, rcull_merge **out);
+/* capacity: commands one merged list can hold (per view); capacity_per_rank: survivors of one
+ * view one rank can send (0 = capacity).  The window -- record regions of every source rank,
+ * double-buffered, plus a mailbox -- is allocated by the library (cudaMalloc, exportable with
+ * rcull_merge_ipc_handle) or supplied by the caller (rcull_merge_create_on: e.g. symmetric
+ * memory that every rank has mapped, rcull_merge_window_bytes bytes). */
+int rcull_merge_window_bytes(rcull_ctx *ctx, uint32_t world, uint64_t capacity_per_rank, uint64_t *bytes);
+int rcull_merge_create(rcull_ctx *ctx, uint32_t world, uint32_t rank, uint64_t capacity,
+                       uint64_t capacity_per_rank, rcull_merge **out);
+int rcull_merge_create_on(rcull_ctx *ctx, uint32_t world, uint32_t rank, uint64_t capacity,
+                          uint64_t capacity_per_rank, void *window, rcull_merge **out);
 void rcull_merge_destroy(rcull_merge *m);
-/* cudaIpcMemHandle_t of this rank's merged allocation, to be sent to the other processes. */
+/* cudaIpcMemHandle_t of this rank's window, to be sent to the other processes. */
 int rcull_merge_ipc_handle(rcull_merge *m, void *handle_out);
-/* Maps a peer process' allocation (cudaIpcOpenMemHandle). */
+/* Maps a peer process' window (cudaIpcOpenMemHandle). */
 int rcull_merge_open_peer(rcull_merge *m, uint32_t peer, const void *handle);
-/* Same-process peers (tests, single-process multi-GPU): the peer's base pointer itself. */
-int rcull_merge_set_peer_ptr(rcull_merge *m, uint32_t peer, void *base);
-int rcull_merge_base(rcull_merge *m, void **base);
-/* Device buffers of the exchange: meta_local [3 output sets][2*max_views] u64 (row = buffer_ix),
- * meta_all [world][2*max_views] u64. */
-int rcull_merge_meta_ptrs(rcull_merge *m, uint64_t **meta_local, uint64_t **meta_all);
-/* Only needed for a frame issued BEFORE rcull_merge_create: later frames write meta_local themselves. */
-int rcull_merge_pack_meta(rcull_merge *m, uint32_t buffer_ix, void *stream);
-int rcull_merge_scatter(rcull_merge *m, uint32_t buffer_ix, uint32_t n_views, void *stream);
-/* The merged allocation on caller-owned memory of rcull_merge_bytes(capacity) bytes (for instance
- * symmetric memory that every rank has mapped, with an NVLS multicast mapping): peers are named with
- * rcull_merge_set_peer_ptr; with rcull_merge_set_multicast_ptr the exchange stores each list ONCE
- * through the multicast address and the NVSwitch replicates it into every rank's allocation
- * (multimem.st), instead of one store per peer. */
-int rcull_merge_bytes(rcull_ctx *ctx, uint64_t capacity, uint64_t *bytes);
-int rcull_merge_create_on(rcull_ctx *ctx, uint32_t world, uint32_t rank, uint64_t capacity, void *base, rcull_merge **out);
-int rcull_merge_set_multicast_ptr(rcull_merge *m, void *multicast_base);
-/* The whole exchange in ONE kernel, no collective call: this rank's (count, index total) words go
- * into every rank's mailbox over NVLink, the kernel waits for every rank's words of the same
- * exchange, computes its slot and stores its rebased lists into that slot of every rank's
- * allocation (16-byte peer stores), then raises a done tag everywhere.  Every rank must issue
- * its exchanges in the same order.  The kernel (128 threads, 64 registers) is resident beside the
- * frame kernel, so on its own stream the exchange of frame i overlaps frame i + 1 (use two
- * output sets).  rcull_merge_wait enqueues a kernel that returns once every rank's slices of the
- * exchanges issued so far have landed in THIS rank's allocation.  One process driving several
- * ranks must enqueue every rank's exchange before any rank's wait (streams of one process may share
- * a hardware queue). */
-int rcull_merge_exchange(rcull_merge *m, uint32_t buffer_ix, uint32_t n_views, void *stream);
-int rcull_merge_wait(rcull_merge *m, void *stream);
-/* Device pointers of the merged lists of one view and of the merged counts / index totals. */
+/* Same-process peers (single-process multi-GPU with peer access enabled, tests) or windows mapped
+ * by the caller: the peer's window address itself. */
+int rcull_merge_set_peer_ptr(rcull_merge *m, uint32_t peer, void *window);
+int rcull_merge_window(rcull_merge *m, void **window);
+/* NVLS multicast mapping of all ranks' windows: records then leave the GPU ONCE and the NVSwitch
+ * replicates them (multimem.st), instead of one store per peer. */
+int rcull_merge_set_multicast_ptr(rcull_merge *m, void *multicast_window);
+/* expand_sms > 0: split the chip between the frame kernel and the expand.  The frame kernel's
+ * persistent grid leaves expand_sms SMs free and rcull_merge_expand launches exactly that many CTAs,
+ * each of which takes a whole SM; issued on a SECOND stream after frame i (event), the expand of
+ * frame i then runs beside frame i + 1 instead of between frames.  0 (default): the expand is an
+ * ordinary full-chip kernel on the stream it is given. */
+int rcull_merge_set_overlap(rcull_merge *m, uint32_t expand_sms);
+/* Expands the oldest merged frame that has not been expanded yet into this rank's merged lists;
+ * asynchronous on stream.  After it, rcull_merge_lists names the results. */
+int rcull_merge_expand(rcull_merge *m, void *stream);
+/* Device pointers of the merged lists of one view and of the merged counts / index totals
+ * (per-mesh mode: commands per non-empty slot, bucketed visible list, counts = commands,
+ * index totals = instances). */
 int rcull_merge_lists(rcull_merge *m, uint32_t view, rcull_draw_cmd **cmds, uint32_t **visible,
                       uint32_t **counts, uint64_t **index_totals);
 

@@ -124,20 +124,17 @@ SYMBOLS = {
     "rcull_get_as_instances": (C.c_int, [_P, C.POINTER(_P)]),
     "rcull_download_as_instances": (C.c_int, [_P, _u64, _u64, _P]),
     "rcull_rebase_into": (C.c_int, [_P, _u32, _u32, _u64, _P, _P, _P]),
-    "rcull_merge_create": (C.c_int, [_P, _u32, _u32, _u64, C.POINTER(_P)]),
+    "rcull_merge_window_bytes": (C.c_int, [_P, _u32, _u64, _P]),
+    "rcull_merge_create": (C.c_int, [_P, _u32, _u32, _u64, _u64, C.POINTER(_P)]),
+    "rcull_merge_create_on": (C.c_int, [_P, _u32, _u32, _u64, _u64, _P, C.POINTER(_P)]),
     "rcull_merge_destroy": (None, [_P]),
     "rcull_merge_ipc_handle": (C.c_int, [_P, _P]),
     "rcull_merge_open_peer": (C.c_int, [_P, _u32, _P]),
     "rcull_merge_set_peer_ptr": (C.c_int, [_P, _u32, _P]),
-    "rcull_merge_base": (C.c_int, [_P, C.POINTER(_P)]),
-    "rcull_merge_meta_ptrs": (C.c_int, [_P, C.POINTER(_P), C.POINTER(_P)]),
-    "rcull_merge_pack_meta": (C.c_int, [_P, _u32, _P]),
-    "rcull_merge_scatter": (C.c_int, [_P, _u32, _u32, _P]),
-    "rcull_merge_bytes": (C.c_int, [_P, _u64, _P]),
-    "rcull_merge_create_on": (C.c_int, [_P, _u32, _u32, _u64, _P, C.POINTER(_P)]),
+    "rcull_merge_window": (C.c_int, [_P, C.POINTER(_P)]),
     "rcull_merge_set_multicast_ptr": (C.c_int, [_P, _P]),
-    "rcull_merge_exchange": (C.c_int, [_P, _u32, _u32, _P]),
-    "rcull_merge_wait": (C.c_int, [_P, _P]),
+    "rcull_merge_set_overlap": (C.c_int, [_P, _u32]),
+    "rcull_merge_expand": (C.c_int, [_P, _P]),
     "rcull_merge_lists": (C.c_int, [_P, _u32, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)]),
     "rcull_synth_entities": (C.c_int, [_P, _u64, _u64, _u64, _f, _u32, _P]),
     "rcull_launch_count": (_u64, [_P]),

@@ -82,6 +82,7 @@ struct OutputSet {
 
 }  // namespace
 
+struct rcull_merge;
 struct rcull_ctx {
     rcull_config cfg{};
     int sm_count = 0;
@@ -100,8 +101,8 @@ struct rcull_ctx {
     uint32_t* slot_base = nullptr;
     size_t bucket_hist_words = 0;
     uint64_t cap_cmds = 0;  // command capacity per view: cap_vis, or max_meshes * 6 in per-mesh mode
-    int reserved_sms = 0;  // SMs the frame kernel leaves to the exchange kernel of an attached merge (world > 1)
-    unsigned long long* meta_out = nullptr;  // set by rcull_merge_create: the frame kernel writes the exchange words itself
+    int reserved_sms = 0;  // SMs the frame kernel's grid leaves to a concurrent expand kernel (rcull_merge_set_overlap)
+    struct rcull_merge* merge = nullptr;  // attached range-shard merge: frames send their survivors as records (rcull_merge_create)
     OutputSet out[3];
     ulonglong2* status = nullptr;
     size_t status_bytes = 0;
@@ -456,6 +457,10 @@ int rcull_pack_components(uint64_t n, const float* position, const float* rotati
 // ---------------------------------------------------------------------------------
 // frame
 // ---------------------------------------------------------------------------------
+namespace {
+int merge_frame_issued(rcull_ctx* c, uint32_t n_views, const uint32_t* counts, const unsigned long long* totals, RecordArgs* out, bool empty,
+                       cudaStream_t s);
+}
 extern "C" {
 
 int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_views, const float cam_pos[3],
@@ -475,7 +480,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     if (n == 0) {  // empty query: cull_pass still clears the buffers (cull_pipeline.rs:498-511)
         CU(cudaMemsetAsync(o.counts, 0, kMaxViews * 4, s));
         CU(cudaMemsetAsync(o.totals, 0, kMaxViews * 8, s));
-        if (c->meta_out) CU(cudaMemsetAsync(c->meta_out + (size_t)buffer_ix * 2 * c->cfg.max_views, 0, 2 * c->cfg.max_views * 8, s));
+        if (c->merge) return merge_frame_issued(c, n_views, o.counts, o.totals, nullptr, true, s);
         if (per_mesh) CU(cudaMemsetAsync(c->slot_total, 0, (size_t)c->n_meshes * kMaxLods * c->cfg.max_views * 4, s));  // rcull_get_slot_counts
         return RCULL_OK;
     }
@@ -521,7 +526,10 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     a.src_first = o.src_first;
     a.counts = o.counts;
     a.totals = o.totals;
-    a.meta_out = c->meta_out ? c->meta_out + (size_t)buffer_ix * 2 * c->cfg.max_views : nullptr;
+    if (c->merge) {
+        int mrc = merge_frame_issued(c, n_views, o.counts, o.totals, &a.rec, false, s);
+        if (mrc) return mrc;
+    }
     a.max_views = c->cfg.max_views;
     a.status = c->status;
     a.ticket = c->ticket;
@@ -556,7 +564,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     if (e != cudaSuccess) return fail(RCULL_ERR_CUDA, "transform_cull_compact launch failed: %s", cudaGetErrorString(e));
     c->ticket_base += n_tiles + (uint32_t)grid;  // every tile is a ticket, and every CTA draws one ticket past the end
     c->launches += 1;
-    if (per_mesh) {
+    if (per_mesh && !c->merge) {  // with a merge attached the pairs leave as records and are bucketed after the expand (merged order)
         // Stable bucketing by (mesh, lod) slot: counting sort over tiles of the survivor pairs
         // (rcull_aux.cuh), then one command per non-empty slot.
         const uint32_t n_slots = c->n_meshes * kMaxLods;
@@ -737,6 +745,7 @@ int rcull_rebase_into(rcull_ctx* c, uint32_t buffer_ix, uint32_t view, uint64_t 
                       uint32_t* dst_visible, void* stream) {
     Scope scope("rcull::rebase_into");
     if (!c || !dst_cmds || !dst_visible) return fail(RCULL_ERR_INVALID, "rcull_rebase_into: null argument");
+    if (c->merge) return fail(RCULL_ERR_INVALID, "rcull_rebase_into: a merge is attached -- the frame kernel sends records, the rank's own lists are not written");
     if (buffer_ix >= c->cfg.n_buffers || view >= c->cfg.max_views) return fail(RCULL_ERR_INVALID, "rcull_rebase_into: bad buffer/view");
     CU(cudaSetDevice(c->cfg.device));
     const OutputSet& o = c->out[lists_of(c, buffer_ix)];
@@ -963,28 +972,155 @@ int rcull_debug_stats(uint64_t out[16], int reset) {
 }  // extern "C"
 
 // ---------------------------------------------------------------------------------
-// range-shard merge over peer memory
+// range-shard merge over peer memory (records + expand, rcull_aux.cuh)
 // ---------------------------------------------------------------------------------
 struct rcull_merge {
     rcull_ctx* ctx = nullptr;
     uint32_t world = 0, rank = 0;
-    uint64_t cap = 0;
-    size_t bytes = 0;
-    unsigned char* base = nullptr;
+    uint64_t cap = 0;    // merged list capacity per view
+    uint64_t cap_r = 0;  // records one rank can send per view
+    size_t window_bytes = 0, ckpt_off = 0, sync_off = 0;
+    unsigned char* window = nullptr;  // peer-visible: the record regions of every source rank + the mailbox
+    bool owns_window = true;          // false: caller's allocation (symmetric memory), rcull_merge_create_on
     unsigned char* peer[kMaxRanks] = {};
     bool opened[kMaxRanks] = {};
-    unsigned long long* meta_local = nullptr;
-    unsigned long long* meta_all = nullptr;
+    unsigned char* mc = nullptr;      // NVLS multicast mapping of all windows, or null
+    // local outputs: the merged draw lists
+    uint32_t* cmds[kMaxViews] = {};
+    uint32_t* visible[kMaxViews] = {};
+    uint32_t* keys[kMaxViews] = {};     // per-mesh mode: merged slot keys / draw indices before bucketing
+    uint32_t* vis_tmp[kMaxViews] = {};
     uint32_t* counts = nullptr;
     unsigned long long* totals = nullptr;
-    bool owns_base = true;         // false: the caller's (symmetric-memory) allocation, rcull_merge_create_on
-    unsigned char* mc_base = nullptr;  // NVLS multicast mapping of the same allocation on every rank, or null
-    size_t sync_off = 0;           // MergeSync mailbox at the end of the (peer-mapped) allocation
-    unsigned long long epoch = 0;  // exchanges issued so far
-    uint32_t* cta_done = nullptr;
+    uint32_t* ticket = nullptr;    // [0] expand tile ticket, [1] expand CTAs done, [2] frame CTAs done
+    unsigned long long frame_epoch = 0, expand_epoch = 0;  // merged frames issued / expanded
+    uint32_t views_of[2] = {0, 0};  // n_views of the frame with that epoch parity
+    int expand_sms = 0;             // > 0: the expand runs on that many SMs of its own beside the next frame (rcull_merge_set_overlap)
+    std::vector<void*> allocs;
 };
 
 static_assert(RCULL_MAX_RANKS == kMaxRanks && RCULL_IPC_HANDLE_BYTES == sizeof(cudaIpcMemHandle_t), "merge ABI constants");
+
+namespace {
+
+// window = records [2][world][views][cap_r] x 8 B | checkpoints [2][world][views][cap_r / 2048 + 1] x 4 B | mailbox
+size_t merge_ckpt_view_stride(uint64_t cap_r) { return ((size_t)(cap_r / kExpandTile + 1) * 4 + 15) / 16 * 16; }
+size_t merge_window_layout(uint32_t world, uint32_t max_views, uint64_t cap_r, size_t* ckpt_off, size_t* sync_off) {
+    const size_t rec = (size_t)2 * world * max_views * cap_r * 8;
+    const size_t co = (rec + 255) / 256 * 256;
+    const size_t so = (co + (size_t)2 * world * max_views * merge_ckpt_view_stride(cap_r) + 255) / 256 * 256;
+    if (ckpt_off) *ckpt_off = co;
+    if (sync_off) *sync_off = so;
+    return so + sizeof(MergeSync);
+}
+
+// Called by rcull_frame on a context with a merge attached: numbers the frame, fills the kernel's RecordArgs (or, for
+// an empty frame, sends the zero counts and the tag right away).
+int merge_frame_issued(rcull_ctx* c, uint32_t n_views, const uint32_t* counts, const unsigned long long* totals, RecordArgs* out,
+                       bool empty, cudaStream_t s) {
+    rcull_merge* m = c->merge;
+    for (uint32_t p = 0; p < m->world; ++p)
+        if (!m->peer[p]) return fail(RCULL_ERR_INVALID, "merge: peer %u has not been mapped (rcull_merge_open_peer / rcull_merge_set_peer_ptr)", p);
+    if (m->frame_epoch - m->expand_epoch >= 2)
+        return fail(RCULL_ERR_INVALID, "merge: two merged frames are in flight -- call rcull_merge_expand before the next rcull_frame");
+    RecordArgs r;
+    memset(&r, 0, sizeof r);
+    for (uint32_t p = 0; p < m->world; ++p) r.peer[p] = m->peer[p];
+    r.mc = m->mc;
+    r.epoch = ++m->frame_epoch;
+    r.base = (size_t)(((r.epoch & 1ull) * m->world + m->rank) * c->cfg.max_views) * m->cap_r * 8;
+    r.view_stride = (size_t)m->cap_r * 8;
+    r.ckpt_view_stride = merge_ckpt_view_stride(m->cap_r);
+    r.ckpt_base = m->ckpt_off + (size_t)(((r.epoch & 1ull) * m->world + m->rank) * c->cfg.max_views) * r.ckpt_view_stride;
+    r.sync_off = m->sync_off;
+    r.cta_done = m->ticket + 2;
+    r.world = m->world;
+    r.rank = m->rank;
+    r.cap_r = (uint32_t)m->cap_r;
+    m->views_of[r.epoch & 1ull] = n_views;
+    if (empty) {
+        record_empty_frame<<<1, 32, 0, s>>>(r, counts, totals);
+        CU(cudaGetLastError());
+        c->launches += 1;
+        return RCULL_OK;
+    }
+    *out = r;
+    return RCULL_OK;
+}
+
+template <typename T>
+int merge_alloc(rcull_merge* m, T** p, size_t count) {
+    void* q = nullptr;
+    CU(cudaMalloc(&q, count * sizeof(T) + 256));
+    m->allocs.push_back(q);
+    *p = static_cast<T*>(q);
+    return 0;
+}
+
+int merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t capacity, uint64_t capacity_per_rank, void* external_window,
+                 rcull_merge** out) {
+    if (!c || !out) return fail(RCULL_ERR_INVALID, "rcull_merge_create: null argument");
+    *out = nullptr;
+    if (world < 1 || world > kMaxRanks || rank >= world) return fail(RCULL_ERR_INVALID, "rank %u of world %u (max %d)", rank, world, kMaxRanks);
+    if (capacity == 0 || capacity > 0xffffffffull) return fail(RCULL_ERR_INVALID, "merged capacity must be 1..2^32-1 commands");
+    if (capacity_per_rank == 0) capacity_per_rank = capacity;
+    if (capacity_per_rank > capacity) capacity_per_rank = capacity;
+    capacity_per_rank = (capacity_per_rank + 1) & ~1ull;  // record regions are copied in 16-byte units
+    if (c->merge) return fail(RCULL_ERR_INVALID, "the context already has a merge attached");
+    if (c->cfg.capacity_tri_indices) return fail(RCULL_ERR_INVALID, "the per-triangle stage works on a rank's own lists: create the context without capacity_tri_indices");
+    CU(cudaSetDevice(c->cfg.device));
+    rcull_merge* m = new rcull_merge();
+    m->ctx = c;
+    m->world = world;
+    m->rank = rank;
+    m->cap = capacity;
+    m->cap_r = capacity_per_rank;
+    const uint32_t mv = c->cfg.max_views;
+    const bool per_mesh = c->cfg.output_mode == RCULL_PER_MESH_INSTANCED;
+    m->window_bytes = merge_window_layout(world, mv, m->cap_r, &m->ckpt_off, &m->sync_off);
+    int rc = 0;
+#define MTRY(x)                      \
+    if ((rc = (x)) != 0) {           \
+        rcull_merge_destroy(m);      \
+        return rc;                   \
+    }
+    if (external_window) {
+        m->window = static_cast<unsigned char*>(external_window);
+        m->owns_window = false;
+    } else if (cudaMalloc((void**)&m->window, m->window_bytes) != cudaSuccess) {
+        rcull_merge_destroy(m);
+        return fail(RCULL_ERR_CUDA, "rcull_merge_create: cudaMalloc of a %zu-byte window failed", m->window_bytes);
+    }
+    const uint64_t cmd_cap = per_mesh ? (uint64_t)c->cfg.max_meshes * kMaxLods : capacity;
+    for (uint32_t v = 0; v < mv; ++v) {
+        MTRY(merge_alloc(m, &m->cmds[v], cmd_cap * 5));
+        MTRY(merge_alloc(m, &m->visible[v], capacity));
+        if (per_mesh) {
+            MTRY(merge_alloc(m, &m->keys[v], capacity));
+            MTRY(merge_alloc(m, &m->vis_tmp[v], capacity));
+        }
+    }
+    MTRY(merge_alloc(m, &m->counts, kMaxViews));
+    MTRY(merge_alloc(m, &m->totals, kMaxViews));
+    MTRY(merge_alloc(m, &m->ticket, 4));
+#undef MTRY
+    cudaMemset(m->window + m->sync_off, 0, sizeof(MergeSync));
+    cudaMemset(m->counts, 0, kMaxViews * 4);
+    cudaMemset(m->totals, 0, kMaxViews * 8);
+    cudaMemset(m->ticket, 0, 16);
+    if (cudaDeviceSynchronize() != cudaSuccess) {
+        rcull_merge_destroy(m);
+        return fail(RCULL_ERR_CUDA, "rcull_merge_create: clearing the window failed");
+    }
+    cudaFuncSetAttribute(merge_expand, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kExpandSmem);
+    cudaFuncSetAttribute(merge_expand_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kExpandBigSmem);
+    m->peer[rank] = m->window;
+    c->merge = m;  // frames issued from now on send records
+    *out = m;
+    return RCULL_OK;
+}
+
+}  // namespace
 
 extern "C" {
 
@@ -992,89 +1128,36 @@ void rcull_merge_destroy(rcull_merge* m) {
     if (!m) return;
     cudaSetDevice(m->ctx->cfg.device);
     cudaDeviceSynchronize();
-    if (m->ctx->meta_out == m->meta_local) {
-        m->ctx->meta_out = nullptr;
+    if (m->ctx->merge == m) {
+        m->ctx->merge = nullptr;
         m->ctx->reserved_sms = 0;
     }
     for (uint32_t p = 0; p < m->world; ++p)
         if (m->opened[p]) cudaIpcCloseMemHandle(m->peer[p]);
-    if (m->owns_base) cudaFree(m->base);
-    cudaFree(m->meta_local);
-    cudaFree(m->meta_all);
-    cudaFree(m->counts);
-    cudaFree(m->totals);
-    cudaFree(m->cta_done);
+    if (m->owns_window && m->window) cudaFree(m->window);
+    for (void* p : m->allocs) cudaFree(p);
     delete m;
 }
 
-static int merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t capacity, void* external_base, rcull_merge** out) {
-    if (!c || !out) return fail(RCULL_ERR_INVALID, "rcull_merge_create: null argument");
-    *out = nullptr;
-    if (world < 1 || world > kMaxRanks || rank >= world) return fail(RCULL_ERR_INVALID, "rank %u of world %u (max %d)", rank, world, kMaxRanks);
-    if (capacity == 0 || capacity > 0xffffffffull) return fail(RCULL_ERR_INVALID, "merged capacity must be 1..2^32-1 commands");
-    CU(cudaSetDevice(c->cfg.device));
-    rcull_merge* m = new rcull_merge();
-    m->ctx = c;
-    m->world = world;
-    m->rank = rank;
-    m->cap = capacity;
-    m->sync_off = ((size_t)c->cfg.max_views * capacity * 24 + 255) / 256 * 256;
-    m->bytes = m->sync_off + sizeof(MergeSync);
-    const uint32_t mv = c->cfg.max_views;
-    // meta_local: one row of exchange words per output set, so a pipelined frame never overwrites the row a merge still reads
-    if (external_base) {
-        m->base = static_cast<unsigned char*>(external_base);
-        m->owns_base = false;
-    }
-    if ((!external_base && cudaMalloc((void**)&m->base, m->bytes) != cudaSuccess) || cudaMalloc((void**)&m->meta_local, 3 * 2 * mv * 8) != cudaSuccess ||
-        cudaMalloc((void**)&m->cta_done, 4) != cudaSuccess ||
-        cudaMalloc((void**)&m->meta_all, (size_t)world * 2 * mv * 8) != cudaSuccess ||
-        cudaMalloc((void**)&m->counts, mv * 4) != cudaSuccess || cudaMalloc((void**)&m->totals, mv * 8) != cudaSuccess) {
-        rcull_merge_destroy(m);
-        return fail(RCULL_ERR_CUDA, "rcull_merge_create: cudaMalloc of %zu bytes failed", m->bytes);
-    }
-    cudaMemset(m->meta_local, 0, 3 * 2 * mv * 8);
-    cudaMemset(m->cta_done, 0, 4);
-    cudaMemset(m->base + m->sync_off, 0, sizeof(MergeSync));
-    cudaMemset(m->meta_all, 0, (size_t)world * 2 * mv * 8);
-    cudaMemset(m->counts, 0, mv * 4);
-    cudaMemset(m->totals, 0, mv * 8);
-    m->peer[rank] = m->base;
-    // the same shared-memory carveout as the frame kernel: an SM's split cannot change while CTAs are resident,
-    // so a CTA of a kernel that prefers another split would keep the next frame's CTA off its SM until it exits
-    cudaFuncSetAttribute(merge_exchange, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    cudaFuncSetAttribute(merge_wait, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    c->meta_out = m->meta_local;  // frames issued from now on write the exchange words directly
-    // Tuning knob (default off): leave RCULL_EXCHANGE_SMS SMs to the exchange kernel instead of letting its CTAs
-    // sit beside the frame's.  Measured slower at N = 2 and N = 8.
-    if (world > 1) {
-        if (const char* e = getenv("RCULL_EXCHANGE_SMS")) {
-            const int v = atoi(e);
-            if (v >= 0 && v < c->sm_count / 2) c->reserved_sms = v;
-        }
-    }
-    *out = m;
+int rcull_merge_window_bytes(rcull_ctx* c, uint32_t world, uint64_t capacity_per_rank, uint64_t* bytes) {
+    if (!c || !bytes || world < 1 || world > kMaxRanks || capacity_per_rank == 0) return fail(RCULL_ERR_INVALID, "rcull_merge_window_bytes: bad argument");
+    *bytes = merge_window_layout(world, c->cfg.max_views, (capacity_per_rank + 1) & ~1ull, nullptr, nullptr);
     return RCULL_OK;
 }
 
-int rcull_merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t capacity, rcull_merge** out) {
-    return merge_create(c, world, rank, capacity, nullptr, out);
+int rcull_merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t capacity, uint64_t capacity_per_rank, rcull_merge** out) {
+    return merge_create(c, world, rank, capacity, capacity_per_rank, nullptr, out);
 }
 
-int rcull_merge_bytes(rcull_ctx* c, uint64_t capacity, uint64_t* bytes) {
-    if (!c || !bytes) return fail(RCULL_ERR_INVALID, "rcull_merge_bytes: null argument");
-    *bytes = ((uint64_t)c->cfg.max_views * capacity * 24 + 255) / 256 * 256 + sizeof(MergeSync);
-    return RCULL_OK;
+int rcull_merge_create_on(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t capacity, uint64_t capacity_per_rank, void* window,
+                          rcull_merge** out) {
+    if (!window) return fail(RCULL_ERR_INVALID, "rcull_merge_create_on: null window");
+    return merge_create(c, world, rank, capacity, capacity_per_rank, window, out);
 }
 
-int rcull_merge_create_on(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t capacity, void* base, rcull_merge** out) {
-    if (!base) return fail(RCULL_ERR_INVALID, "rcull_merge_create_on: null base");
-    return merge_create(c, world, rank, capacity, base, out);
-}
-
-int rcull_merge_set_multicast_ptr(rcull_merge* m, void* multicast_base) {
+int rcull_merge_set_multicast_ptr(rcull_merge* m, void* multicast_window) {
     if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_set_multicast_ptr: null argument");
-    m->mc_base = static_cast<unsigned char*>(multicast_base);
+    m->mc = static_cast<unsigned char*>(multicast_window);
     return RCULL_OK;
 }
 
@@ -1082,7 +1165,7 @@ int rcull_merge_ipc_handle(rcull_merge* m, void* handle_out) {
     if (!m || !handle_out) return fail(RCULL_ERR_INVALID, "rcull_merge_ipc_handle: null argument");
     CU(cudaSetDevice(m->ctx->cfg.device));
     cudaIpcMemHandle_t h;
-    CU(cudaIpcGetMemHandle(&h, m->base));
+    CU(cudaIpcGetMemHandle(&h, m->window));
     memcpy(handle_out, &h, sizeof h);
     return RCULL_OK;
 }
@@ -1100,109 +1183,105 @@ int rcull_merge_open_peer(rcull_merge* m, uint32_t peer, const void* handle) {
     return RCULL_OK;
 }
 
-int rcull_merge_set_peer_ptr(rcull_merge* m, uint32_t peer, void* base) {
-    if (!m || !base) return fail(RCULL_ERR_INVALID, "rcull_merge_set_peer_ptr: null argument");
+int rcull_merge_set_peer_ptr(rcull_merge* m, uint32_t peer, void* window) {
+    if (!m || !window) return fail(RCULL_ERR_INVALID, "rcull_merge_set_peer_ptr: null argument");
     if (peer >= m->world) return fail(RCULL_ERR_INVALID, "peer %u of world %u", peer, m->world);
-    m->peer[peer] = static_cast<unsigned char*>(base);
+    m->peer[peer] = static_cast<unsigned char*>(window);
     return RCULL_OK;
 }
 
-int rcull_merge_base(rcull_merge* m, void** base) {
-    if (!m || !base) return fail(RCULL_ERR_INVALID, "rcull_merge_base: null argument");
-    *base = m->base;
+int rcull_merge_window(rcull_merge* m, void** window) {
+    if (!m || !window) return fail(RCULL_ERR_INVALID, "rcull_merge_window: null argument");
+    *window = m->window;
     return RCULL_OK;
 }
 
-int rcull_merge_meta_ptrs(rcull_merge* m, uint64_t** meta_local, uint64_t** meta_all) {
-    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_meta_ptrs: null argument");
-    if (meta_local) *meta_local = reinterpret_cast<uint64_t*>(m->meta_local);
-    if (meta_all) *meta_all = reinterpret_cast<uint64_t*>(m->meta_all);
+int rcull_merge_set_overlap(rcull_merge* m, uint32_t expand_sms) {
+    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_set_overlap: null argument");
+    if ((int)expand_sms >= m->ctx->sm_count / 2) return fail(RCULL_ERR_INVALID, "rcull_merge_set_overlap: %u of %d SMs", expand_sms, m->ctx->sm_count);
+    CU(cudaSetDevice(m->ctx->cfg.device));
+    m->expand_sms = (int)expand_sms;
+    m->ctx->reserved_sms = (int)expand_sms;  // the frame kernel's persistent grid leaves them free
     return RCULL_OK;
 }
 
-int rcull_merge_pack_meta(rcull_merge* m, uint32_t buffer_ix, void* stream) {
-    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_pack_meta: null argument");
+int rcull_merge_expand(rcull_merge* m, void* stream) {
+    Scope scope("rcull::merge_expand (records of every rank -> merged draw lists)");
+    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_expand: null argument");
     rcull_ctx* c = m->ctx;
-    if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
-    CU(cudaSetDevice(c->cfg.device));
-    pack_meta<<<1, 32, 0, (cudaStream_t)stream>>>(c->out[buffer_ix].counts, c->out[buffer_ix].totals, c->cfg.max_views,
-                                                  m->meta_local + (size_t)buffer_ix * 2 * c->cfg.max_views);
-    CU(cudaGetLastError());
-    c->launches += 1;
-    return RCULL_OK;
-}
-
-static int merge_args(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, MergeArgs* out) {
-    rcull_ctx* c = m->ctx;
-    if (buffer_ix >= c->cfg.n_buffers || n_views < 1 || n_views > c->cfg.max_views) return fail(RCULL_ERR_INVALID, "merge: bad buffer/view count");
+    if (m->expand_epoch >= m->frame_epoch) return fail(RCULL_ERR_INVALID, "rcull_merge_expand: no merged frame is waiting (call rcull_frame first)");
     for (uint32_t p = 0; p < m->world; ++p)
-        if (!m->peer[p]) return fail(RCULL_ERR_INVALID, "peer %u has not been mapped (rcull_merge_open_peer / rcull_merge_set_peer_ptr)", p);
+        if (!m->peer[p]) return fail(RCULL_ERR_INVALID, "merge: peer %u has not been mapped", p);
     CU(cudaSetDevice(c->cfg.device));
-    MergeArgs& a = *out;
+    cudaStream_t s = (cudaStream_t)stream;
+    const unsigned long long epoch = ++m->expand_epoch;
+    const uint32_t n_views = m->views_of[epoch & 1ull];
+    const bool per_mesh = c->cfg.output_mode == RCULL_PER_MESH_INSTANCED;
+    ExpandArgs a;
     memset(&a, 0, sizeof a);
+    a.window = m->window;
     for (uint32_t p = 0; p < m->world; ++p) a.peer[p] = m->peer[p];
-    for (uint32_t k = 0; k < n_views; ++k) {
-        a.src_cmds[k] = c->out[buffer_ix].cmds[k];
-        a.src_visible[k] = c->out[buffer_ix].visible[k];
-    }
-    a.meta_all = m->meta_all;
-    a.merged_counts = m->counts;
-    a.merged_totals = m->totals;
+    a.sync_off = m->sync_off;
+    a.view_stride = (size_t)m->cap_r * 8;
+    a.ckpt_off = m->ckpt_off;
+    a.ckpt_view_stride = merge_ckpt_view_stride(m->cap_r);
+    a.epoch = epoch;
     a.world = m->world;
     a.rank = m->rank;
     a.n_views = n_views;
     a.max_views = c->cfg.max_views;
+    a.cap_r = (uint32_t)m->cap_r;
     a.cap = (uint32_t)m->cap;
-    a.meta_mine = m->meta_local + (size_t)buffer_ix * 2 * c->cfg.max_views;
-    a.sync_off = m->sync_off;
-    a.cta_done = m->cta_done;
-    a.mc = m->mc_base;
-    return RCULL_OK;
-}
-
-int rcull_merge_scatter(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, void* stream) {
-    Scope scope("rcull::merge_scatter");
-    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_scatter: null argument");
-    MergeArgs a;
-    int rc = merge_args(m, buffer_ix, n_views, &a);
-    if (rc) return rc;
-    scatter_rebased<<<m->ctx->sm_count * 4, 256, 0, (cudaStream_t)stream>>>(a);
-    CU(cudaGetLastError());
-    m->ctx->launches += 1;
-    return RCULL_OK;
-}
-
-int rcull_merge_exchange(rcull_merge* m, uint32_t buffer_ix, uint32_t n_views, void* stream) {
-    Scope scope("rcull::merge_exchange");
-    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_exchange: null argument");
-    MergeArgs a;
-    int rc = merge_args(m, buffer_ix, n_views, &a);
-    if (rc) return rc;
-    a.epoch = ++m->epoch;
-    // one CTA per SM: it fits beside the frame kernel's CTA, and every CTA of the grid is resident at
-    // once (none of them waits behind a spinning sibling)
-    // CTAs of 128 threads x 64 registers: one fits beside the frame kernel's CTA on an SM.  How many: enough
-    // to keep NVLink busy, few enough not to slow the co-running frame (measured: 64-74 at N <= 4, 32 at N = 8,
-    // where every received byte also lands in this GPU's HBM under the frame).
-    int ctas = m->world >= 8 ? 32 : m->ctx->sm_count / 2;
-    if (const char* e = getenv("RCULL_EXCHANGE_CTAS")) {
-        const int v = atoi(e);
-        if (v >= 1 && v <= 8 * m->ctx->sm_count) ctas = v;
+    for (uint32_t v = 0; v < n_views; ++v) {
+        a.cmds[v] = per_mesh ? m->keys[v] : m->cmds[v];
+        a.visible[v] = per_mesh ? m->vis_tmp[v] : m->visible[v];
     }
-    if (m->ctx->reserved_sms > 0) ctas = m->ctx->reserved_sms * 8;  // dedicated SMs: 8 CTAs fill a register file
-    merge_exchange<<<ctas, 128, m->ctx->reserved_sms > 0 ? 2048 : 0, (cudaStream_t)stream>>>(a);
+    a.counts = m->counts;
+    a.totals = m->totals;
+    a.lod_tab = c->lod_tab;
+    a.n_slots = c->n_meshes * kMaxLods;
+    a.pairs = per_mesh ? 1u : 0u;
+    a.cta_done = m->ticket + 1;
+    if (m->expand_sms > 0) {
+        // R CTAs that each take a whole SM, on the caller's second stream: beside the next frame, whose grid leaves R SMs
+        merge_expand_big<<<m->expand_sms, 1024, kExpandBigSmem, s>>>(a);
+    } else {
+        merge_expand<<<c->sm_count * 4, 256, kExpandSmem, s>>>(a);
+    }
     CU(cudaGetLastError());
-    m->ctx->launches += 1;
-    return RCULL_OK;
-}
-
-int rcull_merge_wait(rcull_merge* m, void* stream) {
-    Scope scope("rcull::merge_wait");
-    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_wait: null argument");
-    CU(cudaSetDevice(m->ctx->cfg.device));
-    merge_wait<<<1, 32, 0, (cudaStream_t)stream>>>(reinterpret_cast<const MergeSync*>(m->base + m->sync_off), m->world, m->epoch);
-    CU(cudaGetLastError());
-    m->ctx->launches += 1;
+    c->launches += 1;
+    if (per_mesh && n_views) {
+        // the merged pairs are in draw order (rank order = ascending ranges): the single-GPU bucketing passes finish the job
+        const uint32_t n_slots = c->n_meshes * kMaxLods;
+        BucketArgs b;
+        memset(&b, 0, sizeof b);
+        for (uint32_t v = 0; v < n_views; ++v) {
+            b.keys[v] = m->keys[v];
+            b.draw_ix[v] = m->vis_tmp[v];
+            b.visible[v] = m->visible[v];
+            b.cmds[v] = m->cmds[v];
+        }
+        b.counts = m->counts;
+        b.totals = m->totals;
+        b.hist = c->bucket_hist;
+        b.slot_total = c->slot_total;
+        b.slot_base = c->slot_base;
+        b.lod_tab = c->lod_tab;
+        b.n_slots = n_slots;
+        b.cap = (uint32_t)m->cap;
+        const uint64_t rows_max = c->bucket_hist_words / ((uint64_t)n_slots * n_views);
+        b.rows_max = (uint32_t)(rows_max < 0xffffffffull ? rows_max : 0xffffffffull);
+        uint32_t sweep_ctas = (uint32_t)c->sm_count * 7 / n_views;
+        if (sweep_ctas == 0) sweep_ctas = 1;
+        b.rows_target = sweep_ctas * kBucketWarps;
+        const dim3 sweep_grid(sweep_ctas, n_views);
+        bucket_hist<<<sweep_grid, kBucketWarps * 32, 0, s>>>(b);
+        bucket_colscan<<<dim3((n_slots + 31) / 32, n_views), 1024, 0, s>>>(b);
+        bucket_cmds<<<dim3(1, n_views), 1024, 0, s>>>(b);
+        bucket_scatter<<<sweep_grid, kBucketWarps * 32, 0, s>>>(b);
+        CU(cudaGetLastError());
+        c->launches += 4;
+    }
     return RCULL_OK;
 }
 
@@ -1210,8 +1289,8 @@ int rcull_merge_lists(rcull_merge* m, uint32_t view, rcull_draw_cmd** cmds, uint
     if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_lists: null argument");
     const uint32_t mv = m->ctx->cfg.max_views;
     if (view >= mv) return fail(RCULL_ERR_INVALID, "view %u of %u", view, mv);
-    if (cmds) *cmds = reinterpret_cast<rcull_draw_cmd*>(m->base + (size_t)view * m->cap * 20);
-    if (visible) *visible = reinterpret_cast<uint32_t*>(m->base + (size_t)mv * m->cap * 20 + (size_t)view * m->cap * 4);
+    if (cmds) *cmds = reinterpret_cast<rcull_draw_cmd*>(m->cmds[view]);
+    if (visible) *visible = m->visible[view];
     if (counts) *counts = m->counts;
     if (index_totals) *index_totals = reinterpret_cast<uint64_t*>(m->totals);
     return RCULL_OK;

@@ -28,42 +28,27 @@ __global__ void __launch_bounds__(256) rebase_into(const uint32_t* __restrict__ 
         dst_visible[i] = src_visible[i];
 }
 
-// ---- range-shard merge over peer memory (NVLink P2P) ----------------------
-// Every rank holds a MERGED allocation with the same layout:
-//   cmds of view k at  k * cap * 20 bytes,  visible of view k at  V * cap * 20 + k * cap * 4.
-// After an all_gather of the per-rank (count, index_total) words, ONE kernel per rank
-// computes its slot from the gathered words and stores its rebased list into that slot
-// of every rank's allocation -- its own and, through peer-mapped pointers, the others'.
-// The stores are the transfer: no staging copy, no per-slice collective, no host round trip.
+// ---- range-shard merge over peer memory (NVLink peer / NVLS multicast stores) --------
+// What crosses NVLink is the information content of a survivor, not its command: an 8-byte RECORD
+// {draw_index, slot = mesh * 6 + lod}.  The frame kernel itself sends it -- at emission time, one store per
+// peer (or ONE multimem.st when the window has an NVLS multicast mapping) into the region of every rank's
+// WINDOW that belongs to the sending rank -- so the transfer is spread over the whole frame, tile by tile, and
+// there is no exchange kernel.  When a rank's frame kernel has sent everything it stores its per-view
+// (count, index total) words and a tag into every window.  Every rank then EXPANDS the records of all ranks
+// into the merged draw lists locally (merge_expand): indexCount / vertexOffset come from the mesh table,
+// firstIndex from a running sum over the merged order -- the rank prefix of SURVEY 8e falls out of the same scan.
+// Window layout (identical on every rank):
+//   records of parity p (= frame epoch & 1), source rank r, view k:  ((p * world + r) * max_views + k) * cap_r * 8
+//   MergeSync mailbox at sync_off.
 constexpr int kMaxRanks = 8;
+constexpr int kExpandTile = 256;  // records per expand tile (one warp) = the sender's checkpoint spacing
 
-struct MergeArgs {
-    unsigned char* peer[kMaxRanks];         // merged allocation of every rank (peer-mapped)
-    const uint32_t* src_cmds[8];            // this rank's lists, per view
-    const uint32_t* src_visible[8];
-    const unsigned long long* meta_all;     // [world][2 * max_views]: counts then index totals (u64)
-    uint32_t* merged_counts;                // [max_views] outputs in the local allocation's header
-    unsigned long long* merged_totals;
-    uint32_t world, rank, n_views, max_views;
-    uint32_t cap;                           // merged list capacity (commands per view)
-    // fused exchange (merge_exchange): no collective library on the path
-    const unsigned long long* meta_mine;    // this rank's (counts, index totals) of the frame being merged
-    size_t sync_off;                        // byte offset of the MergeSync block in every merged allocation
-    unsigned long long epoch;               // exchange number, the same on every rank
-    uint32_t* cta_done;                     // local counter: CTAs of this launch that have stored their share
-    unsigned char* mc;                      // NVLS multicast mapping of every rank's merged allocation (one store, the switch replicates), or null
-    __host__ __device__ size_t n_views_cap_bytes() const { return (size_t)max_views * cap * 20; }
+struct MergeSync {
+    // [parity][source rank]: counts[8] then index totals[8] of the frame whose epoch is frame_tag[parity][rank]
+    unsigned long long meta[2][kMaxRanks][16];
+    unsigned long long frame_tag[2][kMaxRanks];  // every record of that frame from that rank has landed in this window
+    unsigned long long expand_tag[kMaxRanks];    // rank r has finished reading ITS window for every epoch <= this
 };
-
-__global__ void __launch_bounds__(256) pack_meta(const uint32_t* __restrict__ counts,
-                                                 const unsigned long long* __restrict__ totals, uint32_t max_views,
-                                                 unsigned long long* __restrict__ meta_local) {
-    const uint32_t i = threadIdx.x;
-    if (i < max_views) {
-        meta_local[i] = counts[i];
-        meta_local[max_views + i] = totals[i];
-    }
-}
 
 // Flags other GPUs write into this GPU's memory over NVLink: system-scope release / acquire.
 __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
@@ -79,188 +64,247 @@ __device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long
     asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
-
-// Stores through an NVLS multicast address: one store leaves the GPU, the NVSwitch writes it into every
-// member's memory (egress per rank = its own lists once, not once per peer).
-__device__ __forceinline__ void multimem_st_v4(void* mc, uint4 v) {
-    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(__uint_as_float(v.x)),
-                 "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
-                 : "memory");
+__device__ __forceinline__ uint32_t ld_relaxed_gpu_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
 }
-__device__ __forceinline__ void multimem_st_u32(void* mc, uint32_t v) {
-    asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
+// A store through an NVLS multicast address: one store leaves the GPU, the NVSwitch writes it into every
+// member's memory (egress per rank = its records once, not once per peer).
+__device__ __forceinline__ void multimem_st_v2(void* mc, uint32_t a, uint32_t b) {
+    asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(mc), "f"(__uint_as_float(a)), "f"(__uint_as_float(b)) : "memory");
 }
 
-// Per-rank mailbox at the end of every merged allocation; slot [r] is written by rank r only.
-struct MergeSync {
-    // two slots, by exchange parity: a rank can be one exchange ahead of a peer's late CTAs, never two
-    // (its exchange e + 2 needs the peer's words of e + 1, which the peer sends after finishing e)
-    unsigned long long meta[2][kMaxRanks][16];  // counts[8] then index totals[8] of rank r
-    unsigned long long meta_tag[2][kMaxRanks];  // epoch of the exchange meta[.][r] belongs to
-    unsigned long long done_tag[kMaxRanks];  // rank r has stored all its slices of exchange `epoch` here
+// What the frame kernel needs to send records (part of FrameArgs; world == 0: no merge attached).
+struct RecordArgs {
+    unsigned char* peer[kMaxRanks];  // window of every rank (own included), peer-mapped
+    unsigned char* mc;               // NVLS multicast mapping of all windows, or null
+    size_t base;                     // byte offset of this frame's records of view 0 from this rank
+    size_t view_stride;              // cap_r * 8
+    size_t sync_off;                 // MergeSync inside the window
+    unsigned long long epoch;        // number of this merged frame (the same on every rank), from 1
+    uint32_t* cta_done;              // local counter: CTAs of this launch whose records are out
+    size_t ckpt_base;                // byte offset of this frame's checkpoints of view 0 from this rank
+    size_t ckpt_view_stride;         // bytes of checkpoints per view
+    uint32_t world, rank, cap_r, pad;
 };
 
-// Copies n_words 32-bit words of one of this rank's lists to byte offset dst_off of EVERY
-// rank's merged allocation.  Stores are 16 bytes wide wherever the destination is 16-byte
-// aligned (NVLink moves full 16-byte-multiple packets: word-wide stores reached 0.3 TB/s, a third
-// of the link); the up-to-3 words before the first aligned address and after the last go out as
-// single words.  kCmds: word w of the 5-word command stream is firstIndex iff w % 5 == 2.
-template <bool kCmds>
-__device__ __forceinline__ void store_to_peers(const MergeArgs& a, const uint32_t* __restrict__ src, size_t n_words, size_t dst_off,
-                                               uint32_t add, size_t t0, size_t stride) {
-    const size_t head = ((16u - (uint32_t)(dst_off & 15u)) & 15u) / 4u;  // words until the destination is 16-byte aligned
-    const size_t h = head < n_words ? head : n_words;
-    const size_t n_vec = (n_words - h) / 4;
-    // four vectors per thread in flight: the loop is bound by the latency of the local loads, not by issue
-    constexpr int kUnroll = 4;
-    for (size_t v0 = t0; v0 < n_vec; v0 += kUnroll * stride) {
-        uint4 x[kUnroll];
-#pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
-            const size_t v = v0 + u * stride;
-            if (v < n_vec) {
-                const size_t w = h + 4 * v;
-                x[u] = make_uint4(src[w], src[w + 1], src[w + 2], src[w + 3]);
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
-            const size_t v = v0 + u * stride;
-            if (v < n_vec) {
-                const size_t w = h + 4 * v;
-                if (kCmds) {
-                    const uint32_t m = (uint32_t)(w % 5);  // firstIndex sits where (w + j) % 5 == 2
-                    if (m == 2) x[u].x += add;
-                    if (m == 1) x[u].y += add;
-                    if (m == 0) x[u].z += add;
-                    if (m == 4) x[u].w += add;
-                }
-                if (a.mc != nullptr) {
-                    multimem_st_v4(a.mc + dst_off + 4 * w, x[u]);  // NVSwitch replicates the store into every rank's allocation
-                } else {
-                    for (uint32_t p = 0; p < a.world; ++p) *reinterpret_cast<uint4*>(a.peer[p] + dst_off + 4 * w) = x[u];
-                }
-            }
-        }
-    }
-    // head and tail words (at most 6 in total)
-    const size_t tail0 = h + 4 * n_vec;
-    for (size_t i = t0; i < h + (n_words - tail0); i += stride) {
-        const size_t w = i < h ? i : tail0 + (i - h);
-        uint32_t x = src[w];
-        if (kCmds && w % 5 == 2) x += add;
-        if (a.mc != nullptr) {
-            multimem_st_u32(a.mc + dst_off + 4 * w, x);
-        } else {
-            for (uint32_t p = 0; p < a.world; ++p) *reinterpret_cast<uint32_t*>(a.peer[p] + dst_off + 4 * w) = x;
-        }
+__device__ __forceinline__ void record_store(const RecordArgs& r, uint32_t view, uint32_t pos, uint32_t draw_index, uint32_t slot) {
+    if (pos >= r.cap_r) return;  // clamp writes, like cap_visible; the count still says how many there were
+    const size_t off = r.base + (size_t)view * r.view_stride + (size_t)pos * 8;
+    if (r.mc != nullptr) {
+        multimem_st_v2(r.mc + off, draw_index, slot);
+    } else {
+        for (uint32_t p = 0; p < r.world; ++p) *reinterpret_cast<uint2*>(r.peer[p] + off) = make_uint2(draw_index, slot);
     }
 }
-
-__global__ void __launch_bounds__(256) scatter_rebased(const __grid_constant__ MergeArgs a) {
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    const size_t t0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    for (uint32_t k = 0; k < a.n_views; ++k) {
-        unsigned long long cnt_prefix = 0, len_prefix = 0, cnt_all = 0, len_all = 0;
-        for (uint32_t r = 0; r < a.world; ++r) {
-            const unsigned long long c = a.meta_all[(size_t)r * 2 * a.max_views + k];
-            const unsigned long long l = a.meta_all[(size_t)r * 2 * a.max_views + a.max_views + k];
-            if (r < a.rank) {
-                cnt_prefix += c;
-                len_prefix += l;
-            }
-            cnt_all += c;
-            len_all += l;
-        }
-        if (t0 == 0) {
-            a.merged_counts[k] = (uint32_t)cnt_all;
-            a.merged_totals[k] = len_all;
-        }
-        unsigned long long count = a.meta_all[(size_t)a.rank * 2 * a.max_views + k];
-        if (cnt_prefix >= a.cap) continue;
-        if (cnt_prefix + count > a.cap) count = a.cap - cnt_prefix;  // clamp writes, like cap_visible
-        const size_t words = (size_t)count * 5;
-        const uint32_t add = (uint32_t)len_prefix;
-        const uint32_t* __restrict__ sc = a.src_cmds[k];
-        const uint32_t* __restrict__ sv = a.src_visible[k];
-        const size_t cmd_off = ((size_t)k * a.cap + cnt_prefix) * 20;
-        const size_t vis_off = (size_t)a.n_views_cap_bytes() + ((size_t)k * a.cap + cnt_prefix) * 4;
-        store_to_peers<true>(a, sc, words, cmd_off, add, t0, stride);
-        store_to_peers<false>(a, sv, (size_t)count, vis_off, 0u, t0, stride);
+// Every kExpandTile-th survivor of a view also leaves its LOCAL firstIndex behind (4 bytes per 256 survivors): the
+// receivers restart their running sums there, so no expand tile depends on another.
+__device__ __forceinline__ void record_checkpoint(const RecordArgs& r, uint32_t view, uint32_t pos, uint32_t first_index_local) {
+    if (pos >= r.cap_r || (pos % kExpandTile) != 0u) return;
+    const size_t off = r.ckpt_base + (size_t)view * r.ckpt_view_stride + (size_t)(pos / kExpandTile) * 4;
+    for (uint32_t p = 0; p < r.world; ++p) *reinterpret_cast<uint32_t*>(r.peer[p] + off) = first_index_local;
+}
+// Back-pressure: the records of epoch e reuse the region of epoch e - 2, which every rank must have expanded.
+__device__ __forceinline__ void record_wait_window_free(const RecordArgs& r, uint32_t tid) {
+    if (tid < r.world) {
+        const MergeSync* mine = reinterpret_cast<const MergeSync*>(r.peer[r.rank] + r.sync_off);
+        while (ld_acquire_sys(&mine->expand_tag[tid]) + 2 < r.epoch) __nanosleep(200);
     }
 }
-
-// The whole exchange step in ONE kernel, no collective library call on the path:
-//   1. CTA 0 stores this rank's (count, index total) words into every rank's mailbox and raises its tag;
-//   2. every CTA waits until all ranks' words of this epoch have arrived in the LOCAL mailbox;
-//   3. exclusive prefixes over ranks -> this rank's slot; the rebased lists are stored into that
-//      slot of every rank's merged allocation (16-byte peer stores over NVLink);
-//   4. the last CTA to finish raises this rank's done tag in every mailbox.
-// 128 threads x 64 registers (the 8192 registers the frame kernel's CTA leaves free) and no shared memory: such a CTA is resident beside
-// the frame kernel's CTA, so the exchange of frame i runs under frame i + 1.
-__global__ void __maxnreg__(64) merge_exchange(const __grid_constant__ MergeArgs a) {
-    const uint32_t tid = threadIdx.x;
-    if (blockIdx.x == 0) {
-        if (tid < 16) {
-            const uint32_t k = tid & 7u;
-            const unsigned long long v = k < a.max_views ? a.meta_mine[(tid >> 3) * a.max_views + k] : 0ull;
-            for (uint32_t p = 0; p < a.world; ++p) reinterpret_cast<MergeSync*>(a.peer[p] + a.sync_off)->meta[a.epoch & 1][a.rank][tid] = v;
+// Called by ONE thread of a CTA after every record-storing thread of the CTA has fenced (system scope) and the CTA
+// has synchronised: the last CTA of the launch sends the frame's counts / index totals and raises the tag everywhere.
+__device__ __forceinline__ void record_finish(const RecordArgs& r, const uint32_t* counts, const unsigned long long* totals, uint32_t n_views) {
+    const uint32_t done = atomicAdd(r.cta_done, 1u);
+    if (done != gridDim.x - 1) return;
+    *r.cta_done = 0;  // the next launch on this stream starts from zero
+    __threadfence();
+    const uint32_t par = (uint32_t)(r.epoch & 1ull);
+    for (uint32_t k = 0; k < 8; ++k) {
+        const unsigned long long c = k < n_views ? ld_relaxed_gpu_u32(counts + k) : 0ull;
+        const unsigned long long t = k < n_views ? ld_relaxed(reinterpret_cast<const uint64_t*>(totals + k)) : 0ull;
+        for (uint32_t p = 0; p < r.world; ++p) {
+            MergeSync* s = reinterpret_cast<MergeSync*>(r.peer[p] + r.sync_off);
+            s->meta[par][r.rank][k] = c;
+            s->meta[par][r.rank][8 + k] = t;
         }
-        __threadfence_system();
-        __syncthreads();
-        if (tid < a.world) st_release_sys(&reinterpret_cast<MergeSync*>(a.peer[tid] + a.sync_off)->meta_tag[a.epoch & 1][a.rank], a.epoch);
     }
-    const MergeSync* mine = reinterpret_cast<const MergeSync*>(a.peer[a.rank] + a.sync_off);
+    __threadfence_system();
+    for (uint32_t p = 0; p < r.world; ++p)
+        st_release_sys(&reinterpret_cast<MergeSync*>(r.peer[p] + r.sync_off)->frame_tag[par][r.rank], r.epoch);
+}
+
+// An empty frame (n == 0) of a context with a merge attached: zero counts and the tag, nothing else.
+__global__ void record_empty_frame(const __grid_constant__ RecordArgs r, const uint32_t* counts, const unsigned long long* totals) {
+    record_wait_window_free(r, threadIdx.x);
+    __syncthreads();
+    if (threadIdx.x == 0) record_finish(r, counts, totals, 0);
+}
+
+// ---- merge_expand: every rank's records -> the merged draw lists, on the receiving GPU -------------------------
+// A tile is one CHUNK of kExpandTile (256) consecutive records of one (view, source rank), and it belongs to ONE WARP.
+// Its commands start at merged position  (survivors of earlier ranks) + chunk * 256  and its first firstIndex is
+// (index totals of earlier ranks) + (the sender's checkpoint of that chunk): both known without looking at any other
+// tile, so the kernel is a plain streaming pass -- no look-back, no ticket, no barrier, no dependency between warps;
+// latency is hidden by the number of independent warps (32 per SM).
+// Two launch shapes of the same body:
+//   merge_expand      CTAs of 8 warps, four per SM over the whole chip: the expand runs between frames;
+//   merge_expand_big  ONE CTA of 32 warps and 200 KB of shared memory per SM: a grid of R such CTAs occupies exactly R
+//                     SMs while the frame kernel (one persistent CTA per SM, grid cut to the other SMs) runs on the
+//                     rest -- a deterministic split of the chip, whichever kernel is placed first.  (Light expand CTAs
+//                     SHARING the frame kernel's SMs were measured and rejected: the frame kernel is latency-bound and
+//                     its look-back couples every CTA to the slowest SM.)
+// A warp stages its 256 commands in shared memory and writes them as 16-byte vectors: the 20-byte stride of a
+// command would otherwise cost five scattered 4-byte stores per survivor.
+constexpr int kExpandItems = kExpandTile / 32;           // 8 records per lane
+constexpr int kExpandStageWords = kExpandTile * 5 + 12;  // + the alignment shift, rounded to 16 bytes
+
+struct ExpandArgs {
+    const unsigned char* window;       // this rank's window
+    unsigned char* peer[kMaxRanks];    // every rank's window (for the expand tag)
+    size_t sync_off, view_stride, ckpt_off, ckpt_view_stride;
+    unsigned long long epoch;
+    uint32_t world, rank, n_views, max_views, cap_r, cap;
+    uint32_t* cmds[8];                 // merged lists (5 words per command), or slot keys in pair mode
+    uint32_t* visible[8];              // merged visible indices, or draw indices in pair mode
+    uint32_t* counts;                  // [max_views] merged survivor counts
+    unsigned long long* totals;        // [max_views] merged index totals
+    const uint4* lod_tab;              // index_len, first_index, vertex_offset per (mesh, lod) slot
+    uint32_t n_slots;
+    uint32_t pairs;                    // per-mesh mode: write (slot key, draw_index) pairs in merged draw order for the bucketing passes
+    uint32_t* cta_done;                // CTAs of this launch that are through
+};
+
+template <int kWarps>
+__device__ __forceinline__ void merge_expand_body(const ExpandArgs& a) {
+    extern __shared__ uint4 s_stage4[];  // per warp: kExpandStageWords words
+    __shared__ uint32_t s_cnt[8][kMaxRanks];      // records (view, rank) stored
+    __shared__ uint32_t s_pos[8][kMaxRanks + 1];  // merged position of the rank's first survivor (exclusive prefix of s_cnt, clamped to cap)
+    __shared__ uint32_t s_first[8][kMaxRanks];    // firstIndex the rank's first survivor starts from (exclusive prefix of the index totals)
+    __shared__ uint32_t s_tiles[8 * kMaxRanks + 1];  // exclusive prefix of the tile counts over (view, rank)
+    __shared__ unsigned long long s_meta[2][8][kMaxRanks];  // counts, index totals: one mailbox word per thread
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint32_t par = (uint32_t)(a.epoch & 1ull);
+    const MergeSync* mine = reinterpret_cast<const MergeSync*>(a.window + a.sync_off);
     if (tid < a.world) {
-        while (ld_acquire_sys(&mine->meta_tag[a.epoch & 1][tid]) != a.epoch) __nanosleep(200);
+        while (ld_acquire_sys(&mine->frame_tag[par][tid]) != a.epoch) __nanosleep(200);
     }
     __syncthreads();
-    const unsigned long long (*meta)[16] = mine->meta[a.epoch & 1];  // every rank's words, now in local memory
-
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    const size_t t0 = (size_t)blockIdx.x * blockDim.x + tid;
-    for (uint32_t k = 0; k < a.n_views; ++k) {
-        unsigned long long cnt_prefix = 0, len_prefix = 0, cnt_all = 0, len_all = 0;
-        for (uint32_t r = 0; r < a.world; ++r) {
-            const unsigned long long c = ld_relaxed_sys(&meta[r][k]), l = ld_relaxed_sys(&meta[r][8 + k]);
-            if (r < a.rank) {
-                cnt_prefix += c;
-                len_prefix += l;
-            }
-            cnt_all += c;
-            len_all += l;
-        }
-        if (t0 == 0) {
-            a.merged_counts[k] = (uint32_t)cnt_all;
-            a.merged_totals[k] = len_all;
-        }
-        unsigned long long count = ld_relaxed_sys(&meta[a.rank][k]);
-        if (cnt_prefix >= a.cap) continue;
-        if (cnt_prefix + count > a.cap) count = a.cap - cnt_prefix;  // clamp writes, like cap_visible
-        const size_t cmd_off = ((size_t)k * a.cap + cnt_prefix) * 20;
-        const size_t vis_off = (size_t)a.n_views_cap_bytes() + ((size_t)k * a.cap + cnt_prefix) * 4;
-        store_to_peers<true>(a, a.src_cmds[k], (size_t)count * 5, cmd_off, (uint32_t)len_prefix, t0, stride);
-        store_to_peers<false>(a, a.src_visible[k], (size_t)count, vis_off, 0u, t0, stride);
+    if (tid < 2 * 8 * kMaxRanks) {
+        const uint32_t what = tid / (8 * kMaxRanks), k = (tid / kMaxRanks) % 8, r = tid % kMaxRanks;
+        s_meta[what][k][r] = (k < a.n_views && r < a.world) ? ld_relaxed_sys(&mine->meta[par][r][what * 8 + k]) : 0ull;
     }
-    __threadfence_system();  // this thread's peer stores are visible system-wide before the CTA counts itself
+    __syncthreads();
+    if (tid < a.n_views) {
+        unsigned long long run = 0, all = 0, len_all = 0;
+        for (uint32_t r = 0; r < a.world; ++r) {
+            const unsigned long long c = s_meta[0][tid][r];
+            const uint32_t pos = (uint32_t)(run < a.cap ? run : a.cap);
+            s_pos[tid][r] = pos;
+            const uint32_t stored = (uint32_t)(c < a.cap_r ? c : a.cap_r);  // what the rank could send
+            s_cnt[tid][r] = stored < a.cap - pos ? stored : a.cap - pos;    // what the merged list can take
+            s_first[tid][r] = (uint32_t)len_all;                            // u32: firstIndex wraps like the reference's
+            run += stored;
+            all += c;
+            len_all += s_meta[1][tid][r];
+        }
+        s_pos[tid][a.world] = (uint32_t)(run < a.cap ? run : a.cap);
+        if (blockIdx.x == 0) {
+            a.counts[tid] = (uint32_t)all;  // the true count, even when the lists are clamped
+            a.totals[tid] = len_all;
+        }
+    }
     __syncthreads();
     if (tid == 0) {
+        uint32_t t = 0;
+        for (uint32_t k = 0; k < a.n_views; ++k)
+            for (uint32_t r = 0; r < a.world; ++r) {
+                s_tiles[k * a.world + r] = t;
+                t += (s_cnt[k][r] + kExpandTile - 1) / kExpandTile;
+            }
+        s_tiles[a.n_views * a.world] = t;
+    }
+    __syncthreads();
+    const uint32_t n_pairs = a.n_views * a.world, n_tiles = s_tiles[n_pairs];
+    uint32_t* const stage = reinterpret_cast<uint32_t*>(s_stage4) + warp * kExpandStageWords;
+    uint32_t kr = 0;  // (view, rank) of the current tile; a warp's tiles only move forward
+    for (uint32_t t = blockIdx.x * kWarps + warp; t < n_tiles; t += gridDim.x * kWarps) {
+        while (kr + 1 < n_pairs && t >= s_tiles[kr + 1]) ++kr;
+        const uint32_t k = kr / a.world, r = kr % a.world, c = t - s_tiles[kr];
+        const uint32_t n_kr = s_cnt[k][r], first_local = c * kExpandTile;
+        const uint32_t n_here = n_kr - first_local < (uint32_t)kExpandTile ? n_kr - first_local : (uint32_t)kExpandTile;
+        const uint2* recs = reinterpret_cast<const uint2*>(a.window + ((size_t)(par * a.world + r) * a.max_views + k) * a.view_stride) + first_local;
+        const uint32_t dst0 = s_pos[k][r] + first_local;  // merged position of the tile's first survivor
+        uint2 rec[kExpandItems];  // lane-striped: coalesced 8-byte loads
+#pragma unroll
+        for (int q = 0; q < kExpandItems; ++q) rec[q] = lane + 32 * q < n_here ? __ldcg(recs + lane + 32 * q) : make_uint2(0u, 0xffffffffu);
+        if (a.pairs) {  // merged (slot key, draw_index) pairs: the input of the bucketing passes
+#pragma unroll
+            for (int q = 0; q < kExpandItems; ++q)
+                if (lane + 32 * q < n_here) {
+                    a.cmds[k][dst0 + lane + 32 * q] = rec[q].y;
+                    a.visible[k][dst0 + lane + 32 * q] = rec[q].x;
+                }
+            continue;
+        }
+        const uint32_t ckpt = __ldcg(reinterpret_cast<const uint32_t*>(a.window + a.ckpt_off + ((size_t)(par * a.world + r) * a.max_views + k) * a.ckpt_view_stride) + c);
+        uint32_t len[kExpandItems], voff[kExpandItems];
+#pragma unroll
+        for (int q = 0; q < kExpandItems; ++q) {
+            const bool ok = lane + 32 * q < n_here;
+            const uint4 L = ok ? __ldg(a.lod_tab + (rec[q].y < a.n_slots ? rec[q].y : 0u)) : make_uint4(0, 0, 0, 0);
+            len[q] = L.x;
+            voff[q] = L.z;
+        }
+        // running sum of index_len inside the chunk, from the sender's checkpoint
+        uint32_t carry = s_first[k][r] + ckpt;
+        const size_t g0 = (size_t)dst0 * 5u;
+        const uint32_t sh = (uint32_t)(g0 & 3u);  // word address of the tile's first command word in the list, and its phase in a 16-byte unit
+#pragma unroll
+        for (int q = 0; q < kExpandItems; ++q) {
+            const uint32_t incl = warp_incl_scan_u32(len[q], lane);
+            const uint32_t l = lane + 32 * q;
+            if (l < n_here) {
+                uint32_t* cw = stage + sh + l * 5;  // stride of 5 words across the lanes: no bank conflict
+                cw[0] = len[q];                      // indexCount
+                cw[1] = 1u;                          // instanceCount
+                cw[2] = carry + incl - len[q];       // firstIndex: running sum over the MERGED order
+                cw[3] = voff[q];                     // vertexOffset
+                cw[4] = rec[q].x;                    // firstInstance = global draw_index
+                a.visible[k][dst0 + l] = rec[q].x;
+            }
+            carry += __shfl_sync(kFullMask, incl, 31);
+        }
+        __syncwarp();
+        {   // staged words [sh, sh + n_words) go to list words [g0, g0 + n_words): word i of the staging area and word
+            // g0 - sh + i of the list have the same phase, so whole 16-byte units move as vectors
+            uint32_t* const dst = a.cmds[k] + (g0 - sh);
+            const uint32_t end = sh + n_here * 5u;
+            const uint32_t v0 = sh ? 1u : 0u, v1 = end / 4u;
+            for (uint32_t v = v0 + lane; v < v1; v += 32) reinterpret_cast<uint4*>(dst)[v] = reinterpret_cast<const uint4*>(stage)[v];
+            if (sh && lane >= sh && lane < 4u && lane < end) dst[lane] = stage[lane];         // head: up to the first boundary
+            if (v1 >= v0 && lane < end - 4u * v1 && 4u * v1 >= sh) dst[4u * v1 + lane] = stage[4u * v1 + lane];  // tail
+        }
+        __syncwarp();  // the staging area is free again
+    }
+    // this rank is done reading its window for this epoch: tell everyone (they may reuse the region two frames on)
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
         const uint32_t done = atomicAdd(a.cta_done, 1u);
         if (done == gridDim.x - 1) {
             *a.cta_done = 0;
             __threadfence_system();
             for (uint32_t p = 0; p < a.world; ++p)
-                st_release_sys(&reinterpret_cast<MergeSync*>(a.peer[p] + a.sync_off)->done_tag[a.rank], a.epoch);
+                st_release_sys(&reinterpret_cast<MergeSync*>(a.peer[p] + a.sync_off)->expand_tag[a.rank], a.epoch);
         }
     }
 }
 
-// Returns when every rank's slices of exchange `epoch` have landed in this rank's allocation.
-__global__ void merge_wait(const MergeSync* mine, uint32_t world, unsigned long long epoch) {
-    if (threadIdx.x < world) {
-        while (ld_acquire_sys(&mine->done_tag[threadIdx.x]) < epoch) __nanosleep(200);
-    }
-}
+__global__ void __launch_bounds__(256, 4) merge_expand(const __grid_constant__ ExpandArgs a) { merge_expand_body<8>(a); }
+__global__ void __launch_bounds__(1024, 1) merge_expand_big(const __grid_constant__ ExpandArgs a) { merge_expand_body<32>(a); }
+constexpr size_t kExpandSmem = 8 * (size_t)kExpandStageWords * 4;
+constexpr size_t kExpandBigSmem = 32 * (size_t)kExpandStageWords * 4 + 36 * 1024;  // + ballast: no second CTA, of any kernel, fits beside it
 
 // ---- per-mesh instanced emission (BASELINE config 4; compact_draw_stream.comp:41 keep-rule on
 // instanceCount) ----------------------------------------------------------------------

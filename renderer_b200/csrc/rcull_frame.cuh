@@ -20,6 +20,7 @@
 #include <cuda.h>  // CUtensorMap (type only; the encoder is resolved at run time)
 #include <cuda/std/type_traits>
 
+#include "rcull_aux.cuh"  // RecordArgs: the range-shard merge sends its records from this kernel
 #include "rcull_device.cuh"
 
 namespace rcull {
@@ -96,7 +97,6 @@ struct FrameArgs {
     uint32_t* src_first;  // optional, view 0 only: first_index of the LOD behind each command (work list of the triangle stage)
     uint32_t* counts;
     unsigned long long* totals;
-    unsigned long long* meta_out;  // optional [2 * max_views]: counts then totals as u64 (merge exchange words)
     uint32_t max_views;
     ulonglong2* status;   // [views][n_tiles]
     uint32_t* ticket;
@@ -114,6 +114,7 @@ struct FrameArgs {
     float cam[3];
     float lod_d2_max;  // lod 1 iff |cam-pos|^2 > lod_d2_max  (== sqrt(d2) > lod_distance)
     PlaneC planes[kMaxViews][6];
+    RecordArgs rec;  // rec.world > 0: a range-shard merge is attached -- survivors leave as 8-byte records to every rank's window
 };
 
 struct FrameSmem {
@@ -331,10 +332,6 @@ __device__ __forceinline__ void scan_warp(const FrameArgs& args, FrameSmem& sm, 
                             if (tile == n_tiles - 1) {
                                 args.counts[k] = ic;
                                 args.totals[k] = il;
-                                if (args.meta_out != nullptr) {
-                                    args.meta_out[k] = ic;
-                                    args.meta_out[args.max_views + k] = il;
-                                }
                             }
                         }
                     }
@@ -397,6 +394,14 @@ __device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameS
         const uint32_t incl = warp_incl_scan_u32(L.x, lane);
         const uint32_t excl = carry + incl - L.x;
         carry += __shfl_sync(kFullMask, incl, 31);
+        if (args.rec.world != 0u) {  // merge attached: the record is the whole message; the receivers rebuild the command
+            if (act) {
+                const uint32_t pos = sm.adj_cnt[buf][k][warp] + i;
+                record_store(args.rec, k, pos, args.draw_index_base + tile_base + e, slot);
+                record_checkpoint(args.rec, k, pos, sm.adj_len[buf][k][warp] + excl);  // every 256th survivor: its local firstIndex
+            }
+            continue;
+        }
         if (act) {
             const uint32_t pos = sm.adj_cnt[buf][k][warp] + i;
             if (pos < args.cap_visible) {
@@ -497,6 +502,7 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
         mesh_tab = sm_mesh;
         sm_lod01 = sm_lod;
     }
+    if (args.rec.world != 0u) record_wait_window_free(args.rec, tid);  // the region these records go to has been expanded by every rank
     __syncthreads();
 
     if (warp == kComputeWarps) {
@@ -795,6 +801,16 @@ __global__ void __maxnreg__(RCULL_FRAME_REGS)
     __syncwarp();
     if (lane == 0) mbar_arrive(&sm.done[it % B]);
     if (lane == 0) bulk_wait_read0();
+    if (args.rec.world != 0u) {
+        // Every record of this CTA is visible system-wide before the CTA counts itself: the barrier orders all compute
+        // threads' stores before thread 0's system-scope fence (fences are cumulative), so ONE fence per CTA does it.
+        // The last CTA of the launch sends the frame's (count, index total) words and raises the tag in every window.
+        asm volatile("bar.sync 1, %0;" ::"r"(kComputeWarps * 32) : "memory");  // the compute warps only: the scan warp has left
+        if (tid == 0) {
+            __threadfence_system();
+            record_finish(args.rec, args.counts, args.totals, V);
+        }
+    }
     if (tid == 0) {
         RCULL_STAT(7, RCULL_CLOCK() - k0);
         RCULL_STAT(10, 1);

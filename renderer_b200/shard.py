@@ -194,10 +194,11 @@ def per_mesh_permutation(plan: PerMeshMergePlan) -> np.ndarray:
 
 
 class PerMeshShardMerger:
-    """Host side of the per-mesh merge: all_gather of the slot counts, in-place allgatherv of the ranks' bucketed
-    visible lists into a rank-ordered staging buffer (one broadcast per rank, as ShardMerger does), then the
-    slot-major permutation.  The permutation runs as a torch index_select here; a segmented peer-store kernel
-    (one warp per (slot, rank) bucket, like rcull_merge_scatter) is the device-side follow-up."""
+    """REFERENCE of the per-mesh merge order for the CPU (gloo, world 2 / 3) tests -- not the GPU path.  On GPUs the
+    merge is rcull_merge_expand: the ranks' (slot, draw_index) records arrive in every window, are concatenated in rank
+    order (= draw order) and bucketed by the single-GPU counting sort, all on the device (RecordMerger).  This class
+    states the same result with collectives and a permutation: all_gather of the slot counts, in-place allgatherv of the
+    ranks' bucketed visible lists into a rank-ordered staging buffer, then the slot-major permutation."""
 
     def __init__(self, n_slots: int, capacity: int, device, group=None):
         import torch
@@ -255,14 +256,14 @@ def _wrap_device(torch, ptr: int, n: int, dtype, device):
     return torch.as_tensor(_Holder(), device=device)
 
 
-class PeerMerger:
-    """The merge over peer memory (rcull_merge_*): per frame, one tiny all_gather of the
-    per-rank (count, index_total) words, then ONE kernel per rank that stores its rebased
-    lists into its slot of every rank's merged allocation through NVLink peer pointers,
-    then a one-word all_reduce as the "everyone has written" barrier.  Nothing in the
-    step touches the host: all of it is enqueued on the current torch stream."""
+class RecordMerger:
+    """The merge over peer memory (rcull_merge_*, include/rcull.h): once attached, every frame of `ctx` sends its
+    survivors as 8-byte records straight from the frame kernel into every rank's window (NVLink peer stores, or one
+    multimem.st through an NVLS multicast mapping), and expand() rebuilds the merged draw lists on this GPU.
+    Python only bootstraps the windows (IPC handles over torch.distributed, or torch symmetric memory); nothing in a
+    step touches the host or calls a collective."""
 
-    def __init__(self, ctx, n_views: int, capacity: int, device, group=None, symmetric: bool = True):
+    def __init__(self, ctx, capacity: int, capacity_per_rank: int, device, group=None, symmetric: bool = False):
         import ctypes as C
 
         import torch
@@ -271,25 +272,25 @@ class PeerMerger:
         from . import _lib
 
         self.torch, self.dist, self.C, self._lib = torch, dist, C, _lib.load()
-        self.ctx, self.group, self.n_views, self.capacity, self.device = ctx, group, n_views, capacity, device
+        self.ctx, self.group, self.capacity, self.device = ctx, group, capacity, device
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self._h = C.c_void_p()
         self.transport = "cuda-ipc peer stores"
         self._symm = None
         if symmetric and self.world > 1:
-            # Symmetric memory: every rank maps every rank's allocation AND one NVLS multicast address that
-            # stands for all of them -- the exchange then stores each list once and the NVSwitch replicates it.
+            # Symmetric memory: every rank maps every rank's window AND one NVLS multicast address that stands for all
+            # of them -- a record then leaves the GPU once and the NVSwitch replicates it.
             try:
                 import torch.distributed._symmetric_memory as symm
 
                 nbytes = C.c_uint64()
-                _lib.check(self._lib.rcull_merge_bytes(ctx._h, capacity, C.byref(nbytes)))
+                _lib.check(self._lib.rcull_merge_window_bytes(ctx._h, self.world, capacity_per_rank, C.byref(nbytes)))
                 buf = symm.empty(int(nbytes.value), dtype=torch.uint8, device=device)
                 g = group if group is not None else dist.group.WORLD
                 hdl = symm.rendezvous(buf, g.group_name)
                 ptrs = [int(p) for p in hdl.buffer_ptrs]
-                _lib.check(self._lib.rcull_merge_create_on(ctx._h, self.world, self.rank, capacity, C.c_void_p(ptrs[self.rank]), C.byref(self._h)))
+                _lib.check(self._lib.rcull_merge_create_on(ctx._h, self.world, self.rank, capacity, capacity_per_rank, C.c_void_p(ptrs[self.rank]), C.byref(self._h)))
                 for p in range(self.world):
                     _lib.check(self._lib.rcull_merge_set_peer_ptr(self._h, p, C.c_void_p(ptrs[p])))
                 mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
@@ -298,24 +299,16 @@ class PeerMerger:
                 self.transport = "symmetric memory, " + ("NVLS multicast stores" if mc else "peer stores")
                 self._symm = (buf, hdl)
             except Exception as e:  # no symmetric-memory support in this torch / on this fabric: CUDA IPC below
+                if self._h:
+                    self._lib.rcull_merge_destroy(self._h)
                 self._symm = None
                 self._h = C.c_void_p()
                 self.transport = f"cuda-ipc peer stores (symmetric memory unavailable: {type(e).__name__})"
         if not self._h:
-            _lib.check(self._lib.rcull_merge_create(ctx._h, self.world, self.rank, capacity, C.byref(self._h)))
-        mv = ctx.cfg.max_views
-        a, b = C.c_void_p(), C.c_void_p()
-        _lib.check(self._lib.rcull_merge_meta_ptrs(self._h, C.byref(a), C.byref(b)))
-        self.meta_rows = _wrap_device(torch, a.value, 3 * 2 * mv, torch.int64, device).view(3, 2 * mv)  # row = output set
-        self.meta_local = self.meta_rows[0]
-        self.meta_all = _wrap_device(torch, b.value, self.world * 2 * mv, torch.int64, device)
-        self._flag = torch.zeros(1, dtype=torch.int32, device=device)
-        # pipelined use (exchange of frame i overlapping frame i + 1 on another stream): the event the
-        # caller orders the reuse of an output set by
-        self.ev_scatter_done = [torch.cuda.Event() for _ in range(3)]
+            _lib.check(self._lib.rcull_merge_create(ctx._h, self.world, self.rank, capacity, capacity_per_rank, C.byref(self._h)))
         if self.world > 1 and self._symm is not None:
             dist.barrier(group=group)  # every mailbox is cleared before anyone stores into it
-        elif self.world > 1:  # one-time exchange of the IPC handles of the merged allocations
+        elif self.world > 1:  # one-time exchange of the IPC handles of the windows
             handle = (C.c_ubyte * 64)()
             _lib.check(self._lib.rcull_merge_ipc_handle(self._h, handle))
             handles = [None] * self.world
@@ -325,43 +318,29 @@ class PeerMerger:
                     buf = (C.c_ubyte * 64).from_buffer_copy(h)
                     _lib.check(self._lib.rcull_merge_open_peer(self._h, p, buf))
             dist.barrier(group=group)
-        self.bytes_sent = 0
 
     def destroy(self):
         if self._h:
             if self.world > 1:
-                self.dist.barrier(group=self.group)  # nobody may still be storing into this allocation
+                self.torch.cuda.synchronize(self.device)
+                self.dist.barrier(group=self.group)  # nobody may still be storing into this window
             self._lib.rcull_merge_destroy(self._h)
             self._h = self.C.c_void_p()
 
-    def merge(self, buffer_ix: int = 0) -> None:
-        """Enqueue one merge on the current torch stream (after the frame on the same stream)."""
+    def set_overlap(self, expand_sms: int) -> None:
+        """expand_sms > 0: the frame kernel leaves that many SMs free and expand() launches as many whole-SM CTAs (issue
+        it on a second stream after the frame's event: it then runs beside the next frame); 0: full-chip expand."""
         from ._lib import check
 
-        s = self.C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
-        # no pack step: a context with a merge attached writes the exchange words from the
-        # frame kernel itself (frames must be issued after this object was created)
-        if self.world > 1:
-            self.dist.all_gather_into_tensor(self.meta_all, self.meta_rows[buffer_ix], group=self.group)
-        else:
-            self.meta_all.copy_(self.meta_rows[buffer_ix])
-        check(self._lib.rcull_merge_scatter(self._h, buffer_ix, self.n_views, s))
-        if self.world > 1:
-            self.dist.all_reduce(self._flag, group=self.group)  # every rank has stored its slices
+        check(self._lib.rcull_merge_set_overlap(self._h, int(expand_sms)))
 
-    def exchange(self, buffer_ix: int = 0, wait: bool = True) -> None:
-        """The fused exchange (rcull_merge_exchange): ONE kernel on the current stream -- meta words to every
-        peer's mailbox, wait for everyone's, rebased lists into every rank's allocation, done tags -- and no
-        collective call.  Records ev_scatter_done[buffer_ix] (output set buffer_ix may be overwritten);
-        wait=True appends the kernel that returns when every rank's slices have landed here."""
+    def expand(self, stream: int | None = None) -> None:
+        """Enqueue the expand of the oldest unexpanded merged frame (default: the current torch stream)."""
         from ._lib import check
 
-        st = self.torch.cuda.current_stream(self.device)
-        s = self.C.c_void_p(st.cuda_stream)
-        check(self._lib.rcull_merge_exchange(self._h, buffer_ix, self.n_views, s))
-        self.ev_scatter_done[buffer_ix].record(st)
-        if wait:
-            check(self._lib.rcull_merge_wait(self._h, s))
+        if stream is None:
+            stream = self.torch.cuda.current_stream(self.device).cuda_stream
+        check(self._lib.rcull_merge_expand(self._h, self.C.c_void_p(stream)))
 
     def lists(self, view: int):
         """(cmds_ptr, visible_ptr, counts_ptr, totals_ptr) device addresses of the merged outputs."""
@@ -372,8 +351,8 @@ class PeerMerger:
         check(self._lib.rcull_merge_lists(self._h, view, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
         return a.value, b.value, c.value, d.value
 
-    def download(self, view: int):
-        """Blocking read-back of one merged view (tests)."""
+    def download(self, view: int, per_mesh: bool = False):
+        """Blocking read-back of one merged view (tests): cmds, visible, count, index total."""
         torch = self.torch
         from ._lib import CMD_DTYPE
 
@@ -383,6 +362,7 @@ class PeerMerger:
         counts = _wrap_device(torch, np_, mv, torch.int32, self.device).cpu().numpy().view(np.uint32)
         totals = _wrap_device(torch, tp, mv, torch.int64, self.device).cpu().numpy().view(np.uint64)
         n = int(min(counts[view], self.capacity))
+        n_vis = int(min(totals[view], self.capacity)) if per_mesh else n
         cmds = _wrap_device(torch, cp, max(n, 1) * 5, torch.int32, self.device).cpu().numpy()[: n * 5].view(CMD_DTYPE)
-        vis = _wrap_device(torch, vp, max(n, 1), torch.int32, self.device).cpu().numpy()[:n].view(np.uint32)
+        vis = _wrap_device(torch, vp, max(n_vis, 1), torch.int32, self.device).cpu().numpy()[:n_vis].view(np.uint32)
         return cmds, vis, int(counts[view]), int(totals[view])

@@ -345,72 +345,196 @@ def test_range_shards_merge_to_the_single_gpu_lists():
             c.destroy()
 
 
-def test_peer_store_merge_two_ranks_in_one_process():
-    """rcull_merge_* with world = 2 emulated in one process (peer pointers set directly):
-    after both ranks scatter, BOTH merged allocations equal the unsharded lists."""
+def _merged_rank_setup(shards, n_views, meshes, cap, cap_r, output_mode=None):
+    """world = len(shards) ranks emulated in ONE process on one GPU: a context + merge per rank, windows named to each
+    other directly (rcull_merge_set_peer_ptr).  Returns (contexts, merge handles)."""
+    import ctypes as C
+
+    from renderer_b200 import _lib
+
+    lib = _lib.load()
+    world = len(shards)
+    ctxs, merges, windows = [], [], []
+    kw = {} if output_mode is None else {"output_mode": output_mode}
+    for r, (lo, hi, ps, rot, mesh) in enumerate(shards):
+        c = CullContext(max(hi - lo, 1), max_views=n_views, max_meshes=len(meshes), **kw)
+        c.set_mesh_table(meshes)
+        c.upload_entities(ps[lo:hi], rot[lo:hi], mesh[lo:hi])
+        c.n = hi - lo
+        h = C.c_void_p()
+        _lib.check(lib.rcull_merge_create(c._h, world, r, cap, cap_r, C.byref(h)))
+        w = C.c_void_p()
+        _lib.check(lib.rcull_merge_window(h, C.byref(w)))
+        ctxs.append(c)
+        merges.append(h)
+        windows.append(w)
+    for h in merges:
+        for p in range(world):
+            _lib.check(lib.rcull_merge_set_peer_ptr(h, p, windows[p]))
+    return ctxs, merges
+
+
+def _merged_lists(h, k, n_views, per_mesh=False, cap=None):
     import ctypes as C
 
     import torch
 
     from renderer_b200 import _lib
-    from renderer_b200.shard import _wrap_device, shard_range
+    from renderer_b200._lib import CMD_DTYPE
+    from renderer_b200.shard import _wrap_device
+
+    lib, dev = _lib.load(), torch.device("cuda", 0)
+    a, b, c_, d = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+    _lib.check(lib.rcull_merge_lists(h, k, C.byref(a), C.byref(b), C.byref(c_), C.byref(d)))
+    torch.cuda.synchronize()
+    counts = _wrap_device(torch, c_.value, n_views, torch.int32, dev).cpu().numpy().view(np.uint32)
+    totals = _wrap_device(torch, d.value, n_views, torch.int64, dev).cpu().numpy().view(np.uint64)
+    n_cmd = int(counts[k]) if cap is None else min(int(counts[k]), cap)
+    n_vis = int(totals[k]) if per_mesh else n_cmd
+    cmds = _wrap_device(torch, a.value, max(n_cmd, 1) * 5, torch.int32, dev).cpu().numpy()[: n_cmd * 5].view(CMD_DTYPE)
+    vis = _wrap_device(torch, b.value, max(n_vis, 1), torch.int32, dev).cpu().numpy()[:n_vis].view(np.uint32)
+    return cmds, vis, int(counts[k]), int(totals[k])
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_record_merge_ranks_in_one_process(world):
+    """SURVEY 8e through the record path (rcull_merge_*): ragged range shards, every rank's frame kernel sends 8-byte
+    records into every window, every rank expands them -- the merged lists on EVERY rank are byte-identical to the
+    single-range oracle lists (firstIndex = running sum over the merged order, u32 wrap included).  Four frames, so
+    both record regions and the epoch tags are reused; one rank has an empty shard.  The ranks share one GPU here, so
+    all frames complete before any expand (no launch ever waits on another launch)."""
+    import torch
+
+    from renderer_b200 import _lib
+    from renderer_b200.shard import shard_range
 
     lib = _lib.load()
-    n, n_views, world = 150_003, 3, 2
+    n, n_views = 150_001, 3
     views = scene.scene_views(n_views)
-    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, 50.0)
-    with CullContext(n, max_views=n_views, max_meshes=len(MESHES)) as whole:
-        whole.set_mesh_table(MESHES)
-        whole.upload_entities(ps, rot, mesh)
-        whole.frame(views, scene.CAMERA_POS)
-        wc, wt = whole.counts()
-        want_cmds = [whole.cmds(k, int(wc[k])) for k in range(n_views)]
-        want_vis = [whole.visible(k, int(wc[k])) for k in range(n_views)]
-    cap = int(wc.max()) + 7
-    ctxs, merges = [], []
-    dev = torch.device("cuda", 0)
+    ctxs = merges = None
     try:
-        for r in range(world):
-            lo, hi = shard_range(n, world, r)
-            c = CullContext(hi - lo, max_views=n_views, max_meshes=len(MESHES))
-            c.set_mesh_table(MESHES)
-            c.upload_entities(ps[lo:hi], rot[lo:hi], mesh[lo:hi])
-            c.frame(views, scene.CAMERA_POS, draw_index_base=lo)
-            h = C.c_void_p()
-            _lib.check(lib.rcull_merge_create(c._h, world, r, cap, C.byref(h)))
-            ctxs.append(c), merges.append(h)
-        bases = []
+        for frame in range(4):
+            ps, rot, mesh = scene.synth_entities(scene.SEED + frame, 0, n, 70.0 + 10 * frame, len(MESHES))
+            pos, quat, scale = scene.to_components(ps, rot)
+            ref = O.frame(pos, quat, scale, mesh, MESHES, views, scene.CAMERA_POS, n_threads=8, want=("cmds", "visible"))
+            bounds = [shard_range(n, world, r) for r in range(world)]
+            if world == 3:  # rank 1 owns nothing
+                bounds = [(0, n // 3), (n // 3, n // 3), (n // 3, n)]
+            if ctxs is None:
+                shards = [(lo, hi, ps, rot, mesh) for lo, hi in bounds]
+                ctxs, merges = _merged_rank_setup(shards, n_views, MESHES, cap=n, cap_r=n)
+            else:
+                for c, (lo, hi) in zip(ctxs, bounds):
+                    if hi > lo:
+                        c.upload_entities(ps[lo:hi], rot[lo:hi], mesh[lo:hi])
+            for c, (lo, hi) in zip(ctxs, bounds):
+                c.frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+            torch.cuda.synchronize()
+            for h in merges:
+                _lib.check(lib.rcull_merge_expand(h, None))
+            torch.cuda.synchronize()
+            for h in merges:
+                for k in range(n_views):
+                    cmds, vis, cnt, tot = _merged_lists(h, k, n_views)
+                    assert cnt == int(ref["counts"][k]) and tot == int(ref["totals"][k]), (frame, k)
+                    assert np.array_equal(vis, ref["visible"][k]), (frame, k)
+                    assert np.array_equal(cmds, ref["cmds"][k]), (frame, k)
+        # protocol errors are loud: a third frame in flight, an expand with nothing to expand
+        with pytest.raises(RcullError, match="nothing|no merged frame"):
+            _lib.check(lib.rcull_merge_expand(merges[0], None))
+        lo, hi = bounds[0]
+        ctxs[0].frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+        ctxs[0].frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+        with pytest.raises(RcullError, match="in flight"):
+            ctxs[0].frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+        for c, (lo, hi) in list(zip(ctxs, bounds))[1:]:  # let the other ranks catch up so that teardown is clean
+            c.frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+            c.frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+        torch.cuda.synchronize()
+        for _ in range(2):
+            for h in merges:
+                _lib.check(lib.rcull_merge_expand(h, None))
+            torch.cuda.synchronize()
+    finally:
+        for h in merges or []:
+            lib.rcull_merge_destroy(h)
+        for c in ctxs or []:
+            c.destroy()
+
+
+def test_record_merge_clamps_to_the_capacities():
+    """capacity_per_rank and the merged capacity clamp WRITES; the merged counts still say how many survivors there were."""
+    import torch
+
+    from renderer_b200 import _lib
+    from renderer_b200.shard import shard_range
+
+    lib = _lib.load()
+    n, n_views, world = 60_000, 2, 2
+    views = scene.scene_views(n_views)
+    ps, rot, mesh = scene.synth_entities(scene.SEED, 0, n, 30.0, len(MESHES))
+    pos, quat, scale = scene.to_components(ps, rot)
+    ref = O.frame(pos, quat, scale, mesh, MESHES, views, scene.CAMERA_POS, n_threads=8, want=("cmds", "visible"))
+    bounds = [shard_range(n, world, r) for r in range(world)]
+    cap_r = 700
+    ctxs, merges = _merged_rank_setup([(lo, hi, ps, rot, mesh) for lo, hi in bounds], n_views, MESHES, cap=1000, cap_r=cap_r)
+    try:
+        for c, (lo, hi) in zip(ctxs, bounds):
+            c.frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+        torch.cuda.synchronize()
         for h in merges:
-            b = C.c_void_p()
-            _lib.check(lib.rcull_merge_base(h, C.byref(b)))
-            bases.append(b)
-        metas = []
-        for r, h in enumerate(merges):
-            for p in range(world):
-                _lib.check(lib.rcull_merge_set_peer_ptr(h, p, bases[p]))
-            _lib.check(lib.rcull_merge_pack_meta(h, 0, None))
-            a, b = C.c_void_p(), C.c_void_p()
-            _lib.check(lib.rcull_merge_meta_ptrs(h, C.byref(a), C.byref(b)))
-            metas.append((_wrap_device(torch, a.value, 2 * n_views, torch.int64, dev), _wrap_device(torch, b.value, world * 2 * n_views, torch.int64, dev)))
+            _lib.check(lib.rcull_merge_expand(h, None))
         torch.cuda.synchronize()
-        gathered = torch.cat([m[0] for m in metas])  # what the all_gather delivers
-        for m in metas:
-            m[1].copy_(gathered)
-        torch.cuda.synchronize()
+        k = 1
+        assert int(ref["counts"][k]) > 2 * cap_r
+        cmds, got, cnt, tot = _merged_lists(merges[0], k, n_views, cap=1000)
+        assert cnt == int(ref["counts"][k]) and tot == int(ref["totals"][k])
+        # what IS stored: the first cap_r survivors of rank 0, then the first survivors of rank 1, 1000 in all
+        v = ref["visible"][k]
+        r0 = v[v < bounds[0][1]][:cap_r]
+        r1 = v[v >= bounds[1][0]][: 1000 - len(r0)]
+        assert np.array_equal(got, np.concatenate([r0, r1]))
+        assert np.array_equal(cmds["firstInstance"], got)
+    finally:
         for h in merges:
-            _lib.check(lib.rcull_merge_scatter(h, 0, n_views, None))
-        torch.cuda.synchronize()
+            lib.rcull_merge_destroy(h)
+        for c in ctxs:
+            c.destroy()
+
+
+def test_record_merge_per_mesh_mode_two_ranks():
+    """RCULL_PER_MESH_INSTANCED over range shards, on the device: the ranks' (slot, draw_index) records are merged in
+    draw order by the expand and bucketed by the single-GPU counting sort -- commands (instanceCount summed over
+    ranks) and the bucketed visible list equal the single-range oracle's."""
+    import torch
+
+    from renderer_b200 import PER_MESH_INSTANCED, _lib
+    from renderer_b200.shard import shard_range
+
+    lib = _lib.load()
+    table, node_scale = scene.sponza_mesh_table()
+    n, n_views, world = 250_000, 2, 2
+    ps, rot, mesh = scene.sponza_instances(n, len(table), node_scale)
+    views = scene.scene_views(n_views)
+    pos, quat, scale = scene.to_components(ps, rot)
+    ref = O.frame(pos, quat, scale, mesh, table, views, scene.CAMERA_POS, n_threads=8, want=("flags",))
+    bounds = [shard_range(n, world, r) for r in range(world)]
+    ctxs, merges = _merged_rank_setup([(lo, hi, ps, rot, mesh) for lo, hi in bounds], n_views, table, cap=n, cap_r=n,
+                                      output_mode=PER_MESH_INSTANCED)
+    try:
+        for _ in range(2):
+            for c, (lo, hi) in zip(ctxs, bounds):
+                c.frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+            torch.cuda.synchronize()
+            for h in merges:
+                _lib.check(lib.rcull_merge_expand(h, None))
+            torch.cuda.synchronize()
         for h in merges:
             for k in range(n_views):
-                a, b, c_, d = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
-                _lib.check(lib.rcull_merge_lists(h, k, C.byref(a), C.byref(b), C.byref(c_), C.byref(d)))
-                counts = _wrap_device(torch, c_.value, n_views, torch.int32, dev).cpu().numpy().view(np.uint32)
-                totals = _wrap_device(torch, d.value, n_views, torch.int64, dev).cpu().numpy().view(np.uint64)
-                assert counts[k] == wc[k] and totals[k] == wt[k]
-                got = _wrap_device(torch, a.value, int(wc[k]) * 5, torch.int32, dev).cpu().numpy().view(np.uint32)
-                assert np.array_equal(got, want_cmds[k].view(np.uint32).reshape(-1)), k
-                got = _wrap_device(torch, b.value, int(wc[k]), torch.int32, dev).cpu().numpy().view(np.uint32)
-                assert np.array_equal(got, want_vis[k]), k
+                want_cmds, want_vis = O.emit_per_mesh(pos, mesh, ref["flags"][k], table, scene.CAMERA_POS, 10.0, 0)
+                cmds, vis, cnt, tot = _merged_lists(h, k, n_views, per_mesh=True)
+                assert cnt == len(want_cmds) and tot == len(want_vis), (k, cnt, len(want_cmds))
+                assert np.array_equal(cmds, want_cmds) and np.array_equal(vis, want_vis), k
     finally:
         for h in merges:
             lib.rcull_merge_destroy(h)
@@ -511,79 +635,6 @@ def test_frozen_culling_frame_updates_models_only():
         assert np.array_equal(counts0, counts1) and np.array_equal(totals0, totals1)
         for k in range(2):
             assert np.array_equal(ctx.cmds(k, int(counts0[k])), cmds0[k])
-
-
-def test_fused_exchange_two_ranks_in_one_process():
-    """rcull_merge_exchange with world = 2 emulated in one process on two streams: no collective call, the
-    kernels exchange their counts through the mailboxes and store into both allocations; three exchanges
-    in a row (mailbox parity slots, epoch tags, both output sets), each equal to the unsharded lists."""
-    import ctypes as C
-
-    import torch
-
-    from renderer_b200 import _lib
-    from renderer_b200.shard import _wrap_device, shard_range
-
-    lib = _lib.load()
-    n, n_views, world = 120_001, 2, 2
-    dev = torch.device("cuda", 0)
-    streams = [torch.cuda.Stream(device=dev) for _ in range(world)]
-    ctxs, merges = [], []
-    try:
-        for r in range(world):
-            lo, hi = shard_range(n, world, r)
-            c = CullContext(hi - lo, max_views=n_views, max_meshes=len(MESHES), n_buffers=2)
-            c.set_mesh_table(MESHES)
-            h = C.c_void_p()
-            _lib.check(lib.rcull_merge_create(c._h, world, r, n, C.byref(h)))
-            ctxs.append(c), merges.append(h)
-        bases = []
-        for h in merges:
-            b = C.c_void_p()
-            _lib.check(lib.rcull_merge_base(h, C.byref(b)))
-            bases.append(b)
-        for h in merges:
-            for p in range(world):
-                _lib.check(lib.rcull_merge_set_peer_ptr(h, p, bases[p]))
-        for it, (seed, half_box) in enumerate([(scene.SEED, 50.0), (scene.SEED + 7, 20.0), (scene.SEED + 9, 35.0)]):
-            views = scene.scene_views(n_views)
-            ps, rot, mesh = scene.synth_entities(seed, 0, n, half_box)
-            with CullContext(n, max_views=n_views, max_meshes=len(MESHES)) as whole:
-                whole.set_mesh_table(MESHES)
-                whole.upload_entities(ps, rot, mesh)
-                whole.frame(views, scene.CAMERA_POS)
-                wc, wt = whole.counts()
-                want_cmds = [whole.cmds(k, int(wc[k])) for k in range(n_views)]
-                want_vis = [whole.visible(k, int(wc[k])) for k in range(n_views)]
-            b = it & 1
-            for r, c in enumerate(ctxs):
-                lo, hi = shard_range(n, world, r)
-                c.upload_entities(ps[lo:hi], rot[lo:hi], mesh[lo:hi])
-                c.frame(views, scene.CAMERA_POS, draw_index_base=lo, buffer_ix=b, stream=streams[r].cuda_stream)
-            # both exchange kernels must be in flight together: two streams, and every exchange is enqueued
-            # before any wait (streams of one process can share a hardware queue: a wait queued ahead of
-            # the other rank's exchange would block it for good)
-            for r, h in enumerate(merges):
-                _lib.check(lib.rcull_merge_exchange(h, b, n_views, C.c_void_p(streams[r].cuda_stream)))
-            for r, h in enumerate(merges):
-                _lib.check(lib.rcull_merge_wait(h, C.c_void_p(streams[r].cuda_stream)))
-            torch.cuda.synchronize()
-            for h in merges:
-                for k in range(n_views):
-                    a, b_, c_, d = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
-                    _lib.check(lib.rcull_merge_lists(h, k, C.byref(a), C.byref(b_), C.byref(c_), C.byref(d)))
-                    counts = _wrap_device(torch, c_.value, n_views, torch.int32, dev).cpu().numpy().view(np.uint32)
-                    totals = _wrap_device(torch, d.value, n_views, torch.int64, dev).cpu().numpy().view(np.uint64)
-                    assert counts[k] == wc[k] and totals[k] == wt[k], (it, k)
-                    got = _wrap_device(torch, a.value, max(int(wc[k]), 1) * 5, torch.int32, dev).cpu().numpy().view(np.uint32)[: int(wc[k]) * 5]
-                    assert np.array_equal(got, want_cmds[k].view(np.uint32).reshape(-1)), (it, k)
-                    got = _wrap_device(torch, b_.value, max(int(wc[k]), 1), torch.int32, dev).cpu().numpy().view(np.uint32)[: int(wc[k])]
-                    assert np.array_equal(got, want_vis[k]), (it, k)
-    finally:
-        for h in merges:
-            lib.rcull_merge_destroy(h)
-        for c in ctxs:
-            c.destroy()
 
 
 # ---- round 2: host-path ordering, frozen frames across output sets, loud errors ---------------------
