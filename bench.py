@@ -248,7 +248,9 @@ def gpu_arm(args, wl):
         dist.all_reduce(c_max, op=dist.ReduceOp.MAX)
         cap = int(c_sum.max().item() * 1.05) + 1024
         cap_r = int(c_max.max().item() * 1.05) + 1024
-        merger = RecordMerger(ctx, cap, cap_r, dev, symmetric=args.multicast) if args.merge == "p2p" else ShardMerger(n_views, cap, dev)
+        # transport: windows in torch symmetric memory with an NVLS multicast mapping when the fabric offers one (a record
+        # then leaves the GPU once; measured equal to or better than one peer store per rank at N = 2 and 4), else CUDA IPC
+        merger = RecordMerger(ctx, cap, cap_r, dev, symmetric=args.transport != "ipc") if args.merge == "p2p" else ShardMerger(n_views, cap, dev)
         if beside:
             merger.set_overlap(args.expand_sms)
     # expand beside the next frame: the chip is split -- the frame kernel's grid leaves expand_sms SMs, the expand's CTAs
@@ -745,7 +747,7 @@ def main():
     ap.add_argument("--merge", default="p2p", choices=["p2p", "nccl"], help="N > 1: peer-store merge kernel or NCCL broadcasts")
     ap.add_argument("--pipeline", action="store_true", help="N > 1: queue the expand of frame i behind frame i + 1 instead of frame, expand, frame, expand (measured slower: with two record regions the next frame then waits for the peers' expand of the frame before)")
     ap.add_argument("--expand-sms", type=int, default=0, help="N > 1: > 0 splits the chip -- the frame kernel leaves that many SMs to the expand of the previous frame, which runs beside it on a second stream; 0: the expand runs between frames")
-    ap.add_argument("--multicast", action="store_true", help="N > 1: windows in torch symmetric memory, records leave through the NVLS multicast mapping (default: CUDA IPC peer stores)")
+    ap.add_argument("--transport", default="auto", choices=["auto", "ipc"], help="N > 1: auto = windows in torch symmetric memory, records through the NVLS multicast mapping when there is one (falls back to CUDA IPC peer stores); ipc = CUDA IPC peer stores")
     ap.add_argument("--no-verify", action="store_true", help="N > 1: skip the oracle / NCCL verification of the merged lists")
     ap.add_argument("--workload", default="16m_5view", choices=sorted(WORKLOADS))
     ap.add_argument("--no-also", action="store_true", help="N = 1: skip the resident timings of the other entity-stage workloads")

@@ -12,10 +12,10 @@ try:
 except Exception as e:
     print(' no line:', e)
 "; }
-run ipc
+run auto
 [ -n "$QUICK" ] || run ipc_pipeline --pipeline --no-verify
 [ -n "$QUICK" ] || run split --expand-sms ${SPLIT:-8} --no-verify
-[ -n "$QUICK" ] || run mc --multicast --no-verify
+[ -n "$QUICK" ] || run ipc --transport ipc --no-verify
 [ -n "$QUICK" ] || run nccl --merge nccl
 timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu --no-also > gpurun_out/n${NG}_n1.log 2>&1; tail -1 gpurun_out/n${NG}_n1.log | python -c "
 import sys, json

@@ -134,6 +134,7 @@ struct rcull_ctx {
     bool set_frozen[3] = {false, false, false};  // the last call on set j was rcull_frame_frozen
     uint32_t* h_error = nullptr;         // pinned: device error word read back by rcull_frame_host
     uint4* instances = nullptr;          // F4: VkAccelerationStructureInstanceKHR [cap]
+    CUtensorMap instances_map;           // the instance buffer as [cap/2 rows][32 floats], like OutputSet.model_map
     std::vector<void*> allocs;
 };
 
@@ -781,7 +782,7 @@ int rcull_frame_frozen(rcull_ctx* c, uint64_t n, uint32_t buffer_ix, void* strea
     c->set_frozen[buffer_ix] = buffer_ix != c->lists_ix;  // the lists of this set are now those of set lists_ix
     if (n == 0) return RCULL_OK;
     CU(cudaSetDevice(c->cfg.device));
-    model_only<<<c->sm_count * 8, 256, 0, (cudaStream_t)stream>>>(c->pos_scale, c->rot, (uint32_t)n, c->out[buffer_ix].model);
+    model_only<<<c->sm_count * 8, kRecordWarps * 32, 0, (cudaStream_t)stream>>>(c->pos_scale, c->rot, (uint32_t)n, c->out[buffer_ix].model_map);
     CU(cudaGetLastError());
     c->launches += 1;
     return RCULL_OK;
@@ -818,6 +819,8 @@ int rcull_set_blas_table(rcull_ctx* c, const uint64_t* blas, uint32_t n) {
         if (rc) return rc;
         rc = dev_alloc(c, &c->instances, c->cap * 4);
         if (rc) return rc;
+        rc = make_model_map(&c->instances_map, reinterpret_cast<float4*>(c->instances), c->cap);  // same shape as a model buffer: 64-byte records
+        if (rc) return rc;
     }
     CU(cudaDeviceSynchronize());
     CU(cudaMemcpy(c->blas, blas, (size_t)n * 8, cudaMemcpyHostToDevice));
@@ -835,8 +838,8 @@ int rcull_as_instances(rcull_ctx* c, uint64_t n, uint32_t draw_index_base, uint3
     if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
     if (n == 0) return RCULL_OK;
     CU(cudaSetDevice(c->cfg.device));
-    as_instances<<<c->sm_count * 8, 256, 0, (cudaStream_t)stream>>>(c->out[buffer_ix].model, c->mesh, c->blas, c->n_meshes, (uint32_t)n,
-                                                                    draw_index_base, c->instances);
+    as_instances<<<c->sm_count * 8, kRecordWarps * 32, 0, (cudaStream_t)stream>>>(c->out[buffer_ix].model, c->mesh, c->blas, c->n_meshes, (uint32_t)n,
+                                                                                  draw_index_base, c->instances_map);
     CU(cudaGetLastError());
     c->launches += 1;
     return RCULL_OK;

@@ -797,3 +797,40 @@ def test_packed_sum_plane_tests_fall_back_on_tiny_factors():
         for k in range(3):
             assert np.array_equal(ctx.flags(k, n), ref["flags"][k])
             assert np.array_equal(ctx.visible(k, int(counts[k])), ref["visible"][k])
+
+
+def test_repeatability_stress_ragged_frames():
+    """compute-sanitizer is closed on this pool (profiles/r02_sanitizer_closed.txt), so the race evidence for the
+    look-back descriptors, the mbarrier rings and the deferred emission is behavioural: 240 frames of ragged sizes on one
+    context (epoch / ticket / ring reuse, every tile-count residue of the persistent grid), every frame's counts,
+    index totals and a digest of all five lists equal to the oracle's -- a lost update, a stale descriptor or an early
+    read would show up as a wrong list in at least one of them."""
+    import hashlib
+
+    n_max, n_views = 400_000, 5
+    views = scene.scene_views(n_views)
+    ps, rot, mesh = scene.synth_entities(scene.SEED + 77, 0, n_max, 150.0, len(MESHES))
+    pos, quat, scale = scene.to_components(ps, rot)
+    sizes = [n_max, 1, 1919, 1920, 1921, 148 * 1920, 148 * 1920 + 1, 200_003, 77_777, 399_999, 31, 5 * 1920 - 1]
+    want = {}
+    for n in sizes:
+        ref = O.frame(pos[:n], quat[:n], scale[:n], mesh[:n], MESHES, views, scene.CAMERA_POS, n_threads=8, want=("cmds", "visible"))
+        h = hashlib.sha256()
+        for k in range(n_views):
+            h.update(ref["visible"][k].tobytes())
+            h.update(ref["cmds"][k].tobytes())
+        want[n] = (ref["counts"].copy(), ref["totals"].copy(), h.hexdigest())
+    with CullContext(n_max, max_views=n_views, max_meshes=len(MESHES)) as ctx:
+        ctx.set_mesh_table(MESHES)
+        ctx.upload_entities(ps, rot, mesh)
+        for it in range(240):
+            n = sizes[it % len(sizes)]
+            ctx.frame(views, scene.CAMERA_POS, n=n)
+            if it % 3 == 2:  # back-to-back launches without a host sync in between, then a checked one
+                counts, totals = ctx.counts()
+                assert np.array_equal(counts[:n_views], want[n][0]) and np.array_equal(totals[:n_views], want[n][1]), (it, n)
+                h = hashlib.sha256()
+                for k in range(n_views):
+                    h.update(ctx.visible(k, int(counts[k])).tobytes())
+                    h.update(ctx.cmds(k, int(counts[k])).tobytes())
+                assert h.hexdigest() == want[n][2], (it, n)
