@@ -304,6 +304,38 @@ int rcull_merge_expand(rcull_merge *m, void *stream);
 int rcull_merge_lists(rcull_merge *m, uint32_t view, rcull_draw_cmd **cmds, uint32_t **visible,
                       uint32_t **counts, uint64_t **index_totals);
 
+/* Blocking copy for tests and hosts without CUDA code of their own: the merged count and index total of
+ * one view, and (pointers not NULL) the first n commands / visible entries (per-mesh mode: n commands and
+ * n visible entries as far as each list goes). */
+int rcull_merge_download(rcull_merge *m, uint32_t view, uint32_t *count, uint64_t *index_total,
+                         rcull_draw_cmd *cmds, uint32_t *visible, uint64_t n);
+
+/* ---- Single-process multi-GPU bootstrap (rcull_mgpu.cpp) ---------------------------------------
+ * The reference's caller is ONE process stepping one schedule per frame (src/main.rs:907-910).
+ * rcull_mgpu_create stands up n_gpus ranks for such a host without Python, torch or NCCL: one context
+ * (cfg with device = devices[r], or r when devices is NULL) and one merge per GPU, every window
+ * mapped into every device (peer access), and -- use_multicast != 0 and the driver offers it -- the
+ * windows allocated with the virtual-memory API and bound to an NVLS multicast object
+ * (cuMulticastCreate), whose mapping becomes rcull_merge_set_multicast_ptr.  Falls back to plain peer
+ * pointers; rcull_mgpu_transport says which path is live.  Multi-PROCESS hosts exchange
+ * rcull_merge_ipc_handle blobs over their own transport instead (renderer_b200/shard.py does it with
+ * torch.distributed). */
+typedef struct rcull_mgpu rcull_mgpu;
+int rcull_mgpu_create(const rcull_config *cfg, uint32_t n_gpus, const int32_t *devices, uint64_t capacity,
+                      uint64_t capacity_per_rank, uint32_t use_multicast, rcull_mgpu **out);
+void rcull_mgpu_destroy(rcull_mgpu *g);
+/* The context, merge and stream of one rank (upload its shard with rcull_upload_entities, read its
+ * merged lists with rcull_merge_lists). */
+int rcull_mgpu_rank(rcull_mgpu *g, uint32_t rank, rcull_ctx **ctx, rcull_merge **merge, void **stream);
+const char *rcull_mgpu_transport(rcull_mgpu *g);
+const char *rcull_mgpu_last_error(void);
+/* One merged frame on every rank: rank r culls entities [0, n[r]) of its shard with
+ * draw_index_base[r], then every rank expands; asynchronous (each rank's own stream).  Every rank's
+ * frame is enqueued before any rank's expand. */
+int rcull_mgpu_frame(rcull_mgpu *g, const uint64_t *n, const uint32_t *draw_index_base, const rcull_view *views,
+                     uint32_t n_views, const float cam_pos[3]);
+int rcull_mgpu_synchronize(rcull_mgpu *g);
+
 /* Harness utility: fills the input columns on the device with the counter-based
  * synthetic scene (entity i of the global scene = first_global + slot), bit-
  * identical to renderer_b200/scene.py; avoids shipping 128 M entities from host. */

@@ -203,6 +203,102 @@ inline void gpu_as_instances(RcullRes& rc, ImageIndex image_index, uint32_t draw
     expect(rcull_as_instances(rc.ctx(), rc.n_entities, draw_index_base, image_index.ix, rc.stream()), "rcull_as_instances");
 }
 
+// ---- range shards over several GPUs of one process ---------------------------------
+// The same stage with the query's entities split into contiguous ranges, one per GPU: every GPU culls its range, the
+// frame kernels send their survivors to every GPU as 8-byte records, every GPU expands them into the merged draw
+// lists -- byte-identical on every GPU to what one GPU would have produced (rcull_mgpu_*, rcull_merge_* in rcull.h).
+class MultiGpuRes {
+  public:
+    MultiGpuRes(const rcull_config& cfg, uint32_t n_gpus, uint64_t merged_capacity, uint64_t capacity_per_rank = 0, bool multicast = true)
+        : n_gpus_(n_gpus) {
+        if (rcull_mgpu_create(&cfg, n_gpus, nullptr, merged_capacity, capacity_per_rank, multicast ? 1u : 0u, &g_) != RCULL_OK)
+            panic(std::string("rcull_mgpu_create: ") + rcull_mgpu_last_error());
+    }
+    ~MultiGpuRes() { destroy(); }
+    MultiGpuRes(const MultiGpuRes&) = delete;
+    MultiGpuRes& operator=(const MultiGpuRes&) = delete;
+    void destroy() {
+        if (g_) rcull_mgpu_destroy(g_);
+        g_ = nullptr;
+    }
+    uint32_t n_gpus() const { return n_gpus_; }
+    rcull_mgpu* handle() const { return g_; }
+    rcull_ctx* ctx(uint32_t rank) const {
+        rcull_ctx* c = nullptr;
+        expect(rcull_mgpu_rank(g_, rank, &c, nullptr, nullptr), "rcull_mgpu_rank");
+        return c;
+    }
+    rcull_merge* merge(uint32_t rank) const {
+        rcull_merge* m = nullptr;
+        expect(rcull_mgpu_rank(g_, rank, nullptr, &m, nullptr), "rcull_mgpu_rank");
+        return m;
+    }
+    void* stream(uint32_t rank) const {
+        void* s = nullptr;
+        expect(rcull_mgpu_rank(g_, rank, nullptr, nullptr, &s), "rcull_mgpu_rank");
+        return s;
+    }
+    void set_mesh_table(const MeshTable& t) {
+        for (uint32_t r = 0; r < n_gpus_; ++r)
+            expect(rcull_set_mesh_table(ctx(r), t.rows.data(), static_cast<uint32_t>(t.rows.size())), "rcull_set_mesh_table");
+    }
+    std::vector<float> pos_scale, rot;  // staging columns (all ranks, entity order)
+    std::vector<uint32_t> mesh;
+
+  private:
+    uint32_t n_gpus_ = 0;
+    rcull_mgpu* g_ = nullptr;
+};
+
+// Contiguous range of rank r: [n * r / world, n * (r + 1) / world).
+inline uint64_t shard_begin(uint64_t n, uint32_t world, uint32_t rank) { return n * rank / world; }
+
+// gpu_transform_cull over range shards: rank r gets entities [shard_begin(r), shard_begin(r + 1)) with
+// draw_index_base = shard_begin(r); asynchronous -- mg.synchronize-style waits are the caller's (download_merged does).
+inline void gpu_transform_cull_sharded(MultiGpuRes& mg, const Camera& camera, const std::vector<Light>& lights, const Position* position,
+                                       const Rotation* rotation, const Scale* scale, const GltfMesh* gltf_mesh, uint64_t n_entities) {
+    mg.pos_scale.resize(4 * n_entities);
+    mg.rot.resize(4 * n_entities);
+    mg.mesh.resize(n_entities);
+    expect(rcull_pack_components(n_entities, reinterpret_cast<const float*>(position), reinterpret_cast<const float*>(rotation),
+                                 reinterpret_cast<const float*>(scale), mg.pos_scale.data(), mg.rot.data()),
+           "rcull_pack_components");
+    for (uint64_t e = 0; e < n_entities; ++e) mg.mesh[e] = gltf_mesh[e].table_row;
+    std::vector<rcull_view> views;
+    views.push_back(camera.frustum_planes);
+    for (const Light& l : lights) views.push_back(light_frustum(l));
+    std::vector<uint64_t> n(mg.n_gpus());
+    std::vector<uint32_t> base(mg.n_gpus());
+    for (uint32_t r = 0; r < mg.n_gpus(); ++r) {
+        const uint64_t lo = shard_begin(n_entities, mg.n_gpus(), r), hi = shard_begin(n_entities, mg.n_gpus(), r + 1);
+        n[r] = hi - lo;
+        base[r] = static_cast<uint32_t>(lo);
+        expect(rcull_upload_entities(mg.ctx(r), 0, n[r], mg.pos_scale.data() + 4 * lo, mg.rot.data() + 4 * lo, mg.mesh.data() + lo, mg.stream(r)),
+               "rcull_upload_entities");
+    }
+    if (rcull_mgpu_frame(mg.handle(), n.data(), base.data(), views.data(), static_cast<uint32_t>(views.size()), camera.position) != RCULL_OK)
+        panic(std::string("rcull_mgpu_frame: ") + rcull_mgpu_last_error());
+}
+
+// The merged draw list of one view as one rank holds it (blocking).
+struct MergedList {
+    uint32_t count = 0;
+    uint64_t index_total = 0;
+    std::vector<rcull_draw_cmd> commands;
+    std::vector<DrawIndex> visible;
+};
+inline MergedList download_merged(MultiGpuRes& mg, uint32_t rank, uint32_t view) {
+    if (rcull_mgpu_synchronize(mg.handle()) != RCULL_OK) panic(std::string("rcull_mgpu_synchronize: ") + rcull_mgpu_last_error());
+    MergedList out;
+    expect(rcull_merge_download(mg.merge(rank), view, &out.count, &out.index_total, nullptr, nullptr, 0), "rcull_merge_download");
+    out.commands.resize(out.count);
+    out.visible.resize(out.count);
+    if (out.count)
+        expect(rcull_merge_download(mg.merge(rank), view, &out.count, &out.index_total, out.commands.data(), &out.visible[0].ix, out.count),
+               "rcull_merge_download");
+    return out;
+}
+
 // ---- read-back (tests, debug_aabb-style consumers; blocking) -----------------------------------
 inline std::vector<ModelMatrix> download_model(RcullRes& rc, ImageIndex ix) {
     std::vector<ModelMatrix> out(rc.n_entities);

@@ -136,6 +136,14 @@ SYMBOLS = {
     "rcull_merge_set_overlap": (C.c_int, [_P, _u32]),
     "rcull_merge_expand": (C.c_int, [_P, _P]),
     "rcull_merge_lists": (C.c_int, [_P, _u32, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)]),
+    "rcull_merge_download": (C.c_int, [_P, _u32, _P, _P, _P, _P, _u64]),
+    "rcull_mgpu_create": (C.c_int, [C.POINTER(Config), _u32, _P, _u64, _u64, _u32, C.POINTER(_P)]),
+    "rcull_mgpu_destroy": (None, [_P]),
+    "rcull_mgpu_rank": (C.c_int, [_P, _u32, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)]),
+    "rcull_mgpu_transport": (C.c_char_p, [_P]),
+    "rcull_mgpu_last_error": (C.c_char_p, []),
+    "rcull_mgpu_frame": (C.c_int, [_P, _P, _P, _P, _u32, _P]),
+    "rcull_mgpu_synchronize": (C.c_int, [_P]),
     "rcull_synth_entities": (C.c_int, [_P, _u64, _u64, _u64, _f, _u32, _P]),
     "rcull_launch_count": (_u64, [_P]),
     "rcull_frustum_planes": (None, [_P, C.POINTER(View)]),

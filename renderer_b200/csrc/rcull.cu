@@ -1299,4 +1299,24 @@ int rcull_merge_lists(rcull_merge* m, uint32_t view, rcull_draw_cmd** cmds, uint
     return RCULL_OK;
 }
 
+int rcull_merge_download(rcull_merge* m, uint32_t view, uint32_t* count, uint64_t* index_total, rcull_draw_cmd* cmds, uint32_t* visible,
+                         uint64_t n) {
+    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_download: null argument");
+    const uint32_t mv = m->ctx->cfg.max_views;
+    if (view >= mv) return fail(RCULL_ERR_INVALID, "view %u of %u", view, mv);
+    CU(cudaSetDevice(m->ctx->cfg.device));
+    CU(cudaDeviceSynchronize());
+    uint32_t c[kMaxViews];
+    unsigned long long t[kMaxViews];
+    CU(cudaMemcpy(c, m->counts, sizeof c, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(t, m->totals, sizeof t, cudaMemcpyDeviceToHost));
+    if (count) *count = c[view];
+    if (index_total) *index_total = t[view];
+    const bool per_mesh = m->ctx->cfg.output_mode == RCULL_PER_MESH_INSTANCED;
+    const uint64_t have_cmds = per_mesh ? (uint64_t)m->ctx->cfg.max_meshes * kMaxLods : m->cap;
+    if (cmds && n) CU(cudaMemcpy(cmds, m->cmds[view], (n < have_cmds ? n : have_cmds) * 20, cudaMemcpyDeviceToHost));
+    if (visible && n) CU(cudaMemcpy(visible, m->visible[view], (n < m->cap ? n : m->cap) * 4, cudaMemcpyDeviceToHost));
+    return RCULL_OK;
+}
+
 }  // extern "C"

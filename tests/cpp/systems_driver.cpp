@@ -6,6 +6,7 @@
 //   systems_driver planes <scene> <result>    host-only: camera + light frusta (no CUDA device needed)
 //   systems_driver frame  <scene> <result>    the full stage through librcull.so (panics without a GPU)
 //   systems_driver stage2 <scene> <result>    camera view only, then gpu_cull_triangles + gpu_as_instances
+//   systems_driver mgpu<N> <scene> <result>   N = 1..8 GPUs of this process: range shards, record merge, every rank's merged lists
 //
 // Scene file (little endian): u64 n, u32 n_meshes, u32 n_lights, u32 draw_index_base, f32 aspect,
 // f32 lod_distance, Camera position[3] rotation[4], Light[n_lights] (position[3], rotation[4]),
@@ -13,6 +14,8 @@
 // Result file: u32 n_views, u32 counts[8], u64 index_totals[8], rcull_view[n_views]; then for `frame`:
 // ModelMatrix[n], AABB[n], per view: CoarseCulled[n], rcull_draw_cmd[count], DrawIndex[count];
 // ModelMatrix[n] after a frozen frame over entities whose Scale was doubled, u32 counts[8] after it.
+// `mgpu<N>` result: u32 n_views, u32 n_gpus, the transport string (u32 length + bytes), then per rank and view: u32 count,
+// u64 index_total, rcull_draw_cmd[count], DrawIndex[count] (two frames are run; the second one's lists are written).
 // `stage2` scenes continue with: u64 n_vertices, u64 n_indices, u64 capacity_tri_indices, f32 positions[3 * n_vertices],
 // u32 indices[n_indices], u64 blas[n_meshes]; its result: u32 n_views (= 1), u32 counts[8], u64 index_totals[8],
 // f32 pv[16], u32 tri_count, u64 kept_indices, rcull_draw_cmd[tri_count], u32 culled_indices[index_totals[0]],
@@ -100,8 +103,9 @@ Scene load(const char* path, bool stage2) {
 }  // namespace
 
 int main(int argc, char** argv) {
-    if (argc != 4 || (std::strcmp(argv[1], "planes") && std::strcmp(argv[1], "frame") && std::strcmp(argv[1], "stage2"))) {
-        std::fprintf(stderr, "usage: %s planes|frame|stage2 <scene> <result>\n", argv[0]);
+    const bool mgpu = argc == 4 && !std::strncmp(argv[1], "mgpu", 4) && argv[1][4] >= '1' && argv[1][4] <= '8' && !argv[1][5];
+    if (argc != 4 || (!mgpu && std::strcmp(argv[1], "planes") && std::strcmp(argv[1], "frame") && std::strcmp(argv[1], "stage2"))) {
+        std::fprintf(stderr, "usage: %s planes|frame|stage2|mgpu<N> <scene> <result>\n", argv[0]);
         return 2;
     }
     const bool stage2 = !std::strcmp(argv[1], "stage2");
@@ -112,6 +116,39 @@ int main(int argc, char** argv) {
 
     std::ofstream out(argv[3], std::ios::binary);
     if (!out) panic(std::string("cannot create ") + argv[3]);
+
+    if (mgpu) {
+        const uint32_t n_gpus = static_cast<uint32_t>(argv[1][4] - '0');
+        rcull_config cfg;
+        std::memset(&cfg, 0, sizeof cfg);
+        cfg.max_views = n_views;
+        cfg.capacity_entities = s.n ? s.n : 1;  // any rank could own everything
+        cfg.max_meshes = s.n_meshes;
+        cfg.output_mode = RCULL_PER_ENTITY;
+        cfg.n_buffers = 1;
+        cfg.lod_distance = s.lod_distance;
+        MultiGpuRes mg(cfg, n_gpus, s.n ? s.n : 1);  // panics without n_gpus CUDA devices
+        mg.set_mesh_table(s.meshes);
+        for (int frame = 0; frame < 2; ++frame)  // twice: both record regions, tags reused
+            gpu_transform_cull_sharded(mg, s.camera, s.lights, s.position.data(), s.rotation.data(), s.scale.data(), s.gltf_mesh.data(), s.n);
+        put(out, &n_views);
+        put(out, &n_gpus);
+        const std::string transport = rcull_mgpu_transport(mg.handle());
+        const uint32_t tl = static_cast<uint32_t>(transport.size());
+        put(out, &tl);
+        put(out, transport.data(), tl);
+        for (uint32_t r = 0; r < n_gpus; ++r)
+            for (uint32_t v = 0; v < n_views; ++v) {
+                const MergedList m = download_merged(mg, r, v);
+                put(out, &m.count);
+                put(out, &m.index_total);
+                put(out, m.commands.data(), m.commands.size());
+                put(out, m.visible.data(), m.visible.size());
+            }
+        mg.destroy();
+        out.flush();
+        return out.good() ? 0 : 1;
+    }
 
     if (stage2) {
         rcull_config cfg;

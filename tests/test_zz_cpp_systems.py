@@ -211,3 +211,58 @@ def test_gpu_cull_triangles_and_as_instances_systems_match_oracle(driver, tmp_pa
     assert np.array_equal(instances["transform"], want_inst["transform"])  # == on floats, like the model matrices
     for field in ("custom_index_and_mask", "sbt_offset_and_flags", "blas"):
         assert np.array_equal(instances[field], want_inst[field]), field
+
+
+def _read_mgpu_result(path, n_views):
+    from renderer_b200._lib import CMD_DTYPE
+
+    b = open(path, "rb").read()
+    v, n_gpus, tl = struct.unpack_from("<III", b, 0)
+    assert v == n_views
+    transport = b[12 : 12 + tl].decode()
+    off = 12 + tl
+    ranks = []
+    for _ in range(n_gpus):
+        views = []
+        for _ in range(n_views):
+            count, total = struct.unpack_from("<IQ", b, off)
+            off += 12
+            cmds = np.frombuffer(b, CMD_DTYPE, count, off)
+            off += 20 * count
+            vis = np.frombuffer(b, "<u4", count, off)
+            off += 4 * count
+            views.append((count, total, cmds, vis))
+        ranks.append(views)
+    assert off == len(b)
+    return transport, ranks
+
+
+def _gpu_count():
+    try:
+        import torch
+
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_gpus,n,n_lights", [(1, 40_000, 2), (2, 120_001, 4), (2, 3, 0), (4, 200_000, 1), (8, 300_007, 4)])
+def test_sharded_system_over_the_gpus_of_one_process_matches_oracle(driver, tmp_path, n_gpus, n, n_lights):
+    """SURVEY 8e without Python in the data plane: the C++ host stands up n_gpus ranks in ONE process through
+    rcull_mgpu_create (peer access, NVLS multicast when the driver offers it), shards the query by contiguous range,
+    runs two merged frames, and every rank's merged lists are bit-equal to the single-range oracle's."""
+    if _gpu_count() < n_gpus:
+        pytest.skip(f"needs {n_gpus} GPUs")
+    pos, quat, scale, mesh = O.synth_entities(scene.SEED, 0, n, 80.0, len(MESHES))
+    write_scene(tmp_path / "s.bin", pos, quat, scale, mesh, MESHES, n_lights)
+    subprocess.check_call([driver, f"mgpu{n_gpus}", str(tmp_path / "s.bin"), str(tmp_path / "r.bin")], timeout=300)
+    v = 1 + n_lights
+    transport, ranks = _read_mgpu_result(tmp_path / "r.bin", v)
+    assert len(ranks) == n_gpus and transport
+    ref = O.frame(pos, quat, scale, mesh, MESHES, scene.scene_views(v), scene.CAMERA_POS, n_threads=8, want=("cmds", "visible"))
+    for r in range(n_gpus):
+        for k in range(v):
+            count, total, cmds, vis = ranks[r][k]
+            assert count == int(ref["counts"][k]) and total == int(ref["totals"][k]), (r, k)
+            assert np.array_equal(vis, ref["visible"][k]) and np.array_equal(cmds, ref["cmds"][k]), (r, k, transport)
