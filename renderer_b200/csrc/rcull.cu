@@ -76,7 +76,7 @@ struct OutputSet {
     uint32_t* vis_tmp[kMaxViews] = {};  // per-mesh mode: draw_index of every survivor before bucketing
     uint32_t* counts = nullptr;
     unsigned long long* totals = nullptr;
-    uint32_t* src_first = nullptr;  // triangle stage: indexOffset of every camera-view command
+    uint32_t* src_slot = nullptr;  // triangle stage: (mesh, lod) slot of every camera-view command
     CUtensorMap model_map;  // model buffer as [cap/2 rows][32 floats], 16-row boxes, 128-B swizzle
 };
 
@@ -119,6 +119,14 @@ struct rcull_ctx {
     float* positions = nullptr;
     uint32_t* indices = nullptr;
     uint64_t n_vertices = 0, n_indices = 0;
+    // chunk table of the triangle stage (rcull_tri.cuh): built on the host from the index buffer and the mesh table
+    std::vector<rcull_mesh> h_meshes;
+    std::vector<uint32_t> h_indices;
+    bool chunks_dirty = true;
+    uint2* slot_chunks = nullptr;
+    uint4* chunks = nullptr;
+    uint32_t n_chunks = 0;
+    bool any_window_slot = false, any_gather_slot = false;  // which of the two tri_cull kernels has anything to do
     uint32_t* tri_cmds = nullptr;
     uint32_t* tri_count = nullptr;
     uint64_t* tri_kept = nullptr;
@@ -232,6 +240,8 @@ void rcull_destroy(rcull_ctx* c) {
     for (void* p : c->allocs) cudaFree(p);
     if (c->positions) cudaFree(c->positions);
     if (c->indices) cudaFree(c->indices);
+    if (c->slot_chunks) cudaFree(c->slot_chunks);
+    if (c->chunks) cudaFree(c->chunks);
     if (c->h_counts) cudaFreeHost(c->h_counts);
     if (c->h_totals) cudaFreeHost(c->h_totals);
     if (c->h_error) cudaFreeHost(c->h_error);
@@ -300,7 +310,7 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
                 TRY(dev_alloc(c, &o.vis_tmp[v], c->cap_vis));
             }
         }
-        if (cfg->capacity_tri_indices) TRY(dev_alloc(c, &o.src_first, c->cap_vis));
+        if (cfg->capacity_tri_indices) TRY(dev_alloc(c, &o.src_slot, c->cap_vis));
         TRY(dev_alloc(c, &o.counts, kMaxViews));
         TRY(dev_alloc(c, &o.totals, kMaxViews));
         cudaMemset(o.counts, 0, kMaxViews * 4);
@@ -408,6 +418,10 @@ int rcull_set_mesh_table(rcull_ctx* c, const rcull_mesh* meshes, uint32_t n) {
     CU(cudaMemcpy(c->mesh_len1, len1.data(), len1.size() * 4, cudaMemcpyHostToDevice));
     c->n_meshes = n;
     c->len_small = max_len < (1u << 25) ? 1u : 0u;
+    if (c->cfg.capacity_tri_indices) {
+        c->h_meshes.assign(meshes, meshes + n);
+        c->chunks_dirty = true;
+    }
     return RCULL_OK;
 }
 
@@ -524,7 +538,7 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
                 if (!(f == 0.f || f >= kFtzSafe)) a.planes_ftz_safe = 0u;  // tiny, or NaN
             }
     if (getenv("RCULL_NO_PACKED_SUMS")) a.planes_ftz_safe = 0u;  // A/B switch: the scalar-sum body for every tile
-    a.src_first = o.src_first;
+    a.src_slot = o.src_slot;
     a.counts = o.counts;
     a.totals = o.totals;
     if (c->merge) {
@@ -878,6 +892,84 @@ int rcull_set_geometry(rcull_ctx* c, const float* positions, uint64_t n_vertices
     CU(cudaMemcpy(c->indices, indices, n_indices * 4, cudaMemcpyHostToDevice));
     c->n_vertices = n_vertices;
     c->n_indices = n_indices;
+    c->h_indices.assign(indices, indices + n_indices);
+    c->chunks_dirty = true;
+    return RCULL_OK;
+}
+
+// Chunk table of the triangle stage: every LOD's triangle list cut into runs of 256-triangle steps whose indices stay
+// inside a window of at most kTriVertCap vertices (those runs get their window transformed once into shared memory);
+// a step with a wider window -- random index triples -- becomes a chunk of its own on the gather path (v_count = 0).
+static int build_tri_chunks(rcull_ctx* c) {
+    const uint32_t n_slots = c->n_meshes * kMaxLods;
+    std::vector<uint2> sc(n_slots, make_uint2(0, 0));
+    std::vector<uint4> ch;
+    bool any_window = false, any_gather = false;
+    const uint32_t kStep = kTriThreads * kTriItems;
+    for (uint32_t m = 0; m < c->n_meshes && m < c->h_meshes.size(); ++m) {
+        const rcull_mesh& mesh = c->h_meshes[m];
+        for (uint32_t l = 0; l < mesh.n_lods && l < (uint32_t)kMaxLods; ++l) {
+            const uint64_t first = mesh.lod[l].first_index / 3u, n_tri = mesh.lod[l].index_len / 3u;
+            sc[m * kMaxLods + l].x = (uint32_t)ch.size();
+            if (3 * (first + n_tri) > c->h_indices.size()) continue;  // the kernel flags the command
+            bool open = false, wide = false;  // wide: a run of steps that each reference more than kTriVertCap vertices (gather path)
+            uint32_t c_begin = 0, c_count = 0, c_lo = 0, c_hi = 0;
+            auto flush = [&]() {
+                if (!open) return;
+                const uint64_t window = (uint64_t)c_hi - c_lo + 1;
+                // worth it when the window holds fewer vertices than the triangles have corners (3 per triangle), with some
+                // slack for tiny LODs so that they do not drag a second kernel launch in
+                const bool cached = !wide && window <= (uint64_t)kTriVertCap && (2 * window <= 5ull * c_count || window <= 512);
+                ch.push_back(make_uint4(c_begin, c_count, cached ? c_lo : 0u, cached ? (uint32_t)window : 0u));
+                open = false;
+            };
+            for (uint64_t s0 = 0; s0 < n_tri; s0 += kStep) {
+                const uint64_t e = s0 + kStep < n_tri ? s0 + kStep : n_tri;
+                uint32_t lo = 0xffffffffu, hi = 0;
+                for (uint64_t i = 3 * (first + s0); i < 3 * (first + e); ++i) {
+                    const uint32_t x = c->h_indices[i];
+                    lo = x < lo ? x : lo;
+                    hi = x > hi ? x : hi;
+                }
+                const bool step_wide = (uint64_t)hi - lo + 1 > (uint64_t)kTriVertCap;
+                if (open && wide == step_wide) {
+                    const uint32_t nlo = lo < c_lo ? lo : c_lo, nhi = hi > c_hi ? hi : c_hi;
+                    if (wide || (uint64_t)nhi - nlo + 1 <= (uint64_t)kTriVertCap) {  // wide runs just grow: one chunk for the whole run
+                        c_lo = nlo;
+                        c_hi = nhi;
+                        c_count += (uint32_t)(e - s0);
+                        continue;
+                    }
+                }
+                flush();
+                open = true;
+                wide = step_wide;
+                c_begin = (uint32_t)s0;
+                c_count = (uint32_t)(e - s0);
+                c_lo = lo;
+                c_hi = hi;
+            }
+            flush();
+            sc[m * kMaxLods + l].y = (uint32_t)ch.size() - sc[m * kMaxLods + l].x;
+            bool all_cached = sc[m * kMaxLods + l].y > 0;
+            for (uint32_t i = sc[m * kMaxLods + l].x; i < ch.size(); ++i) all_cached = all_cached && ch[i].w != 0u;
+            if (all_cached) sc[m * kMaxLods + l].y |= kSlotAllCached;
+            if (l < 2) (all_cached ? any_window : any_gather) = true;  // pick_lod only ever returns lod 0 or 1 (helpers.rs:3-11)
+        }
+    }
+    CU(cudaDeviceSynchronize());
+    if (c->slot_chunks) cudaFree(c->slot_chunks);
+    if (c->chunks) cudaFree(c->chunks);
+    c->slot_chunks = nullptr;
+    c->chunks = nullptr;
+    CU(cudaMalloc((void**)&c->slot_chunks, sc.size() * sizeof(uint2) + 256));
+    CU(cudaMalloc((void**)&c->chunks, ch.size() * sizeof(uint4) + 256));
+    CU(cudaMemcpy(c->slot_chunks, sc.data(), sc.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+    if (!ch.empty()) CU(cudaMemcpy(c->chunks, ch.data(), ch.size() * sizeof(uint4), cudaMemcpyHostToDevice));
+    c->n_chunks = (uint32_t)ch.size();
+    c->any_window_slot = any_window;
+    c->any_gather_slot = any_gather;
+    c->chunks_dirty = false;
     return RCULL_OK;
 }
 
@@ -887,7 +979,12 @@ int rcull_tri_cull(rcull_ctx* c, const float pv[16], uint32_t draw_index_base, u
     if (!c->cfg.capacity_tri_indices) return fail(RCULL_ERR_INVALID, "context created without capacity_tri_indices");
     if (!c->positions) return fail(RCULL_ERR_INVALID, "rcull_set_geometry has not been called");
     if (buffer_ix >= c->cfg.n_buffers) return fail(RCULL_ERR_INVALID, "buffer_ix %u of %u", buffer_ix, c->cfg.n_buffers);
+    if (c->merge) return fail(RCULL_ERR_INVALID, "rcull_tri_cull: a merge is attached -- the rank's own lists are not written");
     CU(cudaSetDevice(c->cfg.device));
+    if (c->chunks_dirty) {
+        int rc = build_tri_chunks(c);
+        if (rc) return rc;
+    }
     cudaStream_t s = (cudaStream_t)stream;
     OutputSet& o = c->out[lists_of(c, buffer_ix)];  // a frozen set draws from the lists of the last unfrozen frame
     CU(cudaMemsetAsync(c->tri_status, 0, c->tri_status_bytes, s));  // descriptors + the two tickets behind them
@@ -896,7 +993,13 @@ int rcull_tri_cull(rcull_ctx* c, const float pv[16], uint32_t draw_index_base, u
     TriArgs t;
     memset(&t, 0, sizeof t);
     t.cmds = o.cmds[0];
-    t.src_first = o.src_first;
+    t.src_slot = o.src_slot;
+    t.lod_tab = c->lod_tab;
+    t.slot_chunks = c->slot_chunks;
+    t.chunks = c->chunks;
+    t.n_slots = c->n_meshes * kMaxLods;
+    t.n_chunks = c->n_chunks;
+    t.mixed_kinds = c->any_window_slot && c->any_gather_slot ? 1u : 0u;
     t.count = o.counts;
     t.model = reinterpret_cast<const float*>(c->out[buffer_ix].model);
     t.positions = c->positions;
@@ -911,7 +1014,16 @@ int rcull_tri_cull(rcull_ctx* c, const float pv[16], uint32_t draw_index_base, u
     t.cap_cmds = (uint32_t)(c->cap_cmds > 0xffffffffull ? 0xffffffffull : c->cap_cmds);
     t.draw_index_base = draw_index_base;
     for (int i = 0; i < 16; ++i) t.pv.m[i] = make_float2(pv[i], pv[i]);
-    tri_cull<<<c->sm_count * 8, kTriThreads, 0, s>>>(t);
+    // the LODs with a cacheable vertex window, then the others (no shared memory: a large L1 for their gathers);
+    // the two kernels touch disjoint commands and may overlap
+    if (c->any_window_slot || !c->any_gather_slot) {
+        tri_cull<true><<<c->sm_count * 8, kTriThreads, 0, s>>>(t);
+        c->launches += 1;
+    }
+    if (c->any_gather_slot) {
+        tri_cull<false><<<c->sm_count * 8, kTriThreads, 0, s>>>(t);
+        c->launches += 1;
+    }
     CU(cudaGetLastError());
     CompactArgs k;
     memset(&k, 0, sizeof k);
@@ -926,7 +1038,7 @@ int rcull_tri_cull(rcull_ctx* c, const float pv[16], uint32_t draw_index_base, u
     k.cap_cmds = t.cap_cmds;
     compact_draw_stream<<<c->sm_count * 2, kCompactThreads, 0, s>>>(k);
     CU(cudaGetLastError());
-    c->launches += 2;
+    c->launches += 1;
     return RCULL_OK;
 }
 

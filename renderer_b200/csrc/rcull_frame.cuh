@@ -94,7 +94,7 @@ struct FrameArgs {
     uint8_t* flags[kMaxViews];  // optional [n]
     uint32_t* cmds[kMaxViews];  // 5 words per command
     uint32_t* visible[kMaxViews];
-    uint32_t* src_first;  // optional, view 0 only: first_index of the LOD behind each command (work list of the triangle stage)
+    uint32_t* src_slot;  // optional, view 0 only: (mesh, lod) slot behind each command (work list of the triangle stage)
     uint32_t* counts;
     unsigned long long* totals;
     uint32_t max_views;
@@ -417,7 +417,7 @@ __device__ __forceinline__ void emit_pending(const FrameArgs& args, const FrameS
                 c[2] = sm.adj_len[buf][k][warp] + excl;   // firstIndex: running sum of earlier survivors' index_len
                 c[3] = L.z;                               // vertexOffset
                 c[4] = draw_index;                        // firstInstance
-                if (k == 0 && args.src_first != nullptr) args.src_first[pos] = L.y;  // indexOffset of generate_work.comp's push constants
+                if (k == 0 && args.src_slot != nullptr) args.src_slot[pos] = slot;  // names the LOD: indexOffset of generate_work.comp's push constants = its first_index
             }
         }
     }

@@ -27,19 +27,26 @@ struct Mat4x2 {
     float2 m[16];
 };
 
+constexpr int kTriVertCap = 2048;  // clip-space vertices of one chunk kept in shared memory (x, y, w: 24 KB)
+constexpr uint32_t kSlotAllCached = 0x80000000u;  // flag in slot_chunks[].y: every chunk of the LOD has a cacheable vertex window
+
 struct TriArgs {
     const uint32_t* cmds;        // view's draw list from the frame kernel, 5 words per command
-    const uint32_t* src_first;   // indexOffset push constant of each command (first_index of the chosen LOD)
+    const uint32_t* src_slot;    // (mesh, lod) slot of each command: its LOD row gives the indexOffset push constant
+    const uint4* lod_tab;        // per slot: index_len, first_index, vertex_offset, 0
+    const uint2* slot_chunks;    // per slot: first chunk, number of chunks | kSlotAllCached (built on the host from the index buffer)
+    const uint4* chunks;         // tri_begin (within the LOD), tri_count, v_min, v_count (0: gather path)
     const uint32_t* count;       // how many commands (device)
     const float* model;          // mat4 column-major, slot = firstInstance - draw_index_base
     const float* positions;      // ConsolidatedMeshBuffers.position_buffer, vec3 scalar layout
     const uint32_t* indices;     // ConsolidatedMeshBuffers.index_buffer
     uint32_t* out_indices;       // CulledIndexBuffer (uvec3 out_index_buffer[], generate_work.comp:40-42)
     uint32_t* refined;           // [count] refined indexCount of every command
-    uint32_t* ticket;            // [0] command ticket of the cull kernel, [1] tile ticket of the compaction
+    uint32_t* ticket;            // [0], [1] command tickets of the two cull kernels, [2] tile ticket of the compaction
     uint32_t* error_flag;
     uint64_t n_vertices, n_indices, out_capacity;
-    uint32_t cap_cmds, draw_index_base;
+    uint32_t cap_cmds, draw_index_base, n_slots, n_chunks;
+    uint32_t mixed_kinds;        // both kinds of LOD exist: each tri_cull kernel skips the commands of the other
     Mat4x2 pv;  // read straight out of the constant bank (kernel parameter): no loads
 };
 
@@ -112,19 +119,16 @@ __device__ __forceinline__ bool ndc_culled(float c0x, float c0y, float c0w, floa
     return (x0 < -1.0f && x1 < -1.0f && x2 < -1.0f) || (x0 > 1.0f && x1 > 1.0f && x2 > 1.0f) ||
            (y0 < -1.0f && y1 < -1.0f && y2 < -1.0f) || (y0 > 1.0f && y1 > 1.0f && y2 > 1.0f);
 }
-// generate_work.comp:139-155 for triangles 0 and 1 of the step; v[j][k] = vertex k of triangle j.
+// clip = pv * (model * vec4(v, 1)) for TWO vertices at once (one per half); only the x, y, w rows of pv are needed.
 template <typename PV>
-__device__ __forceinline__ void tri_culled2(const Mat4x2& model, const PV& pv, const float (&v)[2][3][3], bool& culled0, bool& culled1) {
-    float2 cx[3], cy[3], cw[3];  // clip-space x, y, w of vertex k, one triangle per half
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const float2 x = make_float2(v[0][k][0], v[1][k][0]), y = make_float2(v[0][k][1], v[1][k][1]),
-                     z = make_float2(v[0][k][2], v[1][k][2]);
-        const float2 w[4] = {row_w1(model, 0, x, y, z), row_w1(model, 1, x, y, z), row_w1(model, 2, x, y, z), row_w1(model, 3, x, y, z)};
-        cx[k] = row_full(pv, 0, w);
-        cy[k] = row_full(pv, 1, w);
-        cw[k] = row_full(pv, 3, w);
-    }
+__device__ __forceinline__ void clip2(const Mat4x2& model, const PV& pv, float2 x, float2 y, float2 z, float2& cx, float2& cy, float2& cw) {
+    const float2 w[4] = {row_w1(model, 0, x, y, z), row_w1(model, 1, x, y, z), row_w1(model, 2, x, y, z), row_w1(model, 3, x, y, z)};
+    cx = row_full(pv, 0, w);
+    cy = row_full(pv, 1, w);
+    cw = row_full(pv, 3, w);
+}
+// generate_work.comp:139-155 on the clip-space corners of two triangles (one per half): cx[k] = clip x of corner k.
+__device__ __forceinline__ void cull_from_clip(const float2 (&cx)[3], const float2 (&cy)[3], const float2 (&cw)[3], bool& culled0, bool& culled1) {
     // determinant(mat3(c0.xyw, c1.xyw, c2.xyw)) > 0: cofactors along the first row of columns
     const float2 t0 = sub2s(mul2_rn(cy[1], cw[2]), mul2_rn(cy[2], cw[1]));
     const float2 t1 = sub2s(mul2_rn(cy[0], cw[2]), mul2_rn(cy[2], cw[0]));
@@ -147,25 +151,59 @@ __device__ __forceinline__ void tri_culled2(const Mat4x2& model, const PV& pv, c
     if (!culled1 && !in1) culled1 = ndc_culled(cx[0].y, cy[0].y, cw[0].y, cx[1].y, cy[1].y, cw[1].y, cx[2].y, cy[2].y, cw[2].y);
     // the area test of :159-167 is overwritten by `cull = false` (:166): nothing to compute
 }
+// generate_work.comp:139-155 for triangles 0 and 1 of the step; v[j][k] = vertex k of triangle j.
+template <typename PV>
+__device__ __forceinline__ void tri_culled2(const Mat4x2& model, const PV& pv, const float (&v)[2][3][3], bool& culled0, bool& culled1) {
+    float2 cx[3], cy[3], cw[3];  // clip-space x, y, w of vertex k, one triangle per half
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+        clip2(model, pv, make_float2(v[0][k][0], v[1][k][0]), make_float2(v[0][k][1], v[1][k][1]), make_float2(v[0][k][2], v[1][k][2]), cx[k], cy[k], cw[k]);
+    cull_from_clip(cx, cy, cw, culled0, culled1);
+}
 
-// One CTA per command at a time (ticket order): the command's triangles in steps of 256,
-// ballot compaction with a running base, so the kept triples land in ascending triangle
-// order at out_index_buffer[firstIndex / 3 + rank] (the reference's order inside a mesh is
-// atomic-arrival order; ascending is one of its outcomes).
+// One CTA per command at a time (ticket order).  The LOD behind the command comes as CHUNKS of its triangle list
+// (built on the host from the index buffer, rcull.cu): a chunk whose triangles reference a window of at most
+// kTriVertCap vertices has that window transformed ONCE into shared memory (clip-space x, y, w), and its triangles --
+// 256 per step, two per thread -- pick their corners from there: an indexed mesh shares every vertex among ~6
+// triangles, so this is a third to a sixth of the transforms of the reference's shader, which transforms three
+// vertices per triangle (generate_work.comp:132-137).  Chunks with a wide window (random index triples) gather and
+// transform per triangle as the shader does.  Either way each vertex goes through exactly the operations of
+// glsl_mul / glsl_mul_w1, so the result does not depend on which path ran.  Kept triples land in ascending triangle order at
+// out_index_buffer[firstIndex / 3 + rank] through ballot compaction with a running base (the reference's order
+// inside a mesh is atomic-arrival order; ascending is one of its outcomes).
+// Two instantiations split the commands between them by the kind of their LOD: kWindow = true takes the LODs whose
+// chunks all have a cacheable vertex window (24 KB of shared memory per CTA), kWindow = false the others with NO shared
+// memory -- the gathers of a mesh with random index triples live on a large L1 (a mesh's vertices fit it), which a
+// shared-memory carveout for eight CTAs would take away (measured: 0.78 -> 1.5 ms on the random-triple scene).
+template <bool kWindow>
 __global__ void __launch_bounds__(kTriThreads) tri_cull(const __grid_constant__ TriArgs a) {
     __shared__ uint32_t s_cmd, s_warp[2][kTriItems][kTriThreads / 32];
+    __shared__ float s_cx[kWindow ? kTriVertCap : 1], s_cy[kWindow ? kTriVertCap : 1], s_cw[kWindow ? kTriVertCap : 1];
+    uint32_t* const ticket = a.ticket + (kWindow ? 0 : 1);
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     uint32_t count = *a.count;
     if (count > a.cap_cmds) count = a.cap_cmds;
     for (;;) {
-        if (tid == 0) s_cmd = atomicAdd(a.ticket, 1u);
+        if (tid == 0) {  // the next command of this kernel's kind
+            uint32_t c = atomicAdd(ticket, 1u);
+            while (a.mixed_kinds && c < count) {
+                const uint32_t sl = a.src_slot[c];
+                if (((a.slot_chunks[sl < a.n_slots ? sl : 0u].y & kSlotAllCached) != 0u) == kWindow) break;
+                c = atomicAdd(ticket, 1u);
+            }
+            s_cmd = c;
+        }
         __syncthreads();
         const uint32_t c = s_cmd;
         if (c >= count) break;
         const uint32_t* cmd = a.cmds + (size_t)c * 5;
         const uint32_t n_tri = cmd[0] / 3u, out_first = cmd[2] / 3u, first_instance = cmd[4];
         const int32_t vertex_offset = (int32_t)cmd[3];
-        const uint64_t src = a.src_first[c] / 3u;
+        uint32_t slot = a.src_slot[c];
+        if (slot >= a.n_slots) slot = 0;  // cannot happen: the frame kernel wrote it
+        const uint64_t src = a.lod_tab[slot].y / 3u;
+        uint2 sc = a.slot_chunks[slot];
+        sc.y &= ~kSlotAllCached;
         Mat4x2 model;  // the command's model matrix in registers, every entry twice: one load per command, not per product
         {
             const float4* mp = reinterpret_cast<const float4*>(a.model + (size_t)(first_instance - a.draw_index_base) * 16);
@@ -179,80 +217,112 @@ __global__ void __launch_bounds__(kTriThreads) tri_cull(const __grid_constant__ 
         __syncthreads();  // everyone has read s_cmd
         // Range checks once per command, not per triangle: the command's index range must lie inside the
         // index buffer, and an index is in range iff it is below v_limit (32-bit compare).
-        uint32_t n_steps_tri = n_tri;
-        if (3ull * (src + n_tri) > a.n_indices || vertex_offset < 0 || (uint64_t)vertex_offset >= a.n_vertices) {
-            if (tid == 0) atomicOr(a.error_flag, 2u);
-            n_steps_tri = 0;
-        }
+        bool bad = 3ull * (src + n_tri) > a.n_indices || vertex_offset < 0 || (uint64_t)vertex_offset >= a.n_vertices;
+        if (bad && tid == 0) atomicOr(a.error_flag, 2u);
         const uint64_t room = a.n_vertices - (uint64_t)(vertex_offset < 0 ? 0 : vertex_offset);
         const uint32_t v_limit = room > 0xffffffffull ? 0xffffffffu : (uint32_t)room;
         const uint32_t* __restrict__ ib = a.indices + 3ull * src;
         const float* __restrict__ vb = a.positions + 3ll * vertex_offset;
         uint32_t running = 0, step = 0;
-        for (uint32_t t0 = 0; t0 < n_steps_tri; t0 += kTriThreads * kTriItems, ++step) {
-            bool keep[kTriItems];
-            uint32_t ix[kTriItems][3], b[kTriItems];
-            float v[kTriItems][3][3];
-            // all loads of the step first (index triples, then the nine position words per triangle), then the math
-#pragma unroll
-            for (int j = 0; j < kTriItems; ++j) {  // item-major: triangle t0 + j * 128 + tid (coalesced index loads)
-                const uint32_t t = t0 + j * kTriThreads + tid;
-                const bool act = t < n_tri;
-#pragma unroll
-                for (int k = 0; k < 3; ++k) ix[j][k] = act ? __ldg(ib + 3u * t + k) : 0u;
-                keep[j] = act;
-            }
-#pragma unroll
-            for (int j = 0; j < kTriItems; ++j) {
-                const bool ok = ix[j][0] < v_limit && ix[j][1] < v_limit && ix[j][2] < v_limit;
-                if (keep[j] && !ok) atomicOr(a.error_flag, 2u);
-                keep[j] = keep[j] && ok;
-#pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    const float* q = vb + 3ull * (keep[j] ? ix[j][k] : 0u);  // a safe address for inactive lanes
-                    v[j][k][0] = __ldg(q);
-                    v[j][k][1] = __ldg(q + 1);
-                    v[j][k][2] = __ldg(q + 2);
+        for (uint32_t ci = sc.x; ci < sc.x + sc.y && !bad; ++ci) {
+            const uint4 ch = a.chunks[ci];  // tri_begin, tri_count, v_min, v_count
+            const uint32_t t_end = min(ch.x + ch.y, n_tri);
+            const bool cached = kWindow && ch.w != 0u && ch.z + ch.w <= v_limit;
+            if (cached) {
+                // the chunk's vertex window through model and pv, two vertices per thread and trip
+                for (uint32_t v = 2 * tid; v < ch.w; v += 2 * kTriThreads) {
+                    const uint32_t v1 = v + 1 < ch.w ? v + 1 : v;
+                    const float* q0 = vb + 3ull * (ch.z + v);
+                    const float* q1 = vb + 3ull * (ch.z + v1);
+                    float2 cx, cy, cw;
+                    clip2(model, a.pv, make_float2(__ldg(q0), __ldg(q1)), make_float2(__ldg(q0 + 1), __ldg(q1 + 1)), make_float2(__ldg(q0 + 2), __ldg(q1 + 2)), cx, cy, cw);
+                    s_cx[v] = cx.x; s_cy[v] = cy.x; s_cw[v] = cw.x;
+                    s_cx[v1] = cx.y; s_cy[v1] = cy.y; s_cw[v1] = cw.y;
                 }
+                __syncthreads();
             }
-            {
-                static_assert(kTriItems == 2, "tri_culled2 works on the two triangles of a step");
+            for (uint32_t t0 = ch.x; t0 < t_end; t0 += kTriThreads * kTriItems, ++step) {
+                bool keep[kTriItems];
+                uint32_t ix[kTriItems][3], b[kTriItems];
+                // all loads of the step first (index triples, then the corners), then the math
+#pragma unroll
+                for (int j = 0; j < kTriItems; ++j) {  // item-major: triangle t0 + j * 128 + tid (coalesced index loads)
+                    const uint32_t t = t0 + j * kTriThreads + tid;
+                    const bool act = t < t_end;
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) ix[j][k] = act ? __ldg(ib + 3u * t + k) : 0u;
+                    keep[j] = act;
+                }
                 bool culled0, culled1;
-                tri_culled2(model, a.pv, v, culled0, culled1);
+                if (cached) {
+                    float2 cx[3], cy[3], cw[3];
+#pragma unroll
+                    for (int j = 0; j < kTriItems; ++j) {
+                        // the chunk table was built from this index buffer: an index outside the window means the buffers changed under us
+                        const bool ok = ix[j][0] - ch.z < ch.w && ix[j][1] - ch.z < ch.w && ix[j][2] - ch.z < ch.w;
+                        if (keep[j] && !ok) atomicOr(a.error_flag, 2u);
+                        keep[j] = keep[j] && ok;
+                    }
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) {
+                        const uint32_t i0 = keep[0] ? ix[0][k] - ch.z : 0u, i1 = keep[1] ? ix[1][k] - ch.z : 0u;
+                        cx[k] = make_float2(s_cx[i0], s_cx[i1]);
+                        cy[k] = make_float2(s_cy[i0], s_cy[i1]);
+                        cw[k] = make_float2(s_cw[i0], s_cw[i1]);
+                    }
+                    cull_from_clip(cx, cy, cw, culled0, culled1);
+                } else {
+                    float v[kTriItems][3][3];
+#pragma unroll
+                    for (int j = 0; j < kTriItems; ++j) {
+                        const bool ok = ix[j][0] < v_limit && ix[j][1] < v_limit && ix[j][2] < v_limit;
+                        if (keep[j] && !ok) atomicOr(a.error_flag, 2u);
+                        keep[j] = keep[j] && ok;
+#pragma unroll
+                        for (int k = 0; k < 3; ++k) {
+                            const float* q = vb + 3ull * (keep[j] ? ix[j][k] : 0u);  // a safe address for inactive lanes
+                            v[j][k][0] = __ldg(q);
+                            v[j][k][1] = __ldg(q + 1);
+                            v[j][k][2] = __ldg(q + 2);
+                        }
+                    }
+                    static_assert(kTriItems == 2, "tri_culled2 works on the two triangles of a step");
+                    tri_culled2(model, a.pv, v, culled0, culled1);
+                }
                 keep[0] = keep[0] && !culled0;
                 keep[1] = keep[1] && !culled1;
-            }
-            // per-warp kept counts, double-buffered by step parity: one barrier per step is enough
-            uint32_t (*sw)[kTriThreads / 32] = s_warp[step & 1u];
+                // per-warp kept counts, double-buffered by step parity: one barrier per step is enough
+                uint32_t (*sw)[kTriThreads / 32] = s_warp[step & 1u];
 #pragma unroll
-            for (int j = 0; j < kTriItems; ++j) {
-                b[j] = __ballot_sync(kFullMask, keep[j]);
-                if (lane == 0) sw[j][warp] = __popc(b[j]);
-            }
-            __syncthreads();
-            uint32_t base = running;
-#pragma unroll
-            for (int j = 0; j < kTriItems; ++j) {
-                uint32_t before = 0, total = 0;
-#pragma unroll
-                for (int w = 0; w < kTriThreads / 32; ++w) {
-                    const uint32_t x = sw[j][w];
-                    before += (uint32_t)w < warp ? x : 0u;
-                    total += x;
+                for (int j = 0; j < kTriItems; ++j) {
+                    b[j] = __ballot_sync(kFullMask, keep[j]);
+                    if (lane == 0) sw[j][warp] = __popc(b[j]);
                 }
-                if (keep[j]) {
-                    const uint64_t dst = 3ull * ((uint64_t)out_first + base + before + __popc(b[j] & ((1u << lane) - 1u)));
-                    if (dst + 2 < a.out_capacity) {
-                        a.out_indices[dst] = ix[j][0];
-                        a.out_indices[dst + 1] = ix[j][1];
-                        a.out_indices[dst + 2] = ix[j][2];
-                    } else {
-                        atomicOr(a.error_flag, 4u);  // CulledIndexBuffer too small
+                __syncthreads();  // also: every corner of this step has been read from the vertex window
+                uint32_t base = running;
+#pragma unroll
+                for (int j = 0; j < kTriItems; ++j) {
+                    uint32_t before = 0, total = 0;
+#pragma unroll
+                    for (int w = 0; w < kTriThreads / 32; ++w) {
+                        const uint32_t x = sw[j][w];
+                        before += (uint32_t)w < warp ? x : 0u;
+                        total += x;
                     }
+                    if (keep[j]) {
+                        const uint64_t dst = 3ull * ((uint64_t)out_first + base + before + __popc(b[j] & ((1u << lane) - 1u)));
+                        if (dst + 2 < a.out_capacity) {
+                            a.out_indices[dst] = ix[j][0];
+                            a.out_indices[dst + 1] = ix[j][1];
+                            a.out_indices[dst + 2] = ix[j][2];
+                        } else {
+                            atomicOr(a.error_flag, 4u);  // CulledIndexBuffer too small
+                        }
+                    }
+                    base += total;
                 }
-                base += total;
+                running = base;
             }
-            running = base;
         }
         if (tid == 0) a.refined[c] = 3u * running;
     }

@@ -41,7 +41,7 @@ def run_tri(n, half_box, *, base=0, cam_pos=scene.CAMERA_POS, capacity=None, thr
         for c in want["cmds"]:  # only the ranges the commands own are defined
             a, b = int(c["firstIndex"]), int(c["firstIndex"]) + int(c["indexCount"])
             assert np.array_equal(got_idx[a:b], want["indices"][a:b])
-        assert ctx.launch_count == 3  # frame + tri_cull + compact_draw_stream
+        assert ctx.launch_count in (3, 4)  # frame + tri_cull (one kernel per kind of LOD present) + compact_draw_stream
         return count, kept, total, int(ref["counts"][0])
 
 
