@@ -336,6 +336,45 @@ int rcull_mgpu_frame(rcull_mgpu *g, const uint64_t *n, const uint32_t *draw_inde
                      uint32_t n_views, const float cam_pos[3]);
 int rcull_mgpu_synchronize(rcull_mgpu *g);
 
+/* rcull_frame for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that
+ * forbid cudaMalloc.  It needs no rcull_ctx: the caller passes every input and output as device memory,
+ * and the kernel's scratch (tile tickets, the look-back descriptors of the prefix scan, the device form of
+ * the mesh table) lives in a file-scope `static __device__` array of RCULL_NOALLOC_SCRATCH_BYTES that every
+ * GPU which loads librcull holds until the process exits.  The call issues no cudaMalloc / cudaFree and no
+ * allocating library routine; it is asynchronous on `stream` (per-entity output mode, no optional
+ * AABB / flag outputs, same kernel and bit-identical results as rcull_frame).
+ *   limits   n <= RCULL_NOALLOC_MAX_ENTITIES, n_meshes <= RCULL_NOALLOC_MAX_MESHES, n_views <= RCULL_MAX_VIEWS;
+ *            anything larger is rejected with RCULL_ERR_INVALID and a message naming the limit.
+ *   sharing  every call on a device uses the same array and re-initialises the part it needs on `stream`:
+ *            calls that can overlap on the GPU (different streams without an ordering between them) race.
+ *   sizes    pos_scale / rot / mesh are read in whole tiles: they must be READABLE up to
+ *            RCULL_NOALLOC_PADDED(n) entities (contents past n are ignored), 16-byte aligned.
+ *            model holds n rounded up to 2 matrices, 16-byte aligned.  cmds[k] / visible[k] hold
+ *            capacity_visible entries for every k < n_views (survivors past it are counted, not stored,
+ *            as in rcull_frame).  counts / index_totals hold RCULL_MAX_VIEWS entries (the first n_views
+ *            are written).  error is one word: 0, or nonzero when a mesh id was outside the table. */
+#define RCULL_NOALLOC_TILE 1920u
+#define RCULL_NOALLOC_MAX_ENTITIES (1u << 20)
+#define RCULL_NOALLOC_MAX_MESHES 256u
+#define RCULL_NOALLOC_SCRATCH_BYTES (128u * 1024u)
+#define RCULL_NOALLOC_PADDED(n) (((uint64_t)(n) + RCULL_NOALLOC_TILE - 1) / RCULL_NOALLOC_TILE * RCULL_NOALLOC_TILE)
+typedef struct {
+    const float *pos_scale;                /* in:  [RCULL_NOALLOC_PADDED(n)][4] */
+    const float *rot;                      /* in:  [RCULL_NOALLOC_PADDED(n)][4] */
+    const uint32_t *mesh;                  /* in:  [RCULL_NOALLOC_PADDED(n)] */
+    float *model;                          /* out: mat4 column-major [n rounded up to 2] */
+    rcull_draw_cmd *cmds[RCULL_MAX_VIEWS]; /* out: [capacity_visible] per view */
+    uint32_t *visible[RCULL_MAX_VIEWS];    /* out: [capacity_visible] per view */
+    uint32_t *counts;                      /* out: [RCULL_MAX_VIEWS] */
+    uint64_t *index_totals;                /* out: [RCULL_MAX_VIEWS] */
+    uint32_t *error;                       /* out: [1] */
+    uint64_t capacity_visible;
+} rcull_noalloc_io;
+int rcull_frame_noalloc(int32_t device, uint64_t n, const rcull_noalloc_io *io, const rcull_mesh *meshes,
+                        uint32_t n_meshes, const rcull_view *views, uint32_t n_views, const float cam_pos[3],
+                        float lod_distance, uint32_t draw_index_base, void *stream);
+
 /* Harness utility: fills the input columns on the device with the counter-based
  * synthetic scene (entity i of the global scene = first_global + slot), bit-
  * identical to renderer_b200/scene.py; avoids shipping 128 M entities from host. */

@@ -64,6 +64,27 @@ class Outputs(C.Structure):
     ]
 
 
+class NoallocIO(C.Structure):
+    """rcull_noalloc_io: device pointers the caller owns (rcull_frame_noalloc)."""
+
+    _fields_ = [
+        ("pos_scale", C.c_void_p),
+        ("rot", C.c_void_p),
+        ("mesh", C.c_void_p),
+        ("model", C.c_void_p),
+        ("cmds", C.c_void_p * MAX_VIEWS),
+        ("visible", C.c_void_p * MAX_VIEWS),
+        ("counts", C.c_void_p),
+        ("index_totals", C.c_void_p),
+        ("error", C.c_void_p),
+        ("capacity_visible", C.c_uint64),
+    ]
+
+
+NOALLOC_TILE = 1920
+NOALLOC_MAX_ENTITIES = 1 << 20
+NOALLOC_MAX_MESHES = 256
+
 # numpy twins of the POD structs
 MESH_DTYPE = np.dtype(
     [
@@ -144,6 +165,7 @@ SYMBOLS = {
     "rcull_mgpu_last_error": (C.c_char_p, []),
     "rcull_mgpu_frame": (C.c_int, [_P, _P, _P, _P, _u32, _P]),
     "rcull_mgpu_synchronize": (C.c_int, [_P]),
+    "rcull_frame_noalloc": (C.c_int, [C.c_int32, _u64, C.POINTER(NoallocIO), _P, _u32, _P, _u32, _P, _f, _u32, _P]),
     "rcull_synth_entities": (C.c_int, [_P, _u64, _u64, _u64, _f, _u32, _P]),
     "rcull_launch_count": (_u64, [_P]),
     "rcull_frustum_planes": (None, [_P, C.POINTER(View)]),

@@ -10,6 +10,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 
@@ -799,6 +800,251 @@ int rcull_frame_frozen(rcull_ctx* c, uint64_t n, uint32_t buffer_ix, void* strea
     model_only<<<c->sm_count * 8, kRecordWarps * 32, 0, (cudaStream_t)stream>>>(c->pos_scale, c->rot, (uint32_t)n, c->out[buffer_ix].model_map);
     CU(cudaGetLastError());
     c->launches += 1;
+    return RCULL_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------
+// rcull_frame_noalloc: the frame kernel without a context and without an allocation
+// (no counterpart in the reference)
+// ---------------------------------------------------------------------------------
+// The scratch of the frame kernel in a file-scope device array: every GPU that loads librcull holds these
+// bytes until the process exits.  In HOST code this name is only a stand-in for the symbol -- it is not a
+// device address; the address comes from cudaGetSymbolAddress, once per device (noalloc_device below).
+static __device__ __align__(256) unsigned char g_noalloc_scratch[RCULL_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr uint32_t kNoallocMaxTiles = (RCULL_NOALLOC_MAX_ENTITIES + kTile - 1) / kTile;
+// layout of g_noalloc_scratch (byte offsets; every part 256-byte aligned)
+constexpr size_t kNaTicket = 0;                                                          // tile ticket word
+constexpr size_t kNaMeshAabb = 256;                                                      // float4 [meshes][2]
+constexpr size_t kNaLodTab = kNaMeshAabb + RCULL_NOALLOC_MAX_MESHES * 2 * sizeof(float4);  // uint4 [meshes][kMaxLods]
+constexpr size_t kNaLen1 = kNaLodTab + RCULL_NOALLOC_MAX_MESHES * kMaxLods * sizeof(uint4);  // uint32 [meshes]
+constexpr size_t kNaStatus = kNaLen1 + RCULL_NOALLOC_MAX_MESHES * sizeof(uint32_t);      // ulonglong2 [views][tiles]
+constexpr size_t kNaEnd = kNaStatus + (size_t)kMaxViews * kNoallocMaxTiles * sizeof(ulonglong2);
+static_assert(RCULL_NOALLOC_TILE == kTile, "rcull.h states the tile the no-alloc inputs are padded to");
+static_assert(kNaLodTab % 256 == 0 && kNaLen1 % 256 == 0 && kNaStatus % 256 == 0, "scratch parts stay aligned");
+static_assert(kNaEnd <= RCULL_NOALLOC_SCRATCH_BYTES, "scratch layout exceeds the stated maximum");
+
+struct NoallocDevice {
+    bool ready = false;
+    unsigned char* scratch = nullptr;  // device address of g_noalloc_scratch on this device
+    int sm_count = 0;
+    int blocks_per_sm[kMaxViews + 1][2] = {};
+};
+constexpr int kNoallocMaxDevices = 64;
+NoallocDevice g_noalloc_dev[kNoallocMaxDevices];
+std::mutex g_noalloc_mu;
+
+template <int V, bool M>
+int noalloc_configure(NoallocDevice& d) {
+    auto k = transform_cull_compact<V, M>;
+    CU(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)frame_smem_bytes<V>()));
+    CU(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    int b = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k, kThreads, frame_smem_bytes<V>()));
+    if (b < 1) return fail(RCULL_ERR_CUDA, "transform_cull_compact<%d,%d> does not fit on an SM", V, (int)M);
+    d.blocks_per_sm[V][M] = b;
+    return 0;
+}
+
+// Set-up, once per device and with that device current: the device address of the scratch array and the
+// launch attributes of the frame kernel.  Nothing here allocates device memory.
+int noalloc_device(int device, NoallocDevice** out) {
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    NoallocDevice& d = g_noalloc_dev[device];
+    if (!d.ready) {
+        cudaDeviceProp prop;
+        CU(cudaGetDeviceProperties(&prop, device));
+        if (prop.major != 10)
+            return fail(RCULL_ERR_NO_DEVICE, "device %d is sm_%d%d; librcull is built for sm_100a only", device, prop.major, prop.minor);
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(RCULL_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch) on device %d failed: %s", device, cudaGetErrorString(e));
+        d.scratch = static_cast<unsigned char*>(p);
+        d.sm_count = prop.multiProcessorCount;
+        int rc = 0;
+#define NA_TRY(x) \
+    if ((rc = (x)) != 0) return rc;
+        NA_TRY((noalloc_configure<1, false>(d)));
+        NA_TRY((noalloc_configure<1, true>(d)));
+        NA_TRY((noalloc_configure<2, false>(d)));
+        NA_TRY((noalloc_configure<2, true>(d)));
+        NA_TRY((noalloc_configure<3, false>(d)));
+        NA_TRY((noalloc_configure<3, true>(d)));
+        NA_TRY((noalloc_configure<4, false>(d)));
+        NA_TRY((noalloc_configure<4, true>(d)));
+        NA_TRY((noalloc_configure<5, false>(d)));
+        NA_TRY((noalloc_configure<5, true>(d)));
+        NA_TRY((noalloc_configure<6, false>(d)));
+        NA_TRY((noalloc_configure<6, true>(d)));
+        NA_TRY((noalloc_configure<7, false>(d)));
+        NA_TRY((noalloc_configure<7, true>(d)));
+        NA_TRY((noalloc_configure<8, false>(d)));
+        NA_TRY((noalloc_configure<8, true>(d)));
+#undef NA_TRY
+        d.ready = true;
+    }
+    *out = &d;
+    return 0;
+}
+
+// The caller's model buffer as [ceil(n / 2) rows][32 floats]: rows past the end are clipped by the TMA
+// store, so the buffer needs no padding to whole tiles (make_model_map sizes a context's own buffer).
+int noalloc_model_map(CUtensorMap* map, float* model, uint64_t n) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    CU(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (qres != cudaDriverEntryPointSuccess || !fn) return fail(RCULL_ERR_CUDA, "cuTensorMapEncodeTiled is not available in this driver");
+    const cuuint64_t dims[2] = {32, (n + 1) / 2};
+    const cuuint64_t strides[1] = {128};
+    const cuuint32_t box[2] = {32, 16};
+    const cuuint32_t elem[2] = {1, 1};
+    CUresult r = reinterpret_cast<EncodeTiledFn>(fn)(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, model, dims, strides, box, elem,
+                                                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                                     CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(RCULL_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return 0;
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+}  // namespace
+
+extern "C" {
+
+int rcull_frame_noalloc(int32_t device, uint64_t n, const rcull_noalloc_io* io, const rcull_mesh* meshes, uint32_t n_meshes,
+                        const rcull_view* views, uint32_t n_views, const float cam_pos[3], float lod_distance,
+                        uint32_t draw_index_base, void* stream) {
+    Scope scope("rcull::frame_noalloc");
+    if (!io || !meshes || !views || !cam_pos) return fail(RCULL_ERR_INVALID, "rcull_frame_noalloc: null argument");
+    if (n > RCULL_NOALLOC_MAX_ENTITIES)
+        return fail(RCULL_ERR_INVALID, "rcull_frame_noalloc: n = %llu exceeds RCULL_NOALLOC_MAX_ENTITIES = %u (the static scratch is sized for it; use rcull_create + rcull_frame)",
+                    (unsigned long long)n, RCULL_NOALLOC_MAX_ENTITIES);
+    if (n_meshes < 1 || n_meshes > RCULL_NOALLOC_MAX_MESHES)
+        return fail(RCULL_ERR_INVALID, "rcull_frame_noalloc: n_meshes = %u not in 1..RCULL_NOALLOC_MAX_MESHES = %u", n_meshes, RCULL_NOALLOC_MAX_MESHES);
+    if (n_views < 1 || n_views > RCULL_MAX_VIEWS) return fail(RCULL_ERR_INVALID, "rcull_frame_noalloc: n_views %u not in 1..%d", n_views, RCULL_MAX_VIEWS);
+    if (!io->counts || !io->index_totals || !io->error) return fail(RCULL_ERR_INVALID, "rcull_frame_noalloc: counts / index_totals / error are required");
+    if (n && (!io->pos_scale || !io->rot || !io->mesh || !io->model)) return fail(RCULL_ERR_INVALID, "rcull_frame_noalloc: null entity column or model buffer");
+    if (!aligned16(io->pos_scale) || !aligned16(io->rot) || !aligned16(io->mesh) || !aligned16(io->model))
+        return fail(RCULL_ERR_INVALID, "rcull_frame_noalloc: pos_scale, rot, mesh and model must be 16-byte aligned");
+    if (n && io->capacity_visible == 0) return fail(RCULL_ERR_INVALID, "rcull_frame_noalloc: capacity_visible is 0");
+    for (uint32_t v = 0; n && v < n_views; ++v)
+        if (!io->cmds[v] || !io->visible[v]) return fail(RCULL_ERR_INVALID, "rcull_frame_noalloc: view %u has no cmds / visible buffer", v);
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) return fail(RCULL_ERR_NO_DEVICE, "no CUDA device: librcull has no CPU path");
+    if (device < 0 || device >= n_dev || device >= kNoallocMaxDevices) return fail(RCULL_ERR_INVALID, "device %d of %d", device, n_dev);
+    CU(cudaSetDevice(device));
+    NoallocDevice* d = nullptr;
+    int rc = noalloc_device(device, &d);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+
+    // mesh table in the kernel's form (rcull_set_mesh_table), built on the stack
+    float4 aabb[2 * RCULL_NOALLOC_MAX_MESHES];
+    uint4 lods[kMaxLods * RCULL_NOALLOC_MAX_MESHES];
+    uint32_t len1[RCULL_NOALLOC_MAX_MESHES];
+    uint32_t max_len = 0;
+    for (uint32_t i = 0; i < n_meshes; ++i) {
+        const rcull_mesh& m = meshes[i];
+        if (m.n_lods < 1 || m.n_lods > kMaxLods) return fail(RCULL_ERR_INVALID, "mesh %u: n_lods %u not in 1..%d", i, m.n_lods, kMaxLods);
+        float nl, l0;
+        memcpy(&nl, &m.n_lods, 4);
+        memcpy(&l0, &m.lod[0].index_len, 4);
+        aabb[2 * i] = make_float4(m.aabb_min[0], m.aabb_min[1], m.aabb_min[2], nl);
+        aabb[2 * i + 1] = make_float4(m.aabb_max[0], m.aabb_max[1], m.aabb_max[2], l0);
+        len1[i] = m.n_lods > 1 ? m.lod[1].index_len : m.lod[0].index_len;
+        for (uint32_t l = 0; l < (uint32_t)kMaxLods; ++l) {
+            if (l < m.n_lods) {
+                if (m.lod[l].index_len > max_len) max_len = m.lod[l].index_len;
+                lods[(size_t)i * kMaxLods + l] = make_uint4(m.lod[l].index_len, m.lod[l].first_index, (uint32_t)m.vertex_offset, 0);
+            } else {
+                lods[(size_t)i * kMaxLods + l] = make_uint4(0, 0, 0, 0);
+            }
+        }
+    }
+    const uint32_t len_small = max_len < (1u << 25) ? 1u : 0u;
+
+    // what must start at zero, on the caller's stream: outputs, then the scan state this frame will use
+    CU(cudaMemsetAsync(io->counts, 0, kMaxViews * 4, s));
+    CU(cudaMemsetAsync(io->index_totals, 0, kMaxViews * 8, s));
+    CU(cudaMemsetAsync(io->error, 0, 4, s));
+    if (n == 0) return RCULL_OK;  // empty query: cull_pass still clears the buffers (cull_pipeline.rs:498-511)
+    const uint32_t n_tiles = (uint32_t)((n + kTile - 1) / kTile);
+    CU(cudaMemsetAsync(d->scratch + kNaTicket, 0, 256, s));
+    CU(cudaMemsetAsync(d->scratch + kNaStatus, 0, (size_t)n_views * n_tiles * sizeof(ulonglong2), s));
+    // pageable (stack) sources: the runtime stages them before these calls return
+    CU(cudaMemcpyAsync(d->scratch + kNaMeshAabb, aabb, (size_t)n_meshes * 2 * sizeof(float4), cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(d->scratch + kNaLodTab, lods, (size_t)n_meshes * kMaxLods * sizeof(uint4), cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(d->scratch + kNaLen1, len1, (size_t)n_meshes * 4, cudaMemcpyHostToDevice, s));
+
+    CUtensorMap map;
+    rc = noalloc_model_map(&map, io->model, n);
+    if (rc) return rc;
+    FrameArgs a;
+    memset(&a, 0, sizeof a);
+    a.pos_scale = reinterpret_cast<const float4*>(io->pos_scale);
+    a.rot = reinterpret_cast<const float4*>(io->rot);
+    a.mesh = io->mesh;
+    a.mesh_aabb = reinterpret_cast<const float4*>(d->scratch + kNaMeshAabb);
+    a.lod_tab = reinterpret_cast<const uint4*>(d->scratch + kNaLodTab);
+    a.mesh_len1 = reinterpret_cast<const uint32_t*>(d->scratch + kNaLen1);
+    a.planes_ftz_safe = 1u;
+    for (uint32_t v = 0; v < n_views; ++v) {
+        a.cmds[v] = reinterpret_cast<uint32_t*>(io->cmds[v]);
+        a.visible[v] = io->visible[v];
+        for (int p = 0; p < 6; ++p) {
+            const float* pl = views[v].planes[p];
+            PlaneC& pc = a.planes[v][p];
+            pc.ax = fabsf(pl[0]);
+            pc.ay = fabsf(pl[1]);
+            pc.az = fabsf(pl[2]);
+            pc.px = pl[0];
+            pc.py = pl[1];
+            pc.pz = pl[2];
+            pc.pw = pl[3];
+            for (int x = 0; x < 3; ++x) {
+                const float f = fabsf(pl[x]);
+                if (!(f == 0.f || f >= kFtzSafe)) a.planes_ftz_safe = 0u;  // tiny, or NaN: the scalar-sum body (as rcull_frame)
+            }
+        }
+    }
+    a.counts = io->counts;
+    a.totals = reinterpret_cast<unsigned long long*>(io->index_totals);
+    a.max_views = n_views;
+    a.status = reinterpret_cast<ulonglong2*>(d->scratch + kNaStatus);
+    a.ticket = reinterpret_cast<uint32_t*>(d->scratch + kNaTicket);
+    a.error_flag = io->error;
+    a.ticket_base = 0;  // ticket and descriptors were cleared above: first epoch, first ticket
+    a.epoch = 1;
+    a.n = (uint32_t)n;
+    a.n_tiles = n_tiles;
+    a.n_meshes = n_meshes;
+    a.len_small = len_small;
+    a.draw_index_base = draw_index_base;
+    a.cap_visible = (uint32_t)(io->capacity_visible > 0xffffffffull ? 0xffffffffull : io->capacity_visible);
+    a.cam[0] = cam_pos[0];
+    a.cam[1] = cam_pos[1];
+    a.cam[2] = cam_pos[2];
+    a.lod_d2_max = lod_threshold(lod_distance);
+    const bool mat = !len_small;
+    int grid = d->sm_count * d->blocks_per_sm[n_views][mat];
+    if ((uint32_t)grid > n_tiles) grid = (int)n_tiles;
+    cudaError_t e = cudaSuccess;
+    switch (n_views) {
+        case 1: e = launch<1>(mat, a, map, grid, s); break;
+        case 2: e = launch<2>(mat, a, map, grid, s); break;
+        case 3: e = launch<3>(mat, a, map, grid, s); break;
+        case 4: e = launch<4>(mat, a, map, grid, s); break;
+        case 5: e = launch<5>(mat, a, map, grid, s); break;
+        case 6: e = launch<6>(mat, a, map, grid, s); break;
+        case 7: e = launch<7>(mat, a, map, grid, s); break;
+        case 8: e = launch<8>(mat, a, map, grid, s); break;
+    }
+    if (e != cudaSuccess) return fail(RCULL_ERR_CUDA, "transform_cull_compact launch failed: %s", cudaGetErrorString(e));
     return RCULL_OK;
 }
 
