@@ -223,7 +223,8 @@ def gpu_arm(args, wl):
     # N > 1, record merge: the frame kernel sends its survivors itself; then frame, expand, frame, expand on one stream
     # (--pipeline queues the expand of frame i behind frame i + 1; --expand-sms splits the chip between the two kernels)
     beside = world > 1 and args.merge == "p2p" and args.expand_sms > 0
-    pipelined = world > 1 and args.merge == "p2p" and args.pipeline and not beside
+    ce = world > 1 and args.merge == "p2p" and args.records == "ce"  # records travel by copy engine (rcull_merge_send), not by SM stores
+    pipelined = world > 1 and args.merge == "p2p" and (args.pipeline or ce) and not beside
     ctx = CullContext(n, max_views=n_views, max_meshes=len(meshes), device=local_rank, capacity_tri_indices=tri_cap)
     ctx.set_mesh_table(meshes)
     pv = None
@@ -253,6 +254,9 @@ def gpu_arm(args, wl):
         merger = RecordMerger(ctx, cap, cap_r, dev, symmetric=args.transport != "ipc") if args.merge == "p2p" else ShardMerger(n_views, cap, dev)
         if beside:
             merger.set_overlap(args.expand_sms)
+        if ce:
+            merger.set_transport(True)
+    copy_stream = torch.cuda.Stream(device=dev) if ce else None
     # expand beside the next frame: the chip is split -- the frame kernel's grid leaves expand_sms SMs, the expand's CTAs
     # (one whole SM each) run there, on a second stream
     expand_stream = torch.cuda.Stream(device=dev, priority=0) if beside else None
@@ -266,6 +270,8 @@ def gpu_arm(args, wl):
         if ev0 is not None:
             ev0.record(stream)
         ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, stream=sh)
+        if ce:  # peer copies of this frame's records, behind the frame (the library orders the streams); they travel under the next frame
+            merger.send(copy_stream.cuda_stream)
         pending[0] += 1
 
     def do_merge(final=False):
@@ -337,6 +343,8 @@ def gpu_arm(args, wl):
         c, _ = ctx.frame_host(a_ps, a_rot, a_mesh, views, scene.CAMERA_POS, draw_index_base=lo)
         if merger:
             if record:
+                if ce:
+                    merger.send(ctx.stream)
                 merger.expand(ctx.stream)  # frame_host has completed on the context's stream: the records are out
             else:
                 merger.merge_from_context(ctx, stream=sh)
@@ -456,6 +464,7 @@ def gpu_arm(args, wl):
             t_expand = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps / 1e3
             inbound = 8.0 * (float(vis.sum()) - float(counts.sum())) if record else 24.0 * (float(vis.sum()) - float(counts.sum()))
             merge_report = {
+                "records": ("copy engines" if ce else "stores from the frame kernel") if record else None,
                 "expand_ms_per_step" if record else "ms_per_step": t_expand * 1e3,
                 "step_minus_frame_ms": (t_step - t_frame) / args.steps * 1e3,
                 "expand_queued_behind_next_frame": pipelined, "expand_beside_next_frame": beside,
@@ -480,7 +489,8 @@ def gpu_arm(args, wl):
                 "workload": args.workload, "entities_per_gpu": n, "entities_total": n_total, "n_views": n_views,
                 "half_box": wl["half_box"], "visible_fraction_per_view": [round(float(x), 6) for x in vis / float(n_total)],
                 "sharding": "contiguous range per rank" if world > 1 else "none",
-                "merge": (("records: the frame kernel stores an 8-byte {draw_index, slot} record per survivor into every rank's window over NVLink as it emits (no exchange kernel, no collective); merge_expand rebuilds the merged commands on every GPU"
+                "merge": (((("records: the frame kernel leaves an 8-byte {draw_index, slot} record per survivor in its own window and the copy engines move each rank's region to every peer while the next frame runs (rcull_merge_send: peer copies, no exchange kernel, no collective)") if ce else
+                            "records: the frame kernel stores an 8-byte {draw_index, slot} record per survivor into every rank's window over NVLink as it emits (no exchange kernel, no collective)") + "; merge_expand rebuilds the merged commands on every GPU"
                            + (f"; the expand of frame i runs beside frame i+1 on {args.expand_sms} SMs of its own (second stream)" if beside else
                               "; the expand of frame i is queued behind frame i+1" if pipelined else "; frame, expand, frame, expand"))
                           if args.merge == "p2p" else "NCCL all_gather(counts) + in-place broadcast allgatherv") if world > 1 else "none",
@@ -747,6 +757,7 @@ def main():
     ap.add_argument("--merge", default="p2p", choices=["p2p", "nccl"], help="N > 1: peer-store merge kernel or NCCL broadcasts")
     ap.add_argument("--pipeline", action="store_true", help="N > 1: queue the expand of frame i behind frame i + 1 instead of frame, expand, frame, expand (measured slower: with two record regions the next frame then waits for the peers' expand of the frame before)")
     ap.add_argument("--expand-sms", type=int, default=0, help="N > 1: > 0 splits the chip -- the frame kernel leaves that many SMs to the expand of the previous frame, which runs beside it on a second stream; 0: the expand runs between frames")
+    ap.add_argument("--records", default="push", choices=["push", "ce"], help="N > 1: push = the frame kernel stores its records into every rank's window; ce = it keeps them local and the copy engines move them under the next frame (implies --pipeline)")
     ap.add_argument("--transport", default="auto", choices=["auto", "ipc"], help="N > 1: auto = windows in torch symmetric memory, records through the NVLS multicast mapping when there is one (falls back to CUDA IPC peer stores); ipc = CUDA IPC peer stores")
     ap.add_argument("--no-verify", action="store_true", help="N > 1: skip the oracle / NCCL verification of the merged lists")
     ap.add_argument("--workload", default="16m_5view", choices=sorted(WORKLOADS))

@@ -295,6 +295,17 @@ int rcull_merge_set_multicast_ptr(rcull_merge *m, void *multicast_window);
  * frame i then runs beside frame i + 1 instead of between frames.  0 (default): the expand is an
  * ordinary full-chip kernel on the stream it is given. */
 int rcull_merge_set_overlap(rcull_merge *m, uint32_t expand_sms);
+/* How a rank's records reach the peers.  0 (default): the frame kernel stores every record into every rank's window as
+ * it emits (peer stores, or one multimem.st through the multicast mapping).  1: the COPY ENGINES move them -- the frame
+ * kernel keeps its records, checkpoints, counts and tag in its own window (no store leaves the GPU from an SM, so the
+ * frame runs at its single-GPU speed) and rcull_merge_send(m, stream) queues, on a stream of the caller's choice, one
+ * peer copy of the rank's region per peer and the tag behind it.  The library orders the streams itself: the send waits
+ * for the frame it belongs to (event), the frame two epochs later waits for the send that read the region it
+ * overwrites.  Per merged frame: rcull_frame, rcull_merge_send, rcull_merge_expand (the expand may be queued behind
+ * the next frame; the records then travel while that frame runs).  No kernel is involved in the transfer, so nothing
+ * a spinning expand could be waiting for can be held up behind another kernel.  Callable only between merged frames. */
+int rcull_merge_set_transport(rcull_merge *m, uint32_t transport);
+int rcull_merge_send(rcull_merge *m, void *stream);
 /* Expands the oldest merged frame that has not been expanded yet into this rank's merged lists;
  * asynchronous on stream.  After it, rcull_merge_lists names the results. */
 int rcull_merge_expand(rcull_merge *m, void *stream);

@@ -8,7 +8,9 @@
 
 #include <cmath>
 #include <cstdarg>
+#include <cstddef>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -476,6 +478,7 @@ int rcull_pack_components(uint64_t n, const float* position, const float* rotati
 namespace {
 int merge_frame_issued(rcull_ctx* c, uint32_t n_views, const uint32_t* counts, const unsigned long long* totals, RecordArgs* out, bool empty,
                        cudaStream_t s);
+int merge_frame_launched(rcull_ctx* c, cudaStream_t s);
 }
 extern "C" {
 
@@ -580,6 +583,10 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
     if (e != cudaSuccess) return fail(RCULL_ERR_CUDA, "transform_cull_compact launch failed: %s", cudaGetErrorString(e));
     c->ticket_base += n_tiles + (uint32_t)grid;  // every tile is a ticket, and every CTA draws one ticket past the end
     c->launches += 1;
+    if (c->merge) {
+        int mrc = merge_frame_launched(c, s);
+        if (mrc) return mrc;
+    }
     if (per_mesh && !c->merge) {  // with a merge attached the pairs leave as records and are bucketed after the expand (merged order)
         // Stable bucketing by (mesh, lod) slot: counting sort over tiles of the survivor pairs
         // (rcull_aux.cuh), then one command per non-empty slot.
@@ -1357,6 +1364,16 @@ struct rcull_merge {
     unsigned long long frame_epoch = 0, expand_epoch = 0;  // merged frames issued / expanded
     uint32_t views_of[2] = {0, 0};  // n_views of the frame with that epoch parity
     int expand_sms = 0;             // > 0: the expand runs on that many SMs of its own beside the next frame (rcull_merge_set_overlap)
+    // transport 1 (rcull_merge_set_transport): the frame kernel keeps its records in its OWN window and rcull_merge_send
+    // moves them to the peers with the copy engines -- no SM stores over NVLink, no store traffic beside the frame's own
+    int transport = 0;
+    unsigned long long sent_epoch = 0;          // merged frames whose records rcull_merge_send has queued
+    cudaEvent_t frame_done[2] = {nullptr, nullptr};  // [parity] the frame of that parity has finished on its stream
+    cudaEvent_t sent[2] = {nullptr, nullptr};        // [parity] the copies of that parity's region have finished
+    bool sent_valid[2] = {false, false};
+    cudaStream_t ce_stream[kMaxRanks] = {};  // one stream per peer: the peer copies of a send run on several copy engines at once
+    cudaEvent_t ce_fork = nullptr, ce_join[kMaxRanks] = {};
+    int ce_streams = 0;  // 0: every copy on the caller's stream, one after the other (RCULL_CE_STREAMS=0)
     std::vector<void*> allocs;
 };
 
@@ -1386,8 +1403,19 @@ int merge_frame_issued(rcull_ctx* c, uint32_t n_views, const uint32_t* counts, c
         return fail(RCULL_ERR_INVALID, "merge: two merged frames are in flight -- call rcull_merge_expand before the next rcull_frame");
     RecordArgs r;
     memset(&r, 0, sizeof r);
-    for (uint32_t p = 0; p < m->world; ++p) r.peer[p] = m->peer[p];
-    r.mc = m->mc;
+    if (m->transport == 1) {  // copy engines: the kernel writes into its own window only
+        if (m->frame_epoch != m->sent_epoch)
+            return fail(RCULL_ERR_INVALID, "merge: the records of the last frame have not been sent -- call rcull_merge_send before the next rcull_frame");
+        r.peer[0] = m->window;
+        r.n_dst = 1;
+        // this frame overwrites the region the copies of two frames ago read from
+        if (m->sent_valid[(m->frame_epoch + 1) & 1ull]) CU(cudaStreamWaitEvent(s, m->sent[(m->frame_epoch + 1) & 1ull], 0));
+    } else {
+        for (uint32_t p = 0; p < m->world; ++p) r.peer[p] = m->peer[p];
+        r.n_dst = m->world;
+        r.mc = m->mc;
+    }
+    r.own = m->window;
     r.epoch = ++m->frame_epoch;
     r.base = (size_t)(((r.epoch & 1ull) * m->world + m->rank) * c->cfg.max_views) * m->cap_r * 8;
     r.view_stride = (size_t)m->cap_r * 8;
@@ -1403,9 +1431,17 @@ int merge_frame_issued(rcull_ctx* c, uint32_t n_views, const uint32_t* counts, c
         record_empty_frame<<<1, 32, 0, s>>>(r, counts, totals);
         CU(cudaGetLastError());
         c->launches += 1;
+        if (m->transport == 1) CU(cudaEventRecord(m->frame_done[r.epoch & 1ull], s));
         return RCULL_OK;
     }
     *out = r;
+    return RCULL_OK;
+}
+
+// After the frame kernel of a merged frame has been launched on s (copy-engine transport): the point rcull_merge_send waits for.
+int merge_frame_launched(rcull_ctx* c, cudaStream_t s) {
+    rcull_merge* m = c->merge;
+    if (m->transport == 1) CU(cudaEventRecord(m->frame_done[m->frame_epoch & 1ull], s));
     return RCULL_OK;
 }
 
@@ -1495,6 +1531,15 @@ void rcull_merge_destroy(rcull_merge* m) {
     }
     for (uint32_t p = 0; p < m->world; ++p)
         if (m->opened[p]) cudaIpcCloseMemHandle(m->peer[p]);
+    for (int i = 0; i < 2; ++i) {
+        if (m->frame_done[i]) cudaEventDestroy(m->frame_done[i]);
+        if (m->sent[i]) cudaEventDestroy(m->sent[i]);
+    }
+    for (int i = 0; i < kMaxRanks; ++i) {
+        if (m->ce_stream[i]) cudaStreamDestroy(m->ce_stream[i]);
+        if (m->ce_join[i]) cudaEventDestroy(m->ce_join[i]);
+    }
+    if (m->ce_fork) cudaEventDestroy(m->ce_fork);
     if (m->owns_window && m->window) cudaFree(m->window);
     for (void* p : m->allocs) cudaFree(p);
     delete m;
@@ -1563,6 +1608,83 @@ int rcull_merge_set_overlap(rcull_merge* m, uint32_t expand_sms) {
     CU(cudaSetDevice(m->ctx->cfg.device));
     m->expand_sms = (int)expand_sms;
     m->ctx->reserved_sms = (int)expand_sms;  // the frame kernel's persistent grid leaves them free
+    return RCULL_OK;
+}
+
+int rcull_merge_set_transport(rcull_merge* m, uint32_t transport) {
+    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_set_transport: null argument");
+    if (transport > 1) return fail(RCULL_ERR_INVALID, "rcull_merge_set_transport: 0 = peer stores from the frame kernel, 1 = copy engines");
+    if (m->frame_epoch != m->expand_epoch || m->frame_epoch != (m->transport == 1 ? m->sent_epoch : m->frame_epoch))
+        return fail(RCULL_ERR_INVALID, "rcull_merge_set_transport: a merged frame is in flight");
+    CU(cudaSetDevice(m->ctx->cfg.device));
+    if (transport == 1) {
+        for (int i = 0; i < 2; ++i) {
+            if (!m->frame_done[i]) CU(cudaEventCreateWithFlags(&m->frame_done[i], cudaEventDisableTiming));
+            if (!m->sent[i]) CU(cudaEventCreateWithFlags(&m->sent[i], cudaEventDisableTiming));
+        }
+        const char* e = getenv("RCULL_CE_STREAMS");  // A/B switch: 0 = serial copies on the caller's stream
+        m->ce_streams = (e && atoi(e) == 0) ? 0 : 1;
+        if (m->ce_streams) {
+            if (!m->ce_fork) CU(cudaEventCreateWithFlags(&m->ce_fork, cudaEventDisableTiming));
+            for (uint32_t i = 1; i < m->world; ++i) {
+                if (!m->ce_stream[i]) CU(cudaStreamCreateWithFlags(&m->ce_stream[i], cudaStreamNonBlocking));
+                if (!m->ce_join[i]) CU(cudaEventCreateWithFlags(&m->ce_join[i], cudaEventDisableTiming));
+            }
+        }
+    }
+    m->transport = (int)transport;
+    m->sent_epoch = m->frame_epoch;
+    return RCULL_OK;
+}
+
+int rcull_merge_send(rcull_merge* m, void* stream) {
+    Scope scope("rcull::merge_send (a rank's records -> every peer's window, copy engines)");
+    if (!m) return fail(RCULL_ERR_INVALID, "rcull_merge_send: null argument");
+    if (m->transport != 1) return fail(RCULL_ERR_INVALID, "rcull_merge_send: the merge sends from the frame kernel (rcull_merge_set_transport(m, 1) selects the copy engines)");
+    if (m->sent_epoch >= m->frame_epoch) return fail(RCULL_ERR_INVALID, "rcull_merge_send: no merged frame is waiting to be sent");
+    for (uint32_t p = 0; p < m->world; ++p)
+        if (!m->peer[p]) return fail(RCULL_ERR_INVALID, "merge: peer %u has not been mapped", p);
+    rcull_ctx* c = m->ctx;
+    CU(cudaSetDevice(c->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const unsigned long long epoch = ++m->sent_epoch;
+    const uint32_t par = (uint32_t)(epoch & 1ull);
+    const size_t slot = (size_t)(par * m->world + m->rank) * c->cfg.max_views;
+    const size_t rec_off = slot * m->cap_r * 8, rec_bytes = (size_t)c->cfg.max_views * m->cap_r * 8;
+    const size_t ck_stride = merge_ckpt_view_stride(m->cap_r);
+    const size_t ck_off = m->ckpt_off + slot * ck_stride, ck_bytes = (size_t)c->cfg.max_views * ck_stride;
+    const size_t meta_off = m->sync_off + offsetof(MergeSync, meta) + ((size_t)par * kMaxRanks + m->rank) * 16 * 8;
+    const size_t tag_off = m->sync_off + offsetof(MergeSync, frame_tag) + ((size_t)par * kMaxRanks + m->rank) * 8;
+    CU(cudaStreamWaitEvent(s, m->frame_done[par], 0));  // the frame kernel has written its region, its counts and its own tag
+    // Copies on one stream run in order: for every peer the tag goes last, behind everything it announces.  Peers are
+    // visited starting behind this rank so that the ranks do not all write into the same GPU at once.
+    if (m->ce_streams) {  // one stream per peer, forked from and joined back into the caller's: the copy engines work side by side
+        CU(cudaEventRecord(m->ce_fork, s));
+        for (uint32_t i = 1; i < m->world; ++i) {
+            unsigned char* dst = m->peer[(m->rank + i) % m->world];
+            cudaStream_t t = m->ce_stream[i];
+            CU(cudaStreamWaitEvent(t, m->ce_fork, 0));
+            CU(cudaMemcpyAsync(dst + rec_off, m->window + rec_off, rec_bytes, cudaMemcpyDeviceToDevice, t));
+            CU(cudaMemcpyAsync(dst + ck_off, m->window + ck_off, ck_bytes, cudaMemcpyDeviceToDevice, t));
+            CU(cudaMemcpyAsync(dst + meta_off, m->window + meta_off, 16 * 8, cudaMemcpyDeviceToDevice, t));
+            CU(cudaMemcpyAsync(dst + tag_off, m->window + tag_off, 8, cudaMemcpyDeviceToDevice, t));
+            CU(cudaEventRecord(m->ce_join[i], t));
+            CU(cudaStreamWaitEvent(s, m->ce_join[i], 0));
+        }
+    } else {
+        for (uint32_t i = 1; i < m->world; ++i) {
+            unsigned char* dst = m->peer[(m->rank + i) % m->world];
+            CU(cudaMemcpyAsync(dst + rec_off, m->window + rec_off, rec_bytes, cudaMemcpyDeviceToDevice, s));
+            CU(cudaMemcpyAsync(dst + ck_off, m->window + ck_off, ck_bytes, cudaMemcpyDeviceToDevice, s));
+            CU(cudaMemcpyAsync(dst + meta_off, m->window + meta_off, 16 * 8, cudaMemcpyDeviceToDevice, s));
+        }
+        for (uint32_t i = 1; i < m->world; ++i) {
+            unsigned char* dst = m->peer[(m->rank + i) % m->world];
+            CU(cudaMemcpyAsync(dst + tag_off, m->window + tag_off, 8, cudaMemcpyDeviceToDevice, s));
+        }
+    }
+    CU(cudaEventRecord(m->sent[par], s));
+    m->sent_valid[par] = true;
     return RCULL_OK;
 }
 

@@ -79,7 +79,9 @@ __device__ __forceinline__ void multimem_st_v2(void* mc, uint32_t a, uint32_t b)
 
 // What the frame kernel needs to send records (part of FrameArgs; world == 0: no merge attached).
 struct RecordArgs {
-    unsigned char* peer[kMaxRanks];  // window of every rank (own included), peer-mapped
+    unsigned char* peer[kMaxRanks];  // the n_dst windows this kernel stores into: every rank's (own included, peer-mapped), or --
+                                     // copy-engine transport -- only its own (rcull_merge_send then copies the region to the peers)
+    unsigned char* own;              // this rank's window (mailbox with the peers' expand tags)
     unsigned char* mc;               // NVLS multicast mapping of all windows, or null
     size_t base;                     // byte offset of this frame's records of view 0 from this rank
     size_t view_stride;              // cap_r * 8
@@ -88,7 +90,7 @@ struct RecordArgs {
     uint32_t* cta_done;              // local counter: CTAs of this launch whose records are out
     size_t ckpt_base;                // byte offset of this frame's checkpoints of view 0 from this rank
     size_t ckpt_view_stride;         // bytes of checkpoints per view
-    uint32_t world, rank, cap_r, pad;
+    uint32_t world, rank, cap_r, n_dst;
 };
 
 __device__ __forceinline__ void record_store(const RecordArgs& r, uint32_t view, uint32_t pos, uint32_t draw_index, uint32_t slot) {
@@ -97,7 +99,7 @@ __device__ __forceinline__ void record_store(const RecordArgs& r, uint32_t view,
     if (r.mc != nullptr) {
         multimem_st_v2(r.mc + off, draw_index, slot);
     } else {
-        for (uint32_t p = 0; p < r.world; ++p) *reinterpret_cast<uint2*>(r.peer[p] + off) = make_uint2(draw_index, slot);
+        for (uint32_t p = 0; p < r.n_dst; ++p) *reinterpret_cast<uint2*>(r.peer[p] + off) = make_uint2(draw_index, slot);
     }
 }
 // Every kExpandTile-th survivor of a view also leaves its LOCAL firstIndex behind (4 bytes per 256 survivors): the
@@ -105,12 +107,12 @@ __device__ __forceinline__ void record_store(const RecordArgs& r, uint32_t view,
 __device__ __forceinline__ void record_checkpoint(const RecordArgs& r, uint32_t view, uint32_t pos, uint32_t first_index_local) {
     if (pos >= r.cap_r || (pos % kExpandTile) != 0u) return;
     const size_t off = r.ckpt_base + (size_t)view * r.ckpt_view_stride + (size_t)(pos / kExpandTile) * 4;
-    for (uint32_t p = 0; p < r.world; ++p) *reinterpret_cast<uint32_t*>(r.peer[p] + off) = first_index_local;
+    for (uint32_t p = 0; p < r.n_dst; ++p) *reinterpret_cast<uint32_t*>(r.peer[p] + off) = first_index_local;
 }
 // Back-pressure: the records of epoch e reuse the region of epoch e - 2, which every rank must have expanded.
 __device__ __forceinline__ void record_wait_window_free(const RecordArgs& r, uint32_t tid) {
     if (tid < r.world) {
-        const MergeSync* mine = reinterpret_cast<const MergeSync*>(r.peer[r.rank] + r.sync_off);
+        const MergeSync* mine = reinterpret_cast<const MergeSync*>(r.own + r.sync_off);
         while (ld_acquire_sys(&mine->expand_tag[tid]) + 2 < r.epoch) __nanosleep(200);
     }
 }
@@ -125,14 +127,14 @@ __device__ __forceinline__ void record_finish(const RecordArgs& r, const uint32_
     for (uint32_t k = 0; k < 8; ++k) {
         const unsigned long long c = k < n_views ? ld_relaxed_gpu_u32(counts + k) : 0ull;
         const unsigned long long t = k < n_views ? ld_relaxed(reinterpret_cast<const uint64_t*>(totals + k)) : 0ull;
-        for (uint32_t p = 0; p < r.world; ++p) {
+        for (uint32_t p = 0; p < r.n_dst; ++p) {
             MergeSync* s = reinterpret_cast<MergeSync*>(r.peer[p] + r.sync_off);
             s->meta[par][r.rank][k] = c;
             s->meta[par][r.rank][8 + k] = t;
         }
     }
     __threadfence_system();
-    for (uint32_t p = 0; p < r.world; ++p)
+    for (uint32_t p = 0; p < r.n_dst; ++p)
         st_release_sys(&reinterpret_cast<MergeSync*>(r.peer[p] + r.sync_off)->frame_tag[par][r.rank], r.epoch);
 }
 

@@ -334,6 +334,23 @@ class RecordMerger:
 
         check(self._lib.rcull_merge_set_overlap(self._h, int(expand_sms)))
 
+    def set_transport(self, copy_engines: bool) -> None:
+        """True: the frame kernel keeps its records in its own window and send() moves them to the peers with the copy
+        engines (no SM store crosses NVLink); False (default): the frame kernel stores into every window itself."""
+        from ._lib import check
+
+        check(self._lib.rcull_merge_set_transport(self._h, 1 if copy_engines else 0))
+        self.copy_engines = bool(copy_engines)
+        base = self.transport.split(" + ")[0]
+        self.transport = base + (" + copy engines (rcull_merge_send)" if copy_engines else "")
+
+    def send(self, stream: int) -> None:
+        """Copy-engine transport: queue the peer copies of the last frame's records on `stream` (the library makes the
+        stream wait for that frame, and a later frame for these copies)."""
+        from ._lib import check
+
+        check(self._lib.rcull_merge_send(self._h, self.C.c_void_p(stream)))
+
     def expand(self, stream: int | None = None) -> None:
         """Enqueue the expand of the oldest unexpanded merged frame (default: the current torch stream)."""
         from ._lib import check

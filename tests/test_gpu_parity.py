@@ -396,13 +396,15 @@ def _merged_lists(h, k, n_views, per_mesh=False, cap=None):
     return cmds, vis, int(counts[k]), int(totals[k])
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_record_merge_ranks_in_one_process(world):
+@pytest.mark.parametrize("world,ce", [(2, False), (3, False), (2, True), (3, True)])
+def test_record_merge_ranks_in_one_process(world, ce):
     """SURVEY 8e through the record path (rcull_merge_*): ragged range shards, every rank's frame kernel sends 8-byte
     records into every window, every rank expands them -- the merged lists on EVERY rank are byte-identical to the
     single-range oracle lists (firstIndex = running sum over the merged order, u32 wrap included).  Four frames, so
     both record regions and the epoch tags are reused; one rank has an empty shard.  The ranks share one GPU here, so
-    all frames complete before any expand (no launch ever waits on another launch)."""
+    all frames complete before any expand (no launch ever waits on another launch).  ce: the copy-engine transport
+    (rcull_merge_set_transport(m, 1)): the frame kernels keep their records in their own windows and rcull_merge_send
+    moves them with peer copies."""
     import torch
 
     from renderer_b200 import _lib
@@ -423,6 +425,11 @@ def test_record_merge_ranks_in_one_process(world):
             if ctxs is None:
                 shards = [(lo, hi, ps, rot, mesh) for lo, hi in bounds]
                 ctxs, merges = _merged_rank_setup(shards, n_views, MESHES, cap=n, cap_r=n)
+                if ce:
+                    for h in merges:
+                        _lib.check(lib.rcull_merge_set_transport(h, 1))
+                    with pytest.raises(RcullError, match="copy engines|transport"):
+                        _lib.check(lib.rcull_merge_set_transport(merges[0], 2))
             else:
                 for c, (lo, hi) in zip(ctxs, bounds):
                     if hi > lo:
@@ -430,6 +437,16 @@ def test_record_merge_ranks_in_one_process(world):
             for c, (lo, hi) in zip(ctxs, bounds):
                 c.frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
             torch.cuda.synchronize()
+            if ce:
+                side = torch.cuda.Stream()  # the sends go on a stream of their own: the library orders it behind the frame
+                for h in merges:
+                    _lib.check(lib.rcull_merge_send(h, side.cuda_stream))
+                torch.cuda.synchronize()
+                with pytest.raises(RcullError, match="no merged frame is waiting to be sent"):
+                    _lib.check(lib.rcull_merge_send(merges[0], None))
+            else:
+                with pytest.raises(RcullError, match="copy engines"):
+                    _lib.check(lib.rcull_merge_send(merges[0], None))
             for h in merges:
                 _lib.check(lib.rcull_merge_expand(h, None))
             torch.cuda.synchronize()
@@ -443,13 +460,24 @@ def test_record_merge_ranks_in_one_process(world):
         with pytest.raises(RcullError, match="nothing|no merged frame"):
             _lib.check(lib.rcull_merge_expand(merges[0], None))
         lo, hi = bounds[0]
-        ctxs[0].frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
-        ctxs[0].frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+        def frame_and_send(c, h, lo, hi):
+            c.frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+            if ce:
+                _lib.check(lib.rcull_merge_send(h, None))
+
+        if ce:  # a frame whose records have not been sent blocks the next one
+            ctxs[0].frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+            with pytest.raises(RcullError, match="have not been sent"):
+                ctxs[0].frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+            _lib.check(lib.rcull_merge_send(merges[0], None))
+        else:
+            frame_and_send(ctxs[0], merges[0], lo, hi)
+        frame_and_send(ctxs[0], merges[0], lo, hi)
         with pytest.raises(RcullError, match="in flight"):
             ctxs[0].frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
-        for c, (lo, hi) in list(zip(ctxs, bounds))[1:]:  # let the other ranks catch up so that teardown is clean
-            c.frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
-            c.frame(views, scene.CAMERA_POS, n=hi - lo, draw_index_base=lo)
+        for c, h, (lo, hi) in list(zip(ctxs, merges, bounds))[1:]:  # let the other ranks catch up so that teardown is clean
+            frame_and_send(c, h, lo, hi)
+            frame_and_send(c, h, lo, hi)
         torch.cuda.synchronize()
         for _ in range(2):
             for h in merges:
