@@ -256,6 +256,8 @@ def gpu_arm(args, wl):
             merger.set_overlap(args.expand_sms)
         if ce:
             merger.set_transport(True)
+            if args.send_bound:  # copy what a frame of this scene produces (+ 5 %) view by view instead of the rank's whole slot in one piece
+                merger.set_send_bound([int(c * 1.05) + 1024 for c in own_counts[:n_views]])  # (measured slower: a peer copy costs ~13 us before it moves a byte)
     copy_stream = torch.cuda.Stream(device=dev) if ce else None
     # expand beside the next frame: the chip is split -- the frame kernel's grid leaves expand_sms SMs, the expand's CTAs
     # (one whole SM each) run there, on a second stream
@@ -266,12 +268,14 @@ def gpu_arm(args, wl):
     record = world > 1 and args.merge == "p2p"
     pending = [0]  # merged frames issued and not expanded yet
 
-    def step(ev0=None):
+    def step(ev0=None, sent_ev=None):
         if ev0 is not None:
             ev0.record(stream)
         ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, stream=sh)
         if ce:  # peer copies of this frame's records, behind the frame (the library orders the streams); they travel under the next frame
             merger.send(copy_stream.cuda_stream)
+            if sent_ev is not None:
+                sent_ev.record(copy_stream)
         pending[0] += 1
 
     def do_merge(final=False):
@@ -308,10 +312,11 @@ def gpu_arm(args, wl):
                 flush_l2(flush)
         sync_all()
         ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+        sent_evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)] if ce else None
         launches0 = ctx.launch_count
         with ClockSampler(local_rank) as clocks:
             for i in range(args.steps):
-                step(ev[i][0])
+                step(ev[i][0], sent_evs[i] if ce else None)
                 ev[i][1].record(stream)
                 if merger:
                     do_merge(final=i == args.steps - 1)  # the timed region holds K frames AND K expands
@@ -465,6 +470,8 @@ def gpu_arm(args, wl):
             inbound = 8.0 * (float(vis.sum()) - float(counts.sum())) if record else 24.0 * (float(vis.sum()) - float(counts.sum()))
             merge_report = {
                 "records": ("copy engines" if ce else "stores from the frame kernel") if record else None,
+                # copy-engine transport: from the end of a frame to the last peer copy of its records (rank 0; they run under the next frame)
+                "send_ms_per_step": (sum(e[1].elapsed_time(s_) for e, s_ in zip(ev, sent_evs)) / args.steps) if ce else None,
                 "expand_ms_per_step" if record else "ms_per_step": t_expand * 1e3,
                 "step_minus_frame_ms": (t_step - t_frame) / args.steps * 1e3,
                 "expand_queued_behind_next_frame": pipelined, "expand_beside_next_frame": beside,
@@ -758,6 +765,7 @@ def main():
     ap.add_argument("--pipeline", action="store_true", help="N > 1: queue the expand of frame i behind frame i + 1 instead of frame, expand, frame, expand (measured slower: with two record regions the next frame then waits for the peers' expand of the frame before)")
     ap.add_argument("--expand-sms", type=int, default=0, help="N > 1: > 0 splits the chip -- the frame kernel leaves that many SMs to the expand of the previous frame, which runs beside it on a second stream; 0: the expand runs between frames")
     ap.add_argument("--records", default="push", choices=["push", "ce"], help="N > 1: push = the frame kernel stores its records into every rank's window; ce = it keeps them local and the copy engines move them under the next frame (implies --pipeline)")
+    ap.add_argument("--send-bound", action="store_true", help="--records ce: per-view copies of an estimate of the survivors (rcull_merge_set_send_bound) instead of one copy of the rank's whole slot")
     ap.add_argument("--transport", default="auto", choices=["auto", "ipc"], help="N > 1: auto = windows in torch symmetric memory, records through the NVLS multicast mapping when there is one (falls back to CUDA IPC peer stores); ipc = CUDA IPC peer stores")
     ap.add_argument("--no-verify", action="store_true", help="N > 1: skip the oracle / NCCL verification of the merged lists")
     ap.add_argument("--workload", default="16m_5view", choices=sorted(WORKLOADS))

@@ -306,6 +306,12 @@ int rcull_merge_set_overlap(rcull_merge *m, uint32_t expand_sms);
  * a spinning expand could be waiting for can be held up behind another kernel.  Callable only between merged frames. */
 int rcull_merge_set_transport(rcull_merge *m, uint32_t transport);
 int rcull_merge_send(rcull_merge *m, void *stream);
+/* Copy-engine transport: how many records of each view a send copies (a host cannot know a frame's survivor counts when
+ * it queues the copies; without a bound the whole capacity_per_rank of every view travels).  records_per_view[k] is an
+ * ESTIMATE, rounded up to whole expand tiles of 256 -- e.g. the last known count plus a margin.  It is never a
+ * correctness matter: records past the bound stay in the sender's window and every receiver's expand reads them from
+ * there over NVLink.  n_views = 0 removes the bounds.  Callable only between merged frames. */
+int rcull_merge_set_send_bound(rcull_merge *m, const uint32_t *records_per_view, uint32_t n_views);
 /* Expands the oldest merged frame that has not been expanded yet into this rank's merged lists;
  * asynchronous on stream.  After it, rcull_merge_lists names the results. */
 int rcull_merge_expand(rcull_merge *m, void *stream);

@@ -11,7 +11,7 @@ import sys, json
 try:
     l = json.loads(sys.stdin.read())
     m = l['merge']
-    print(' ms/step', round(l['ms_per_step'], 4), 'value', round(l['value'] / 1e9, 2), 'G/s frame', round(l['roofline']['ms_per_launch'], 4), 'expand', round(m.get('expand_ms_per_step', m.get('ms_per_step', 0)), 4), 'e2e ms', round(l['e2e']['ms_per_step'], 2), 'verified', m['verified_against_oracle_per_rank'], m['verified_against_nccl_allgatherv'], m['transport'])
+    print(' ms/step', round(l['ms_per_step'], 4), 'value', round(l['value'] / 1e9, 2), 'G/s frame', round(l['roofline']['ms_per_launch'], 4), 'expand', round(m.get('expand_ms_per_step', m.get('ms_per_step', 0)), 4), 'e2e ms', round(l['e2e']['ms_per_step'], 2), 'send', m.get('send_ms_per_step'), 'verified', m['verified_against_oracle_per_rank'], m['verified_against_nccl_allgatherv'], m['transport'])
 except Exception as e:
     print(' no line:', e)
 "; }
@@ -19,7 +19,8 @@ if [ -n "$PYTEST" ]; then timeout 300 python -m pytest tests/test_gpu_parity.py 
 for v in $VARIANTS; do
   case $v in
     ce) run ce --records ce ;;
-    ce_serial) RCULL_CE_STREAMS=0 run ce_serial --records ce --no-verify ;;
+    ce_streams) RCULL_CE_STREAMS=1 run ce_streams --records ce --no-verify ;;
+    ce_bound) run ce_bound --records ce --send-bound --no-verify ;;
     ce_noverify) run ce_noverify --records ce --no-verify ;;
     push) run push ;;
     push_pipeline) run push_pipeline --pipeline --no-verify ;;

@@ -157,6 +157,7 @@ SYMBOLS = {
     "rcull_merge_set_overlap": (C.c_int, [_P, _u32]),
     "rcull_merge_set_transport": (C.c_int, [_P, _u32]),
     "rcull_merge_send": (C.c_int, [_P, _P]),
+    "rcull_merge_set_send_bound": (C.c_int, [_P, _P, _u32]),
     "rcull_merge_expand": (C.c_int, [_P, _P]),
     "rcull_merge_lists": (C.c_int, [_P, _u32, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)]),
     "rcull_merge_download": (C.c_int, [_P, _u32, _P, _P, _P, _P, _u64]),

@@ -1347,7 +1347,8 @@ struct rcull_merge {
     uint32_t world = 0, rank = 0;
     uint64_t cap = 0;    // merged list capacity per view
     uint64_t cap_r = 0;  // records one rank can send per view
-    size_t window_bytes = 0, ckpt_off = 0, sync_off = 0;
+    size_t window_bytes = 0, sync_off = 0;
+    size_t slot_stride = 0, ckpt_in_slot = 0, meta_in_slot = 0;  // window layout (rcull_aux.cuh)
     unsigned char* window = nullptr;  // peer-visible: the record regions of every source rank + the mailbox
     bool owns_window = true;          // false: caller's allocation (symmetric memory), rcull_merge_create_on
     unsigned char* peer[kMaxRanks] = {};
@@ -1373,7 +1374,8 @@ struct rcull_merge {
     bool sent_valid[2] = {false, false};
     cudaStream_t ce_stream[kMaxRanks] = {};  // one stream per peer: the peer copies of a send run on several copy engines at once
     cudaEvent_t ce_fork = nullptr, ce_join[kMaxRanks] = {};
-    int ce_streams = 0;  // 0: every copy on the caller's stream, one after the other (RCULL_CE_STREAMS=0)
+    int ce_streams = 0;  // 0 (default): every copy on the caller's stream, one after the other; 1: one stream per peer (RCULL_CE_STREAMS=1)
+    uint32_t send_bound[kMaxViews] = {};  // records of a view that rcull_merge_send copies (rcull_merge_set_send_bound); 0 = the whole capacity
     std::vector<void*> allocs;
 };
 
@@ -1381,13 +1383,18 @@ static_assert(RCULL_MAX_RANKS == kMaxRanks && RCULL_IPC_HANDLE_BYTES == sizeof(c
 
 namespace {
 
-// window = records [2][world][views][cap_r] x 8 B | checkpoints [2][world][views][cap_r / 2048 + 1] x 4 B | mailbox
+// window = [2][world] slots { records [views][cap_r] x 8 B | checkpoints [views][cap_r / 256 + 1] x 4 B | meta 24 x 8 B } | mailbox
+constexpr size_t kMetaBytes = 24 * 8;
 size_t merge_ckpt_view_stride(uint64_t cap_r) { return ((size_t)(cap_r / kExpandTile + 1) * 4 + 15) / 16 * 16; }
-size_t merge_window_layout(uint32_t world, uint32_t max_views, uint64_t cap_r, size_t* ckpt_off, size_t* sync_off) {
-    const size_t rec = (size_t)2 * world * max_views * cap_r * 8;
-    const size_t co = (rec + 255) / 256 * 256;
-    const size_t so = (co + (size_t)2 * world * max_views * merge_ckpt_view_stride(cap_r) + 255) / 256 * 256;
-    if (ckpt_off) *ckpt_off = co;
+size_t merge_window_layout(uint32_t world, uint32_t max_views, uint64_t cap_r, size_t* slot_stride, size_t* ckpt_in_slot, size_t* meta_in_slot,
+                           size_t* sync_off) {
+    const size_t ck = (size_t)max_views * cap_r * 8;  // cap_r is even: 16-byte aligned
+    const size_t mt = ck + (size_t)max_views * merge_ckpt_view_stride(cap_r);
+    const size_t st = (mt + kMetaBytes + 255) / 256 * 256;
+    const size_t so = (size_t)2 * world * st;
+    if (slot_stride) *slot_stride = st;
+    if (ckpt_in_slot) *ckpt_in_slot = ck;
+    if (meta_in_slot) *meta_in_slot = mt;
     if (sync_off) *sync_off = so;
     return so + sizeof(MergeSync);
 }
@@ -1417,10 +1424,11 @@ int merge_frame_issued(rcull_ctx* c, uint32_t n_views, const uint32_t* counts, c
     }
     r.own = m->window;
     r.epoch = ++m->frame_epoch;
-    r.base = (size_t)(((r.epoch & 1ull) * m->world + m->rank) * c->cfg.max_views) * m->cap_r * 8;
+    r.base = (size_t)((r.epoch & 1ull) * m->world + m->rank) * m->slot_stride;
     r.view_stride = (size_t)m->cap_r * 8;
     r.ckpt_view_stride = merge_ckpt_view_stride(m->cap_r);
-    r.ckpt_base = m->ckpt_off + (size_t)(((r.epoch & 1ull) * m->world + m->rank) * c->cfg.max_views) * r.ckpt_view_stride;
+    r.ckpt_base = r.base + m->ckpt_in_slot;
+    r.meta_base = r.base + m->meta_in_slot;
     r.sync_off = m->sync_off;
     r.cta_done = m->ticket + 2;
     r.world = m->world;
@@ -1474,7 +1482,7 @@ int merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t capacity,
     m->cap_r = capacity_per_rank;
     const uint32_t mv = c->cfg.max_views;
     const bool per_mesh = c->cfg.output_mode == RCULL_PER_MESH_INSTANCED;
-    m->window_bytes = merge_window_layout(world, mv, m->cap_r, &m->ckpt_off, &m->sync_off);
+    m->window_bytes = merge_window_layout(world, mv, m->cap_r, &m->slot_stride, &m->ckpt_in_slot, &m->meta_in_slot, &m->sync_off);
     int rc = 0;
 #define MTRY(x)                      \
     if ((rc = (x)) != 0) {           \
@@ -1502,6 +1510,7 @@ int merge_create(rcull_ctx* c, uint32_t world, uint32_t rank, uint64_t capacity,
     MTRY(merge_alloc(m, &m->ticket, 4));
 #undef MTRY
     cudaMemset(m->window + m->sync_off, 0, sizeof(MergeSync));
+    for (uint32_t sl = 0; sl < 2 * world; ++sl) cudaMemset(m->window + (size_t)sl * m->slot_stride + m->meta_in_slot, 0, kMetaBytes);
     cudaMemset(m->counts, 0, kMaxViews * 4);
     cudaMemset(m->totals, 0, kMaxViews * 8);
     cudaMemset(m->ticket, 0, 16);
@@ -1547,7 +1556,7 @@ void rcull_merge_destroy(rcull_merge* m) {
 
 int rcull_merge_window_bytes(rcull_ctx* c, uint32_t world, uint64_t capacity_per_rank, uint64_t* bytes) {
     if (!c || !bytes || world < 1 || world > kMaxRanks || capacity_per_rank == 0) return fail(RCULL_ERR_INVALID, "rcull_merge_window_bytes: bad argument");
-    *bytes = merge_window_layout(world, c->cfg.max_views, (capacity_per_rank + 1) & ~1ull, nullptr, nullptr);
+    *bytes = merge_window_layout(world, c->cfg.max_views, (capacity_per_rank + 1) & ~1ull, nullptr, nullptr, nullptr, nullptr);
     return RCULL_OK;
 }
 
@@ -1622,8 +1631,8 @@ int rcull_merge_set_transport(rcull_merge* m, uint32_t transport) {
             if (!m->frame_done[i]) CU(cudaEventCreateWithFlags(&m->frame_done[i], cudaEventDisableTiming));
             if (!m->sent[i]) CU(cudaEventCreateWithFlags(&m->sent[i], cudaEventDisableTiming));
         }
-        const char* e = getenv("RCULL_CE_STREAMS");  // A/B switch: 0 = serial copies on the caller's stream
-        m->ce_streams = (e && atoi(e) == 0) ? 0 : 1;
+        const char* e = getenv("RCULL_CE_STREAMS");  // A/B switch: 1 = one stream per peer instead of serial copies on the caller's stream
+        m->ce_streams = (e && atoi(e) != 0) ? 1 : 0;
         if (m->ce_streams) {
             if (!m->ce_fork) CU(cudaEventCreateWithFlags(&m->ce_fork, cudaEventDisableTiming));
             for (uint32_t i = 1; i < m->world; ++i) {
@@ -1634,6 +1643,26 @@ int rcull_merge_set_transport(rcull_merge* m, uint32_t transport) {
     }
     m->transport = (int)transport;
     m->sent_epoch = m->frame_epoch;
+    return RCULL_OK;
+}
+
+int rcull_merge_set_send_bound(rcull_merge* m, const uint32_t* records_per_view, uint32_t n_views) {
+    if (!m || (n_views && !records_per_view)) return fail(RCULL_ERR_INVALID, "rcull_merge_set_send_bound: null argument");
+    if (m->transport != 1) return fail(RCULL_ERR_INVALID, "rcull_merge_set_send_bound: only the copy-engine transport has a send (rcull_merge_set_transport(m, 1))");
+    if (n_views > m->ctx->cfg.max_views) return fail(RCULL_ERR_INVALID, "rcull_merge_set_send_bound: %u views of %u", n_views, m->ctx->cfg.max_views);
+    if (m->frame_epoch != m->expand_epoch || m->frame_epoch != m->sent_epoch) return fail(RCULL_ERR_INVALID, "rcull_merge_set_send_bound: a merged frame is in flight");
+    CU(cudaSetDevice(m->ctx->cfg.device));
+    CU(cudaDeviceSynchronize());
+    unsigned long long words[2][8] = {};
+    for (uint32_t v = 0; v < (uint32_t)kMaxViews; ++v) {
+        uint64_t b = v < n_views ? ((uint64_t)records_per_view[v] + kExpandTile - 1) / kExpandTile * kExpandTile : 0;  // whole expand tiles
+        if (v >= n_views || b >= m->cap_r) b = 0;  // 0: the whole capacity is copied, nothing is left behind
+        m->send_bound[v] = (uint32_t)b;
+        words[0][v] = words[1][v] = b ? b + 1 : 0;
+    }
+    // the bound words ride behind this rank's counts in its own mailbox slot (both parities); every send copies them along
+    for (uint32_t par = 0; par < 2; ++par)
+        CU(cudaMemcpy(m->window + (size_t)(par * m->world + m->rank) * m->slot_stride + m->meta_in_slot + 16 * 8, words[par], 8 * 8, cudaMemcpyHostToDevice));
     return RCULL_OK;
 }
 
@@ -1649,24 +1678,36 @@ int rcull_merge_send(rcull_merge* m, void* stream) {
     cudaStream_t s = (cudaStream_t)stream;
     const unsigned long long epoch = ++m->sent_epoch;
     const uint32_t par = (uint32_t)(epoch & 1ull);
-    const size_t slot = (size_t)(par * m->world + m->rank) * c->cfg.max_views;
-    const size_t rec_off = slot * m->cap_r * 8, rec_bytes = (size_t)c->cfg.max_views * m->cap_r * 8;
-    const size_t ck_stride = merge_ckpt_view_stride(m->cap_r);
-    const size_t ck_off = m->ckpt_off + slot * ck_stride, ck_bytes = (size_t)c->cfg.max_views * ck_stride;
-    const size_t meta_off = m->sync_off + offsetof(MergeSync, meta) + ((size_t)par * kMaxRanks + m->rank) * 16 * 8;
+    // The slot of (parity, this rank): records | checkpoints | meta in one piece.  A peer copy costs ~13 us before its
+    // first byte moves (profiles/p2p_copy_bench.py), so the NUMBER of copies is what matters: one for the slot, one for
+    // the tag.  With send bounds the records go view by view (what the bound covers; the rest stays here and the
+    // receivers read it over NVLink themselves) and the checkpoints + meta follow as one copy.
+    const size_t slot_off = (size_t)(par * m->world + m->rank) * m->slot_stride;
+    const size_t slot_bytes = m->meta_in_slot + kMetaBytes;
+    bool bounded = false;
+    for (uint32_t v = 0; v < c->cfg.max_views; ++v) bounded = bounded || m->send_bound[v] != 0;
+    auto copy_slot = [&](unsigned char* dst, cudaStream_t t) -> cudaError_t {
+        if (!bounded) return cudaMemcpyAsync(dst + slot_off, m->window + slot_off, slot_bytes, cudaMemcpyDeviceToDevice, t);
+        const uint32_t nv = m->views_of[par];
+        for (uint32_t v = 0; v < nv; ++v) {
+            const size_t off = slot_off + (size_t)v * m->cap_r * 8, bytes = (size_t)(m->send_bound[v] ? m->send_bound[v] : m->cap_r) * 8;
+            cudaError_t e = cudaMemcpyAsync(dst + off, m->window + off, bytes, cudaMemcpyDeviceToDevice, t);
+            if (e != cudaSuccess) return e;
+        }
+        return cudaMemcpyAsync(dst + slot_off + m->ckpt_in_slot, m->window + slot_off + m->ckpt_in_slot, slot_bytes - m->ckpt_in_slot,
+                               cudaMemcpyDeviceToDevice, t);
+    };
     const size_t tag_off = m->sync_off + offsetof(MergeSync, frame_tag) + ((size_t)par * kMaxRanks + m->rank) * 8;
-    CU(cudaStreamWaitEvent(s, m->frame_done[par], 0));  // the frame kernel has written its region, its counts and its own tag
+    CU(cudaStreamWaitEvent(s, m->frame_done[par], 0));  // the frame kernel has written its slot and its own tag
     // Copies on one stream run in order: for every peer the tag goes last, behind everything it announces.  Peers are
     // visited starting behind this rank so that the ranks do not all write into the same GPU at once.
-    if (m->ce_streams) {  // one stream per peer, forked from and joined back into the caller's: the copy engines work side by side
+    if (m->ce_streams) {  // one stream per peer, forked from and joined back into the caller's (RCULL_CE_STREAMS=1; measured no faster, and heavier on the host)
         CU(cudaEventRecord(m->ce_fork, s));
         for (uint32_t i = 1; i < m->world; ++i) {
             unsigned char* dst = m->peer[(m->rank + i) % m->world];
             cudaStream_t t = m->ce_stream[i];
             CU(cudaStreamWaitEvent(t, m->ce_fork, 0));
-            CU(cudaMemcpyAsync(dst + rec_off, m->window + rec_off, rec_bytes, cudaMemcpyDeviceToDevice, t));
-            CU(cudaMemcpyAsync(dst + ck_off, m->window + ck_off, ck_bytes, cudaMemcpyDeviceToDevice, t));
-            CU(cudaMemcpyAsync(dst + meta_off, m->window + meta_off, 16 * 8, cudaMemcpyDeviceToDevice, t));
+            CU(copy_slot(dst, t));
             CU(cudaMemcpyAsync(dst + tag_off, m->window + tag_off, 8, cudaMemcpyDeviceToDevice, t));
             CU(cudaEventRecord(m->ce_join[i], t));
             CU(cudaStreamWaitEvent(s, m->ce_join[i], 0));
@@ -1674,12 +1715,7 @@ int rcull_merge_send(rcull_merge* m, void* stream) {
     } else {
         for (uint32_t i = 1; i < m->world; ++i) {
             unsigned char* dst = m->peer[(m->rank + i) % m->world];
-            CU(cudaMemcpyAsync(dst + rec_off, m->window + rec_off, rec_bytes, cudaMemcpyDeviceToDevice, s));
-            CU(cudaMemcpyAsync(dst + ck_off, m->window + ck_off, ck_bytes, cudaMemcpyDeviceToDevice, s));
-            CU(cudaMemcpyAsync(dst + meta_off, m->window + meta_off, 16 * 8, cudaMemcpyDeviceToDevice, s));
-        }
-        for (uint32_t i = 1; i < m->world; ++i) {
-            unsigned char* dst = m->peer[(m->rank + i) % m->world];
+            CU(copy_slot(dst, s));
             CU(cudaMemcpyAsync(dst + tag_off, m->window + tag_off, 8, cudaMemcpyDeviceToDevice, s));
         }
     }
@@ -1706,7 +1742,9 @@ int rcull_merge_expand(rcull_merge* m, void* stream) {
     for (uint32_t p = 0; p < m->world; ++p) a.peer[p] = m->peer[p];
     a.sync_off = m->sync_off;
     a.view_stride = (size_t)m->cap_r * 8;
-    a.ckpt_off = m->ckpt_off;
+    a.slot_stride = m->slot_stride;
+    a.ckpt_in_slot = m->ckpt_in_slot;
+    a.meta_in_slot = m->meta_in_slot;
     a.ckpt_view_stride = merge_ckpt_view_stride(m->cap_r);
     a.epoch = epoch;
     a.world = m->world;

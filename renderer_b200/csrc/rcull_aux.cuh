@@ -39,15 +39,19 @@ __global__ void __launch_bounds__(256) rebase_into(const uint32_t* __restrict__ 
 // (count, index total) words and a tag into every window.  Every rank then EXPANDS the records of all ranks
 // into the merged draw lists locally (merge_expand): indexCount / vertexOffset come from the mesh table,
 // firstIndex from a running sum over the merged order -- the rank prefix of SURVEY 8e falls out of the same scan.
-// Window layout (identical on every rank):
-//   records of parity p (= frame epoch & 1), source rank r, view k:  ((p * world + r) * max_views + k) * cap_r * 8
-//   MergeSync mailbox at sync_off.
+// Window layout (identical on every rank): one SLOT per (parity p = frame epoch & 1, source rank r) at
+// (p * world + r) * slot_stride, holding everything that rank has to say about that frame in one contiguous piece --
+//   records [max_views][cap_r] x 8 B | checkpoints [max_views][cap_r / 256 + 1] x 4 B | meta: 24 x 8 B
+// (meta = counts[8], index totals[8], send bounds[8]) -- so that the copy-engine transport moves a slot with ONE peer
+// copy; then the MergeSync mailbox (tags) at sync_off.
 constexpr int kMaxRanks = 8;
 constexpr int kExpandTile = 256;  // records per expand tile (one warp) = the sender's checkpoint spacing
 
 struct MergeSync {
-    // [parity][source rank]: counts[8] then index totals[8] of the frame whose epoch is frame_tag[parity][rank]
-    unsigned long long meta[2][kMaxRanks][16];
+    // A slot's meta words: counts[8] then index totals[8] of the frame whose epoch is frame_tag[parity][rank], then
+    // send bounds[8]: b + 1 = only the first b records of that view were DELIVERED into this window, the rest stay in
+    // the source rank's own window and are read from there (copy-engine transport with rcull_merge_set_send_bound);
+    // 0 = everything was delivered.  The frame kernel writes words 0..15 only.
     unsigned long long frame_tag[2][kMaxRanks];  // every record of that frame from that rank has landed in this window
     unsigned long long expand_tag[kMaxRanks];    // rank r has finished reading ITS window for every epoch <= this
 };
@@ -86,6 +90,7 @@ struct RecordArgs {
     size_t base;                     // byte offset of this frame's records of view 0 from this rank
     size_t view_stride;              // cap_r * 8
     size_t sync_off;                 // MergeSync inside the window
+    size_t meta_base;                // byte offset of this frame's meta words from this rank
     unsigned long long epoch;        // number of this merged frame (the same on every rank), from 1
     uint32_t* cta_done;              // local counter: CTAs of this launch whose records are out
     size_t ckpt_base;                // byte offset of this frame's checkpoints of view 0 from this rank
@@ -128,9 +133,9 @@ __device__ __forceinline__ void record_finish(const RecordArgs& r, const uint32_
         const unsigned long long c = k < n_views ? ld_relaxed_gpu_u32(counts + k) : 0ull;
         const unsigned long long t = k < n_views ? ld_relaxed(reinterpret_cast<const uint64_t*>(totals + k)) : 0ull;
         for (uint32_t p = 0; p < r.n_dst; ++p) {
-            MergeSync* s = reinterpret_cast<MergeSync*>(r.peer[p] + r.sync_off);
-            s->meta[par][r.rank][k] = c;
-            s->meta[par][r.rank][8 + k] = t;
+            unsigned long long* mt = reinterpret_cast<unsigned long long*>(r.peer[p] + r.meta_base);
+            mt[k] = c;
+            mt[8 + k] = t;
         }
     }
     __threadfence_system();
@@ -166,7 +171,8 @@ constexpr int kExpandStageWords = kExpandTile * 5 + 12;  // + the alignment shif
 struct ExpandArgs {
     const unsigned char* window;       // this rank's window
     unsigned char* peer[kMaxRanks];    // every rank's window (for the expand tag)
-    size_t sync_off, view_stride, ckpt_off, ckpt_view_stride;
+    size_t sync_off, view_stride, ckpt_view_stride;
+    size_t slot_stride, ckpt_in_slot, meta_in_slot;  // a (parity, rank) slot: records, then checkpoints, then meta words
     unsigned long long epoch;
     uint32_t world, rank, n_views, max_views, cap_r, cap;
     uint32_t* cmds[8];                 // merged lists (5 words per command), or slot keys in pair mode
@@ -186,7 +192,7 @@ __device__ __forceinline__ void merge_expand_body(const ExpandArgs& a) {
     __shared__ uint32_t s_pos[8][kMaxRanks + 1];  // merged position of the rank's first survivor (exclusive prefix of s_cnt, clamped to cap)
     __shared__ uint32_t s_first[8][kMaxRanks];    // firstIndex the rank's first survivor starts from (exclusive prefix of the index totals)
     __shared__ uint32_t s_tiles[8 * kMaxRanks + 1];  // exclusive prefix of the tile counts over (view, rank)
-    __shared__ unsigned long long s_meta[2][8][kMaxRanks];  // counts, index totals: one mailbox word per thread
+    __shared__ unsigned long long s_meta[3][8][kMaxRanks];  // counts, index totals, send bounds: one mailbox word per thread
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t par = (uint32_t)(a.epoch & 1ull);
     const MergeSync* mine = reinterpret_cast<const MergeSync*>(a.window + a.sync_off);
@@ -194,9 +200,11 @@ __device__ __forceinline__ void merge_expand_body(const ExpandArgs& a) {
         while (ld_acquire_sys(&mine->frame_tag[par][tid]) != a.epoch) __nanosleep(200);
     }
     __syncthreads();
-    if (tid < 2 * 8 * kMaxRanks) {
+    if (tid < 3 * 8 * kMaxRanks) {
         const uint32_t what = tid / (8 * kMaxRanks), k = (tid / kMaxRanks) % 8, r = tid % kMaxRanks;
-        s_meta[what][k][r] = (k < a.n_views && r < a.world) ? ld_relaxed_sys(&mine->meta[par][r][what * 8 + k]) : 0ull;
+        s_meta[what][k][r] = (k < a.n_views && r < a.world)
+                                 ? ld_relaxed_sys(reinterpret_cast<const unsigned long long*>(a.window + (size_t)(par * a.world + r) * a.slot_stride + a.meta_in_slot) + what * 8 + k)
+                                 : 0ull;
     }
     __syncthreads();
     if (tid < a.n_views) {
@@ -237,7 +245,11 @@ __device__ __forceinline__ void merge_expand_body(const ExpandArgs& a) {
         const uint32_t k = kr / a.world, r = kr % a.world, c = t - s_tiles[kr];
         const uint32_t n_kr = s_cnt[k][r], first_local = c * kExpandTile;
         const uint32_t n_here = n_kr - first_local < (uint32_t)kExpandTile ? n_kr - first_local : (uint32_t)kExpandTile;
-        const uint2* recs = reinterpret_cast<const uint2*>(a.window + ((size_t)(par * a.world + r) * a.max_views + k) * a.view_stride) + first_local;
+        // delivered into this window, or -- past the sender's bound -- still in the sender's own window (same offset there)
+        const uint32_t bound1 = (uint32_t)s_meta[2][k][r];
+        const unsigned char* src = (bound1 == 0u || r == a.rank || first_local + n_here <= bound1 - 1u) ? a.window : a.peer[r];
+        const size_t slot = (size_t)(par * a.world + r) * a.slot_stride;
+        const uint2* recs = reinterpret_cast<const uint2*>(src + slot + (size_t)k * a.view_stride) + first_local;
         const uint32_t dst0 = s_pos[k][r] + first_local;  // merged position of the tile's first survivor
         uint2 rec[kExpandItems];  // lane-striped: coalesced 8-byte loads
 #pragma unroll
@@ -251,7 +263,7 @@ __device__ __forceinline__ void merge_expand_body(const ExpandArgs& a) {
                 }
             continue;
         }
-        const uint32_t ckpt = __ldcg(reinterpret_cast<const uint32_t*>(a.window + a.ckpt_off + ((size_t)(par * a.world + r) * a.max_views + k) * a.ckpt_view_stride) + c);
+        const uint32_t ckpt = __ldcg(reinterpret_cast<const uint32_t*>(a.window + slot + a.ckpt_in_slot + (size_t)k * a.ckpt_view_stride) + c);  // checkpoints are always delivered whole
         uint32_t len[kExpandItems], voff[kExpandItems];
 #pragma unroll
         for (int q = 0; q < kExpandItems; ++q) {

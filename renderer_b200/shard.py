@@ -344,6 +344,14 @@ class RecordMerger:
         base = self.transport.split(" + ")[0]
         self.transport = base + (" + copy engines (rcull_merge_send)" if copy_engines else "")
 
+    def set_send_bound(self, records_per_view) -> None:
+        """Copy-engine transport: estimated survivors per view (+ margin) that a send copies; what a frame produces past
+        it stays in this rank's window and the receivers read it from there.  None / empty removes the bounds."""
+        from ._lib import check, ptr
+
+        b = np.ascontiguousarray(records_per_view if records_per_view is not None else [], dtype=np.uint32)
+        check(self._lib.rcull_merge_set_send_bound(self._h, ptr(b) if len(b) else None, len(b)))
+
     def send(self, stream: int) -> None:
         """Copy-engine transport: queue the peer copies of the last frame's records on `stream` (the library makes the
         stream wait for that frame, and a later frame for these copies)."""

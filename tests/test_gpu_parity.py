@@ -426,8 +426,12 @@ def test_record_merge_ranks_in_one_process(world, ce):
                 shards = [(lo, hi, ps, rot, mesh) for lo, hi in bounds]
                 ctxs, merges = _merged_rank_setup(shards, n_views, MESHES, cap=n, cap_r=n)
                 if ce:
-                    for h in merges:
+                    for r, h in enumerate(merges):
                         _lib.check(lib.rcull_merge_set_transport(h, 1))
+                        # rank 0 copies at most 512 / 256 / all records of the three views: the rest is read from its window by the others
+                        if r == 0:
+                            bound = np.array([512, 1, 0], np.uint32)
+                            _lib.check(lib.rcull_merge_set_send_bound(h, _lib.ptr(bound), 3))
                     with pytest.raises(RcullError, match="copy engines|transport"):
                         _lib.check(lib.rcull_merge_set_transport(merges[0], 2))
             else:
