@@ -223,7 +223,10 @@ def gpu_arm(args, wl):
     # N > 1, record merge: the frame kernel sends its survivors itself; then frame, expand, frame, expand on one stream
     # (--pipeline queues the expand of frame i behind frame i + 1; --expand-sms splits the chip between the two kernels)
     beside = world > 1 and args.merge == "p2p" and args.expand_sms > 0
-    ce = world > 1 and args.merge == "p2p" and args.records == "ce"  # records travel by copy engine (rcull_merge_send), not by SM stores
+    # records travel by copy engine (rcull_merge_send) or by SM stores from the frame kernel; auto: copy engines beyond 4 GPUs, where
+    # the stores of 7 peers' worth of records slow the frame kernel down more than the copies cost (N = 8: 0.68 against 0.79 ms
+    # per step; N = 2: 0.49 against 0.47)
+    ce = world > 1 and args.merge == "p2p" and (args.records == "ce" or (args.records == "auto" and world > 4))
     pipelined = world > 1 and args.merge == "p2p" and (args.pipeline or ce) and not beside
     ctx = CullContext(n, max_views=n_views, max_meshes=len(meshes), device=local_rank, capacity_tri_indices=tri_cap)
     ctx.set_mesh_table(meshes)
@@ -267,16 +270,29 @@ def gpu_arm(args, wl):
     flush = torch.zeros((2, 256 * 1024 * 1024), dtype=torch.uint8, device=dev) if n * 36 < 256e6 else None
     record = world > 1 and args.merge == "p2p"
     pending = [0]  # merged frames issued and not expanded yet
+    unsent = [None]  # copy-engine transport, send queued behind the expand: the timing event of the frame that still has to be sent
 
     def step(ev0=None, sent_ev=None):
         if ev0 is not None:
             ev0.record(stream)
         ctx.frame(views, scene.CAMERA_POS, draw_index_base=lo, stream=sh)
-        if ce:  # peer copies of this frame's records, behind the frame (the library orders the streams); they travel under the next frame
+        if ce and args.send_early:  # peer copies right behind the frame (the library orders the streams): they then also run beside the expand of the frame before
             merger.send(copy_stream.cuda_stream)
             if sent_ev is not None:
                 sent_ev.record(copy_stream)
+        unsent[0] = sent_ev if (ce and not args.send_early) else None
         pending[0] += 1
+
+    def send_behind_expand():
+        # the copies of frame i start when the expand of frame i - 1 is through, so that they share the memory system with the
+        # next frame only (the expand is HBM-bound and lost 60 % beside 280 MB of copy traffic; the frame is latency-bound)
+        e = frame_ev[pending[0] & 1]
+        e.record(stream)
+        copy_stream.wait_event(e)
+        merger.send(copy_stream.cuda_stream)
+        if unsent[0] is not None:
+            unsent[0].record(copy_stream)
+        unsent[0] = None
 
     def do_merge(final=False):
         if beside:
@@ -289,9 +305,15 @@ def gpu_arm(args, wl):
                 stream.wait_stream(expand_stream)  # the timed region ends when the last expand has
         elif record:
             # pipelined: frame i + 1 is already queued when frame i is expanded; the last step expands both
+            late = ce and not args.send_early
             while pending[0] > (0 if (final or not pipelined) else 1):
+                if late and pending[0] == 1:
+                    send_behind_expand()  # the newest frame has to be sent before it can be expanded
+                    late = False
                 merger.expand(sh)
                 pending[0] -= 1
+            if late:
+                send_behind_expand()
         else:
             pending[0] = 0
             merger.merge_from_context(ctx, stream=sh)
@@ -764,7 +786,8 @@ def main():
     ap.add_argument("--merge", default="p2p", choices=["p2p", "nccl"], help="N > 1: peer-store merge kernel or NCCL broadcasts")
     ap.add_argument("--pipeline", action="store_true", help="N > 1: queue the expand of frame i behind frame i + 1 instead of frame, expand, frame, expand (measured slower: with two record regions the next frame then waits for the peers' expand of the frame before)")
     ap.add_argument("--expand-sms", type=int, default=0, help="N > 1: > 0 splits the chip -- the frame kernel leaves that many SMs to the expand of the previous frame, which runs beside it on a second stream; 0: the expand runs between frames")
-    ap.add_argument("--records", default="push", choices=["push", "ce"], help="N > 1: push = the frame kernel stores its records into every rank's window; ce = it keeps them local and the copy engines move them under the next frame (implies --pipeline)")
+    ap.add_argument("--records", default="auto", choices=["auto", "push", "ce"], help="N > 1: push = the frame kernel stores its records into every rank's window; ce = it keeps them local and the copy engines move them under the next frame (implies --pipeline); auto = ce beyond 4 GPUs")
+    ap.add_argument("--send-early", action="store_true", help="--records ce: queue a frame's peer copies right behind the frame instead of behind the expand of the frame before")
     ap.add_argument("--send-bound", action="store_true", help="--records ce: per-view copies of an estimate of the survivors (rcull_merge_set_send_bound) instead of one copy of the rank's whole slot")
     ap.add_argument("--transport", default="auto", choices=["auto", "ipc"], help="N > 1: auto = windows in torch symmetric memory, records through the NVLS multicast mapping when there is one (falls back to CUDA IPC peer stores); ipc = CUDA IPC peer stores")
     ap.add_argument("--no-verify", action="store_true", help="N > 1: skip the oracle / NCCL verification of the merged lists")

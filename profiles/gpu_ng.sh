@@ -20,10 +20,12 @@ for v in $VARIANTS; do
   case $v in
     ce) run ce --records ce ;;
     ce_streams) RCULL_CE_STREAMS=1 run ce_streams --records ce --no-verify ;;
+    ce_early) run ce_early --records ce --send-early --no-verify ;;
     ce_bound) run ce_bound --records ce --send-bound --no-verify ;;
     ce_noverify) run ce_noverify --records ce --no-verify ;;
-    push) run push ;;
-    push_pipeline) run push_pipeline --pipeline --no-verify ;;
+    push) run push --records push ;;
+    default) run default ;;
+    push_pipeline) run push_pipeline --records push --pipeline --no-verify ;;
     ipc_ce) run ipc_ce --records ce --transport ipc --no-verify ;;
     ipc) run ipc --transport ipc --no-verify ;;
     nccl) run nccl --merge nccl ;;
