@@ -102,6 +102,7 @@ struct rcull_ctx {
     uint32_t* bucket_hist = nullptr;  // per-mesh mode scratch: [tiles][slots] counts, see rcull_aux.cuh
     uint32_t* slot_total = nullptr;
     uint32_t* slot_base = nullptr;
+    uint32_t* bucket_done = nullptr;  // [kMaxViews] bucket_colscan CTAs through, per view (zero between launches)
     size_t bucket_hist_words = 0;
     uint64_t cap_cmds = 0;  // command capacity per view: cap_vis, or max_meshes * 6 in per-mesh mode
     int reserved_sms = 0;  // SMs the frame kernel's grid leaves to a concurrent expand kernel (rcull_merge_set_overlap)
@@ -179,6 +180,39 @@ float lod_threshold(float d) {
     float x;
     memcpy(&x, &lo, 4);
     return x;
+}
+
+// One kernel of the bucketing chain as a programmatic dependent launch: its CTAs may be placed while the kernel in front
+// of it on the stream drains (they wait in pdl_wait()).  Falls back to an ordinary launch where the attribute is refused.
+template <typename K>
+cudaError_t launch_dependent(K kernel, dim3 grid, unsigned block, cudaStream_t s, const BucketArgs& b) {
+    static bool pdl = getenv("RCULL_NO_PDL") == nullptr;
+    if (pdl) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = grid;
+        cfg.blockDim = dim3(block);
+        cfg.dynamicSmemBytes = 0;
+        cfg.stream = s;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        if (cudaLaunchKernelEx(&cfg, kernel, b) == cudaSuccess) return cudaSuccess;
+        (void)cudaGetLastError();  // not supported here (stream kind, driver): ordinary launches from now on
+        pdl = false;
+    }
+    kernel<<<grid, block, 0, s>>>(b);
+    return cudaGetLastError();
+}
+
+// bucket_hist -> bucket_colscan (+ commands, by its last CTA) -> bucket_scatter (rcull_aux.cuh)
+cudaError_t launch_bucketing(const BucketArgs& b, dim3 sweep_grid, uint32_t n_slots, uint32_t n_views, cudaStream_t s) {
+    cudaError_t e = launch_dependent(bucket_hist, sweep_grid, kBucketWarps * 32, s, b);
+    if (e != cudaSuccess) return e;
+    e = launch_dependent(bucket_colscan, dim3((n_slots + 31) / 32, n_views), 1024, s, b);
+    if (e != cudaSuccess) return e;
+    return launch_dependent(bucket_scatter, sweep_grid, kBucketWarps * 32, s, b);
 }
 
 template <int V, bool M>
@@ -339,6 +373,8 @@ int rcull_create(const rcull_config* cfg, rcull_ctx** out) {
         TRY(dev_alloc(c, &c->bucket_hist, c->bucket_hist_words));
         TRY(dev_alloc(c, &c->slot_total, slots_max * cfg->max_views));
         TRY(dev_alloc(c, &c->slot_base, slots_max * cfg->max_views));
+        TRY(dev_alloc(c, &c->bucket_done, (size_t)kMaxViews));
+        cudaMemset(c->bucket_done, 0, kMaxViews * 4);
     }
     if (cfg->capacity_tri_indices) {
         if (cfg->output_mode != RCULL_PER_ENTITY) {
@@ -614,12 +650,9 @@ int rcull_frame(rcull_ctx* c, uint64_t n, const rcull_view* views, uint32_t n_vi
         if (sweep_ctas == 0) sweep_ctas = 1;
         b.rows_target = sweep_ctas * kBucketWarps;
         const dim3 sweep_grid(sweep_ctas, n_views);
-        bucket_hist<<<sweep_grid, kBucketWarps * 32, 0, s>>>(b);
-        bucket_colscan<<<dim3((n_slots + 31) / 32, n_views), 1024, 0, s>>>(b);
-        bucket_cmds<<<dim3(1, n_views), 1024, 0, s>>>(b);
-        bucket_scatter<<<sweep_grid, kBucketWarps * 32, 0, s>>>(b);
-        CU(cudaGetLastError());
-        c->launches += 4;
+        b.colscan_done = c->bucket_done;
+        CU(launch_bucketing(b, sweep_grid, n_slots, n_views, s));
+        c->launches += 3;
     }
     return RCULL_OK;
 }
@@ -1796,12 +1829,9 @@ int rcull_merge_expand(rcull_merge* m, void* stream) {
         if (sweep_ctas == 0) sweep_ctas = 1;
         b.rows_target = sweep_ctas * kBucketWarps;
         const dim3 sweep_grid(sweep_ctas, n_views);
-        bucket_hist<<<sweep_grid, kBucketWarps * 32, 0, s>>>(b);
-        bucket_colscan<<<dim3((n_slots + 31) / 32, n_views), 1024, 0, s>>>(b);
-        bucket_cmds<<<dim3(1, n_views), 1024, 0, s>>>(b);
-        bucket_scatter<<<sweep_grid, kBucketWarps * 32, 0, s>>>(b);
-        CU(cudaGetLastError());
-        c->launches += 4;
+        b.colscan_done = c->bucket_done;
+        CU(launch_bucketing(b, sweep_grid, n_slots, n_views, s));
+        c->launches += 3;
     }
     return RCULL_OK;
 }

@@ -327,13 +327,16 @@ constexpr size_t kExpandBigSmem = 32 * (size_t)kExpandStageWords * 4 + 36 * 1024
 // The frame kernel leaves, per view, the survivors in draw_index order as (slot key,
 // draw_index) pairs.  A stable counting sort buckets them by slot:
 //   bucket_hist     one warp per tile of `tile_len` pairs: per-slot counts -> hist[tile][slot]
-//   bucket_colscan  per slot, exclusive scan down the tiles (in place) + slot totals
-//   bucket_cmds     exclusive scan over the slot totals -> bucket starts, one command per
-//                   NON-EMPTY (mesh, lod) slot in slot order
+//   bucket_colscan  per slot, exclusive scan down the tiles (in place) + slot totals; the LAST CTA of a view to finish
+//                   goes on with bucket_cmds: exclusive scan over the slot totals -> bucket starts, one command per
+//                   NON-EMPTY (mesh, lod) slot in slot order (one launch less on a path that is launch-bound)
 //   bucket_scatter  same tiling as bucket_hist: rank of each pair inside its slot =
 //                   bucket start + tile offset + arrivals before it in the tile (stable)
 // Slot counters live in shared memory, kBucketChunk slots per warp at a time; tables with more
 // slots take one sweep of the tile per chunk.  The survivor count is read on the device.
+// The three launches are programmatic dependent launches: a kernel's CTAs are placed while its predecessor drains and
+// wait in pdl_wait() for the predecessor's memory to be visible, instead of paying a full launch latency each.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 constexpr uint32_t kBucketChunk = 2048;
 constexpr uint32_t kBucketWarps = 4;
 
@@ -351,6 +354,7 @@ struct BucketArgs {
     uint32_t n_slots, cap;      // cap: pairs the lists can hold
     uint32_t rows_max;          // histogram rows available per view
     uint32_t rows_target;       // tiles wanted: about two per resident warp
+    uint32_t* colscan_done;     // [view] CTAs of bucket_colscan that are through (the last one builds the commands)
 };
 
 // The view this CTA works on, its survivor count and the tile length all sweeps agree on:
@@ -426,16 +430,22 @@ __device__ __forceinline__ void bucket_sweep(const BucketArgs& a) {
 }
 
 __global__ void __launch_bounds__(kBucketWarps * 32) bucket_hist(const __grid_constant__ BucketArgs a) {
+    pdl_wait();
     bucket_sweep<false>(a);
 }
 __global__ void __launch_bounds__(kBucketWarps * 32) bucket_scatter(const __grid_constant__ BucketArgs a) {
+    pdl_wait();
     bucket_sweep<true>(a);
 }
 
 // CTA = 32 slots (x) by 32 runs of tiles (y): every thread sums its run of tiles for one slot,
 // the runs are scanned through shared memory, and a second walk writes the exclusive offsets.
+__device__ __forceinline__ void bucket_cmds_body(const BucketArgs& a, const BucketView& bv);
+
 __global__ void __launch_bounds__(1024) bucket_colscan(const __grid_constant__ BucketArgs a) {
     __shared__ uint32_t s_run[32][33];
+    __shared__ uint32_t s_last;
+    pdl_wait();
     const uint32_t x = threadIdx.x & 31u, y = threadIdx.x >> 5;
     const uint32_t slot = blockIdx.x * 32 + x;
     const BucketView bv = bucket_view(a, false);
@@ -458,20 +468,31 @@ __global__ void __launch_bounds__(1024) bucket_colscan(const __grid_constant__ B
         }
         if (y == 31) a.slot_total[(size_t)bv.view * a.n_slots + slot] = before;
     }
+    // the last CTA of this view to get here has every slot total in front of it: it builds the commands
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t done = atomicAdd(a.colscan_done + bv.view, 1u);
+        s_last = done == gridDim.x - 1 ? 1u : 0u;
+        if (s_last) a.colscan_done[bv.view] = 0;  // ready for the next frame
+    }
+    __syncthreads();
+    if (s_last == 0u) return;
+    __threadfence();
+    bucket_cmds_body(a, bv);
 }
 
-__global__ void __launch_bounds__(1024) bucket_cmds(const __grid_constant__ BucketArgs a) {
+__device__ __forceinline__ void bucket_cmds_body(const BucketArgs& a, const BucketView& bv) {
     __shared__ uint32_t warp_cmds[32], warp_inst[32];
     __shared__ uint32_t run_cmds, run_inst;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    const BucketView bv = bucket_view(a, false);
     const uint32_t* slot_total = a.slot_total + (size_t)bv.view * a.n_slots;
     uint32_t* slot_base = a.slot_base + (size_t)bv.view * a.n_slots;
     if (tid == 0) run_cmds = run_inst = 0;
     __syncthreads();
     for (uint32_t s0 = 0; s0 < a.n_slots; s0 += blockDim.x) {
         const uint32_t s = s0 + tid;
-        const uint32_t cnt = s < a.n_slots ? slot_total[s] : 0u;
+        const uint32_t cnt = s < a.n_slots ? __ldcg(slot_total + s) : 0u;  // written by other CTAs of this launch: L2, not this SM's L1
         const uint32_t b = __ballot_sync(kFullMask, cnt > 0);
         uint32_t incl = cnt;  // inclusive scan of the instance counts across the warp
 #pragma unroll
