@@ -87,6 +87,46 @@ def test_invalid_config_is_rejected_before_touching_a_device():
     assert lib.rcull_create(None, C.byref(h)) == -1
 
 
+def test_noalloc_entry_point_checks_its_limits_before_touching_a_device():
+    """rcull_frame_noalloc (no counterpart in the reference): what its 128 KiB of static scratch cannot hold is rejected
+    with a message naming the limit -- argument checks come first, so this needs no GPU; with valid arguments and no device
+    it fails like every other entry point (there is no CPU path)."""
+    lib = renderer_b200.load()
+    assert C.sizeof(_lib.NoallocIO) == 8 * (4 + 2 * _lib.MAX_VIEWS + 3) + 8
+    io = _lib.NoallocIO()
+    io.pos_scale = io.rot = io.mesh = io.model = 0x1000
+    for k in range(_lib.MAX_VIEWS):
+        io.cmds[k] = io.visible[k] = 0x1000
+    io.counts = io.index_totals = io.error = 0x1000
+    io.capacity_visible = 16
+    meshes = np.zeros(1, _lib.MESH_DTYPE)
+    meshes["n_lods"] = 1
+    views = np.zeros((1, 6, 4), np.float32)
+    cam = np.zeros(3, np.float32)
+
+    def call(n, io_=io, m=meshes, n_meshes=1, n_views=1):
+        return lib.rcull_frame_noalloc(0, n, C.byref(io_) if io_ is not None else None, _lib.ptr(m), n_meshes, _lib.ptr(views), n_views,
+                                       _lib.ptr(cam), 10.0, 0, None)
+
+    assert call(10, io_=None) == -1
+    assert call(_lib.NOALLOC_MAX_ENTITIES + 1) == -1 and b"RCULL_NOALLOC_MAX_ENTITIES" in lib.rcull_last_error()
+    assert call(10, n_meshes=_lib.NOALLOC_MAX_MESHES + 1) == -1 and b"RCULL_NOALLOC_MAX_MESHES" in lib.rcull_last_error()
+    assert call(10, n_views=9) == -1
+    io.rot = 0x1004
+    assert call(10) == -1 and b"aligned" in lib.rcull_last_error()
+    io.rot = 0x1000
+    if not _have_gpu():
+        assert call(10) == -3  # RCULL_ERR_NO_DEVICE
+
+
+def test_merge_transport_entry_points_reject_null_handles():
+    lib = renderer_b200.load()
+    assert lib.rcull_merge_set_transport(None, 1) == -1
+    assert lib.rcull_merge_send(None, None) == -1
+    assert lib.rcull_merge_set_send_bound(None, None, 0) == -1
+    assert lib.rcull_merge_expand(None, None) == -1
+
+
 CUOBJDUMP = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
 
 
