@@ -268,7 +268,7 @@ int make_model_map(CUtensorMap* map, float4* model, uint64_t cap) {
 extern "C" {
 
 const char* rcull_last_error(void) { return g_err; }
-uint32_t rcull_version(void) { return (0u << 16) | 4u; }  // 0.2: triangle stage, rcull_config.capacity_tri_indices; 0.3: slot counts; 0.4: rcull_context_stream
+uint32_t rcull_version(void) { return (0u << 16) | 5u; }  // 0.2: triangle stage, rcull_config.capacity_tri_indices; 0.3: slot counts; 0.4: rcull_context_stream; 0.5: rcull_frame_noalloc, merge transports (rcull_merge_set_transport / send / set_send_bound)
 
 void rcull_destroy(rcull_ctx* c) {
     if (!c) return;
