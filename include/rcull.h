@@ -310,7 +310,10 @@ int rcull_merge_send(rcull_merge *m, void *stream);
  * it queues the copies; without a bound the whole capacity_per_rank of every view travels).  records_per_view[k] is an
  * ESTIMATE, rounded up to whole expand tiles of 256 -- e.g. the last known count plus a margin.  It is never a
  * correctness matter: records past the bound stay in the sender's window and every receiver's expand reads them from
- * there over NVLink.  n_views = 0 removes the bounds.  Callable only between merged frames. */
+ * there over NVLink.  An estimate of 0, or one at or above capacity_per_rank, leaves that view unbounded (its whole
+ * capacity is copied); n_views = 0 removes the bounds.  With bounds a send takes one peer copy per view instead of one
+ * per slot, and a peer copy has a fixed cost of ~13 us: worth it only when the capacities are far above the survivor
+ * counts.  Callable only between merged frames. */
 int rcull_merge_set_send_bound(rcull_merge *m, const uint32_t *records_per_view, uint32_t n_views);
 /* Expands the oldest merged frame that has not been expanded yet into this rank's merged lists;
  * asynchronous on stream.  After it, rcull_merge_lists names the results. */
