@@ -173,3 +173,23 @@ def test_rust_ffi_file_is_generated_from_the_current_header():
         params = re.search(r"pub fn %s\((.*?)\)( -> [^;]+)?;" % name, text)
         assert len([p for p in params.group(1).split(",") if p.strip()]) == len(args), name
         assert (params.group(2) is None) == (res is None), name
+
+
+@pytest.mark.skipif(not os.path.exists(CUOBJDUMP), reason="cuobjdump not available")
+def test_sass_of_the_bucketing_chain_waits_for_its_predecessor():
+    """The per-mesh bucketing kernels are programmatic dependent launches: each must execute griddepcontrol.wait (SASS
+    ACQBULK) before it reads what the kernel in front of it wrote; the command pass lives in bucket_colscan now."""
+    out = subprocess.run([CUOBJDUMP, "-sass", _lib.LIB_PATH], capture_output=True, text=True, check=True).stdout
+    funcs, cur = {}, None
+    for line in out.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            cur = m.group(1)
+            funcs[cur] = []
+        elif cur:
+            funcs[cur].append(line)
+    for name in ("bucket_hist", "bucket_colscan", "bucket_scatter"):
+        body = [v for k, v in funcs.items() if name in k]
+        assert len(body) == 1, name
+        assert any("ACQBULK" in l for l in body[0]), f"{name} does not wait for its predecessor grid"
+    assert not any("bucket_cmds" in k for k in funcs)
